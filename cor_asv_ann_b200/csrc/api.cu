@@ -1,0 +1,633 @@
+// api.cu — C ABI (include/cor_b200.h): model lifetime, weight repack, workspace carve,
+// encoder scan, one decoder timestep, greedy driver.
+#include "model.h"
+#include "epilogue.cuh"
+#include <string.h>
+#include <math.h>
+#include <algorithm>
+
+namespace cor {
+
+static thread_local std::string g_error;
+int64_t g_launches = 0;
+void set_error(const std::string& msg) { g_error = msg; }
+
+// GEMM dispatch: tcgen05 3xTF32 when the model keeps split operands and the tile is worth it,
+// exact FFMA otherwise (small M).  Both consume the same operand representation.
+static int gemm_store(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const StoreEpi& e) {
+    if (m->split && M >= 64 && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e);
+    return gemm_store_ffma(st, M, m_dev, N, s, n, e);
+}
+static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const LstmEpi& e) {
+    if (m->split && M >= 64 && tc_available()) return gemm_lstm_tc(st, M, m_dev, N, s, n, e);
+    return gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
+}
+
+// ------------------------------------------------------------------ weights
+static int dev_alloc(cor_model* m, size_t bytes, void** out) {
+    COR_CUDA(cudaMalloc(out, bytes ? bytes : 4));
+    m->allocs.push_back(*out);
+    return 0;
+}
+
+static void host_split(const std::vector<float>& x, std::vector<float>& hi, std::vector<float>& lo) {
+    hi.resize(x.size()); lo.resize(x.size());
+    for (size_t i = 0; i < x.size(); ++i) {
+        uint32_t b; memcpy(&b, &x[i], 4);
+        uint32_t r = (b + 0x1000u) & 0xFFFFE000u;
+        if ((b & 0x7F800000u) == 0x7F800000u || (r & 0x7F800000u) == 0x7F800000u) r = b & 0xFFFFE000u;
+        float h; memcpy(&h, &r, 4);
+        hi[i] = h; lo[i] = x[i] - h;
+    }
+}
+
+// upload a K-major matrix [rows][ld]
+static int upload_mat(cor_model* m, const std::vector<float>& data, int rows, int ld, Mat* out) {
+    out->rows = rows; out->ld = ld;
+    const size_t bytes = data.size() * sizeof(float);
+    if (m->split) {
+        std::vector<float> hi, lo;
+        host_split(data, hi, lo);
+        if (dev_alloc(m, bytes, (void**)&out->hi) || dev_alloc(m, bytes, (void**)&out->lo)) return 1;
+        COR_CUDA(cudaMemcpy(out->hi, hi.data(), bytes, cudaMemcpyHostToDevice));
+        COR_CUDA(cudaMemcpy(out->lo, lo.data(), bytes, cudaMemcpyHostToDevice));
+    } else {
+        if (dev_alloc(m, bytes, (void**)&out->hi)) return 1;
+        COR_CUDA(cudaMemcpy(out->hi, data.data(), bytes, cudaMemcpyHostToDevice));
+    }
+    return 0;
+}
+static int upload_vec(cor_model* m, const std::vector<float>& data, float** out) {
+    if (dev_alloc(m, data.size() * sizeof(float), (void**)out)) return 1;
+    COR_CUDA(cudaMemcpy(*out, data.data(), data.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+// Keras (in, out) kernel rows [r0, r1) -> K-major [out][r1-r0]
+static std::vector<float> transpose_rows(const HostWeight& w, int r0, int r1) {
+    const int out = (int)w.shape[1], k = r1 - r0;
+    std::vector<float> t((size_t)out * k);
+    for (int r = r0; r < r1; ++r)
+        for (int c = 0; c < out; ++c) t[(size_t)c * k + (r - r0)] = w.data[(size_t)r * out + c];
+    return t;
+}
+// Keras LSTM kernel (in, 4W), columns g*W+u -> K-major [4u+g][in rows r0..r1)
+static std::vector<float> lstm_rows(const HostWeight& w, int W, int r0, int r1) {
+    const int k = r1 - r0;
+    std::vector<float> t((size_t)4 * W * k);
+    for (int r = r0; r < r1; ++r)
+        for (int g = 0; g < 4; ++g)
+            for (int u = 0; u < W; ++u) t[(size_t)(4 * u + g) * k + (r - r0)] = w.data[(size_t)r * 4 * W + g * W + u];
+    return t;
+}
+static std::vector<float> lstm_bias(const HostWeight& b, int W) {
+    std::vector<float> t(4 * W);
+    for (int g = 0; g < 4; ++g)
+        for (int u = 0; u < W; ++u) t[4 * u + g] = b.data[g * W + u];
+    return t;
+}
+
+static int need(cor_model* m, const std::string& layer, size_t count, const std::vector<HostWeight>** out) {
+    auto it = m->host.find(layer);
+    COR_CHECK(it != m->host.end(), ("missing weights for layer " + layer).c_str());
+    COR_CHECK(it->second.size() == count, ("wrong number of weights for layer " + layer).c_str());
+    for (auto& w : it->second) COR_CHECK(!w.data.empty(), ("unset weight in layer " + layer).c_str());
+    *out = &it->second;
+    return 0;
+}
+static int check_shape(const HostWeight& w, int64_t a, int64_t b, const std::string& what) {
+    bool ok = b < 0 ? (w.shape.size() == 1 && w.shape[0] == a) : (w.shape.size() == 2 && w.shape[0] == a && w.shape[1] == b);
+    COR_CHECK(ok, ("bad shape for " + what).c_str());
+    return 0;
+}
+static int build_lstm(cor_model* m, const HostWeight* w3, int in_dim, int x_rows, LstmW* out, const std::string& what) {
+    const int W = m->W;
+    if (check_shape(w3[0], in_dim, 4 * W, what + " kernel") || check_shape(w3[1], W, 4 * W, what + " recurrent") ||
+        check_shape(w3[2], 4 * W, -1, what + " bias")) return 1;
+    if (upload_mat(m, lstm_rows(w3[0], W, 0, x_rows), 4 * W, x_rows, &out->Kx)) return 1;
+    if (x_rows < in_dim && upload_mat(m, lstm_rows(w3[0], W, x_rows, in_dim), 4 * W, in_dim - x_rows, &out->Kc)) return 1;
+    if (upload_mat(m, lstm_rows(w3[1], W, 0, W), 4 * W, W, &out->R)) return 1;
+    return upload_vec(m, lstm_bias(w3[2], W), &out->bias);
+}
+
+// ------------------------------------------------------------------ workspace
+struct Carver {
+    char* base; size_t off = 256;   // the first 256 bytes hold the WsHeader
+    template <typename T> T* take(size_t n) {
+        off = (off + 255) & ~size_t(255);
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += n * sizeof(T);
+        return p;
+    }
+};
+
+int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, Ws* ws) {
+    COR_CHECK(B > 0 && T > 0 && k > 0, "empty call geometry");
+    Carver c{(char*)base};
+    const int W = m->W, d = m->d, D = m->D, Vp = m->Vp;
+    const bool sp = m->split;
+    const size_t BT = (size_t)B * T;
+    ws->B = B; ws->T = T; ws->k = k;
+    ws->row_T = c.take<int32_t>(B);
+    ws->idx = c.take<int32_t>(BT * k);
+    ws->val = c.take<float>(BT * k);
+    ws->live = c.take<uint8_t>(B);
+    ws->done = c.take<uint8_t>(B);
+    ws->X = c.take<float>(BT * W);   ws->X_lo = sp ? c.take<float>(BT * W) : nullptr;
+    ws->Xr = c.take<float>(BT * W);  ws->Xr_lo = sp ? c.take<float>(BT * W) : nullptr;
+    ws->seq.assign(d, nullptr); ws->seq_lo.assign(d, nullptr); ws->seqr.assign(d, nullptr); ws->seqr_lo.assign(d, nullptr);
+    for (int n = 0; n < d; ++n) {
+        const size_t e = BT * m->enc_out_dim(n);
+        ws->seq[n] = c.take<float>(e);
+        ws->seq_lo[n] = sp ? c.take<float>(e) : nullptr;
+        if (n + 1 < d && m->layer_bidi(n + 1)) {       // the next layer scans backwards too
+            ws->seqr[n] = c.take<float>(e);
+            ws->seqr_lo[n] = sp ? c.take<float>(e) : nullptr;
+        }
+    }
+    ws->u = c.take<float>(BT * W);
+    const size_t BW = (size_t)B * W;
+    for (int dir = 0; dir < 2; ++dir) {
+        for (int q = 0; q < 2; ++q) {
+            ws->eh[dir][q] = c.take<float>(BW);
+            ws->eh_lo[dir][q] = sp ? c.take<float>(BW) : nullptr;
+        }
+        ws->ec[dir] = c.take<float>(BW);
+    }
+    ws->st_h.assign(d, nullptr); ws->st_c.assign(d, nullptr); ws->dc.assign(d, nullptr);
+    for (int q = 0; q < 2; ++q) { ws->dh[q].assign(d, nullptr); ws->dh_lo[q].assign(d, nullptr); }
+    for (int n = 0; n < d; ++n) {
+        ws->st_h[n] = c.take<float>(BW); ws->st_c[n] = c.take<float>(BW);
+        ws->dc[n] = c.take<float>(BW);
+        for (int q = 0; q < 2; ++q) {
+            ws->dh[q][n] = c.take<float>(BW);
+            ws->dh_lo[q][n] = sp ? c.take<float>(BW) : nullptr;
+        }
+    }
+    ws->a[0] = c.take<float>(BT); ws->a[1] = c.take<float>(BT);
+    ws->x = c.take<float>(BW);  ws->x_lo = sp ? c.take<float>(BW) : nullptr;
+    ws->wq = c.take<float>(BW);
+    ws->ctx = c.take<float>((size_t)B * D); ws->ctx_lo = sp ? c.take<float>((size_t)B * D) : nullptr;
+    ws->logits = c.take<float>((size_t)B * Vp);
+    ws->p = c.take<float>((size_t)B * Vp); ws->p_lo = sp ? c.take<float>((size_t)B * Vp) : nullptr;
+    if (m->cfg.lm_predict) {
+        ws->h_lm = c.take<float>(BW); ws->h_lm_lo = sp ? c.take<float>(BW) : nullptr;
+        ws->c_lm = c.take<float>(BW);
+        ws->logits_lm = c.take<float>((size_t)B * Vp);
+        ws->p_lm = c.take<float>((size_t)B * Vp);
+    }
+    const size_t S = 2 * (size_t)T;
+    ws->o_chars = c.take<int32_t>(B * S);
+    ws->o_probs = c.take<float>(B * S);
+    ws->o_score = c.take<double>(B);
+    ws->o_len = c.take<int32_t>(B);
+    ws->o_align = want_align ? c.take<float>(S * BT) : nullptr;
+    ws->bytes = (c.off + 255) & ~size_t(255);
+    return 0;
+}
+
+// ------------------------------------------------------------------ encoder
+// seq2seq.py:237-314.  Per layer and direction: one GEMM+LSTM launch per timestep over all rows.
+int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
+    const int W = m->W, d = m->d, B = ws.B, T = ws.T;
+    const bool deep = m->cfg.deep_bidirectional_encoder != 0;
+    if (launch_live_rows(st, ws.idx, ws.val, B, T, ws.k, ws.live)) return 1;
+    if (launch_embed(st, ws.idx, ws.val, ws.row_T, B, T, ws.k, m->E_full, W, m->V, ws.X, ws.X_lo, ws.Xr, ws.Xr_lo)) return 1;
+    const size_t BW = (size_t)B * W;
+    for (int n = 0; n < d; ++n) {
+        const bool bidi = m->layer_bidi(n);
+        const int in_dim = m->enc_in_dim(n), out_dim = m->enc_out_dim(n);
+        const float* in[2] = {n == 0 ? ws.X : ws.seq[n - 1], n == 0 ? ws.Xr : ws.seqr[n - 1]};
+        const float* in_lo[2] = {n == 0 ? ws.X_lo : ws.seq_lo[n - 1], n == 0 ? ws.Xr_lo : ws.seqr_lo[n - 1]};
+        const int ndir = bidi ? 2 : 1;
+        for (int dir = 0; dir < ndir; ++dir) {
+            COR_CUDA(cudaMemsetAsync(ws.eh[dir][0], 0, BW * 4, st));
+            if (ws.eh_lo[dir][0]) COR_CUDA(cudaMemsetAsync(ws.eh_lo[dir][0], 0, BW * 4, st));
+            COR_CUDA(cudaMemsetAsync(ws.ec[dir], 0, BW * 4, st));
+        }
+        int cur = 0;
+        for (int s = 0; s < T; ++s) {
+            for (int dir = 0; dir < ndir; ++dir) {
+                const LstmW& lw = dir == 0 ? m->enc_fw[n] : m->enc_bw[n];
+                const size_t slab = (size_t)s * B * in_dim;
+                GemmSeg segs[2] = {
+                    {in[dir] + slab, in_dim, in_lo[dir] ? in_lo[dir] + slab : nullptr, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, in_dim},
+                    {ws.eh[dir][cur], W, ws.eh_lo[dir][cur], lw.R.hi, lw.R.ld, lw.R.lo, W}};
+                LstmEpi e{};
+                e.bias = lw.bias; e.c_in = ws.ec[dir]; e.c_out = ws.ec[dir];
+                e.h_prev = ws.eh[dir][cur]; e.h_prev_lo = ws.eh_lo[dir][cur];
+                e.h_out = ws.eh[dir][cur ^ 1]; e.h_out_lo = ws.eh_lo[dir][cur ^ 1];
+                e.row_T = ws.row_T; e.step = s; e.reverse = dir; e.rows_total = B;
+                e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W;
+                e.seq_rev = ws.seqr[n]; e.seq_rev_lo = ws.seqr_lo[n];
+                if (m->cfg.residual_connections && !bidi && n >= 2) {
+                    e.resid = ws.seq[n - 1]; e.resid_lo = ws.seq_lo[n - 1]; e.resid_ld = m->enc_out_dim(n - 1);
+                }
+                e.cross_sum = deep && n + 1 < d;
+                e.W = W;
+                if (gemm_lstm(m, st, B, nullptr, 4 * W, segs, 2, e)) return 1;
+            }
+            cur ^= 1;
+        }
+        // state handed to decoder layer n: backward final for bidirectional layers (seq2seq.py:280-281),
+        // forward final (after the padding) otherwise (:283)
+        const int sd = bidi ? 1 : 0;
+        const float* fh = ws.eh[sd][cur]; const float* fh_lo = ws.eh_lo[sd][cur];
+        const float* fc = ws.ec[sd];
+        if (m->cfg.bridge_dense) {
+            GemmSeg sh = {fh, W, fh_lo, m->bridge_h[n].hi, m->bridge_h[n].ld, m->bridge_h[n].lo, W};
+            StoreEpi eh_{ws.st_h[n], W, nullptr, m->bridge_hb[n], 1};
+            if (gemm_store_ffma(st, B, nullptr, W, &sh, 1, eh_)) return 1;
+            GemmSeg sc = {fc, W, nullptr, m->bridge_c[n].hi, m->bridge_c[n].ld, m->bridge_c[n].lo, W};
+            StoreEpi ec_{ws.st_c[n], W, nullptr, m->bridge_cb[n], 1};
+            if (gemm_store_ffma(st, B, nullptr, W, &sc, 1, ec_)) return 1;
+        } else {
+            if (fh_lo) { if (launch_join(st, fh, fh_lo, ws.st_h[n], BW)) return 1; }
+            else COR_CUDA(cudaMemcpyAsync(ws.st_h[n], fh, BW * 4, cudaMemcpyDeviceToDevice, st));
+            COR_CUDA(cudaMemcpyAsync(ws.st_c[n], fc, BW * 4, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    // u = enc_out . U for every (t,row) at once — hoisted out of the step loop (the reference
+    // re-evaluates attention_dense inside every decoder call, seq2seq.py:459-460)
+    GemmSeg su = {ws.enc_out(), m->D, ws.enc_out_lo(), m->U.hi, m->U.ld, m->U.lo, m->D};
+    StoreEpi eu{ws.u, W, nullptr, nullptr, 0};
+    const long long rows = (long long)T * B;
+    COR_CHECK(rows < (1ll << 31), "too many (t,row) pairs for one call");
+    return gemm_store(m, st, (int)rows, nullptr, W, &su, 1, eu);
+}
+
+// ------------------------------------------------------------------ decoder step
+int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) {
+    const int W = m->W, d = m->d, D = m->D, R = io.R;
+    if (io.first) {
+        COR_CUDA(cudaMemsetAsync(io.x, 0, (size_t)R * W * 4, st));
+        if (io.x_lo) COR_CUDA(cudaMemsetAsync(io.x_lo, 0, (size_t)R * W * 4, st));
+    } else {
+        GemmSeg s = {io.p, m->Vp, io.p_lo, m->Et.hi, m->Et.ld, m->Et.lo, m->Vp};
+        StoreEpi e{io.x, W, io.x_lo, nullptr, 0};
+        if (gemm_store(m, st, R, io.r_dev, W, &s, 1, e)) return 1;
+    }
+    const float* x = io.x; const float* x_lo = io.x_lo;
+    for (int n = 0; n + 1 < d; ++n) {
+        const LstmW& lw = m->dec[n];
+        GemmSeg segs[2] = {{x, W, x_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, W},
+                           {io.h_in[n], W, io.h_in_lo[n], lw.R.hi, lw.R.ld, lw.R.lo, W}};
+        LstmEpi e{};
+        e.bias = lw.bias; e.c_in = io.c_in[n]; e.c_out = io.c_out[n];
+        e.h_prev = io.h_in[n]; e.h_prev_lo = io.h_in_lo[n]; e.h_out = io.h_out[n]; e.h_out_lo = io.h_out_lo[n];
+        e.W = W;
+        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, 2, e)) return 1;
+        x = io.h_out[n]; x_lo = io.h_out_lo[n];
+    }
+    const int top = d - 1;
+    {   // wq = h_prev . W_a + b_UW   (attention.py:539)
+        GemmSeg s = {io.h_in[top], W, io.h_in_lo[top], m->Wa.hi, m->Wa.ld, m->Wa.lo, W};
+        StoreEpi e{io.wq, W, nullptr, m->b_UW, 0};
+        if (gemm_store(m, st, R, io.r_dev, W, &s, 1, e)) return 1;
+    }
+    AttnArgs a{};
+    a.wq = io.wq; a.u = ws.u; a.enc = ws.enc_out(); a.enc_lo = ws.enc_out_lo();
+    a.a_prev = io.a_in; a.row_line = io.row_line; a.line_T = ws.row_T;
+    a.v_a = m->v_a; a.b_v = m->b_v; a.a_out = io.a_out; a.ctx = io.ctx; a.ctx_lo = io.ctx_lo;
+    a.align_log = io.align_log;
+    a.R = R; a.r_dev = io.r_dev; a.L = ws.B; a.t_max = ws.T; a.W = W; a.D = D;
+    a.window = m->cfg.window_width; a.inclusive = 1;
+    if (launch_attention(st, a)) return 1;
+    const LstmW& tw = m->dec[top];
+    {
+        GemmSeg segs[3] = {{x, W, x_lo, tw.Kx.hi, tw.Kx.ld, tw.Kx.lo, W},
+                           {io.ctx, D, io.ctx_lo, tw.Kc.hi, tw.Kc.ld, tw.Kc.lo, D},
+                           {io.h_in[top], W, io.h_in_lo[top], tw.R.hi, tw.R.ld, tw.R.lo, W}};
+        LstmEpi e{};
+        e.bias = tw.bias; e.c_in = io.c_in[top]; e.c_out = io.c_out[top];
+        e.h_prev = io.h_in[top]; e.h_prev_lo = io.h_in_lo[top]; e.h_out = io.h_out[top]; e.h_out_lo = io.h_out_lo[top];
+        e.W = W;
+        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, 3, e)) return 1;
+    }
+    {   // logits = h . E^T  (tied output projection, seq2seq.py:379)
+        GemmSeg s = {io.h_out[top], W, io.h_out_lo[top], m->E.hi, m->E.ld, m->E.lo, W};
+        StoreEpi e{io.logits, m->Vp, nullptr, nullptr, 0};
+        if (gemm_store(m, st, R, io.r_dev, m->Vp, &s, 1, e)) return 1;
+    }
+    if (m->cfg.lm_predict && io.logits_lm) {
+        // second evaluation of the top cell with attended == u == 0: context is exactly zero
+        // (seq2seq.py:464-469); its states are discarded.
+        GemmSeg segs[2] = {{x, W, x_lo, tw.Kx.hi, tw.Kx.ld, tw.Kx.lo, W},
+                           {io.h_in[top], W, io.h_in_lo[top], tw.R.hi, tw.R.ld, tw.R.lo, W}};
+        LstmEpi e{};
+        e.bias = tw.bias; e.c_in = io.c_in[top]; e.c_out = io.c_lm;
+        e.h_prev = io.h_in[top]; e.h_prev_lo = io.h_in_lo[top]; e.h_out = io.h_lm; e.h_out_lo = io.h_lm_lo;
+        e.W = W;
+        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, 2, e)) return 1;
+        GemmSeg s = {io.h_lm, W, io.h_lm_lo, m->E.hi, m->E.ld, m->E.lo, W};
+        StoreEpi e2{io.logits_lm, m->Vp, nullptr, nullptr, 0};
+        if (gemm_store(m, st, R, io.r_dev, m->Vp, &s, 1, e2)) return 1;
+    }
+    return 0;
+}
+
+static int copy_in(cudaStream_t st, const float* src, float* hi, float* lo, size_t n) {
+    if (lo) return launch_split(st, src, hi, lo, n);
+    COR_CUDA(cudaMemcpyAsync(hi, src, n * 4, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+static int copy_out(cudaStream_t st, const float* hi, const float* lo, float* dst, size_t n) {
+    if (lo) return launch_join(st, hi, lo, dst, n);
+    COR_CUDA(cudaMemcpyAsync(dst, hi, n * 4, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
+    const int B = ws.B, T = ws.T, W = m->W, d = m->d;
+    const size_t BW = (size_t)B * W;
+    for (int n = 0; n < d; ++n) {
+        if (copy_in(st, ws.st_h[n], ws.dh[0][n], ws.dh_lo[0][n], BW)) return 1;
+        COR_CUDA(cudaMemcpyAsync(ws.dc[n], ws.st_c[n], BW * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    COR_CUDA(cudaMemsetAsync(ws.a[0], 0, (size_t)B * T * 4, st));
+    COR_CUDA(cudaMemsetAsync(ws.done, 0, B, st));
+    COR_CUDA(cudaMemsetAsync(ws.o_len, 0, (size_t)B * 4, st));
+    COR_CUDA(cudaMemsetAsync(ws.o_score, 0, (size_t)B * 8, st));
+    COR_CUDA(cudaMemsetAsync(ws.o_chars, 0, (size_t)B * 2 * T * 4, st));
+    COR_CUDA(cudaMemsetAsync(ws.o_probs, 0, (size_t)B * 2 * T * 4, st));
+    int cur = 0;
+    const int S = 2 * T;
+    for (int s = 0; s < S; ++s) {
+        StepIO io{};
+        io.R = B; io.first = (s == 0);
+        io.p = ws.p; io.p_lo = ws.p_lo; io.x = ws.x; io.x_lo = ws.x_lo;
+        for (int n = 0; n < d; ++n) {
+            io.h_in[n] = ws.dh[cur][n]; io.h_in_lo[n] = ws.dh_lo[cur][n];
+            io.h_out[n] = ws.dh[cur ^ 1][n]; io.h_out_lo[n] = ws.dh_lo[cur ^ 1][n];
+            io.c_in[n] = ws.dc[n]; io.c_out[n] = ws.dc[n];
+        }
+        io.a_in = ws.a[cur]; io.a_out = ws.a[cur ^ 1];
+        io.align_log = ws.o_align ? ws.o_align + (size_t)s * B * T : nullptr;
+        io.wq = ws.wq; io.ctx = ws.ctx; io.ctx_lo = ws.ctx_lo; io.logits = ws.logits;
+        if (decoder_core(m, ws, io, st)) return 1;
+        GreedyArgs g{};
+        g.logits = ws.logits; g.p = ws.p; g.p_lo = ws.p_lo; g.row_T = ws.row_T; g.live = ws.live;
+        g.out_chars = ws.o_chars; g.out_probs = ws.o_probs; g.score_sum = ws.o_score; g.out_len = ws.o_len; g.done = ws.done;
+        g.R = B; g.V = m->V; g.step = s; g.s_max = S; g.eos = m->cfg.eos_index;
+        if (launch_softmax_greedy(st, g)) return 1;
+        cur ^= 1;
+    }
+    return launch_finish_scores(st, ws.o_score, ws.o_len, B);
+}
+
+}  // namespace cor
+
+using namespace cor;
+
+extern "C" {
+
+const char* cor_last_error(void) { return g_error.c_str(); }
+int cor_abi_version(void) { return 1; }
+int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launches = 0; return v; }
+
+int cor_model_create(const cor_config* cfg, int device, cor_model** out) {
+    COR_CHECK(cfg && out, "null argument");
+    COR_CHECK(cfg->width > 0 && cfg->width % 32 == 0, "width must be a positive multiple of 32");
+    COR_CHECK(cfg->depth >= 1 && cfg->depth <= 8, "depth must be in 1..8");
+    COR_CHECK(cfg->voc_size >= 2, "voc_size must be at least 2");
+    COR_CHECK(cfg->window_width >= 0 && cfg->window_width <= 6, "window_width must be in 0..6");
+    int ndev = 0;
+    COR_CUDA(cudaGetDeviceCount(&ndev));
+    COR_CHECK(device >= 0 && device < ndev, "no such CUDA device");
+    COR_CUDA(cudaSetDevice(device));
+    cor_model* m = new cor_model();
+    m->cfg = *cfg; m->device = device;
+    m->W = cfg->width; m->d = cfg->depth; m->V = cfg->voc_size; m->Vp = (cfg->voc_size + 127) & ~127;
+    m->D = (cfg->depth == 1 || cfg->deep_bidirectional_encoder) ? 2 * cfg->width : cfg->width;
+    m->split = cfg->gemm_mode == 2 || (cfg->gemm_mode == 0 && tc_available());
+    *out = m;
+    return 0;
+}
+
+int cor_model_set_weight(cor_model* m, const char* layer, int index, const float* host, const int64_t* shape, int rank) {
+    COR_CHECK(m && layer && host && shape, "null argument");
+    COR_CHECK(!m->finalized, "model already finalized");
+    COR_CHECK(index >= 0 && index < 16 && rank >= 1 && rank <= 2, "bad weight index or rank");
+    auto& vec = m->host[layer];
+    if ((int)vec.size() <= index) vec.resize(index + 1);
+    HostWeight& w = vec[index];
+    w.shape.assign(shape, shape + rank);
+    size_t n = 1;
+    for (int i = 0; i < rank; ++i) n *= (size_t)shape[i];
+    w.data.assign(host, host + n);
+    return 0;
+}
+
+int cor_model_finalize(cor_model* m) {
+    COR_CHECK(m && !m->finalized, "bad model state");
+    COR_CUDA(cudaSetDevice(m->device));
+    const int W = m->W, d = m->d, V = m->V, Vp = m->Vp, D = m->D;
+    const std::vector<HostWeight>* w;
+    if (need(m, "char_input_projection", 1, &w) || check_shape((*w)[0], V, W, "char_input_projection")) return 1;
+    {
+        const HostWeight& E = (*w)[0];
+        if (upload_vec(m, E.data, &m->E_full)) return 1;
+        std::vector<float> e((size_t)Vp * W, 0.f), et((size_t)W * Vp, 0.f);
+        for (int v = 0; v < V; ++v)
+            for (int u = 0; u < W; ++u) { e[(size_t)v * W + u] = E.data[(size_t)v * W + u]; et[(size_t)u * Vp + v] = E.data[(size_t)v * W + u]; }
+        if (upload_mat(m, e, Vp, W, &m->E) || upload_mat(m, et, W, Vp, &m->Et)) return 1;
+    }
+    m->enc_fw.resize(d); m->enc_bw.resize(d); m->dec.resize(d);
+    m->bridge_h.resize(d); m->bridge_c.resize(d); m->bridge_hb.assign(d, nullptr); m->bridge_cb.assign(d, nullptr);
+    for (int n = 0; n < d; ++n) {
+        const std::string name = "encoder_lstm_" + std::to_string(n + 1);
+        const int in_dim = m->enc_in_dim(n);
+        if (need(m, name, m->layer_bidi(n) ? 6 : 3, &w)) return 1;
+        if (build_lstm(m, &(*w)[0], in_dim, in_dim, &m->enc_fw[n], name)) return 1;
+        if (m->layer_bidi(n) && build_lstm(m, &(*w)[3], in_dim, in_dim, &m->enc_bw[n], name + " (backward)")) return 1;
+        if (m->cfg.bridge_dense) {
+            for (int hc = 0; hc < 2; ++hc) {
+                const std::string bn = std::string(hc ? "bridge_c_" : "bridge_h_") + std::to_string(n + 1);
+                if (need(m, bn, 2, &w) || check_shape((*w)[0], W, W, bn) || check_shape((*w)[1], W, -1, bn + " bias")) return 1;
+                if (upload_mat(m, transpose_rows((*w)[0], 0, W), W, W, hc ? &m->bridge_c[n] : &m->bridge_h[n])) return 1;
+                if (upload_vec(m, (*w)[1].data, hc ? &m->bridge_cb[n] : &m->bridge_hb[n])) return 1;
+            }
+        }
+    }
+    if (need(m, "attention_dense", 1, &w) || check_shape((*w)[0], D, W, "attention_dense")) return 1;
+    if (upload_mat(m, transpose_rows((*w)[0], 0, D), W, D, &m->U)) return 1;
+    for (int n = 0; n + 1 < d; ++n) {
+        const std::string name = "decoder_lstm_" + std::to_string(n + 1);
+        if (need(m, name, 3, &w) || build_lstm(m, &(*w)[0], W, W, &m->dec[n], name)) return 1;
+    }
+    {
+        const std::string name = "decoder_lstm_" + std::to_string(d);
+        if (need(m, name, 7, &w)) return 1;
+        if (check_shape((*w)[0], W, W, name + " W_a") || check_shape((*w)[1], W, 1, name + " v_a") ||
+            check_shape((*w)[2], W, -1, name + " b_UW") || check_shape((*w)[3], 1, -1, name + " b_v")) return 1;
+        if (upload_mat(m, transpose_rows((*w)[0], 0, W), W, W, &m->Wa)) return 1;
+        if (upload_vec(m, (*w)[1].data, &m->v_a) || upload_vec(m, (*w)[2].data, &m->b_UW)) return 1;
+        m->b_v = (*w)[3].data[0];
+        if (build_lstm(m, &(*w)[4], W + D, W, &m->dec[d - 1], name + " cell")) return 1;
+    }
+    m->host.clear();
+    m->finalized = true;
+    return 0;
+}
+
+void cor_model_destroy(cor_model* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    for (void* p : m->allocs) cudaFree(p);
+    delete m;
+}
+
+int cor_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt, int want_alignments, size_t* bytes) {
+    COR_CHECK(m && bytes, "null argument");
+    Ws ws;
+    if (carve(m, n_rows, t_max, k_alt, want_alignments, nullptr, &ws)) return 1;
+    *bytes = ws.bytes;
+    return 0;
+}
+
+static int bind(cor_model* m, const cor_lines* l, void* workspace, size_t bytes, int want_align, Ws* ws) {
+    COR_CHECK(m && m->finalized, "model not finalized");
+    COR_CHECK(l && workspace, "null argument");
+    COR_CUDA(cudaSetDevice(m->device));
+    if (carve(m, l->n_rows, l->t_max, l->k_alt, want_align, workspace, ws)) return 1;
+    COR_CHECK(ws->bytes <= bytes, "workspace too small");
+    return 0;
+}
+
+static int stage_lines(const Ws& ws, const cor_lines* l, cudaMemcpyKind kind, cudaStream_t st) {
+    const size_t n = (size_t)l->n_rows * l->t_max * l->k_alt;
+    COR_CUDA(cudaMemcpyAsync(ws.row_T, l->row_T, (size_t)l->n_rows * 4, kind, st));
+    COR_CUDA(cudaMemcpyAsync(ws.idx, l->idx, n * 4, kind, st));
+    if (l->val) COR_CUDA(cudaMemcpyAsync(ws.val, l->val, n * 4, kind, st));
+    return 0;
+}
+
+// cor_encode records the call geometry in the first bytes of the workspace; the step and greedy
+// entry points re-derive the carve from it.
+struct WsHeader { int32_t B, T, k, align; uint32_t magic; };
+static int write_header(void* workspace, size_t bytes, const Ws& ws, int align, cudaStream_t st) {
+    COR_CHECK(ws.bytes <= bytes, "workspace too small");
+    WsHeader h{ws.B, ws.T, ws.k, align, 0xC0A5B200u};
+    COR_CUDA(cudaMemcpyAsync(workspace, &h, sizeof(h), cudaMemcpyHostToDevice, st));
+    COR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+static int read_header(cor_model* m, void* workspace, size_t bytes, Ws* ws, int* align, cudaStream_t st) {
+    COR_CHECK(m && m->finalized && workspace && bytes >= 256, "bad arguments");
+    COR_CUDA(cudaSetDevice(m->device));
+    WsHeader h{};
+    COR_CUDA(cudaMemcpyAsync(&h, workspace, sizeof(h), cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaStreamSynchronize(st));
+    COR_CHECK(h.magic == 0xC0A5B200u, "workspace holds no encoded lines (call cor_encode first)");
+    if (carve(m, h.B, h.T, h.k, h.align, workspace, ws)) return 1;
+    COR_CHECK(ws->bytes <= bytes, "workspace smaller than at encode time");
+    if (align) *align = h.align;
+    return 0;
+}
+
+int cor_encode(cor_model* m, const cor_lines* lines, void* workspace, size_t workspace_bytes,
+               float* enc_out, float* states, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    Ws ws;
+    // alignments are decided at encode time: the header records whether room was reserved
+    size_t need_plain = 0, need_align = 0;
+    if (!m || !lines) { set_error("null argument"); return 1; }
+    if (cor_workspace_bytes(m, lines->n_rows, lines->t_max, lines->k_alt, 0, &need_plain)) return 1;
+    if (cor_workspace_bytes(m, lines->n_rows, lines->t_max, lines->k_alt, 1, &need_align)) return 1;
+    const int align = workspace_bytes >= need_align;
+    if (bind(m, lines, workspace, workspace_bytes, align, &ws)) return 1;
+    if (stage_lines(ws, lines, cudaMemcpyDeviceToDevice, st)) return 1;
+    if (!lines->val) ws.val = nullptr;
+    if (run_encoder(m, ws, st)) return 1;
+    const size_t BW = (size_t)ws.B * m->W;
+    if (enc_out && copy_out(st, ws.enc_out(), ws.enc_out_lo(), enc_out, (size_t)ws.T * ws.B * m->D)) return 1;
+    if (states)
+        for (int n = 0; n < m->d; ++n) {
+            COR_CUDA(cudaMemcpyAsync(states + (2 * n) * BW, ws.st_h[n], BW * 4, cudaMemcpyDeviceToDevice, st));
+            COR_CUDA(cudaMemcpyAsync(states + (2 * n + 1) * BW, ws.st_c[n], BW * 4, cudaMemcpyDeviceToDevice, st));
+        }
+    return write_header(workspace, workspace_bytes, ws, align, st);
+}
+
+int cor_decode_step(cor_model* m, void* workspace, size_t workspace_bytes, int n_hyp, const int32_t* row_line,
+                    const float* p_in, const float* h_in, const float* c_in, const float* a_in,
+                    float* p_out, float* lm_out, float* h_out, float* c_out, float* a_out, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    Ws ws;
+    if (read_header(m, workspace, workspace_bytes, &ws, nullptr, st)) return 1;
+    COR_CHECK(n_hyp > 0 && n_hyp <= ws.B, "hypothesis count must be in 1..n_rows of the encoded call");
+    COR_CHECK(p_in && h_in && c_in && a_in && p_out && h_out && c_out && a_out, "null argument");
+    const int R = n_hyp, W = m->W, d = m->d;
+    const size_t RW = (size_t)R * W;
+    // stage the caller's rows into the step buffers of the workspace (stride V -> Vp for p)
+    COR_CUDA(cudaMemsetAsync(ws.p, 0, (size_t)R * m->Vp * 4, st));
+    COR_CUDA(cudaMemcpy2DAsync(ws.p, (size_t)m->Vp * 4, p_in, (size_t)m->V * 4, (size_t)m->V * 4, R, cudaMemcpyDeviceToDevice, st));
+    if (ws.p_lo && launch_split(st, ws.p, ws.p, ws.p_lo, (size_t)R * m->Vp)) return 1;
+    StepIO io{};
+    io.R = R; io.row_line = row_line; io.first = false;
+    io.p = ws.p; io.p_lo = ws.p_lo; io.x = ws.x; io.x_lo = ws.x_lo;
+    for (int n = 0; n < d; ++n) {
+        if (copy_in(st, h_in + n * RW, ws.dh[0][n], ws.dh_lo[0][n], RW)) return 1;
+        io.h_in[n] = ws.dh[0][n]; io.h_in_lo[n] = ws.dh_lo[0][n];
+        io.h_out[n] = ws.dh[1][n]; io.h_out_lo[n] = ws.dh_lo[1][n];
+        io.c_in[n] = c_in + n * RW; io.c_out[n] = c_out + n * RW;
+    }
+    io.a_in = a_in; io.a_out = a_out;
+    io.wq = ws.wq; io.ctx = ws.ctx; io.ctx_lo = ws.ctx_lo; io.logits = ws.logits;
+    if (m->cfg.lm_predict && lm_out) {
+        io.h_lm = ws.h_lm; io.h_lm_lo = ws.h_lm_lo; io.c_lm = ws.c_lm; io.logits_lm = ws.logits_lm;
+    }
+    if (decoder_core(m, ws, io, st)) return 1;
+    if (launch_softmax(st, ws.logits, ws.logits, nullptr, R, nullptr, m->V)) return 1;
+    COR_CUDA(cudaMemcpy2DAsync(p_out, (size_t)m->V * 4, ws.logits, (size_t)m->Vp * 4, (size_t)m->V * 4, R, cudaMemcpyDeviceToDevice, st));
+    if (io.logits_lm) {
+        if (launch_softmax(st, ws.logits_lm, ws.p_lm, nullptr, R, nullptr, m->V)) return 1;
+        COR_CUDA(cudaMemcpy2DAsync(lm_out, (size_t)m->V * 4, ws.p_lm, (size_t)m->Vp * 4, (size_t)m->V * 4, R, cudaMemcpyDeviceToDevice, st));
+    }
+    for (int n = 0; n < d; ++n)
+        if (copy_out(st, ws.dh[1][n], ws.dh_lo[1][n], h_out + n * RW, RW)) return 1;
+    return 0;
+}
+
+static int greedy_results(const Ws& ws, int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len,
+                          float* out_align, cudaMemcpyKind kind, cudaStream_t st) {
+    const size_t BS = (size_t)ws.B * 2 * ws.T;
+    if (out_chars) COR_CUDA(cudaMemcpyAsync(out_chars, ws.o_chars, BS * 4, kind, st));
+    if (out_probs) COR_CUDA(cudaMemcpyAsync(out_probs, ws.o_probs, BS * 4, kind, st));
+    if (out_scores) COR_CUDA(cudaMemcpyAsync(out_scores, ws.o_score, (size_t)ws.B * 8, kind, st));
+    if (out_len) COR_CUDA(cudaMemcpyAsync(out_len, ws.o_len, (size_t)ws.B * 4, kind, st));
+    if (out_align) {
+        COR_CHECK(ws.o_align, "alignments were not reserved in this workspace");
+        COR_CUDA(cudaMemcpyAsync(out_align, ws.o_align, BS * ws.T * 4, kind, st));
+    }
+    return 0;
+}
+
+int cor_decode_greedy_batch(cor_model* m, void* workspace, size_t workspace_bytes,
+                            int32_t* out_chars, float* out_probs, double* out_scores,
+                            int32_t* out_len, float* out_align, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    Ws ws;
+    if (read_header(m, workspace, workspace_bytes, &ws, nullptr, st)) return 1;
+    COR_CHECK(!m->cfg.lm_predict, "fast mode with lm_predict is undefined in the reference (seq2seq.py:1248)");
+    if (greedy_loop(m, ws, st)) return 1;
+    return greedy_results(ws, out_chars, out_probs, out_scores, out_len, out_align, cudaMemcpyDeviceToDevice, st);
+}
+
+int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines, void* workspace, size_t workspace_bytes,
+                            int32_t* out_chars, float* out_probs, double* out_scores,
+                            int32_t* out_len, float* out_align, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    Ws ws;
+    if (bind(m, host_lines, workspace, workspace_bytes, out_align != nullptr, &ws)) return 1;
+    COR_CHECK(!m->cfg.lm_predict, "fast mode with lm_predict is undefined in the reference (seq2seq.py:1248)");
+    if (stage_lines(ws, host_lines, cudaMemcpyHostToDevice, st)) return 1;
+    if (!host_lines->val) ws.val = nullptr;
+    if (run_encoder(m, ws, st)) return 1;
+    if (greedy_loop(m, ws, st)) return 1;
+    if (greedy_results(ws, out_chars, out_probs, out_scores, out_len, out_align, cudaMemcpyDeviceToHost, st)) return 1;
+    COR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,120 @@
+// engine.h — internal interfaces shared by the .cu files of libcor_b200.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+
+namespace cor {
+
+// ------------------------------------------------------------------ errors
+void set_error(const std::string& msg);
+#define COR_CUDA(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t _e = (expr);                                                         \
+        if (_e != cudaSuccess) {                                                         \
+            cor::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e) + " at " + \
+                           __FILE__ + ":" + std::to_string(__LINE__));                   \
+            return 1;                                                                    \
+        }                                                                                \
+    } while (0)
+#define COR_CHECK(cond, msg)                                                   \
+    do {                                                                       \
+        if (!(cond)) {                                                         \
+            cor::set_error(std::string(msg) + " (" #cond ") at " + __FILE__ + \
+                           ":" + std::to_string(__LINE__));                    \
+            return 1;                                                          \
+        }                                                                      \
+    } while (0)
+
+extern int64_t g_launches;   // kernels launched (bench.py's gpu_launches)
+
+// ------------------------------------------------------------------ GEMM
+// C[M,N] = sum_s A_s[M,K_s] * B_s[N,K_s]^T   (A row-major, B "K-major": one row per output column)
+// Every B operand is a weight prepared at load time; `B_lo` is the TF32 residual of B
+// (B = hi + lo with hi = B rounded to TF32), used only by the tcgen05 3xTF32 path, which also
+// wants A split the same way (A = A_hi + A_lo, produced by the epilogue that wrote A).
+struct GemmSeg {
+    const float* A;  int lda;      // fp32 (FFMA path) or TF32-hi part (tensor path)
+    const float* A_lo;             // TF32 residual or nullptr
+    const float* B;  int ldb;
+    const float* B_lo;
+    int K;
+};
+constexpr int kMaxSegs = 3;
+
+// plain epilogue: C = act(acc + bias)
+struct StoreEpi {
+    float* C; int ldc;
+    float* C_lo;               // if set: C gets the TF32-hi part and C_lo the residual
+    const float* bias;         // [N] or nullptr
+    int act;                   // 0 none, 1 tanh
+};
+
+// LSTM-cell epilogue.  N = 4W with columns interleaved n = 4*unit + gate (i,f,c~,o).
+// Row r at scan step `step`: active iff step < row_T[r] (row_T == nullptr: always active);
+// t = reverse ? row_T[r]-1-step : step is the sequence position the output belongs to.
+struct LstmEpi {
+    const float* bias;         // [4W] interleaved
+    const float* c_in;         // [M][W]
+    float* c_out;              // [M][W] (may alias c_in)
+    const float* h_prev;       // [M][W] (copied through for inactive rows)
+    const float* h_prev_lo;
+    float* h_out;              // [M][W]
+    float* h_out_lo;           // TF32 residual of h_out or nullptr
+    const int32_t* row_T;
+    int step;
+    int reverse;
+    int rows_total;            // B: row stride of the time-major sequence buffers
+    float* seq_out;  float* seq_out_lo;  int seq_ld; int seq_col;   // seq_out[t][r][seq_col+u]
+    float* seq_rev;  float* seq_rev_lo;                              // seq_rev[T-1-t][r][seq_col+u]
+    const float* resid; const float* resid_lo; int resid_ld;         // residual add into seq_out
+    int cross_sum;             // seq value = h[2k]+h[2k+1] for both members of a pair
+    int W;
+};
+
+// m_dev != nullptr: the row count is read on the device (beam), M is then the capacity.
+int gemm_store_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi);
+int gemm_lstm_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi);
+int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi);
+int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi);
+bool tc_available();
+
+// ------------------------------------------------------------------ small kernels (kernels.cu)
+// X[t][r][:] = sum_k val*E[idx]; Xr[T_r-1-t][r][:] = same (reversed copy for backward scans)
+int launch_embed(cudaStream_t st, const int32_t* idx, const float* val, const int32_t* row_T,
+                 int n_rows, int t_max, int k_alt, const float* E, int W, int V,
+                 float* X, float* X_lo, float* Xr, float* Xr_lo);
+
+struct AttnArgs {
+    const float* wq;           // [R][W]  = h_prev*W_a + b_UW
+    const float* u;            // [T][L][W]
+    const float* enc;          // [T][L][D]  (hi part when enc_lo set)
+    const float* enc_lo;
+    const float* a_prev;       // [R][t_max]
+    const int32_t* row_line;   // [R] or nullptr
+    const int32_t* line_T;     // [L]
+    const float* v_a; float b_v;
+    float* a_out;              // [R][t_max]
+    float* ctx; float* ctx_lo; // [R][D]
+    float* align_log;          // optional [R][t_max] extra copy (alignment history)
+    int R; const int* r_dev; int L; int t_max; int W; int D; int window; int inclusive;
+};
+int launch_attention(cudaStream_t st, const AttnArgs& a);
+
+struct GreedyArgs {
+    const float* logits;       // [R][V]
+    float* p; float* p_lo;     // [R][V] softmax rows (feedback)
+    const int32_t* row_T;
+    const uint8_t* live;       // [R] line has any input
+    int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len; uint8_t* done;
+    int R; int V; int step; int s_max; int eos;
+};
+int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a);
+int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, int R, const int* r_dev, int V);
+int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n);
+int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, size_t n);
+int launch_finish_scores(cudaStream_t st, double* score_sum, const int32_t* len, int R);
+int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int n_rows, int t_max, int k_alt, uint8_t* live);
+
+}  // namespace cor

@@ -1,0 +1,279 @@
+// kernels.cu — the non-GEMM kernels of the hot path: input projection (gather),
+// local monotonic attention, softmax + greedy selection.  All are HBM/L2-bound row kernels:
+// one warp per row, coalesced 128-bit accesses, no shared memory needed.
+#include "engine.h"
+#include "epilogue.cuh"
+#include <math.h>
+
+namespace cor {
+
+namespace {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// ---------------------------------------------------------------- K1: input projection
+// seq2seq.py:237-244 — x_t = X_t . E with X_t given by its non-zeros.  One block per (t,row).
+__global__ void embed_kernel(const int32_t* __restrict__ idx, const float* __restrict__ val,
+                             const int32_t* __restrict__ row_T, int n_rows, int t_max, int k_alt,
+                             const float* __restrict__ E, int W,
+                             float* X, float* X_lo, float* Xr, float* Xr_lo) {
+    const int t = blockIdx.x, r = blockIdx.y;
+    const int T = row_T[r];
+    if (t >= T) return;
+    const int32_t* ip = idx + ((size_t)r * t_max + t) * k_alt;
+    const float* vp = val ? val + ((size_t)r * t_max + t) * k_alt : nullptr;
+    const size_t o_fw = ((size_t)t * n_rows + r) * W;
+    const size_t o_bw = ((size_t)(T - 1 - t) * n_rows + r) * W;
+    for (int u = threadIdx.x; u < W; u += blockDim.x) {
+        float acc = 0.f;
+        for (int k = 0; k < k_alt; ++k) {
+            int v = ip[k];
+            if (v >= 0) acc = fmaf(vp ? vp[k] : 1.0f, E[(size_t)v * W + u], acc);
+        }
+        store_split(X, X_lo, o_fw + u, acc);
+        if (Xr) store_split(Xr, Xr_lo, o_bw + u, acc);
+    }
+}
+
+__global__ void live_rows_kernel(const int32_t* __restrict__ idx, const float* __restrict__ val,
+                                 int n_rows, int t_max, int k_alt, uint8_t* live) {
+    // not np.any(encoder_input_data[j])  (seq2seq.py:1255): any non-zero entry in the row
+    const int r = blockIdx.x;
+    const size_t n = (size_t)t_max * k_alt;
+    int any = 0;
+    for (size_t i = threadIdx.x; i < n; i += blockDim.x) {
+        int v = idx[(size_t)r * n + i];
+        if (v >= 0 && (!val || val[(size_t)r * n + i] != 0.0f)) any = 1;
+    }
+    any = __syncthreads_or(any);
+    if (threadIdx.x == 0) live[r] = (uint8_t)any;
+}
+
+// ---------------------------------------------------------------- K5c-e: attention
+// attention.py:526-575 restricted to the window: positions outside |centre-j|<=w have e*0 = 0
+// exactly, so evaluating only the window gives the same sums.  One warp per hypothesis row.
+__global__ void __launch_bounds__(128) attention_kernel(AttnArgs a) {
+    const int R = a.r_dev ? min(*a.r_dev, a.R) : a.R;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= R) return;
+    const int lane = threadIdx.x & 31;
+    const int line = a.row_line ? a.row_line[row] : row;
+    const int T = a.line_T[line];
+    const float* ap = a.a_prev + (size_t)row * a.t_max;
+    // centre = sum_j a_prev[j]*j + 1  (fp32, attention.py:551-553)
+    float part = 0.f;
+    for (int j = lane; j < T; j += 32) part = fmaf(ap[j], (float)j, part);
+    const float centre = warp_sum(part) + 1.0f;
+    // window bounds: all j with |centre - j| <= w (inclusive) or < w
+    int j_lo = max(0, (int)ceilf(centre - (float)a.window) - 1);
+    int j_hi = min(T - 1, (int)floorf(centre + (float)a.window) + 1);
+    float e[16];      // window_width <= 6 -> at most 2*6+3 candidate positions
+    int nj = 0, jj[16];
+    const float* wq = a.wq + (size_t)row * a.W;
+    for (int j = j_lo; j <= j_hi && nj < 16; ++j) {
+        const float dist = fabsf(centre - (float)j);
+        const bool keep = a.inclusive ? (dist <= (float)a.window) : (dist < (float)a.window);
+        if (!keep) continue;
+        const float* up = a.u + ((size_t)j * a.L + line) * a.W;
+        float s = 0.f;
+        for (int k = lane * 4; k < a.W; k += 128) {
+            const float4 w4 = *reinterpret_cast<const float4*>(wq + k);
+            const float4 u4 = *reinterpret_cast<const float4*>(up + k);
+            const float4 v4 = *reinterpret_cast<const float4*>(a.v_a + k);
+            s = fmaf(tanhf(w4.x + u4.x), v4.x, s);
+            s = fmaf(tanhf(w4.y + u4.y), v4.y, s);
+            s = fmaf(tanhf(w4.z + u4.z), v4.z, s);
+            s = fmaf(tanhf(w4.w + u4.w), v4.w, s);
+        }
+        s = warp_sum(s);
+        e[nj] = expf(s + a.b_v);
+        jj[nj] = j;
+        ++nj;
+    }
+    float esum = 0.f;
+    for (int q = 0; q < nj; ++q) esum += e[q];
+    // alignment row: zero everywhere, a_j = e_j / sum in the window
+    float* ao = a.a_out + (size_t)row * a.t_max;
+    float* al = a.align_log ? a.align_log + (size_t)row * a.t_max : nullptr;
+    for (int j = lane; j < a.t_max; j += 32) {
+        float v = 0.f;
+        for (int q = 0; q < nj; ++q) if (jj[q] == j) v = e[q] / esum;
+        ao[j] = v;
+        if (al) al[j] = v;
+    }
+    // context = sum_j a_j * enc_j
+    for (int k = lane * 4; k < a.D; k += 128) {
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < nj; ++q) {
+            const float w = e[q] / esum;
+            const size_t off = ((size_t)jj[q] * a.L + line) * a.D + k;
+            float4 x = *reinterpret_cast<const float4*>(a.enc + off);
+            if (a.enc_lo) {
+                const float4 y = *reinterpret_cast<const float4*>(a.enc_lo + off);
+                x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+            }
+            c.x = fmaf(w, x.x, c.x); c.y = fmaf(w, x.y, c.y);
+            c.z = fmaf(w, x.z, c.z); c.w = fmaf(w, x.w, c.w);
+        }
+        const size_t o = (size_t)row * a.D + k;
+        store_split(a.ctx, a.ctx_lo, o + 0, c.x);
+        store_split(a.ctx, a.ctx_lo, o + 1, c.y);
+        store_split(a.ctx, a.ctx_lo, o + 2, c.z);
+        store_split(a.ctx, a.ctx_lo, o + 3, c.w);
+    }
+}
+
+// ---------------------------------------------------------------- K5g softmax (+K6 greedy)
+// softmax(h.E^T) (seq2seq.py:379); greedy bookkeeping of decode_batch_greedy (:1250-1260).
+// One warp per row.  The row stride of logits / p is V rounded up to 128; the pad stays zero.
+template <bool GREEDY>
+__global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r_dev) {
+    const int R = r_dev ? min(*r_dev, g.R) : g.R;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= R) return;
+    const int lane = threadIdx.x & 31;
+    const int ld = (g.V + 127) & ~127;
+    const float* z = g.logits + (size_t)row * ld;
+    float m = -INFINITY;
+    for (int v = lane; v < g.V; v += 32) m = fmaxf(m, z[v]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int v = lane; v < g.V; v += 32) s += expf(z[v] - m);
+    s = warp_sum(s);
+    float best = -INFINITY;
+    int best_v = 0x7fffffff;
+    for (int v = lane; v < ld; v += 32) {
+        float pv = 0.f;
+        if (v < g.V) {
+            pv = expf(z[v] - m) / s;
+            if (GREEDY && v >= 1 && pv > best) { best = pv; best_v = v; }   // first maximum among v>=1
+        }
+        store_split(g.p, g.p_lo, (size_t)row * ld + v, pv);
+    }
+    if (!GREEDY) return;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+        if (ob > best || (ob == best && ov < best_v)) { best = ob; best_v = ov; }
+    }
+    if (lane == 0) {
+        const bool alive = !g.done[row] && g.live[row] && g.step < 2 * g.row_T[row];
+        if (alive) {
+            const int n = g.out_len[row];
+            g.out_chars[(size_t)row * g.s_max + n] = best_v;
+            g.out_probs[(size_t)row * g.s_max + n] = best;
+            g.score_sum[row] += (double)(-logf(best));
+            g.out_len[row] = n + 1;
+            if (best_v == g.eos) g.done[row] = 1;
+        }
+    }
+}
+
+__global__ void split_kernel(const float* __restrict__ x, float* hi, float* lo, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        float h, l;
+        tf32_split(x[i], h, l);
+        hi[i] = h;
+        lo[i] = l;
+    }
+}
+
+__global__ void join_kernel(const float* __restrict__ hi, const float* __restrict__ lo, float* out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out[i] = hi[i] + lo[i];
+}
+
+__global__ void finish_scores_kernel(double* score_sum, const int32_t* len, int R) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < R && len[r] > 0) score_sum[r] /= (double)len[r];
+}
+
+}  // namespace
+
+int launch_embed(cudaStream_t st, const int32_t* idx, const float* val, const int32_t* row_T,
+                 int n_rows, int t_max, int k_alt, const float* E, int W, int V,
+                 float* X, float* X_lo, float* Xr, float* Xr_lo) {
+    (void)V;
+    dim3 grid(t_max, n_rows);
+    embed_kernel<<<grid, 128, 0, st>>>(idx, val, row_T, n_rows, t_max, k_alt, E, W, X, X_lo, Xr, Xr_lo);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int n_rows, int t_max, int k_alt, uint8_t* live) {
+    live_rows_kernel<<<n_rows, 128, 0, st>>>(idx, val, n_rows, t_max, k_alt, live);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_attention(cudaStream_t st, const AttnArgs& a) {
+    COR_CHECK(a.window >= 0 && a.window <= 6, "window_width above 6 is not supported");
+    COR_CHECK(a.W % 4 == 0 && a.D % 4 == 0, "W and D must be multiples of 4");
+    if (a.R <= 0) return 0;
+    attention_kernel<<<(a.R + 3) / 4, 128, 0, st>>>(a);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a) {
+    if (a.R <= 0) return 0;
+    softmax_kernel<true><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, int R, const int* r_dev, int V) {
+    if (R <= 0) return 0;
+    GreedyArgs g{};
+    g.logits = logits; g.p = p; g.p_lo = p_lo; g.R = R; g.V = V;
+    softmax_kernel<false><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n) {
+    if (!n) return 0;
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    split_kernel<<<blocks, 256, 0, st>>>(x, hi, lo, n);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, size_t n) {
+    if (!n) return 0;
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    join_kernel<<<blocks, 256, 0, st>>>(hi, lo, out, n);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_finish_scores(cudaStream_t st, double* score_sum, const int32_t* len, int R) {
+    finish_scores_kernel<<<(R + 255) / 256, 256, 0, st>>>(score_sum, len, R);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace cor

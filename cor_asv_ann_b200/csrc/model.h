@@ -1,0 +1,97 @@
+// model.h — device-resident model and workspace layout (internal).
+#pragma once
+#include "engine.h"
+#include "../../include/cor_b200.h"
+#include <map>
+#include <vector>
+
+namespace cor {
+
+// Weight as a GEMM B operand: [rows = output columns][ld = K], K-major.
+struct Mat {
+    float* hi = nullptr;   // full fp32 when !split, TF32 head when split
+    float* lo = nullptr;
+    int rows = 0, ld = 0;
+};
+
+struct LstmW {
+    Mat Kx;                // [4W][in]   (top cell: the x-rows of the kernel, in = W)
+    Mat Kc;                // [4W][D]    (top cell only: the context rows)
+    Mat R;                 // [4W][W]
+    float* bias = nullptr; // [4W] interleaved 4u+g
+};
+
+struct HostWeight { std::vector<int64_t> shape; std::vector<float> data; };
+
+}  // namespace cor
+
+struct cor_model {
+    cor_config cfg{};
+    int device = 0;
+    int W = 0, d = 0, V = 0, Vp = 0, D = 0;
+    bool split = false;       // activations and weights kept as TF32 (hi, lo) pairs for the tcgen05 path
+    bool finalized = false;
+    std::map<std::string, std::vector<cor::HostWeight>> host;   // until finalize
+    std::vector<void*> allocs;
+
+    float* E_full = nullptr;  // [V][W] for the gather
+    cor::Mat E;               // [Vp][W]  logits = h . E^T
+    cor::Mat Et;              // [W][Vp]  x = p . E
+    std::vector<cor::LstmW> enc_fw, enc_bw;
+    std::vector<cor::Mat> bridge_h, bridge_c;
+    std::vector<float*> bridge_hb, bridge_cb;
+    cor::Mat U;               // [W][D]
+    std::vector<cor::LstmW> dec;   // d entries; the last one is the attention cell's LSTMCell
+    cor::Mat Wa;              // [W][W]
+    float* b_UW = nullptr;    // [W]
+    float* v_a = nullptr;     // [W]
+    float b_v = 0.f;
+
+    bool layer_bidi(int n) const { return n == 0 || cfg.deep_bidirectional_encoder; }
+    int enc_in_dim(int n) const { return n == 0 ? W : ((cfg.deep_bidirectional_encoder || n == 1) ? 2 * W : W); }
+    int enc_out_dim(int n) const { return layer_bidi(n) ? 2 * W : W; }
+};
+
+namespace cor {
+
+// Carve of the caller's workspace for (n_rows, t_max, k_alt).  Pure function of its arguments,
+// so cor_encode / cor_decode_step / cor_decode_greedy_batch agree on where things live.
+struct Ws {
+    int B = 0, T = 0, k = 0;
+    size_t bytes = 0;
+    int32_t* row_T = nullptr; int32_t* idx = nullptr; float* val = nullptr; uint8_t* live = nullptr; uint8_t* done = nullptr;
+    float *X = nullptr, *X_lo = nullptr, *Xr = nullptr, *Xr_lo = nullptr;
+    std::vector<float*> seq, seq_lo, seqr, seqr_lo;     // per encoder layer [T][B][Dn]
+    float* u = nullptr;                                  // [T][B][W]
+    float *eh[2][2] = {}, *eh_lo[2][2] = {}, *ec[2] = {};
+    std::vector<float*> st_h, st_c;                      // encoder final states per layer [B][W]
+    std::vector<float*> dh[2], dh_lo[2], dc;             // decoder state ping-pong
+    float* a[2] = {};
+    float *x = nullptr, *x_lo = nullptr, *wq = nullptr, *ctx = nullptr, *ctx_lo = nullptr;
+    float *logits = nullptr, *p = nullptr, *p_lo = nullptr;
+    float *h_lm = nullptr, *h_lm_lo = nullptr, *c_lm = nullptr, *logits_lm = nullptr, *p_lm = nullptr;
+    int32_t* o_chars = nullptr; float* o_probs = nullptr; double* o_score = nullptr; int32_t* o_len = nullptr;
+    float* o_align = nullptr;
+    float* enc_out() const { return seq.back(); }
+    float* enc_out_lo() const { return seq_lo.back(); }
+};
+int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, Ws* ws);
+
+struct StepIO {
+    int R = 0; const int* r_dev = nullptr;
+    const int32_t* row_line = nullptr;
+    bool first = false;                      // p == 0: x = 0 without the projection
+    const float *p = nullptr, *p_lo = nullptr;
+    float *x = nullptr, *x_lo = nullptr;
+    const float* h_in[8] = {}; const float* h_in_lo[8] = {};
+    float* h_out[8] = {}; float* h_out_lo[8] = {};
+    const float* c_in[8] = {}; float* c_out[8] = {};
+    const float* a_in = nullptr; float* a_out = nullptr; float* align_log = nullptr;
+    float *wq = nullptr, *ctx = nullptr, *ctx_lo = nullptr, *logits = nullptr;
+    float *h_lm = nullptr, *h_lm_lo = nullptr, *c_lm = nullptr, *logits_lm = nullptr;
+};
+// One decoder timestep up to the logits (seq2seq.py:416-470); enc_out/u come from `ws`.
+int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st);
+int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st);
+
+}  // namespace cor

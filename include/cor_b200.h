@@ -1,0 +1,142 @@
+/* cor_b200.h — C ABI of the B200-native cor-asv-ann neural hot path.
+ *
+ * The reference has no FFI of its own: its boundary to the numeric engine is
+ * Keras `Model.predict_on_batch` on three graphs built by
+ * `Sequence2Sequence.configure` (ocrd_cor_asv_ann/lib/seq2seq.py:389,403,477).
+ * Each entry point below names the reference interface it replaces.
+ *
+ * Conventions: C linkage; every call returns 0 on success, non-zero on error with
+ * the message in cor_last_error(); no exceptions cross the boundary.  The caller
+ * owns every host and device buffer it passes; the model handle owns only the
+ * repacked weights.  One handle per device, not thread-safe per handle.
+ * `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *
+ * Device tensor layouts (fp32 unless stated):
+ *   sequences are TIME-MAJOR: seq[t][row][feature];
+ *   per-row state is row-major: h[row][W];
+ *   `row_T[row]` is the padded length T of the reference batch the row belongs to
+ *   (padding is NOT masked in the reference, SURVEY.md A.6 item 1, so T is part of
+ *   the input); rows of several reference batches may share one call.
+ */
+#ifndef COR_B200_H
+#define COR_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cor_model cor_model;
+
+/* Topology switches — seq2seq.py:108-179 (width, depth, voc_size, residual_connections,
+ * deep_bidirectional_encoder, bridge_dense, lm_predict) and attention.py:515 (window_width). */
+typedef struct cor_config {
+    int32_t width;
+    int32_t depth;
+    int32_t voc_size;
+    int32_t residual_connections;
+    int32_t deep_bidirectional_encoder;
+    int32_t bridge_dense;
+    int32_t lm_predict;
+    int32_t window_width;      /* 5 in the reference (seq2seq.py:347,452) */
+    int32_t eos_index;         /* index of '\n' in the mapping (1 when built by map_files, seq2seq.py:580-586) */
+    int32_t gemm_mode;         /* 0 auto, 1 force FFMA fp32, 2 force tcgen05 3xTF32 */
+} cor_config;
+
+/* Input lines of one call — replaces the dense (B,T,V) array of
+ * vectorize_lines (seq2seq.py:1020-1119) by its non-zeros.
+ * idx/val are [n_rows][t_max][k_alt]; idx < 0 marks "no entry" (true-zero padding);
+ * val == NULL means all ones (plain strings).  Host or device pointers as the call says. */
+typedef struct cor_lines {
+    int32_t n_rows;
+    int32_t t_max;
+    int32_t k_alt;
+    const int32_t* row_T;      /* [n_rows] */
+    const int32_t* idx;
+    const float*   val;
+} cor_lines;
+
+/* Beam parameters — seq2seq.py:111,162-169. */
+typedef struct cor_beam_params {
+    int32_t batch_size;          /* 256 */
+    int32_t beam_width_in;       /* 15  */
+    int32_t beam_width_out;      /* 16  */
+    double  beam_threshold_in;   /* 0.2 */
+    double  rejection_threshold; /* 0.3 class default / 0.5 CLI default; 0 disables */
+} cor_beam_params;
+
+const char* cor_last_error(void);
+int cor_abi_version(void);
+
+/* ---- model lifetime: replaces configure()+load_weights()+_resync_decoder()
+ *      (seq2seq.py:190-489, 1164-1174, 526-528). */
+int cor_model_create(const cor_config* cfg, int device, cor_model** out);
+/* One Keras weight by layer name and position inside the layer (SURVEY.md A.5 order), in the
+ * Keras (in, out) layout; the Keras -> kernel repack (transposition to K-major, gate
+ * interleave, TF32 hi/lo split) happens here.  A CuDNN-format LSTM layer (bias 8W) is
+ * detected by its bias length and converted as Keras does on load. */
+int cor_model_set_weight(cor_model* m, const char* keras_layer, int index,
+                         const float* host, const int64_t* shape, int rank);
+int cor_model_finalize(cor_model* m);
+void cor_model_destroy(cor_model* m);
+
+/* ---- workspace: one caller-allocated device buffer per call group. */
+int cor_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
+                        int want_alignments, size_t* bytes);
+
+/* ---- encoder: replaces encoder_model.predict_on_batch (seq2seq.py:811,1231,1306,1383).
+ * `lines` holds DEVICE pointers.  Results stay inside `workspace`; the optional outputs
+ * receive copies: enc_out [t_max][n_rows][D], states [2*depth][n_rows][W] (h1,c1,...,hd,cd). */
+int cor_encode(cor_model* m, const cor_lines* lines, void* workspace, size_t workspace_bytes,
+               float* enc_out, float* states, void* stream);
+
+/* ---- one decoder timestep: replaces decoder_model.predict_on_batch (seq2seq.py:1245,1321,1428).
+ * Rows are hypotheses; row_line[r] (NULL = identity) names the encoded line in `workspace`
+ * each hypothesis attends to (the reference broadcasts a batch-1 enc_out, seq2seq.py:1428).
+ * p_in [R][V] previous softmax rows (zeros at the first step); h_in/c_in [depth][R][W];
+ * a_in [R][t_max].  Outputs p_out [R][V], lm_out [R][V] (only with lm_predict, else NULL),
+ * h_out/c_out [depth][R][W], a_out [R][t_max].  In and out must not alias. */
+int cor_decode_step(cor_model* m, void* workspace, size_t workspace_bytes,
+                    int n_hyp, const int32_t* row_line,
+                    const float* p_in, const float* h_in, const float* c_in, const float* a_in,
+                    float* p_out, float* lm_out, float* h_out, float* c_out, float* a_out,
+                    void* stream);
+
+/* ---- fast mode: replaces decode_batch_greedy (seq2seq.py:1215-1286) for rows already
+ * encoded into `workspace` by cor_encode.  Runs 2*row_T[row] steps per row.
+ * out_chars int32 [n_rows][2*t_max], out_probs [n_rows][2*t_max], out_scores double [n_rows]
+ * (mean -log p), out_len int32 [n_rows], out_align [2*t_max][n_rows][t_max] or NULL. All DEVICE. */
+int cor_decode_greedy_batch(cor_model* m, void* workspace, size_t workspace_bytes,
+                            int32_t* out_chars, float* out_probs, double* out_scores,
+                            int32_t* out_len, float* out_align, void* stream);
+
+/* ---- the call a host program makes: HOST lines in, HOST results out; host<->device copies
+ * happen inside, on `stream`, and the call returns after the results have landed.
+ * Replaces correct_lines(fast=True) (seq2seq.py:782-808). */
+int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines,
+                            void* workspace, size_t workspace_bytes,
+                            int32_t* out_chars, float* out_probs, double* out_scores,
+                            int32_t* out_len, float* out_align, void* stream);
+
+/* ---- beam mode: replaces the per-line loop of correct_lines(fast=False, greedy=False)
+ * over decode_sequence_beam (seq2seq.py:823-836, 1356-1544) for all rows at once.
+ * Workspace size comes from cor_beam_workspace_bytes.  Per row: the best final hypothesis
+ * (out_len = 0 when the search yields none, i.e. the reference's StopIteration fallback),
+ * out_scores = cum_cost/(len-1), out_align compact [n_rows][2*t_max][t_max] or NULL;
+ * stats int64 [n_rows][4] = iterations, hypothesis-steps, finals, open nodes left. All HOST. */
+int cor_beam_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
+                             const cor_beam_params* bp, size_t budget_bytes, size_t* bytes);
+int cor_correct_beam_host(cor_model* m, const cor_lines* host_lines, const cor_beam_params* bp,
+                          void* workspace, size_t workspace_bytes,
+                          int32_t* out_chars, float* out_probs, double* out_scores,
+                          int32_t* out_len, float* out_align, int64_t* stats, void* stream);
+
+/* ---- instrumentation for bench.py: kernels launched since the last reset, and device
+ * time accumulated by the GEMM kernels between cor_prof_enable(1) and cor_prof_enable(0). */
+int64_t cor_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COR_B200_H */
