@@ -12,6 +12,35 @@ static thread_local std::string g_error;
 int64_t g_launches = 0;
 void set_error(const std::string& msg) { g_error = msg; }
 
+// ------------------------------------------------------------------ per-launch timing (bench.py roofline)
+// When enabled, every LSTM-GEMM launch (the dominant kernel) is bracketed by two events on the
+// launching stream; cor_prof_read sums the elapsed times after a synchronize.
+struct Prof {
+    bool on = false;
+    std::vector<cudaEvent_t> ev;     // pairs
+    size_t used = 0;
+    double flops = 0;
+    int64_t launches = 0;
+} g_prof;
+
+static void prof_begin(cudaStream_t st) {
+    if (!g_prof.on) return;
+    if (g_prof.used + 2 > g_prof.ev.size()) {
+        if (g_prof.ev.size() >= 60000) return;
+        for (int i = 0; i < 2; ++i) { cudaEvent_t e; cudaEventCreate(&e); g_prof.ev.push_back(e); }
+    }
+    cudaEventRecord(g_prof.ev[g_prof.used], st);
+}
+static void prof_end(cudaStream_t st, int M, int N, const GemmSeg* s, int n) {
+    if (!g_prof.on || g_prof.used + 2 > g_prof.ev.size()) return;
+    cudaEventRecord(g_prof.ev[g_prof.used + 1], st);
+    g_prof.used += 2;
+    double k = 0;
+    for (int i = 0; i < n; ++i) k += s[i].K;
+    g_prof.flops += 2.0 * M * N * k;
+    g_prof.launches += 1;
+}
+
 // GEMM dispatch: tcgen05 3xTF32 when the model keeps split operands and the tile is worth it,
 // exact FFMA otherwise (small M).  Both consume the same operand representation.
 static int gemm_store(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const StoreEpi& e) {
@@ -19,8 +48,12 @@ static int gemm_store(cor_model* m, cudaStream_t st, int M, const int* m_dev, in
     return gemm_store_ffma(st, M, m_dev, N, s, n, e);
 }
 static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const LstmEpi& e) {
-    if (m->split && M >= 64 && tc_available()) return gemm_lstm_tc(st, M, m_dev, N, s, n, e);
-    return gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
+    prof_begin(st);
+    int rc;
+    if (m->split && M >= 64 && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
+    else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
+    prof_end(st, M, N, s, n);
+    return rc;
 }
 
 // ------------------------------------------------------------------ weights
@@ -384,6 +417,25 @@ extern "C" {
 const char* cor_last_error(void) { return g_error.c_str(); }
 int cor_abi_version(void) { return 1; }
 int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launches = 0; return v; }
+
+int cor_prof_enable(int on) {
+    g_prof.on = on != 0;
+    if (on) { g_prof.used = 0; g_prof.flops = 0; g_prof.launches = 0; }
+    return 0;
+}
+int cor_prof_read(double* total_ms, int64_t* launches, double* flops) {
+    COR_CUDA(cudaDeviceSynchronize());
+    double ms = 0;
+    for (size_t i = 0; i + 1 < g_prof.used; i += 2) {
+        float t = 0;
+        COR_CUDA(cudaEventElapsedTime(&t, g_prof.ev[i], g_prof.ev[i + 1]));
+        ms += t;
+    }
+    if (total_ms) *total_ms = ms;
+    if (launches) *launches = g_prof.launches;
+    if (flops) *flops = g_prof.flops;
+    return 0;
+}
 
 int cor_model_create(const cor_config* cfg, int device, cor_model** out) {
     COR_CHECK(cfg && out, "null argument");

@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(NT) gemm_ffma_kernel(FfmaParams p, Epi epi) {
                 v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
             }
             ra[h] = v;
-            size_t offb = (size_t)(n0 + lrow + 64 * h) * g.ldb + k0 + lk;
+            size_t offb = (size_t)min(n0 + lrow + 64 * h, p.N - 1) * g.ldb + k0 + lk;
             float4 b = *reinterpret_cast<const float4*>(g.B + offb);
             if (g.B_lo) {
                 float4 w = *reinterpret_cast<const float4*>(g.B_lo + offb);
@@ -110,7 +110,8 @@ __global__ void __launch_bounds__(NT) gemm_ffma_kernel(FfmaParams p, Epi epi) {
         if (row >= M) continue;
         if constexpr (EPI == 0) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) store_elem(epi, row, n0 + tx * 8 + j, acc[i][j]);
+            for (int j = 0; j < 8; ++j)
+                if (n0 + tx * 8 + j < p.N) store_elem(epi, row, n0 + tx * 8 + j, acc[i][j]);
         } else {
             float z[2][4];
 #pragma unroll
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(NT) gemm_ffma_kernel(FfmaParams p, Epi epi) {
 
 int check_segs(int N, const GemmSeg* segs, int nseg) {
     COR_CHECK(nseg >= 1 && nseg <= kMaxSegs, "bad segment count");
-    COR_CHECK(N % BN == 0, "N must be a multiple of 128");
+    COR_CHECK(N > 0, "N must be positive");
     for (int s = 0; s < nseg; ++s) {
         COR_CHECK(segs[s].K % BK == 0 && segs[s].K > 0, "K must be a positive multiple of 16");
         COR_CHECK(segs[s].lda % 4 == 0 && segs[s].ldb % 4 == 0, "leading dimensions must be multiples of 4");
@@ -137,7 +138,7 @@ int gemm_store_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmS
     FfmaParams p{};
     for (int s = 0; s < nseg; ++s) p.segs[s] = segs[s];
     p.nseg = nseg; p.M = M; p.m_dev = m_dev; p.N = N;
-    dim3 grid(N / BN, (M + BM - 1) / BM);
+    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
     gemm_ffma_kernel<0, StoreEpi><<<grid, NT, 0, st>>>(p, epi);
     ++g_launches;
     COR_CUDA(cudaGetLastError());
@@ -147,11 +148,11 @@ int gemm_store_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmS
 int gemm_lstm_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi) {
     if (M <= 0) return 0;
     if (check_segs(N, segs, nseg)) return 1;
-    COR_CHECK(N == 4 * epi.W, "LSTM epilogue needs N == 4W");
+    COR_CHECK(N == 4 * epi.W && N % BN == 0, "LSTM epilogue needs N == 4W, a multiple of 128");
     FfmaParams p{};
     for (int s = 0; s < nseg; ++s) p.segs[s] = segs[s];
     p.nseg = nseg; p.M = M; p.m_dev = m_dev; p.N = N;
-    dim3 grid(N / BN, (M + BM - 1) / BM);
+    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
     gemm_ffma_kernel<1, LstmEpi><<<grid, NT, 0, st>>>(p, epi);
     ++g_launches;
     COR_CUDA(cudaGetLastError());

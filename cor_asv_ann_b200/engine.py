@@ -181,6 +181,15 @@ class Engine:
                                                  _ptr(stats), self._stream()))
         return out
 
+    def prof_enable(self, on=True):
+        check(self.lib.cor_prof_enable(int(on)))
+
+    def prof_read(self):
+        """(total ms, launches, algorithmic flops) of the LSTM-GEMM launches since prof_enable(True)."""
+        ms, n, fl = C.c_double(), C.c_int64(), C.c_double()
+        check(self.lib.cor_prof_read(C.byref(ms), C.byref(n), C.byref(fl)))
+        return ms.value, n.value, fl.value
+
     def launch_count(self, reset=False):
         return int(self.lib.cor_launch_count(int(reset)))
 
