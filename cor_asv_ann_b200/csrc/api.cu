@@ -44,13 +44,13 @@ static void prof_end(cudaStream_t st, int M, int N, const GemmSeg* s, int n) {
 // GEMM dispatch: tcgen05 3xTF32 when the model keeps split operands and the tile is worth it,
 // exact FFMA otherwise (small M).  Both consume the same operand representation.
 static int gemm_store(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const StoreEpi& e) {
-    if (m->split && M >= 64 && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e);
+    if (m->split && M >= m->tc_min_rows && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e);
     return gemm_store_ffma(st, M, m_dev, N, s, n, e);
 }
 static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const LstmEpi& e) {
     prof_begin(st);
     int rc;
-    if (m->split && M >= 64 && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
+    if (m->split && M >= m->tc_min_rows && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
     else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
     prof_end(st, M, N, s, n);
     return rc;
@@ -418,6 +418,30 @@ const char* cor_last_error(void) { return g_error.c_str(); }
 int cor_abi_version(void) { return 1; }
 int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launches = 0; return v; }
 
+// Test hook: C[M,N] = A[M,K] . B[N,K]^T through one of the two GEMM kernels (1 = FFMA, 2 = tcgen05 3xTF32).
+int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    COR_CHECK(mode == 1 || mode == 2, "mode must be 1 (FFMA) or 2 (tcgen05)");
+    StoreEpi e{C, N, nullptr, nullptr, 0};
+    if (mode == 1) {
+        GemmSeg s{A, K, nullptr, B, K, nullptr, K};
+        return gemm_store_ffma(st, M, nullptr, N, &s, 1, e);
+    }
+    float *a_hi = nullptr, *a_lo = nullptr, *b_hi = nullptr, *b_lo = nullptr;
+    const size_t na = (size_t)M * K, nb = (size_t)N * K;
+    COR_CUDA(cudaMalloc(&a_hi, na * 4)); COR_CUDA(cudaMalloc(&a_lo, na * 4));
+    COR_CUDA(cudaMalloc(&b_hi, nb * 4)); COR_CUDA(cudaMalloc(&b_lo, nb * 4));
+    int rc = launch_split(st, A, a_hi, a_lo, na) || launch_split(st, B, b_hi, b_lo, nb);
+    if (!rc) {
+        GemmSeg s{a_hi, K, a_lo, b_hi, K, b_lo, K};
+        rc = gemm_store_tc(st, M, nullptr, N, &s, 1, e);
+    }
+    cudaError_t err = cudaStreamSynchronize(st);
+    cudaFree(a_hi); cudaFree(a_lo); cudaFree(b_hi); cudaFree(b_lo);
+    if (!rc && err != cudaSuccess) { set_error(std::string("debug gemm: ") + cudaGetErrorString(err)); rc = 1; }
+    return rc;
+}
+
 int cor_prof_enable(int on) {
     g_prof.on = on != 0;
     if (on) { g_prof.used = 0; g_prof.flops = 0; g_prof.launches = 0; }
@@ -452,6 +476,7 @@ int cor_model_create(const cor_config* cfg, int device, cor_model** out) {
     m->W = cfg->width; m->d = cfg->depth; m->V = cfg->voc_size; m->Vp = (cfg->voc_size + 127) & ~127;
     m->D = (cfg->depth == 1 || cfg->deep_bidirectional_encoder) ? 2 * cfg->width : cfg->width;
     m->split = cfg->gemm_mode == 2 || (cfg->gemm_mode == 0 && tc_available());
+    m->tc_min_rows = cfg->gemm_mode == 2 ? 1 : 64;   // below one half tile the exact FFMA kernel is used
     *out = m;
     return 0;
 }

@@ -1,0 +1,39 @@
+"""The two GEMM kernels against a float64 matmul, through the C-ABI test hook cor_debug_gemm."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(mode, M, N, K, seed=0):
+    from cor_asv_ann_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    A = torch.randn(M, K, device="cuda", generator=g)
+    B = torch.randn(N, K, device="cuda", generator=g) * 0.1
+    Cm = torch.full((M, N), float("nan"), device="cuda")
+    _lib.check(lib.cor_debug_gemm(mode, M, N, K, C.c_void_p(A.data_ptr()), C.c_void_p(B.data_ptr()),
+                                  C.c_void_p(Cm.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    ref = A.double() @ B.double().T
+    scale = (A.double().abs() @ B.double().abs().T)
+    return ((Cm.double() - ref).abs() / scale).max().item()
+
+
+@pytest.mark.parametrize("shape", [(128, 128, 16), (300, 256, 64), (77, 512, 512)])
+def test_ffma_gemm(shape):
+    err = _run(1, *shape)
+    print("ffma %s: %.3g" % (shape, err))
+    assert err < 1e-6
+
+
+@pytest.mark.parametrize("shape", [(128, 256, 32), (128, 256, 128), (256, 512, 512), (1000, 2048, 1536),
+                                   (77, 128, 64), (333, 96, 96), (16384, 512, 512)])
+def test_tcgen05_3xtf32_gemm(shape):
+    """Relative to sum |a||b| the 3xTF32 result must be fp32-grade (a single TF32 pass is ~5e-4)."""
+    err = _run(2, *shape)
+    print("tcgen05 3xTF32 %s: max |err| / sum|a||b| = %.3g" % (shape, err))
+    assert err < 1e-5, err
