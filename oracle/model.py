@@ -63,9 +63,13 @@ def _orthogonal(rng, shape):
     return q.astype(np.float32)
 
 
-def _lstm_weights(rng, in_dim, W):
+def _lstm_weights(rng, in_dim, W, bias_noise=0.0):
     b = np.zeros(4 * W, np.float32)
     b[W:2 * W] = 1.0          # unit_forget_bias
+    if bias_noise:
+        # trained models have non-zero biases; with the Keras default (zeros) an LSTM that starts
+        # in zero padding stays at exactly zero state, which would hide the un-masked padding
+        b += (rng.standard_normal(4 * W) * bias_noise).astype(np.float32)
     return [_glorot(rng, (in_dim, 4 * W)), _orthogonal(rng, (W, 4 * W)), b]
 
 
@@ -74,12 +78,14 @@ def init_weights(topo, seed=0, variant="U"):
 
     variant "K": Keras default initialisers (embedding N(0, 0.001), seq2seq.py:240).
     variant "U": same, embedding rows rescaled to unit norm (what the regulariser
-    at seq2seq.py:549-551 drives trained models to) — gives realistic softmax margins.
+    at seq2seq.py:549-551 drives trained models to) — gives realistic softmax margins —
+    and N(0, 0.1) noise on the LSTM biases (so that padding steps change the state).
     Returns ``{keras_layer_name: [ndarray, ...]}``.
     """
     rng = np.random.default_rng(seed)
     W, d, V, D = topo.width, topo.depth, topo.voc_size, topo.enc_dim
     w = {}
+    bn = 0.1 if variant == "U" else 0.0
     E = (rng.standard_normal((V, W)) * 0.001).astype(np.float32)
     if variant == "U":
         E = (E / np.linalg.norm(E, axis=1, keepdims=True)).astype(np.float32)
@@ -87,21 +93,21 @@ def init_weights(topo, seed=0, variant="U"):
     for n in range(d):
         name = "encoder_lstm_%d" % (n + 1)
         if topo.layer_is_bidi(n):
-            w[name] = _lstm_weights(rng, topo.enc_in_dim(n), W) + _lstm_weights(rng, topo.enc_in_dim(n), W)
+            w[name] = _lstm_weights(rng, topo.enc_in_dim(n), W, bn) + _lstm_weights(rng, topo.enc_in_dim(n), W, bn)
         else:
-            w[name] = _lstm_weights(rng, topo.enc_in_dim(n), W)
+            w[name] = _lstm_weights(rng, topo.enc_in_dim(n), W, bn)
         if topo.bridge_dense:
             w["bridge_h_%d" % (n + 1)] = [_glorot(rng, (W, W)), (rng.standard_normal(W) * 0.05).astype(np.float32)]
             w["bridge_c_%d" % (n + 1)] = [_glorot(rng, (W, W)), (rng.standard_normal(W) * 0.05).astype(np.float32)]
     w["attention_dense"] = [_glorot(rng, (D, W))]
     for n in range(d - 1):
-        w["decoder_lstm_%d" % (n + 1)] = _lstm_weights(rng, W, W)
+        w["decoder_lstm_%d" % (n + 1)] = _lstm_weights(rng, W, W, bn)
     w["decoder_lstm_%d" % d] = [
         _glorot(rng, (W, W)),                                    # W_a
         _glorot(rng, (W, 1)),                                    # v_a
         (rng.standard_normal(W) * 0.05).astype(np.float32),      # b_UW (zeros in Keras; non-zero exercises the path)
         (rng.standard_normal(1) * 0.05).astype(np.float32),      # b_v
-    ] + _lstm_weights(rng, W + D, W)
+    ] + _lstm_weights(rng, W + D, W, bn)
     return w
 
 

@@ -1,0 +1,143 @@
+#!/usr/bin/env python
+"""Generate the committed fixtures under tests/golden/.
+
+Run in the build container (where /root/reference exists):  python tests/make_golden.py
+
+1. ``kant_lines.json`` — the 55 TextLines of the reference's own test workspace
+   (/root/reference/testdata/data/kant_aufklaerung_1784-complex/data/
+   OCR-D-OCR-TESS-Fraktur-SEG-LINE-tesseract-ocropy-DEWARP/*_000{1,2}.xml, the file group
+   tests/test_all.py:110 uses), extracted at glyph level the way
+   wrapper/transcode.py:161-233 (_page_get_line_sequences_at) and :236-277
+   (_line_sequences2confmat_sequences) do: one chunk per glyph with all its TextEquiv alternatives
+   and @conf, a space between words, a newline at the end; one batch per page.
+2. ``*.npz`` — known-answer vectors of the oracle (encoder output digests, decoder-step
+   probabilities, greedy and beamed strings / probabilities / scores / search statistics) on
+   seeded inputs and seeded random-init weights.
+
+PARITY UNPINNED: Keras/TF cannot be imported here, so these vectors are the oracle's own output
+(cross-checked by tests/restatement_torch.py), not the reference's.  They pin the oracle against
+regressions and give the GPU tests fixed targets.
+"""
+import json
+import os
+import sys
+import xml.etree.ElementTree as ET
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+KANT = ("/root/reference/testdata/data/kant_aufklaerung_1784-complex/data/"
+        "OCR-D-OCR-TESS-Fraktur-SEG-LINE-tesseract-ocropy-DEWARP")
+GAP = '\a'
+
+
+def _ns(tag):
+    return tag.split('}', 1)[-1]
+
+
+def page_confmats(path):
+    """One page -> list of lines; line = list of chunks; chunk = list of [string, conf]."""
+    root = ET.parse(path).getroot()
+    lines = []
+    for tl in root.iter():
+        if _ns(tl.tag) != "TextLine":
+            continue
+        seq = []
+        words = [w for w in tl if _ns(w.tag) == "Word"]
+        for word in words:
+            glyphs = [g for g in word if _ns(g.tag) == "Glyph"]
+            if not glyphs:
+                continue
+            for g in glyphs:
+                alts = []
+                for te in g:
+                    if _ns(te.tag) != "TextEquiv":
+                        continue
+                    uni = next((u.text or '' for u in te if _ns(u.tag) == "Unicode"), '')
+                    conf = te.get("conf")
+                    alts.append([uni if uni else GAP, float(conf) if conf is not None else 1.0])
+                seq.append(alts if alts else [[GAP, 1.0]])
+            seq.append([[' ', 1.0]])
+        if seq:
+            seq.pop()
+        seq.append([['\n', 1.0]])
+        if len(seq) > 1:
+            lines.append(seq)
+    return lines
+
+
+def make_kant():
+    pages = []
+    for name in sorted(os.listdir(KANT)):
+        if name.endswith(".xml"):
+            pages.append(page_confmats(os.path.join(KANT, name)))
+    chars = sorted({ch for page in pages for line in page for chunk in line for s, _ in chunk for ch in s
+                    if ch not in (GAP, '\n')})
+    alphabet = ['', '\n'] + chars        # '' -> 0, '\n' -> 1 like map_files (seq2seq.py:580-586)
+    with open(os.path.join(GOLDEN, "kant_lines.json"), "w", encoding="utf-8") as f:
+        json.dump({"source": KANT, "alphabet": alphabet, "pages": pages}, f, ensure_ascii=False)
+    return alphabet, pages
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    from oracle import model as om, decoders as od
+    from tests.common import make_model, synthetic_lines, kant_fixture, kant_model, BEAM_CASES
+    if os.path.isdir(KANT):
+        alphabet, pages = make_kant()
+        print("kant: %d pages, %s lines, %d chars" % (len(pages), [len(p) for p in pages], len(alphabet)))
+
+    # ---- synthetic known answers, one file per topology
+    for name in ("c1", "c2s", "c3res", "c4s"):
+        topo, w, mapping = make_model(name)
+        lines = synthetic_lines(mapping, 7, 17, seed=101, min_length=4) + ['']
+        x = od.vectorize_lines(mapping, topo.voc_size, lines)
+        enc = om.encode(topo, w, x)
+        p0, lm0, st0 = om.decode_step(topo, w, np.zeros((len(lines), topo.voc_size), np.float32), enc[0], enc[1:])
+        p1, lm1, st1 = om.decode_step(topo, w, p0, enc[0], st0)
+        out = dict(lines=np.array(lines, dtype=object), enc_out=enc[0], enc_states=np.stack(enc[1:-1]),
+                   p0=p0, p1=p1, a0=st0[-1], a1=st1[-1])
+        if topo.lm_predict:
+            out.update(lm0=lm0, lm1=lm1)
+        else:
+            text, probs, score, _ = od.decode_batch_greedy(topo, w, mapping, x)
+            out.update(greedy_text=np.array(text, dtype=object), greedy_score=np.array(score),
+                       greedy_probs=np.array([np.array(p, np.float32) for p in probs] + [None], dtype=object)[:-1])
+        np.savez_compressed(os.path.join(GOLDEN, "forward_%s.npz" % name), **out)
+        print("forward_%s ok" % name)
+
+    # ---- beam known answers
+    for case, (name, n, length, seed, params) in BEAM_CASES.items():
+        topo, w, mapping = make_model(name)
+        lines = synthetic_lines(mapping, n, length, seed=seed, min_length=max(3, length // 2))
+        stats = {}
+        text, probs, score, _ = od.correct_lines(topo, w, mapping, lines, fast=False, greedy=False,
+                                                 beam_params=params, stats=stats)
+        st = np.array([[s.get("iterations", 0), s.get("hypothesis_steps", 0), s.get("finals", 0), s.get("open_left", 0)]
+                       for s in stats["lines"]], np.int64)
+        np.savez_compressed(os.path.join(GOLDEN, "beam_%s.npz" % case), lines=np.array(lines, dtype=object),
+                            text=np.array(text, dtype=object), score=np.array(score, np.float64), stats=st,
+                            probs=np.array([np.array(p, np.float32) for p in probs] + [None], dtype=object)[:-1])
+        print("beam_%s ok: %s" % (case, st.tolist()))
+
+    # ---- config 1: the kant lines through depth 1 / width 128 (fast greedy), strings and confmats
+    alphabet, pages = kant_fixture()
+    topo, w, mapping = kant_model(alphabet)
+    res = {}
+    for pno, page in enumerate(pages):
+        plain = [''.join(chunk[0][0] for chunk in line).replace(GAP, '') for line in page]
+        t1, p1, s1, _ = od.correct_lines(topo, w, mapping, plain, fast=True)
+        conf = [[[(s, c) for s, c in chunk] for chunk in line] for line in page]
+        t2, p2, s2, _ = od.correct_lines(topo, w, mapping, conf, conf=conf, fast=True)
+        res["plain_text_%d" % pno] = np.array(t1, dtype=object)
+        res["plain_score_%d" % pno] = np.array(s1)
+        res["confmat_text_%d" % pno] = np.array(t2, dtype=object)
+        res["confmat_score_%d" % pno] = np.array(s2)
+    np.savez_compressed(os.path.join(GOLDEN, "kant_c1.npz"), **res)
+    print("kant_c1 ok")
+
+
+if __name__ == "__main__":
+    main()
