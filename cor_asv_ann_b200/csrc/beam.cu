@@ -1,14 +1,828 @@
-// beam.cu — GPU beam search (decode_sequence_beam, seq2seq.py:1356-1544).  Under construction.
+// beam.cu — GPU beam search: decode_sequence_beam (ocrd_cor_asv_ann/lib/seq2seq.py:1356-1544) and
+// its Node trie (:1546-1608) for many lines at once, entirely on the device.
+//
+// The reference runs, per line, a best-first (A*-like) search: a global sorted list of open
+// hypotheses, from which every iteration pops the <= batch_size best, runs ONE decoder step on them,
+// and inserts up to beam_width_in (+1 rejection) children per hypothesis back into the list.
+// Here a "wave" of L lines runs those iterations in lock step; every iteration is the kernel sequence
+//     pop -> scan -> rowmap -> gather -> [decoder step kernels on R rows] -> expand -> push
+// with R (the number of hypothesis rows over all lines) known only on the device (r_dev).
+//
+// Data layout in HBM (per wave):
+//   * expansion records, one per hypothesis that went through a decoder step, line-local index xid
+//     in a fixed per-line arena of quota_x records: the output softmax row after the rejection
+//     overwrite (V floats), the new LSTM states (2*depth*W), the alignment row (T), and <= 16 children
+//     (character, probability, fp64 cumulative cost, rejection flag).
+//   * a hypothesis (trie node) is the pair (xid of its parent's record, child slot k), numbered
+//     id = 1 + 16*xid + k; id 0 is the root.  Ids grow in insertion order, which is the reference's
+//     tie-break (insort_left + pop(): first inserted, first popped among equal keys).
+//   * the feedback vector of child k is the record's softmax row with children 0..k-1 zeroed
+//     (seq2seq.py:1506-1514: `scores1 = np.copy(scores); scores[idx] = 0`), rebuilt at gather time.
+//   * per line a sorted fringe (fp64 key, id), double-buffered; push = bitonic sort of the new
+//     children in shared memory + rank-merge with the old fringe, truncated to 2T*batch_size (:1531).
+// A line whose arena (or the wave's row capacity) overflows is reported back and re-run by the host
+// loop in a smaller wave with a larger arena; results do not depend on the wave a line ran in.
 #include "model.h"
+#include "epilogue.cuh"
+#include <math.h>
+#include <float.h>
+#include <algorithm>
+#include <vector>
+
+namespace cor {
+
+namespace {
+
+constexpr int KMAX = 16;             // children per expansion: beam_width_in (<= 15) + rejection candidate
+constexpr int MAX_NEW = 4096;        // batch_size (<= 256) * KMAX
+constexpr int ST_ACTIVE = 0, ST_DONE = 1, ST_OVERFLOW = 2, ST_EMPTY = 3;
+constexpr uint32_t FINAL_BIT = 0x80000000u;
+
+struct BeamDev {
+    // geometry and parameters
+    int L, T, V, Vp, W, d, D, k_alt;
+    int batch, width_in, width_out, eos, lm;
+    double thr_in, rej_thr;
+    int quota_x, cap, Rcap;
+    // encoder products (views into the encoder workspace)
+    const int32_t* row_T; const uint8_t* live; const int32_t* idx; const float* val;
+    const float* st_h[8]; const float* st_c[8];
+    // per line
+    int32_t *status, *iter, *x_count, *x_base, *beam_count, *row_base, *fr_len, *fr_off, *fr_buf;
+    int32_t *finals_count, *best_final, *open_left;
+    double* best_key; long long* hyp_steps;
+    double* fr_key; uint32_t* fr_id;       // [2][L][cap]
+    uint32_t* beam_nodes;                  // [L][batch]
+    int32_t* rej_table;                    // [L][T]
+    int32_t* counters;                     // [0] rows this iteration (r_dev), [1] active lines
+    // per record g = line*quota_x + xid
+    float *rec_p, *rec_h, *rec_c, *rec_a;  // [G][Vp], [G][d][W], [G][d][W], [G][T]
+    double* rec_cur; uint8_t* rec_amax1; int32_t *rec_pos, *rec_len, *rec_nacc; uint32_t* rec_parent;
+    int32_t* ch_v; float* ch_p; double* ch_cum; uint8_t* ch_rej;   // [G][KMAX]
+    // per row of the current iteration
+    int32_t *row_line, *row_xid; uint32_t* row_node;
+    long long* o_stats; float* o_align;    // result staging: [L][4], [L][2T][T] (optional)
+    float *p, *p_lo, *logits, *logits_lm, *a_in, *a_out;
+    float *h_in[8], *h_in_lo[8], *h_out[8], *h_out_lo[8], *c_in[8], *c_out[8];
+};
+
+__device__ __forceinline__ bool key_less(double ka, uint32_t ia, double kb, uint32_t ib) {
+    return ka < kb || (ka == kb && (ia & ~FINAL_BIT) < (ib & ~FINAL_BIT));
+}
+
+// ------------------------------------------------------------------ init
+// Root node (seq2seq.py:1389-1394) and the per-position rejection candidates
+// (np.any(source_scores) / np.nanargmax(source_scores), :1458-1462).
+__global__ void beam_init_kernel(BeamDev b) {
+    const int line = blockIdx.x;
+    const int Tl = b.row_T[line];
+    for (int t = threadIdx.x; t < b.T; t += blockDim.x) {
+        int best = -1; float bv = 0.f;
+        if (t < Tl) {
+            for (int a = 0; a < b.k_alt; ++a) {
+                const size_t o = ((size_t)line * b.T + t) * b.k_alt + a;
+                const int v = b.idx[o];
+                if (v < 0) continue;
+                const float x = b.val ? b.val[o] : 1.0f;
+                // the dense row holds zeros elsewhere, so only a positive entry can be the (nan)argmax;
+                // first index among equal maxima
+                if (!(x > 0.0f)) continue;
+                if (best < 0 || x > bv || (x == bv && v < best)) { best = v; bv = x; }
+            }
+        }
+        b.rej_table[(size_t)line * b.T + t] = best;
+    }
+    if (threadIdx.x == 0) {
+        b.status[line] = b.live[line] ? ST_ACTIVE : ST_EMPTY;
+        b.iter[line] = 0; b.x_count[line] = 0; b.x_base[line] = 0; b.beam_count[line] = 0; b.row_base[line] = 0;
+        b.fr_len[line] = 1; b.fr_off[line] = 0; b.fr_buf[line] = 0;
+        b.finals_count[line] = 0; b.best_final[line] = -1; b.open_left[line] = 0;
+        b.best_key[line] = INFINITY; b.hyp_steps[line] = 0;
+        b.fr_key[(size_t)line * b.cap] = 3.0 * fabs(1.0 - (double)Tl);
+        b.fr_id[(size_t)line * b.cap] = 0u;
+    }
+}
+
+// ------------------------------------------------------------------ pop (seq2seq.py:1398-1420)
+__global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
+    const int line = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ int s_wsum[8];
+    __shared__ int s_first_final, s_first_open;
+    if (b.status[line] != ST_ACTIVE) { if (tid == 0) b.beam_count[line] = 0; return; }
+    const int Tl = b.row_T[line];
+    const int len = b.fr_len[line];
+    if (b.iter[line] >= 2 * Tl) {                    // max_batches reached (:1397-1398)
+        if (tid == 0) { b.status[line] = ST_DONE; b.beam_count[line] = 0; b.open_left[line] = len; }
+        return;
+    }
+    const int cur = b.fr_buf[line];
+    const double* keys = b.fr_key + ((size_t)cur * b.L + line) * b.cap;
+    const uint32_t* ids = b.fr_id + ((size_t)cur * b.L + line) * b.cap;
+    if (tid == 0) { s_first_final = 0x7fffffff; s_first_open = 0x7fffffff; }
+    __syncthreads();
+    int open_total = 0, consumed = 0, nfin = 0;
+    for (int base = 0; base < len && open_total < b.batch; base += 256) {
+        const int i = base + tid;
+        const bool valid = i < len;
+        const uint32_t id = valid ? ids[i] : 0u;
+        const bool fin = valid && (id & FINAL_BIT);
+        const bool open = valid && !fin;
+        const unsigned bal = __ballot_sync(0xffffffffu, open);
+        if (lane == 0) s_wsum[warp] = __popc(bal);
+        __syncthreads();
+        int excl = open_total + __popc(bal & ((1u << lane) - 1u));
+        int blk = 0;
+        for (int w = 0; w < 8; ++w) { if (w < warp) excl += s_wsum[w]; blk += s_wsum[w]; }
+        // an entry is popped iff fewer than batch_size open nodes precede it (:1400-1415)
+        const bool take = valid && excl < b.batch;
+        if (take && open) {
+            b.beam_nodes[(size_t)line * b.batch + excl] = id;
+            if (excl == 0) s_first_open = i;
+        }
+        if (take && fin) atomicMin(&s_first_final, i);
+        consumed += __syncthreads_count(take);
+        nfin += __syncthreads_count(take && fin);
+        open_total += blk;
+    }
+    __syncthreads();
+    if (tid != 0) return;
+    const int count = min(open_total, b.batch);
+    int fc = b.finals_count[line] + nfin;
+    double bk = b.best_key[line];
+    if (nfin > 0) {
+        const double kf = keys[s_first_final];
+        if (kf < bk) { bk = kf; b.best_key[line] = kf; b.best_final[line] = (int32_t)(ids[s_first_final] & ~FINAL_BIT); }
+    }
+    b.finals_count[line] = fc;
+    b.fr_off[line] = consumed;
+    int out = count;
+    if (count == 0) {
+        b.status[line] = ST_DONE; b.open_left[line] = len - consumed;
+    } else if (fc > b.width_out && bk < keys[s_first_open]) {       // :1418-1420
+        b.status[line] = ST_DONE; b.open_left[line] = len - consumed; out = 0;
+    } else if (b.x_count[line] + count > b.quota_x) {
+        b.status[line] = ST_OVERFLOW; out = 0;
+    } else {
+        b.iter[line] += 1;
+        b.hyp_steps[line] += count;
+    }
+    b.beam_count[line] = out;
+}
+
+// ------------------------------------------------------------------ scan: row offsets, row total, active lines
+__global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b) {
+    __shared__ int s_wsum[32];
+    __shared__ int s_total, s_active;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { s_total = 0; s_active = 0; }
+    __syncthreads();
+    int running = 0;
+    for (int base = 0; base < b.L; base += 1024) {
+        const int line = base + tid;
+        int c = line < b.L ? b.beam_count[line] : 0;
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int off = 0, blk = 0;
+        for (int w = 0; w < 32; ++w) { if (w < warp) off += s_wsum[w]; blk += s_wsum[w]; }
+        const int rb = running + off + incl - c;
+        if (line < b.L) {
+            if (c > 0 && rb + c > b.Rcap) { b.status[line] = ST_OVERFLOW; b.beam_count[line] = 0; c = 0; }
+            b.row_base[line] = rb;
+            if (c > 0) atomicMax(&s_total, rb + c);
+            if (b.status[line] == ST_ACTIVE) atomicAdd(&s_active, 1);
+        }
+        running += blk;
+        __syncthreads();
+    }
+    if (tid == 0) { b.counters[0] = s_total; b.counters[1] = s_active; }
+}
+
+__global__ void __launch_bounds__(256) beam_rowmap_kernel(BeamDev b) {
+    const int line = blockIdx.x, tid = threadIdx.x;
+    const int c = b.beam_count[line];
+    if (c <= 0) return;
+    const int rb = b.row_base[line], xb = b.x_count[line];
+    if (tid < c) {
+        b.row_line[rb + tid] = line;
+        b.row_node[rb + tid] = b.beam_nodes[(size_t)line * b.batch + tid];
+        b.row_xid[rb + tid] = xb + tid;
+    }
+    __syncthreads();
+    if (tid == 0) { b.x_base[line] = xb; b.x_count[line] = xb + c; }
+}
+
+// ------------------------------------------------------------------ gather: decoder-step inputs of every row
+// (seq2seq.py:1423-1429: vstack of node.scores / node.state)
+__global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) {
+    const int R = b.counters[0];
+    for (int row = blockIdx.x; row < R; row += gridDim.x) {
+        const int line = b.row_line[row];
+        const uint32_t node = b.row_node[row];
+        float* p = b.p + (size_t)row * b.Vp;
+        float* p_lo = split ? b.p_lo + (size_t)row * b.Vp : nullptr;
+        float* a_in = b.a_in + (size_t)row * b.T;
+        if (node == 0u) {          // root: zero feedback, encoder final states, zero alignment
+            for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) { p[v] = 0.f; if (p_lo) p_lo[v] = 0.f; }
+            for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = 0.f;
+            for (int n = 0; n < b.d; ++n)
+                for (int u = threadIdx.x; u < b.W; u += blockDim.x) {
+                    const size_t o = (size_t)row * b.W + u;
+                    store_split(b.h_in[n], split ? b.h_in_lo[n] : nullptr, o, b.st_h[n][(size_t)line * b.W + u]);
+                    b.c_in[n][o] = b.st_c[n][(size_t)line * b.W + u];
+                }
+            continue;
+        }
+        const int k = (int)((node - 1u) % KMAX);
+        const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+        const float* rp = b.rec_p + g * b.Vp;
+        const int32_t* acc = b.ch_v + g * KMAX;
+        for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) {
+            float x = rp[v];
+            for (int q = 0; q < k; ++q) if (acc[q] == v) x = 0.f;     // better siblings were zeroed before the copy
+            store_split(p, p_lo, v, x);
+        }
+        const float* ra = b.rec_a + g * b.T;
+        for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = ra[j];
+        for (int n = 0; n < b.d; ++n) {
+            const float* rh = b.rec_h + (g * b.d + n) * b.W;
+            const float* rc = b.rec_c + (g * b.d + n) * b.W;
+            for (int u = threadIdx.x; u < b.W; u += blockDim.x) {
+                const size_t o = (size_t)row * b.W + u;
+                store_split(b.h_in[n], split ? b.h_in_lo[n] : nullptr, o, rh[u]);
+                b.c_in[n][o] = rc[u];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ expand: softmax, rejection, candidates
+// (seq2seq.py:1436-1529), one block per hypothesis row.
+struct ArgMax { float v; int i; };
+__device__ __forceinline__ ArgMax better(ArgMax a, ArgMax c) {
+    // descending walk of an ascending argsort: among equal scores the higher index comes first
+    return (c.v > a.v || (c.v == a.v && c.i > a.i)) ? c : a;
+}
+
+__global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) {
+    extern __shared__ float sm[];
+    float* sp = sm;                 // [Vp] working copy of the scores (taken entries -> -1)
+    float* slm = sm + b.Vp;         // [Vp] LM scores (lm only)
+    __shared__ float s_red[4];
+    __shared__ double s_dred[4];
+    __shared__ ArgMax s_arg[4];
+    __shared__ int s_cnt[4];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int R = b.counters[0];
+    for (int row = blockIdx.x; row < R; row += gridDim.x) {
+        const int line = b.row_line[row];
+        const uint32_t node = b.row_node[row];
+        const int Tl = b.row_T[line];
+        const size_t g = (size_t)line * b.quota_x + b.row_xid[row];
+        __syncthreads();
+        // ---- softmax of the logits row (and of the LM logits)
+        for (int pass = 0; pass < (b.lm ? 2 : 1); ++pass) {
+            const float* z = (pass ? b.logits_lm : b.logits) + (size_t)row * b.Vp;
+            float* dst = pass ? slm : sp;
+            float m = -INFINITY;
+            for (int v = tid; v < b.V; v += 128) m = fmaxf(m, z[v]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if (lane == 0) s_red[warp] = m;
+            __syncthreads();
+            m = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+            __syncthreads();
+            float s = 0.f;
+            for (int v = tid; v < b.V; v += 128) s += expf(z[v] - m);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0) s_red[warp] = s;
+            __syncthreads();
+            s = (s_red[0] + s_red[1]) + (s_red[2] + s_red[3]);
+            for (int v = tid; v < b.Vp; v += 128) dst[v] = v < b.V ? expf(z[v] - m) / s : 0.f;
+            __syncthreads();
+        }
+        // ---- alignment: expected source position in fp64, max == 1.0 test (:1443-1452)
+        const float* al = b.a_out + (size_t)row * b.T;
+        double cur = 0.0; float amax = 0.f;
+        for (int j = tid; j < Tl; j += 128) { const float a = al[j]; cur += (double)a * (double)j; amax = fmaxf(amax, a); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cur += __shfl_xor_sync(0xffffffffu, cur, o);
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        }
+        if (lane == 0) { s_dred[warp] = cur; s_red[warp] = amax; }
+        __syncthreads();
+        cur = (s_dred[0] + s_dred[1]) + (s_dred[2] + s_dred[3]);
+        amax = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+        __syncthreads();
+        // ---- the expanded node
+        int len_node = 1; double pcum = 0.0, prev = 0.0; bool onehot = false;
+        if (node != 0u) {
+            const int pk = (int)((node - 1u) % KMAX);
+            const size_t pg = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+            len_node = b.rec_len[pg] + 1;
+            pcum = b.ch_cum[pg * KMAX + pk];
+            const bool was_rej = b.ch_rej[pg * KMAX + pk] != 0;
+            onehot = was_rej || b.rec_amax1[pg] != 0;
+            prev = was_rej ? (double)b.rec_pos[pg] : b.rec_cur[pg];
+        }
+        int pos = 0; double mis = 0.0;
+        if (len_node > 1) {
+            mis = fabs(cur - prev - 1.0);
+            pos = onehot ? (int)prev + 1 : (int)rint(cur);
+        }
+        // ---- rejection candidate (:1454-1466); pos == T raises IndexError in the reference: no candidate here
+        int rej = -1;
+        if (b.rej_thr > 0.0 && (mis < 0.1 || onehot) && pos >= 0 && pos < b.T) {
+            const int r = b.rej_table[(size_t)line * b.T + pos];
+            if (r >= 0) rej = r;
+        }
+        if (rej >= 0 && tid == 0 && (double)sp[rej] < b.rej_thr) sp[rej] = (float)b.rej_thr;
+        __syncthreads();
+        // ---- record: scores after the overwrite, states, alignment
+        float* rp = b.rec_p + g * b.Vp;
+        for (int v = tid; v < b.Vp; v += 128) rp[v] = sp[v];
+        float* ra = b.rec_a + g * b.T;
+        for (int j = tid; j < b.T; j += 128) ra[j] = al[j];
+        for (int n = 0; n < b.d; ++n) {
+            float* rh = b.rec_h + (g * b.d + n) * b.W;
+            float* rc = b.rec_c + (g * b.d + n) * b.W;
+            for (int u = tid; u < b.W; u += 128) {
+                const size_t o = (size_t)row * b.W + u;
+                rh[u] = load_split(b.h_out[n], split ? b.h_out_lo[n] : nullptr, o);
+                rc[u] = b.c_out[n][o];
+            }
+        }
+        // ---- beam width from the relative threshold (:1470-1478)
+        float hi = 0.f;
+        for (int v = tid; v < b.V; v += 128) hi = fmaxf(hi, sp[v]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        if (lane == 0) s_red[warp] = hi;
+        __syncthreads();
+        hi = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+        const double bound = (double)hi * b.thr_in;
+        int cnt = 0;
+        for (int v = tid; v < b.V; v += 128) cnt += ((double)sp[v] >= bound);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) s_cnt[warp] = cnt;
+        __syncthreads();
+        const int beampos = min(s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3], b.width_in);
+        // ---- walk the candidates best first (:1480-1529)
+        int nacc = 0, pending = rej;
+        const float rej_p = rej >= 0 ? sp[rej] : 0.f;
+        for (int rank = 1; rank <= beampos + 1; ++rank) {
+            int v; float pv; bool isrej;
+            if (rank <= beampos) {
+                ArgMax best{-1.f, -1};
+                for (int q = tid; q < b.V; q += 128) best = better(best, ArgMax{sp[q], q});
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    ArgMax other{__shfl_xor_sync(0xffffffffu, best.v, o), __shfl_xor_sync(0xffffffffu, best.i, o)};
+                    best = better(best, other);
+                }
+                if (lane == 0) s_arg[warp] = best;
+                __syncthreads();
+                best = better(better(s_arg[0], s_arg[1]), better(s_arg[2], s_arg[3]));
+                __syncthreads();
+                if (best.i < 0 || best.v < 0.f) break;
+                v = best.i; pv = best.v;
+                if (tid == 0) sp[v] = -1.f;            // taken
+                __syncthreads();
+                isrej = (v == pending);
+                if (isrej) pending = -1;
+            } else {
+                // past the beam width only a still pending rejection candidate enters; `if rej_idx:` (:1498)
+                // treats index 0 as not pending
+                if (pending <= 0) break;
+                v = pending; pv = rej_p; isrej = true; pending = -1;
+            }
+            if (v == 0) continue;                       // '' (underspecification) is never a hypothesis (:1504-1507)
+            const float pc = b.lm ? slm[v] : pv;        // LM rates the beam, the decoder enters it (:1486-1489)
+            const float cost = (float)(-log((double)pc));
+            if (cost != cost) continue;
+            if (tid == 0) {
+                b.ch_v[g * KMAX + nacc] = v;
+                b.ch_p[g * KMAX + nacc] = pv;
+                b.ch_cum[g * KMAX + nacc] = pcum + (double)cost;
+                b.ch_rej[g * KMAX + nacc] = isrej ? 1 : 0;
+            }
+            ++nacc;
+        }
+        if (tid == 0) {
+            b.rec_cur[g] = cur; b.rec_amax1[g] = amax == 1.0f ? 1 : 0; b.rec_pos[g] = pos;
+            b.rec_len[g] = len_node; b.rec_nacc[g] = nacc; b.rec_parent[g] = node;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ push: insort of the new children (:1515-1532)
+__global__ void __launch_bounds__(256) beam_push_kernel(BeamDev b) {
+    extern __shared__ unsigned char smraw[];
+    double* skey = reinterpret_cast<double*>(smraw);                 // [npad]
+    uint32_t* sid = reinterpret_cast<uint32_t*>(skey + MAX_NEW);     // [npad]
+    __shared__ int s_wsum[8];
+    const int line = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c = b.beam_count[line];
+    if (c <= 0) return;
+    const int Tl = b.row_T[line];
+    const int xb = b.x_base[line];
+    // ---- collect: row j of this line holds record xb+j with rec_nacc children, in insertion order
+    const int nj = tid < c ? b.rec_nacc[(size_t)line * b.quota_x + xb + tid] : 0;
+    int incl = nj;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    int off = 0, n_new = 0;
+    for (int w = 0; w < 8; ++w) { if (w < warp) off += s_wsum[w]; n_new += s_wsum[w]; }
+    off += incl - nj;
+    if (tid < c) {
+        const size_t g = (size_t)line * b.quota_x + xb + tid;
+        const int len_child = b.rec_len[g] + 1;
+        const double pen = 3.0 * fabs((double)(len_child - Tl));      // cost0 * |length - length0| (:1588-1595)
+        for (int q = 0; q < nj; ++q) {
+            skey[off + q] = b.ch_cum[g * KMAX + q] + pen;
+            sid[off + q] = (1u + (uint32_t)(xb + tid) * KMAX + q) | (b.ch_v[g * KMAX + q] == b.eos ? FINAL_BIT : 0u);
+        }
+    }
+    int npad = 1;
+    while (npad < n_new) npad <<= 1;
+    __syncthreads();
+    for (int i = n_new + tid; i < npad; i += 256) { skey[i] = INFINITY; sid[i] = 0x7fffffffu; }
+    __syncthreads();
+    // ---- bitonic sort ascending by (key, id)
+    for (int k2 = 2; k2 <= npad; k2 <<= 1) {
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < npad; i += 256) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const bool up = (i & k2) == 0;
+                    const double ka = skey[i], kb = skey[ixj];
+                    const uint32_t ia = sid[i], ib = sid[ixj];
+                    const bool a_gt_b = key_less(kb, ib, ka, ia);
+                    if (a_gt_b == up) { skey[i] = kb; skey[ixj] = ka; sid[i] = ib; sid[ixj] = ia; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    // ---- rank-merge with what is left of the old fringe into the other buffer, best first, truncated
+    const int cur = b.fr_buf[line];
+    const int o_off = b.fr_off[line];
+    const int n_old = b.fr_len[line] - o_off;
+    const double* okey = b.fr_key + ((size_t)cur * b.L + line) * b.cap + o_off;
+    const uint32_t* oid = b.fr_id + ((size_t)cur * b.L + line) * b.cap + o_off;
+    double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
+    uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
+    for (int i = tid; i < n_old; i += 256) {
+        const double k = okey[i]; const uint32_t id = oid[i];
+        int lo = 0, hi = n_new;                   // new entries that precede this old one
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo = mid + 1; else hi = mid; }
+        const int pos = i + lo;
+        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+    }
+    for (int j = tid; j < n_new; j += 256) {
+        const double k = skey[j]; const uint32_t id = sid[j];
+        int lo = 0, hi = n_old;                   // old entries that precede this new one
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
+        const int pos = j + lo;
+        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        b.fr_len[line] = min(n_old + n_new, b.cap);
+        b.fr_off[line] = 0;
+        b.fr_buf[line] = cur ^ 1;
+    }
+}
+
+// ------------------------------------------------------------------ finish: best final hypothesis per line (:1538-1544)
+__global__ void __launch_bounds__(128) beam_finish_kernel(BeamDev b, int32_t* o_chars, float* o_probs, double* o_score,
+                                                          int32_t* o_len, float* o_align, long long* o_stats) {
+    const int line = blockIdx.x, tid = threadIdx.x;
+    const int S = 2 * b.T;
+    __shared__ int s_n;
+    const int st = b.status[line];
+    const int best = b.best_final[line];
+    if (tid == 0) {
+        int n = 0;
+        if (st != ST_OVERFLOW && st != ST_EMPTY && best > 0) {
+            // walk to the root, then reverse in place
+            uint32_t node = (uint32_t)best;
+            const size_t g0 = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+            const int length = b.rec_len[g0] + 1;
+            n = length - 1;
+            o_score[line] = b.ch_cum[g0 * KMAX + (node - 1u) % KMAX] / (double)(length - 1);
+            int i = n - 1;
+            while (node != 0u && i >= 0) {
+                const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+                const int k = (int)((node - 1u) % KMAX);
+                o_chars[(size_t)line * S + i] = b.ch_v[g * KMAX + k];
+                o_probs[(size_t)line * S + i] = b.ch_p[g * KMAX + k];
+                if (o_align) {      // temporarily keep the node id in the first cell of its alignment row
+                    reinterpret_cast<uint32_t*>(o_align)[((size_t)line * S + i) * b.T] = node;
+                }
+                node = b.rec_parent[g];
+                --i;
+            }
+        } else {
+            o_score[line] = 0.0;
+        }
+        o_len[line] = n;
+        s_n = n;
+        o_stats[(size_t)line * 4 + 0] = st == ST_OVERFLOW ? -1 : (st == ST_EMPTY ? -2 : b.iter[line]);
+        o_stats[(size_t)line * 4 + 1] = b.hyp_steps[line];
+        o_stats[(size_t)line * 4 + 2] = b.finals_count[line];
+        o_stats[(size_t)line * 4 + 3] = st == ST_ACTIVE ? b.fr_len[line] : b.open_left[line];
+    }
+    __syncthreads();
+    if (!o_align) return;
+    for (int i = 0; i < s_n; ++i) {
+        float* row = o_align + ((size_t)line * S + i) * b.T;
+        const uint32_t node = reinterpret_cast<uint32_t*>(row)[0];
+        __syncthreads();
+        const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+        const bool rej = b.ch_rej[g * KMAX + (node - 1u) % KMAX] != 0;
+        const int pos = b.rec_pos[g];
+        const float* ra = b.rec_a + g * b.T;
+        for (int j = tid; j < b.T; j += 128) row[j] = rej ? (j == pos ? 1.0f : 0.0f) : ra[j];   // np.eye(T)[pos] (:1494-1495)
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ workspace layout of one wave
+struct Carver {
+    char* base; size_t off;
+    template <typename T> T* take(size_t n) {
+        off = (off + 255) & ~size_t(255);
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += n * sizeof(T);
+        return p;
+    }
+};
+
+struct Plan { int L, quota_x, cap, Rcap, want_align; size_t bytes; };
+
+size_t row_bytes(const cor_model* m, int T) {
+    const size_t W = m->W, Vp = m->Vp, D = m->D, d = m->d;
+    const size_t sp = m->split ? 2 : 1;
+    size_t b = sp * Vp * 4 /*p*/ + sp * W * 4 /*x*/ + W * 4 /*wq*/ + sp * D * 4 /*ctx*/ + Vp * 4 /*logits*/ + 2 * (size_t)T * 4 /*a*/ +
+               d * (2 * sp * W * 4 /*h in,out*/ + 2 * W * 4 /*c in,out*/) + 12;
+    if (m->cfg.lm_predict) b += sp * W * 4 + W * 4 + Vp * 4;
+    return b + 64;
+}
+size_t rec_bytes(const cor_model* m, int T) {
+    return (size_t)m->Vp * 4 + 2 * (size_t)m->d * m->W * 4 + (size_t)T * 4 + 8 + 1 + 4 * 4 + KMAX * (4 + 4 + 8 + 1) + 16;
+}
+
+int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, int quota_x, int Rcap, int want_align,
+           void* base, Ws* ws, BeamDev* b, StepIO* io, size_t* bytes) {
+    if (carve(m, L, T, k, 0, base, ws)) return 1;
+    Carver c{(char*)base, ws->bytes};
+    const int W = m->W, d = m->d, D = m->D, Vp = m->Vp;
+    const bool sp = m->split;
+    const int cap = (int)std::min<long long>((long long)2 * T * bp->batch_size, (long long)quota_x * KMAX + 1);
+    *b = BeamDev{};
+    b->L = L; b->T = T; b->V = m->V; b->Vp = Vp; b->W = W; b->d = d; b->D = D; b->k_alt = k;
+    b->batch = bp->batch_size; b->width_in = bp->beam_width_in; b->width_out = bp->beam_width_out;
+    b->eos = m->cfg.eos_index; b->lm = m->cfg.lm_predict ? 1 : 0;
+    b->thr_in = bp->beam_threshold_in; b->rej_thr = bp->rejection_threshold;
+    b->quota_x = quota_x; b->cap = cap; b->Rcap = Rcap;
+    b->row_T = ws->row_T; b->live = ws->live; b->idx = ws->idx; b->val = ws->val;
+    for (int n = 0; n < d; ++n) { b->st_h[n] = ws->st_h[n]; b->st_c[n] = ws->st_c[n]; }
+    b->status = c.take<int32_t>(L); b->iter = c.take<int32_t>(L); b->x_count = c.take<int32_t>(L); b->x_base = c.take<int32_t>(L);
+    b->beam_count = c.take<int32_t>(L); b->row_base = c.take<int32_t>(L); b->fr_len = c.take<int32_t>(L);
+    b->fr_off = c.take<int32_t>(L); b->fr_buf = c.take<int32_t>(L); b->finals_count = c.take<int32_t>(L);
+    b->best_final = c.take<int32_t>(L); b->open_left = c.take<int32_t>(L);
+    b->best_key = c.take<double>(L); b->hyp_steps = c.take<long long>(L);
+    b->fr_key = c.take<double>((size_t)2 * L * cap); b->fr_id = c.take<uint32_t>((size_t)2 * L * cap);
+    b->beam_nodes = c.take<uint32_t>((size_t)L * bp->batch_size);
+    b->rej_table = c.take<int32_t>((size_t)L * T);
+    b->counters = c.take<int32_t>(4);
+    b->o_stats = c.take<long long>((size_t)L * 4);
+    b->o_align = want_align ? c.take<float>((size_t)L * 2 * T * T) : nullptr;
+    const size_t G = (size_t)L * quota_x;
+    b->rec_p = c.take<float>(G * Vp); b->rec_h = c.take<float>(G * d * W); b->rec_c = c.take<float>(G * d * W);
+    b->rec_a = c.take<float>(G * T);
+    b->rec_cur = c.take<double>(G); b->rec_amax1 = c.take<uint8_t>(G); b->rec_pos = c.take<int32_t>(G);
+    b->rec_len = c.take<int32_t>(G); b->rec_nacc = c.take<int32_t>(G); b->rec_parent = c.take<uint32_t>(G);
+    b->ch_v = c.take<int32_t>(G * KMAX); b->ch_p = c.take<float>(G * KMAX); b->ch_cum = c.take<double>(G * KMAX);
+    b->ch_rej = c.take<uint8_t>(G * KMAX);
+    const size_t R = Rcap;
+    b->row_line = c.take<int32_t>(R); b->row_xid = c.take<int32_t>(R); b->row_node = c.take<uint32_t>(R);
+    b->p = c.take<float>(R * Vp); b->p_lo = sp ? c.take<float>(R * Vp) : nullptr;
+    b->logits = c.take<float>(R * Vp);
+    b->a_in = c.take<float>(R * T); b->a_out = c.take<float>(R * T);
+    *io = StepIO{};
+    io->R = Rcap; io->r_dev = b->counters; io->row_line = b->row_line; io->first = false;
+    io->p = b->p; io->p_lo = b->p_lo;
+    io->x = c.take<float>(R * W); io->x_lo = sp ? c.take<float>(R * W) : nullptr;
+    io->wq = c.take<float>(R * W);
+    io->ctx = c.take<float>(R * D); io->ctx_lo = sp ? c.take<float>(R * D) : nullptr;
+    io->logits = b->logits;
+    io->a_in = b->a_in; io->a_out = b->a_out;
+    for (int n = 0; n < d; ++n) {
+        b->h_in[n] = c.take<float>(R * W); b->h_in_lo[n] = sp ? c.take<float>(R * W) : nullptr;
+        b->h_out[n] = c.take<float>(R * W); b->h_out_lo[n] = sp ? c.take<float>(R * W) : nullptr;
+        b->c_in[n] = c.take<float>(R * W); b->c_out[n] = c.take<float>(R * W);
+        io->h_in[n] = b->h_in[n]; io->h_in_lo[n] = b->h_in_lo[n]; io->h_out[n] = b->h_out[n]; io->h_out_lo[n] = b->h_out_lo[n];
+        io->c_in[n] = b->c_in[n]; io->c_out[n] = b->c_out[n];
+    }
+    if (m->cfg.lm_predict) {
+        io->h_lm = c.take<float>(R * W); io->h_lm_lo = sp ? c.take<float>(R * W) : nullptr;
+        io->c_lm = c.take<float>(R * W);
+        io->logits_lm = c.take<float>(R * Vp);
+        b->logits_lm = io->logits_lm;
+    }
+    *bytes = (c.off + 255) & ~size_t(255);
+    return 0;
+}
+
+// Largest wave (<= n_rows lines) whose layout fits `budget`: rows for at least one hypothesis per line,
+// a record arena of at least 2T+2 per line (one hypothesis per iteration), the rest split between them.
+int make_plan(const cor_model* m, int n_rows, int T, int k, const cor_beam_params* bp, int want_align, size_t budget, Plan* out) {
+    const long long q_full = (long long)2 * T * bp->batch_size;
+    for (int L = n_rows; L >= 1; L = L > 1 ? (L + 1) / 2 : 0) {
+        Ws ws; BeamDev b; StepIO io; size_t fixed = 0;
+        if (layout(m, L, T, k, bp, 1, 1, want_align, nullptr, &ws, &b, &io, &fixed)) return 1;
+        const size_t rb = row_bytes(m, T), xb = rec_bytes(m, T) + 2 * KMAX * 12;
+        const long long q_min = std::min<long long>(q_full, 2 * T + 2);
+        const size_t need = fixed + (size_t)L * rb + (size_t)L * q_min * xb;
+        if (need > budget) continue;
+        const size_t rest = budget - fixed;
+        long long Rcap = std::max<long long>(L, std::min<long long>((long long)L * bp->batch_size, (long long)(rest / 4 / rb)));
+        long long quota = std::min<long long>(q_full, (long long)((rest - (size_t)Rcap * rb) / ((size_t)L * xb)));
+        // shrink until the exact layout fits (alignment padding)
+        for (int tries = 0; tries < 64; ++tries) {
+            size_t bytes = 0;
+            if (layout(m, L, T, k, bp, (int)quota, (int)Rcap, want_align, nullptr, &ws, &b, &io, &bytes)) return 1;
+            if (bytes <= budget) { *out = Plan{L, (int)quota, b.cap, (int)Rcap, want_align, bytes}; return 0; }
+            if (quota > q_min) quota = std::max<long long>(q_min, quota - std::max<long long>(1, quota / 32));
+            else if (Rcap > L) Rcap = std::max<long long>(L, Rcap - std::max<long long>(1, Rcap / 32));
+            else break;
+        }
+    }
+    set_error("beam workspace too small for a single line");
+    return 1;
+}
+
+int check_params(const cor_model* m, const cor_beam_params* bp) {
+    COR_CHECK(m && m->finalized, "model not finalized");
+    COR_CHECK(bp, "null beam parameters");
+    COR_CHECK(bp->batch_size >= 1 && bp->batch_size <= 256, "batch_size must be in 1..256");
+    COR_CHECK(bp->beam_width_in >= 1 && bp->beam_width_in <= KMAX - 1, "beam_width_in must be in 1..15");
+    COR_CHECK(bp->beam_width_out >= 0, "beam_width_out must be non-negative");
+    COR_CHECK(m->d <= 8, "depth above 8 is not supported");
+    return 0;
+}
+
+// One wave over `L` lines given as HOST arrays; results to HOST arrays (same row order).
+int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const int32_t* h_idx, const float* h_val,
+             const cor_beam_params* bp, const Plan& plan, void* workspace,
+             int32_t* o_chars, float* o_probs, double* o_scores, int32_t* o_len, float* o_align, int64_t* o_stats,
+             cudaStream_t st) {
+    Ws ws; BeamDev b; StepIO io; size_t bytes = 0;
+    if (layout(m, L, T, k, bp, plan.quota_x, plan.Rcap, o_align != nullptr, workspace, &ws, &b, &io, &bytes)) return 1;
+    const size_t n = (size_t)L * T * k;
+    COR_CUDA(cudaMemcpyAsync(ws.row_T, h_row_T, (size_t)L * 4, cudaMemcpyHostToDevice, st));
+    COR_CUDA(cudaMemcpyAsync(ws.idx, h_idx, n * 4, cudaMemcpyHostToDevice, st));
+    if (h_val) COR_CUDA(cudaMemcpyAsync(ws.val, h_val, n * 4, cudaMemcpyHostToDevice, st));
+    else { ws.val = nullptr; b.val = nullptr; }
+    if (run_encoder(m, ws, st)) return 1;
+    beam_init_kernel<<<L, 128, 0, st>>>(b); ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    const int split = m->split ? 1 : 0;
+    const int row_grid = std::min(plan.Rcap, 148 * 8);
+    const size_t expand_smem = (size_t)(m->cfg.lm_predict ? 2 : 1) * m->Vp * 4;
+    const size_t push_smem = (size_t)MAX_NEW * 12;
+    int t_hi = 0;
+    for (int j = 0; j < L; ++j) t_hi = std::max(t_hi, h_row_T[j]);
+    for (int it = 0; it <= 2 * t_hi; ++it) {
+        beam_pop_kernel<<<L, 256, 0, st>>>(b);
+        beam_scan_kernel<<<1, 1024, 0, st>>>(b);
+        g_launches += 2;
+        if (it % 8 == 7 || it == 2 * t_hi) {          // host check: has every line finished?
+            int32_t cnt[2] = {0, 0};
+            COR_CUDA(cudaMemcpyAsync(cnt, b.counters, 8, cudaMemcpyDeviceToHost, st));
+            COR_CUDA(cudaStreamSynchronize(st));
+            if (cnt[1] == 0 && cnt[0] == 0) break;
+        }
+        beam_rowmap_kernel<<<L, 256, 0, st>>>(b);
+        beam_gather_kernel<<<row_grid, 128, 0, st>>>(b, split);
+        g_launches += 2;
+        COR_CUDA(cudaGetLastError());
+        if (decoder_core(m, ws, io, st)) return 1;
+        beam_expand_kernel<<<row_grid, 128, expand_smem, st>>>(b, split);
+        beam_push_kernel<<<L, 256, push_smem, st>>>(b);
+        g_launches += 2;
+        COR_CUDA(cudaGetLastError());
+    }
+    // results: staged in the encoder workspace's output slots and the wave's own staging buffers
+    const size_t S = 2 * (size_t)T;
+    int32_t* d_chars = ws.o_chars; float* d_probs = ws.o_probs; double* d_score = ws.o_score; int32_t* d_len = ws.o_len;
+    float* d_align = b.o_align;
+    COR_CUDA(cudaMemsetAsync(d_chars, 0, (size_t)L * S * 4, st));
+    COR_CUDA(cudaMemsetAsync(d_probs, 0, (size_t)L * S * 4, st));
+    beam_finish_kernel<<<L, 128, 0, st>>>(b, d_chars, d_probs, d_score, d_len, d_align, b.o_stats);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    COR_CUDA(cudaMemcpyAsync(o_chars, d_chars, (size_t)L * S * 4, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaMemcpyAsync(o_probs, d_probs, (size_t)L * S * 4, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaMemcpyAsync(o_scores, d_score, (size_t)L * 8, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaMemcpyAsync(o_len, d_len, (size_t)L * 4, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * 32, cudaMemcpyDeviceToHost, st));
+    if (o_align) COR_CUDA(cudaMemcpyAsync(o_align, d_align, (size_t)L * S * T * 4, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+}  // namespace
+
+}  // namespace cor
+
 using namespace cor;
+
 extern "C" {
-int cor_beam_workspace_bytes(const cor_model*, int, int, int, const cor_beam_params*, size_t, size_t*) {
-    set_error("beam search is not built yet");
-    return 1;
+
+int cor_beam_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt, const cor_beam_params* bp,
+                             size_t budget_bytes, size_t* bytes) {
+    COR_CHECK(bytes, "null argument");
+    if (check_params(m, bp)) return 1;
+    COR_CHECK(n_rows > 0 && t_max > 0 && k_alt > 0, "empty call geometry");
+    Plan plan;
+    if (make_plan(m, n_rows, t_max, k_alt, bp, 1, budget_bytes, &plan)) return 1;
+    // ask for the whole budget when the full-size arena does not fit, so that retries of heavy lines have room
+    const long long q_full = (long long)2 * t_max * bp->batch_size;
+    *bytes = (plan.L == n_rows && plan.quota_x >= q_full && plan.Rcap >= (long long)n_rows * bp->batch_size) ? plan.bytes : budget_bytes;
+    return 0;
 }
-int cor_correct_beam_host(cor_model*, const cor_lines*, const cor_beam_params*, void*, size_t,
-                          int32_t*, float*, double*, int32_t*, float*, int64_t*, void*) {
-    set_error("beam search is not built yet");
-    return 1;
+
+int cor_correct_beam_host(cor_model* m, const cor_lines* hl, const cor_beam_params* bp, void* workspace, size_t workspace_bytes,
+                          int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len, float* out_align,
+                          int64_t* stats, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (check_params(m, bp)) return 1;
+    COR_CHECK(hl && workspace && out_chars && out_probs && out_scores && out_len && stats, "null argument");
+    COR_CHECK(hl->n_rows > 0 && hl->t_max > 0 && hl->k_alt > 0, "empty call geometry");
+    COR_CUDA(cudaSetDevice(m->device));
+    COR_CUDA(cudaFuncSetAttribute(beam_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
+    const int B = hl->n_rows, T = hl->t_max, k = hl->k_alt;
+    const size_t S = 2 * (size_t)T, tk = (size_t)T * k;
+    std::vector<int> pending(B);
+    for (int j = 0; j < B; ++j) pending[j] = j;
+    int wave_cap = B;
+    for (int level = 0; !pending.empty(); ++level) {
+        COR_CHECK(level < 16, "beam search: retry depth exceeded");
+        Plan plan;
+        if (make_plan(m, std::min<int>(wave_cap, (int)pending.size()), T, k, bp, out_align != nullptr, workspace_bytes, &plan)) return 1;
+        std::vector<int> failed;
+        for (size_t p0 = 0; p0 < pending.size(); p0 += plan.L) {
+            const int L = (int)std::min<size_t>(plan.L, pending.size() - p0);
+            const bool direct = level == 0 && L == B;        // first wave over everything: use the caller's buffers
+            std::vector<int32_t> rT, ix, oc, ol; std::vector<float> vl, op, oa; std::vector<double> os; std::vector<int64_t> stt;
+            const int32_t *h_T = hl->row_T, *h_idx = hl->idx; const float* h_val = hl->val;
+            int32_t *w_chars = out_chars, *w_len = out_len; float *w_probs = out_probs, *w_align = out_align;
+            double* w_scores = out_scores; int64_t* w_stats = stats;
+            if (!direct) {
+                rT.resize(L); ix.resize((size_t)L * tk); if (hl->val) vl.resize((size_t)L * tk);
+                for (int j = 0; j < L; ++j) {
+                    const int src = pending[p0 + j];
+                    rT[j] = hl->row_T[src];
+                    std::copy(hl->idx + (size_t)src * tk, hl->idx + (size_t)(src + 1) * tk, ix.begin() + (size_t)j * tk);
+                    if (hl->val) std::copy(hl->val + (size_t)src * tk, hl->val + (size_t)(src + 1) * tk, vl.begin() + (size_t)j * tk);
+                }
+                oc.resize((size_t)L * S); op.resize((size_t)L * S); os.resize(L); ol.resize(L); stt.resize((size_t)L * 4);
+                if (out_align) oa.resize((size_t)L * S * T);
+                h_T = rT.data(); h_idx = ix.data(); h_val = hl->val ? vl.data() : nullptr;
+                w_chars = oc.data(); w_probs = op.data(); w_scores = os.data(); w_len = ol.data(); w_stats = stt.data();
+                w_align = out_align ? oa.data() : nullptr;
+            }
+            Plan wp = plan;
+            if (L != plan.L && make_plan(m, L, T, k, bp, out_align != nullptr, workspace_bytes, &wp)) return 1;
+            if (run_wave(m, L, T, k, h_T, h_idx, h_val, bp, wp, workspace, w_chars, w_probs, w_scores, w_len, w_align, w_stats, st)) return 1;
+            for (int j = 0; j < L; ++j) {
+                const int dst = pending[p0 + j];
+                if (w_stats[(size_t)j * 4] == -1) { failed.push_back(dst); continue; }
+                if (direct) continue;
+                std::copy(w_chars + (size_t)j * S, w_chars + (size_t)(j + 1) * S, out_chars + (size_t)dst * S);
+                std::copy(w_probs + (size_t)j * S, w_probs + (size_t)(j + 1) * S, out_probs + (size_t)dst * S);
+                out_scores[dst] = w_scores[j]; out_len[dst] = w_len[j];
+                std::copy(w_stats + (size_t)j * 4, w_stats + (size_t)(j + 1) * 4, stats + (size_t)dst * 4);
+                if (out_align) std::copy(w_align + (size_t)j * S * T, w_align + (size_t)(j + 1) * S * T, out_align + (size_t)dst * S * T);
+            }
+        }
+        if (!failed.empty()) {
+            COR_CHECK(plan.L > 1, "beam search: a single line overflows the whole workspace");
+            wave_cap = std::max(1, plan.L / 8);
+        }
+        pending.swap(failed);
+    }
+    return 0;
 }
-}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+"""GPU parity of the beam search (decode_sequence_beam, seq2seq.py:1356-1544) against the oracle's
+committed known answers and against the oracle run live, through the C ABI
+(cor_correct_beam_host).  Strings, search statistics (iterations, hypothesis-steps, finals, open
+nodes left) must be identical; probabilities within 1e-4 abs; scores within 1e-4.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import decoders as od
+from tests.common import make_model, synthetic_lines, topo_dict, BEAM_CASES, GOLDEN_DIR
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(topo, w, gemm_mode=0):
+    from cor_asv_ann_b200.engine import Engine
+    return Engine(topo_dict(topo), w, device=0, eos_index=1, gemm_mode=gemm_mode)
+
+
+def _run_beam(eng, mapping, lines, params, want_align=False, budget=2 << 30, conf=None):
+    from cor_asv_ann_b200.vectorize import lines_to_sparse
+    idx, val = lines_to_sparse(mapping[0], lines, conf)
+    B, T, _ = idx.shape
+    bp = eng.beam_params(**params)
+    chars, probs, scores, lens, align, stats = eng.correct_beam_host(
+        idx, val, np.full(B, T, np.int32), bp, want_align=want_align, budget_bytes=budget)
+    text = [''.join(mapping[1][int(v)] for v in chars[j, :lens[j]]) for j in range(B)]
+    return text, probs.numpy(), scores.numpy(), lens.numpy(), None if align is None else align.numpy(), stats.numpy()
+
+
+@pytest.mark.parametrize("gemm_mode", [1, 2])
+@pytest.mark.parametrize("case", sorted(BEAM_CASES))
+def test_beam_golden(case, gemm_mode):
+    name, n, length, seed, params = BEAM_CASES[case]
+    g = np.load(os.path.join(GOLDEN_DIR, "beam_%s.npz" % case), allow_pickle=True)
+    topo, w, mapping = make_model(name)
+    lines = list(g["lines"])
+    eng = _engine(topo, w, gemm_mode)
+    text, probs, scores, lens, _, stats = _run_beam(eng, mapping, lines, params)
+    want_text, want_score, want_stats, want_probs = list(g["text"]), g["score"], g["stats"], g["probs"]
+    for j, line in enumerate(lines):
+        got = text[j] if lens[j] > 0 else line           # StopIteration fallback (seq2seq.py:826-836)
+        assert got == want_text[j], "line %d: %r != %r (stats %s vs %s)" % (j, got, want_text[j], stats[j], want_stats[j])
+        assert (stats[j] == want_stats[j]).all(), "line %d stats %s != %s" % (j, stats[j], want_stats[j])
+        if lens[j] > 0:
+            assert abs(scores[j] - want_score[j]) < 1e-4
+            assert np.abs(probs[j, :lens[j]] - np.asarray(want_probs[j], np.float32)).max() < 1e-4
+
+
+def test_beam_alignments_and_overflow_retry():
+    """Live oracle comparison incl. alignments; a tiny workspace forces the overflow/retry path."""
+    name, n, length, seed, params = BEAM_CASES["c1_mix"]
+    topo, w, mapping = make_model(name)
+    lines = synthetic_lines(mapping, 5, 10, seed=91, min_length=4) + ['']
+    st = {}
+    r_text, r_probs, r_score, r_align = od.correct_lines(topo, w, mapping, lines, fast=False, greedy=False,
+                                                         beam_params=params, stats=st)
+    eng = _engine(topo, w, 1)
+    for budget in (2 << 30, 24 << 20):
+        text, probs, scores, lens, align, stats = _run_beam(eng, mapping, lines, params, want_align=True, budget=budget)
+        k = 0
+        for j, line in enumerate(lines):
+            if not line:
+                assert lens[j] == 0 and stats[j, 0] == -2
+                continue
+            s = st["lines"][k]
+            k += 1
+            assert list(stats[j]) == [s["iterations"], s["hypothesis_steps"], s["finals"], s["open_left"]]
+            got = text[j] if lens[j] > 0 else line
+            assert got == r_text[j]
+            if lens[j] > 0:
+                n_ = lens[j]
+                assert np.abs(probs[j, :n_] - np.asarray(r_probs[j], np.float32)).max() < 1e-4
+                assert abs(scores[j] - r_score[j]) < 1e-4
+                ref_al = np.stack([np.asarray(a, np.float32) for a in r_align[j]])
+                assert np.abs(align[j, :n_, :] - ref_al).max() < 1e-4
+
+
+def test_beam_confmat_input_rejection_candidates():
+    """Rejection candidates come from the argmax of the (soft) source row (seq2seq.py:1458-1462)."""
+    from tests.common import kant_fixture, kant_model
+    alphabet, pages = kant_fixture()
+    topo, w, mapping = kant_model(alphabet)
+    page = pages[0][:6]
+    conf = [[[(s, c) for s, c in chunk] for chunk in line] for line in page]
+    params = dict(rejection_threshold=0.1, batch_size=32, beam_width_in=4)
+    st = {}
+    r_text, r_probs, r_score, _ = od.correct_lines(topo, w, mapping, conf, conf=conf, fast=False, greedy=False,
+                                                   beam_params=params, stats=st)
+    eng = _engine(topo, w, 1)
+    text, probs, scores, lens, _, stats = _run_beam(eng, mapping, conf, params, conf=conf)
+    for j in range(len(page)):
+        s = st["lines"][j]
+        assert list(stats[j]) == [s["iterations"], s["hypothesis_steps"], s["finals"], s["open_left"]]
+        if lens[j] > 0:
+            assert text[j].replace('\a', '') == r_text[j]
+            assert abs(scores[j] - r_score[j]) < 1e-4
+
+
+def test_beam_c2_size_degenerate_bracket():
+    """Config 2 as configured (depth 2 / width 512 / V 512, beam_width_in 4, rejection 0.5): output == input,
+    score ln 2, T iterations of one hypothesis (SURVEY §8c known answer) — at a size the oracle need not run."""
+    topo, w, mapping = make_model("c2")
+    lines = synthetic_lines(mapping, 300, 80, seed=1002)
+    eng = _engine(topo, w, 0)
+    params = dict(batch_size=256, beam_width_in=4, beam_threshold_in=0.2, beam_width_out=16, rejection_threshold=0.5)
+    text, probs, scores, lens, _, stats = _run_beam(eng, mapping, lines, params, budget=6 << 30)
+    assert text == lines
+    assert np.allclose(scores, np.log(2.0), atol=1e-6)
+    assert (stats[:, 0] == 81).all() and (stats[:, 1] == 81).all() and (stats[:, 2] == 1).all()
