@@ -153,13 +153,136 @@ def run_reference(args):
     }))
 
 
-def workload_config(args, lines_per_step):
-    return {"workload": ("C3 fast batch-greedy decode" if args.workload == "greedy" else
+def workload_config(args, lines_per_step, workload=None):
+    workload = workload or args.workload
+    return {"workload": ("C3 fast batch-greedy decode" if workload == "greedy" else
                          "C2 beamed decode (beam_width_in 4, rejection 0.5)") +
                         ", depth 2 width 512 V 512, synthetic 80-char lines, T=81, random-init weights (variant U)",
             "lines_per_step_per_gpu": lines_per_step, "reference_batch": REF_BATCH,
             "l2": "inputs differ every step; per-step activations (GBs) exceed the 126 MB L2",
             "parallelism": "lines sharded by 256-line reference batch, no data-path collective"}
+
+
+def measure(args, eng, workload, rank, world, local, sample_clocks):
+    """Time `workload` on this rank: device-resident pass (CUDA events) and end-to-end host call."""
+    import torch
+    import torch.distributed as dist
+    L = (args.lines // REF_BATCH) * REF_BATCH
+    if workload == "beam":
+        L = (min(args.lines, args.beam_lines) // REF_BATCH) * REF_BATCH
+    T = LINE_LEN + 1
+    total_steps = args.steps + args.warmup
+    seed0 = 1003 if workload == "greedy" else 1002          # SURVEY.md 8d: config 3 / config 2
+    # distinct lines for every step and rank, resident in HBM before the timed region
+    dev_idx = [torch.as_tensor(make_indices(L, seed0 + 7919 * rank + 101 * s), device="cuda") for s in range(total_steps)]
+    row_T = torch.full((L,), T, dtype=torch.int32, device="cuda")
+    bp = eng.beam_params(**BEAM)
+    budget = int(args.beam_budget_gb * (1 << 30))
+    beam_out = None
+
+    def device_step(s):
+        nonlocal beam_out
+        if workload == "greedy":
+            eng.encode(dev_idx[s], None, row_T)
+            return eng.greedy()
+        beam_out = eng.beam_device(dev_idx[s], None, row_T, bp, budget_bytes=budget, out=beam_out)
+        return beam_out
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for s in range(args.warmup):
+        device_step(s)
+    barrier()
+    sampler = ClockSampler(local)
+    if sample_clocks:
+        sampler.start()
+    eng.launch_count(reset=True)
+    eng.prof_enable(True)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for s in range(args.warmup, total_steps):
+        out = device_step(s)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = eng.launch_count()
+    k_ms, k_n, k_flops = eng.prof_read()
+    eng.prof_enable(False)
+    clocks = sampler.stop() if sample_clocks else None
+    if workload == "greedy":
+        dec_steps = 2 * T * L                            # the fast decoder always runs 2T steps for every line
+        extra = {"decoded_chars_last_step": int(out[3].sum().item())}
+    else:
+        stats = out[5].cpu().numpy()
+        dec_steps = int(stats[:, 1].sum())               # hypothesis-steps actually run (last step)
+        lens = out[3].cpu().numpy()
+        same = int((out[0][:, :LINE_LEN + 1].cpu().numpy() == dev_idx[total_steps - 1][:, :, 0].cpu().numpy()).all(axis=1).sum())
+        extra = {"beam_iterations_per_line": float(stats[:, 0].mean()), "hypothesis_steps_per_line": dec_steps / L,
+                 "lines_without_final": int((lens == 0).sum()), "lines_equal_to_input": same}
+
+    # ---- end to end through the C-ABI host call: pinned host buffers, H2D and D2H inside
+    host_idx = [torch.as_tensor(make_indices(L, seed0 + 4001 + 7919 * rank + 101 * s)).pin_memory() for s in range(args.steps)]
+    host_T = torch.full((L,), T, dtype=torch.int32).pin_memory()
+    if workload == "greedy":
+        host_out = eng.host_outputs(L, T)
+        call = lambda s: eng.correct_greedy_host(host_idx[s], None, host_T, out=host_out)
+        api = "cor_correct_greedy_host (pinned host buffers)"
+    else:
+        host_out = None
+        def call(s):
+            nonlocal host_out
+            host_out = eng.correct_beam_host(host_idx[s], None, host_T, bp, budget_bytes=budget, out=host_out)
+        api = "cor_correct_beam_host (pinned host buffers)"
+    call(0)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        call(s)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    h2d = host_idx[0].numel() * 4 + host_T.numel() * 4
+    d2h = sum(t.numel() * t.element_size() for t in host_out if t is not None)
+
+    t_ms = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t_ms[0]), float(t_ms[1])
+    chars = LINE_LEN * L * args.steps * world
+    algo_flops_line = flops_enc(T) + dec_steps / L * flops_step()
+    del dev_idx, host_idx
+    torch.cuda.empty_cache()
+    return {"L": L, "ms": ms, "value": chars / (ms * 1e-3), "e2e_value": chars / (e2e_ms * 1e-3), "e2e_ms": e2e_ms,
+            "h2d": h2d, "d2h": d2h, "api": api, "launches": launches, "k_ms": k_ms, "k_n": k_n, "k_flops": k_flops,
+            "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra}
+
+
+def bench_line(args, r, workload, world, peaks):
+    peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1400 (of fallback)"
+    achieved = r["k_flops"] / (r["k_ms"] * 1e-3) / 1e12 if r["k_ms"] > 0 else 0.0
+    line = {
+        "metric": "corrected chars/sec (%s)" % workload, "value": r["value"], "unit": "chars/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, r["L"], workload),
+        "e2e": {"value": r["e2e_value"], "unit": "chars/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                "ms_per_step": r["e2e_ms"] / args.steps, "api": r["api"]},
+        "gpu_launches": r["launches"],
+        "clocks": r["clocks"],
+        "roofline": {"bound": "tensor", "kernel": "GEMM + fused LSTM-cell epilogue", "achieved": achieved,
+                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
+                     "peak_source": peak_src, "launches": r["k_n"], "kernel_ms_per_step": r["k_ms"] / args.steps,
+                     "kernel_share_of_step": r["k_ms"] / r["ms"] if r["ms"] else None,
+                     "precision": "fp32 via FFMA" if args.gemm_mode == 1 else "fp32-grade (see DESIGN.md)"},
+        "algorithmic_gflop_per_line": r["algo_flops_line"] / 1e9,
+        "whole_step_tflops": r["algo_flops_line"] * r["L"] * args.steps * world / (r["ms"] * 1e-3) / 1e12,
+    }
+    line.update(r["extra"])
+    return line
 
 
 def main():
@@ -168,11 +291,14 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "greedy"), choices=["greedy", "beam"])
+    ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "beam"), choices=["greedy", "beam"])
     ap.add_argument("--lines", type=int, default=int(os.environ.get("COR_BENCH_LINES", "16384")))
+    ap.add_argument("--beam-lines", type=int, default=8192)
+    ap.add_argument("--beam-budget-gb", type=float, default=72.0)
     ap.add_argument("--gemm-mode", type=int, default=0)
-    ap.add_argument("--cpu-lines", type=int, default=128)
+    ap.add_argument("--cpu-lines", type=int, default=None)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--only", action="store_true", help="measure only --workload (skip the other decoder)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -192,70 +318,9 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     topo, w, mapping = build_model()
     eng = Engine(topo_dict(topo), w, device=local, eos_index=1, gemm_mode=args.gemm_mode)
-    L = (args.lines // REF_BATCH) * REF_BATCH
-    T = LINE_LEN + 1
-    total_steps = args.steps + args.warmup
-    # distinct lines for every step and rank (seed 1003 = config 3), resident in HBM before the timed region
-    dev_idx = [torch.as_tensor(make_indices(L, 1003 + 7919 * rank + s), device="cuda") for s in range(total_steps)]
-    row_T = torch.full((L,), T, dtype=torch.int32, device="cuda")
-    bp = eng.beam_params(**BEAM)
-
-    def device_step(s):
-        if args.workload == "greedy":
-            eng.encode(dev_idx[s], None, row_T)
-            return eng.greedy()
-        raise SystemExit("beam device-resident step is measured through the host call only")
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- kernel-resident timing (inputs in HBM), CUDA events on the launching stream
-    for s in range(args.warmup):
-        device_step(s)
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    eng.launch_count(reset=True)
-    eng.prof_enable(True)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for s in range(args.warmup, total_steps):
-        out = device_step(s)
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = eng.launch_count()
-    k_ms, k_n, k_flops = eng.prof_read()
-    eng.prof_enable(False)
-    clocks = sampler.stop() if rank == 0 else None
-    lens = out[3]
-    steps_decoded = int(lens.sum().item())     # decoder steps actually consumed by live lines (last step)
-
-    # ---- end to end through the C-ABI host call: pinned host buffers, H2D and D2H inside
-    host_idx = [torch.as_tensor(make_indices(L, 5003 + 7919 * rank + s)).pin_memory() for s in range(args.steps)]
-    host_T = torch.full((L,), T, dtype=torch.int32).pin_memory()
-    host_out = eng.host_outputs(L, T)
-    eng.correct_greedy_host(host_idx[0], None, host_T, out=host_out)
-    barrier()
-    t0 = time.perf_counter()
-    for s in range(args.steps):
-        eng.correct_greedy_host(host_idx[s], None, host_T, out=host_out)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    h2d = host_idx[0].numel() * 4 + host_T.numel() * 4
-    d2h = sum(t.numel() * t.element_size() for t in host_out if t is not None)
-
-    t_ms = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = float(t_ms[0]), float(t_ms[1])
-    chars = LINE_LEN * L * args.steps * world
-    value = chars / (ms * 1e-3)
-    e2e_value = chars / (e2e_ms * 1e-3)
+    other = "greedy" if args.workload == "beam" else "beam"
+    main_r = measure(args, eng, args.workload, rank, world, local, sample_clocks=(rank == 0))
+    other_r = None if args.only else measure(args, eng, other, rank, world, local, sample_clocks=(rank == 0))
 
     if rank == 0:
         peaks = {}
@@ -263,34 +328,18 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
-        peak = peaks.get("bf16_tflops_sustained", 1400.0)
-        peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1400 (of fallback)"
-        achieved = k_flops / (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0
-        algo_flops_line = flops_enc(T) + 2 * T * flops_step()
-        line = {
-            "metric": "corrected chars/sec (%s)" % args.workload, "value": value, "unit": "chars/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": workload_config(args, L),
-            "e2e": {"value": e2e_value, "unit": "chars/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms / args.steps, "api": "cor_correct_greedy_host (pinned host buffers)"},
-            "gpu_launches": launches,
-            "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": "GEMM + fused LSTM-cell epilogue", "achieved": achieved,
-                         "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
-                         "peak_source": peak_src, "launches": k_n, "kernel_ms_per_step": k_ms / args.steps,
-                         "kernel_share_of_step": k_ms / ms if ms else None,
-                         "precision": "fp32 via FFMA" if args.gemm_mode == 1 else "fp32-grade (see DESIGN.md)"},
-            "algorithmic_gflop_per_line": algo_flops_line / 1e9,
-            "whole_step_tflops": algo_flops_line * L * args.steps * world / (ms * 1e-3) / 1e12,
-            "decoded_chars_last_step": steps_decoded,
-        }
+        line = bench_line(args, main_r, args.workload, world, peaks)
+        if other_r is not None:
+            o = bench_line(args, other_r, other, world, peaks)
+            line["also"] = {k: o[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "gpu_launches",
+                                               "clocks", "roofline", "algorithmic_gflop_per_line", "whole_step_tflops")}
         if world == 1 and not args.no_cpu:
             cores = host_threads()
-            v, dt = cpu_oracle_rate(args.workload, args.cpu_lines)
+            n_cpu = args.cpu_lines or (128 if args.workload == "greedy" else 48)
+            v, dt = cpu_oracle_rate(args.workload, n_cpu)
             line["cpu_baseline"] = {"value": v, "unit": "chars/s", "cores": cores, "kind": "port",
                                     "sample": "%d lines of the same workload, numpy oracle (Keras/TF unavailable), %.1f s"
-                                              % (args.cpu_lines, dt)}
+                                              % (n_cpu, dt)}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -19,9 +19,14 @@ struct Prof {
     bool on = false;
     std::vector<cudaEvent_t> ev;     // pairs
     size_t used = 0;
-    double flops = 0;
+    double flops = 0;                // launches whose row count is known on the host
     int64_t launches = 0;
+    // launches whose row count lives on the device (beam): the count is copied into pinned memory
+    // right behind the kernel, and the flops are added up in cor_prof_read
+    int32_t* rows = nullptr;         // pinned [kMaxDeferred]
+    std::vector<double> per_row;     // 2*N*K of the deferred launch
 } g_prof;
+constexpr size_t kMaxDeferred = 65536;
 
 static void prof_begin(cudaStream_t st) {
     if (!g_prof.on) return;
@@ -31,13 +36,18 @@ static void prof_begin(cudaStream_t st) {
     }
     cudaEventRecord(g_prof.ev[g_prof.used], st);
 }
-static void prof_end(cudaStream_t st, int M, int N, const GemmSeg* s, int n) {
+static void prof_end(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n) {
     if (!g_prof.on || g_prof.used + 2 > g_prof.ev.size()) return;
     cudaEventRecord(g_prof.ev[g_prof.used + 1], st);
     g_prof.used += 2;
     double k = 0;
     for (int i = 0; i < n; ++i) k += s[i].K;
-    g_prof.flops += 2.0 * M * N * k;
+    if (m_dev && g_prof.rows && g_prof.per_row.size() < kMaxDeferred) {
+        cudaMemcpyAsync(g_prof.rows + g_prof.per_row.size(), m_dev, 4, cudaMemcpyDeviceToHost, st);
+        g_prof.per_row.push_back(2.0 * N * k);
+    } else {
+        g_prof.flops += 2.0 * M * N * k;
+    }
     g_prof.launches += 1;
 }
 
@@ -52,7 +62,7 @@ static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int
     int rc;
     if (m->split && M >= m->tc_min_rows && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
     else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
-    prof_end(st, M, N, s, n);
+    prof_end(st, M, m_dev, N, s, n);
     return rc;
 }
 
@@ -444,7 +454,10 @@ int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B
 
 int cor_prof_enable(int on) {
     g_prof.on = on != 0;
-    if (on) { g_prof.used = 0; g_prof.flops = 0; g_prof.launches = 0; }
+    if (on) {
+        g_prof.used = 0; g_prof.flops = 0; g_prof.launches = 0; g_prof.per_row.clear();
+        if (!g_prof.rows) COR_CUDA(cudaMallocHost((void**)&g_prof.rows, kMaxDeferred * 4));
+    }
     return 0;
 }
 int cor_prof_read(double* total_ms, int64_t* launches, double* flops) {
@@ -455,9 +468,11 @@ int cor_prof_read(double* total_ms, int64_t* launches, double* flops) {
         COR_CUDA(cudaEventElapsedTime(&t, g_prof.ev[i], g_prof.ev[i + 1]));
         ms += t;
     }
+    double fl = g_prof.flops;
+    for (size_t i = 0; i < g_prof.per_row.size(); ++i) fl += g_prof.per_row[i] * (double)g_prof.rows[i];
     if (total_ms) *total_ms = ms;
     if (launches) *launches = g_prof.launches;
-    if (flops) *flops = g_prof.flops;
+    if (flops) *flops = fl;
     return 0;
 }
 

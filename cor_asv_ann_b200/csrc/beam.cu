@@ -26,6 +26,8 @@
 #include "epilogue.cuh"
 #include <math.h>
 #include <float.h>
+#include <string.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <vector>
 
@@ -685,13 +687,17 @@ int check_params(const cor_model* m, const cor_beam_params* bp) {
 int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const int32_t* h_idx, const float* h_val,
              const cor_beam_params* bp, const Plan& plan, void* workspace,
              int32_t* o_chars, float* o_probs, double* o_scores, int32_t* o_len, float* o_align, int64_t* o_stats,
-             cudaStream_t st) {
+             bool on_device, int64_t* host_stats, cudaStream_t st) {
+    // on_device: the line arrays and the result arrays are DEVICE memory; host_stats (always HOST, [L][4])
+    // additionally receives the statistics, which carry the per-line overflow flag the retry loop needs
+    const cudaMemcpyKind kin = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const cudaMemcpyKind kout = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
     Ws ws; BeamDev b; StepIO io; size_t bytes = 0;
     if (layout(m, L, T, k, bp, plan.quota_x, plan.Rcap, o_align != nullptr, workspace, &ws, &b, &io, &bytes)) return 1;
     const size_t n = (size_t)L * T * k;
-    COR_CUDA(cudaMemcpyAsync(ws.row_T, h_row_T, (size_t)L * 4, cudaMemcpyHostToDevice, st));
-    COR_CUDA(cudaMemcpyAsync(ws.idx, h_idx, n * 4, cudaMemcpyHostToDevice, st));
-    if (h_val) COR_CUDA(cudaMemcpyAsync(ws.val, h_val, n * 4, cudaMemcpyHostToDevice, st));
+    COR_CUDA(cudaMemcpyAsync(ws.row_T, h_row_T, (size_t)L * 4, kin, st));
+    COR_CUDA(cudaMemcpyAsync(ws.idx, h_idx, n * 4, kin, st));
+    if (h_val) COR_CUDA(cudaMemcpyAsync(ws.val, h_val, n * 4, kin, st));
     else { ws.val = nullptr; b.val = nullptr; }
     if (run_encoder(m, ws, st)) return 1;
     beam_init_kernel<<<L, 128, 0, st>>>(b); ++g_launches;
@@ -700,8 +706,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const int row_grid = std::min(plan.Rcap, 148 * 8);
     const size_t expand_smem = (size_t)(m->cfg.lm_predict ? 2 : 1) * m->Vp * 4;
     const size_t push_smem = (size_t)MAX_NEW * 12;
-    int t_hi = 0;
-    for (int j = 0; j < L; ++j) t_hi = std::max(t_hi, h_row_T[j]);
+    const int t_hi = T;      // every row_T is <= t_max
     for (int it = 0; it <= 2 * t_hi; ++it) {
         beam_pop_kernel<<<L, 256, 0, st>>>(b);
         beam_scan_kernel<<<1, 1024, 0, st>>>(b);
@@ -731,12 +736,13 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     beam_finish_kernel<<<L, 128, 0, st>>>(b, d_chars, d_probs, d_score, d_len, d_align, b.o_stats);
     ++g_launches;
     COR_CUDA(cudaGetLastError());
-    COR_CUDA(cudaMemcpyAsync(o_chars, d_chars, (size_t)L * S * 4, cudaMemcpyDeviceToHost, st));
-    COR_CUDA(cudaMemcpyAsync(o_probs, d_probs, (size_t)L * S * 4, cudaMemcpyDeviceToHost, st));
-    COR_CUDA(cudaMemcpyAsync(o_scores, d_score, (size_t)L * 8, cudaMemcpyDeviceToHost, st));
-    COR_CUDA(cudaMemcpyAsync(o_len, d_len, (size_t)L * 4, cudaMemcpyDeviceToHost, st));
-    COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * 32, cudaMemcpyDeviceToHost, st));
-    if (o_align) COR_CUDA(cudaMemcpyAsync(o_align, d_align, (size_t)L * S * T * 4, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaMemcpyAsync(o_chars, d_chars, (size_t)L * S * 4, kout, st));
+    COR_CUDA(cudaMemcpyAsync(o_probs, d_probs, (size_t)L * S * 4, kout, st));
+    COR_CUDA(cudaMemcpyAsync(o_scores, d_score, (size_t)L * 8, kout, st));
+    COR_CUDA(cudaMemcpyAsync(o_len, d_len, (size_t)L * 4, kout, st));
+    COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * 32, kout, st));
+    COR_CUDA(cudaMemcpyAsync(host_stats, b.o_stats, (size_t)L * 32, cudaMemcpyDeviceToHost, st));
+    if (o_align) COR_CUDA(cudaMemcpyAsync(o_align, d_align, (size_t)L * S * T * 4, kout, st));
     COR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
@@ -762,10 +768,24 @@ int cor_beam_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_al
     return 0;
 }
 
-int cor_correct_beam_host(cor_model* m, const cor_lines* hl, const cor_beam_params* bp, void* workspace, size_t workspace_bytes,
-                          int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len, float* out_align,
-                          int64_t* stats, void* stream) {
-    cudaStream_t st = (cudaStream_t)stream;
+// Staging memory of the retry waves: host (malloc) or device (cudaMalloc), freed on scope exit.
+struct Stage {
+    bool dev; std::vector<void*> ptrs;
+    explicit Stage(bool d) : dev(d) {}
+    ~Stage() { for (void* p : ptrs) { if (dev) cudaFree(p); else free(p); } }
+    void* take(size_t bytes) {
+        void* p = nullptr;
+        if (!bytes) bytes = 8;
+        if (dev) { if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr; }
+        else p = malloc(bytes);
+        if (p) ptrs.push_back(p);
+        return p;
+    }
+};
+
+static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const cor_beam_params* bp, void* workspace,
+                        size_t workspace_bytes, int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len,
+                        float* out_align, int64_t* stats, cudaStream_t st) {
     if (check_params(m, bp)) return 1;
     COR_CHECK(hl && workspace && out_chars && out_probs && out_scores && out_len && stats, "null argument");
     COR_CHECK(hl->n_rows > 0 && hl->t_max > 0 && hl->k_alt > 0, "empty call geometry");
@@ -773,8 +793,14 @@ int cor_correct_beam_host(cor_model* m, const cor_lines* hl, const cor_beam_para
     COR_CUDA(cudaFuncSetAttribute(beam_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
     const int B = hl->n_rows, T = hl->t_max, k = hl->k_alt;
     const size_t S = 2 * (size_t)T, tk = (size_t)T * k;
+    auto xcopy = [&](void* dst, const void* src, size_t bytes) -> int {
+        if (!on_device) { memcpy(dst, src, bytes); return 0; }
+        COR_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st));
+        return 0;
+    };
     std::vector<int> pending(B);
     for (int j = 0; j < B; ++j) pending[j] = j;
+    std::vector<int64_t> hstats;
     int wave_cap = B;
     for (int level = 0; !pending.empty(); ++level) {
         COR_CHECK(level < 16, "beam search: retry depth exceeded");
@@ -784,37 +810,43 @@ int cor_correct_beam_host(cor_model* m, const cor_lines* hl, const cor_beam_para
         for (size_t p0 = 0; p0 < pending.size(); p0 += plan.L) {
             const int L = (int)std::min<size_t>(plan.L, pending.size() - p0);
             const bool direct = level == 0 && L == B;        // first wave over everything: use the caller's buffers
-            std::vector<int32_t> rT, ix, oc, ol; std::vector<float> vl, op, oa; std::vector<double> os; std::vector<int64_t> stt;
-            const int32_t *h_T = hl->row_T, *h_idx = hl->idx; const float* h_val = hl->val;
+            Stage stage(on_device);
+            const int32_t *w_T = hl->row_T, *w_idx = hl->idx; const float* w_val = hl->val;
             int32_t *w_chars = out_chars, *w_len = out_len; float *w_probs = out_probs, *w_align = out_align;
             double* w_scores = out_scores; int64_t* w_stats = stats;
             if (!direct) {
-                rT.resize(L); ix.resize((size_t)L * tk); if (hl->val) vl.resize((size_t)L * tk);
+                int32_t* rT = (int32_t*)stage.take((size_t)L * 4);
+                int32_t* ix = (int32_t*)stage.take((size_t)L * tk * 4);
+                float* vl = hl->val ? (float*)stage.take((size_t)L * tk * 4) : nullptr;
+                w_chars = (int32_t*)stage.take((size_t)L * S * 4); w_probs = (float*)stage.take((size_t)L * S * 4);
+                w_scores = (double*)stage.take((size_t)L * 8); w_len = (int32_t*)stage.take((size_t)L * 4);
+                w_stats = (int64_t*)stage.take((size_t)L * 32);
+                w_align = out_align ? (float*)stage.take((size_t)L * S * T * 4) : nullptr;
+                COR_CHECK(rT && ix && (vl || !hl->val) && w_chars && w_probs && w_scores && w_len && w_stats && (w_align || !out_align),
+                          "out of memory for beam retry staging");
                 for (int j = 0; j < L; ++j) {
                     const int src = pending[p0 + j];
-                    rT[j] = hl->row_T[src];
-                    std::copy(hl->idx + (size_t)src * tk, hl->idx + (size_t)(src + 1) * tk, ix.begin() + (size_t)j * tk);
-                    if (hl->val) std::copy(hl->val + (size_t)src * tk, hl->val + (size_t)(src + 1) * tk, vl.begin() + (size_t)j * tk);
+                    if (xcopy(rT + j, hl->row_T + src, 4) || xcopy(ix + (size_t)j * tk, hl->idx + (size_t)src * tk, tk * 4)) return 1;
+                    if (hl->val && xcopy(vl + (size_t)j * tk, hl->val + (size_t)src * tk, tk * 4)) return 1;
                 }
-                oc.resize((size_t)L * S); op.resize((size_t)L * S); os.resize(L); ol.resize(L); stt.resize((size_t)L * 4);
-                if (out_align) oa.resize((size_t)L * S * T);
-                h_T = rT.data(); h_idx = ix.data(); h_val = hl->val ? vl.data() : nullptr;
-                w_chars = oc.data(); w_probs = op.data(); w_scores = os.data(); w_len = ol.data(); w_stats = stt.data();
-                w_align = out_align ? oa.data() : nullptr;
+                w_T = rT; w_idx = ix; w_val = vl;
             }
             Plan wp = plan;
             if (L != plan.L && make_plan(m, L, T, k, bp, out_align != nullptr, workspace_bytes, &wp)) return 1;
-            if (run_wave(m, L, T, k, h_T, h_idx, h_val, bp, wp, workspace, w_chars, w_probs, w_scores, w_len, w_align, w_stats, st)) return 1;
+            hstats.assign((size_t)L * 4, 0);
+            if (run_wave(m, L, T, k, w_T, w_idx, w_val, bp, wp, workspace, w_chars, w_probs, w_scores, w_len, w_align, w_stats,
+                         on_device, hstats.data(), st)) return 1;
             for (int j = 0; j < L; ++j) {
                 const int dst = pending[p0 + j];
-                if (w_stats[(size_t)j * 4] == -1) { failed.push_back(dst); continue; }
+                if (hstats[(size_t)j * 4] == -1) { failed.push_back(dst); continue; }
                 if (direct) continue;
-                std::copy(w_chars + (size_t)j * S, w_chars + (size_t)(j + 1) * S, out_chars + (size_t)dst * S);
-                std::copy(w_probs + (size_t)j * S, w_probs + (size_t)(j + 1) * S, out_probs + (size_t)dst * S);
-                out_scores[dst] = w_scores[j]; out_len[dst] = w_len[j];
-                std::copy(w_stats + (size_t)j * 4, w_stats + (size_t)(j + 1) * 4, stats + (size_t)dst * 4);
-                if (out_align) std::copy(w_align + (size_t)j * S * T, w_align + (size_t)(j + 1) * S * T, out_align + (size_t)dst * S * T);
+                if (xcopy(out_chars + (size_t)dst * S, w_chars + (size_t)j * S, S * 4) ||
+                    xcopy(out_probs + (size_t)dst * S, w_probs + (size_t)j * S, S * 4) ||
+                    xcopy(out_scores + dst, w_scores + j, 8) || xcopy(out_len + dst, w_len + j, 4) ||
+                    xcopy(stats + (size_t)dst * 4, w_stats + (size_t)j * 4, 32)) return 1;
+                if (out_align && xcopy(out_align + (size_t)dst * S * T, w_align + (size_t)j * S * T, S * T * 4)) return 1;
             }
+            if (on_device) COR_CUDA(cudaStreamSynchronize(st));      // staging is freed at the end of this scope
         }
         if (!failed.empty()) {
             COR_CHECK(plan.L > 1, "beam search: a single line overflows the whole workspace");
@@ -823,6 +855,20 @@ int cor_correct_beam_host(cor_model* m, const cor_lines* hl, const cor_beam_para
         pending.swap(failed);
     }
     return 0;
+}
+
+int cor_correct_beam_host(cor_model* m, const cor_lines* hl, const cor_beam_params* bp, void* workspace, size_t workspace_bytes,
+                          int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len, float* out_align,
+                          int64_t* stats, void* stream) {
+    return beam_correct(m, hl, false, bp, workspace, workspace_bytes, out_chars, out_probs, out_scores, out_len, out_align,
+                        stats, (cudaStream_t)stream);
+}
+
+int cor_decode_beam_batch(cor_model* m, const cor_lines* dl, const cor_beam_params* bp, void* workspace, size_t workspace_bytes,
+                          int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len, float* out_align,
+                          int64_t* stats, void* stream) {
+    return beam_correct(m, dl, true, bp, workspace, workspace_bytes, out_chars, out_probs, out_scores, out_len, out_align,
+                        stats, (cudaStream_t)stream);
 }
 
 }  // extern "C"

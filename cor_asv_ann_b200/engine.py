@@ -181,6 +181,29 @@ class Engine:
                                                  _ptr(stats), self._stream()))
         return out
 
+    def beam_workspace(self, B, T, k, bp, budget_bytes):
+        n = C.c_size_t()
+        check(self.lib.cor_beam_workspace_bytes(self.handle, B, T, k, C.byref(bp), int(budget_bytes), C.byref(n)))
+        return self._workspace(n.value)
+
+    def beam_device(self, idx, val, row_T, bp, budget_bytes=32 << 30, out=None):
+        """Beam search with the lines already on the device; results stay on the device.
+        Returns (chars [B,2T], probs, scores, lens, None, stats [B,4]) as device tensors."""
+        B, T, k = idx.shape
+        ws = self.beam_workspace(B, T, k, bp, budget_bytes)
+        dev = self.device
+        if out is None:
+            out = (torch.empty((B, 2 * T), dtype=torch.int32, device=dev), torch.empty((B, 2 * T), dtype=torch.float32, device=dev),
+                   torch.empty((B,), dtype=torch.float64, device=dev), torch.empty((B,), dtype=torch.int32, device=dev), None,
+                   torch.empty((B, 4), dtype=torch.int64, device=dev))
+        chars, probs, scores, lens, align, stats = out
+        lines = CorLines(B, T, k, _ptr(row_T), _ptr(idx), _ptr(val))
+        with torch.cuda.device(dev):
+            check(self.lib.cor_decode_beam_batch(self.handle, C.byref(lines), C.byref(bp), _ptr(ws), ws.numel(),
+                                                 _ptr(chars), _ptr(probs), _ptr(scores), _ptr(lens), _ptr(align),
+                                                 _ptr(stats), self._stream()))
+        return out
+
     def prof_enable(self, on=True):
         check(self.lib.cor_prof_enable(int(on)))
 

@@ -1,0 +1,626 @@
+"""Drop-in for ``ocrd_cor_asv_ann.lib.seq2seq.Sequence2Sequence`` on the B200 engine.
+
+Mirrors the reference class (/root/reference/ocrd_cor_asv_ann/lib/seq2seq.py:108-179 attributes,
+:190 configure, :782 correct_lines, :1020 vectorize_lines, :1121-1174 save/load_config/load_weights,
+:1215 decode_batch_greedy, :1288 decode_sequence_greedy, :1356 decode_sequence_beam) for the
+inference path: same attribute names, method signatures, return types and error behaviour, so that
+``cor-asv-ann-proc`` / ``-eval`` and ``ocrd-cor-asv-ann-process`` can import this class instead.
+All arithmetic runs in libcor_b200.so (CUDA, sm_100a) through ``engine.Engine``; there is no CPU
+fallback — decoding without a CUDA device raises.  Training (``train``) is out of scope
+(DESIGN.md), ``evaluate`` needs the reference's own ``alignment`` module.
+"""
+import logging
+import pickle
+import unicodedata
+
+import numpy as np
+
+from . import h5lite
+from .vectorize import lines_to_sparse, dense_to_sparse
+
+GAP = '\a'  # reserved for gap in input (seq2seq.py:29)
+
+
+class _Layer:
+    """What ``scripts/train.py:88`` and weight I/O touch of a Keras layer."""
+
+    def __init__(self, owner, name):
+        self._owner, self.name = owner, name
+
+    def get_weights(self):
+        return [np.array(a) for a in self._owner._weights[self.name]]
+
+    def set_weights(self, weights):
+        self._owner._weights[self.name] = [np.asarray(a, np.float32) for a in weights]
+        self._owner._engine = None
+
+
+class _Model:
+    """Stand-in for the Keras ``Model`` objects callers hold on to (``.layers``, ``.name``)."""
+
+    def __init__(self, owner, name, layer_names, predict=None):
+        self.name = name
+        self.layers = [_Layer(owner, n) for n in layer_names]
+        self._predict = predict
+
+    def get_layer(self, name):
+        for layer in self.layers:
+            if layer.name == name:
+                return layer
+        raise ValueError('No such layer: ' + name)
+
+    def predict_on_batch(self, x):
+        if self._predict is None:
+            raise NotImplementedError('%s.predict_on_batch: use the Sequence2Sequence decoders' % self.name)
+        return self._predict(x)
+
+
+class Node:
+    """Result view of one beam hypothesis (the trie itself lives on the GPU, csrc/beam.cu)."""
+
+    def __init__(self, value, prob, cum_cost, length, alignment):
+        self.value, self.prob, self.cum_cost, self.length, self.alignment = value, prob, cum_cost, length, alignment
+
+
+class Sequence2Sequence(object):
+    '''Sequence to sequence (character-level) error correction, B200 engine behind the reference API.'''
+
+    def __init__(self, logger=None, progbars=True):
+        ### model parameters (seq2seq.py:108-132)
+        self.batch_size = 256
+        self.stateful = False
+        self.width = 512
+        self.depth = 2
+        self.mapping = ({'': 0}, {0: ''})
+        self.voc_size = 1
+        self.residual_connections = False
+        self.deep_bidirectional_encoder = False
+        self.bridge_dense = False
+        ### training parameters (:134-158) — kept for callers that set them
+        self.epochs = 100
+        self.lm_loss = False
+        self.lm_predict = False
+        self.scheduled_sampling = None
+        self.dropout = 0.2
+        ### beam decoder inference parameters (:160-169)
+        self.rejection_threshold = 0.3
+        self.beam_width_in = 15
+        self.beam_threshold_in = 0.2
+        self.beam_width_out = 16
+        ### runtime variables (:171-179)
+        self.logger = logger or logging.getLogger(__name__)
+        self.graph = None
+        self.encoder_decoder_model = None
+        self.encoder_model = None
+        self.decoder_model = None
+        self.aligner = None
+        self.progbars = progbars
+        self.status = 0  # empty / configured / trained?
+        ### engine
+        self.device = 0
+        self.gemm_mode = 0
+        self.beam_budget_bytes = 8 << 30
+        self._weights = {}
+        self._engine = None
+
+    def __repr__(self):
+        return (__name__ +
+                " (width: %d)" % self.width +
+                " (depth: %d)" % self.depth +
+                " (chars: %d)" % self.voc_size +
+                " (attention)" +
+                (" (stateful)" if self.stateful else " (stateless)") +
+                " status: %s" % ("empty" if self.status < 1 else "configured" if self.status < 2 else "trained"))
+
+    # ------------------------------------------------------------------ topology
+    @property
+    def _enc_dim(self):
+        return 2 * self.width if (self.depth == 1 or self.deep_bidirectional_encoder) else self.width
+
+    def _layer_shapes(self):
+        """Keras layer name -> list of weight shapes, in Keras weight order."""
+        W, d, V, D = int(self.width), int(self.depth), int(self.voc_size), int(self._enc_dim)
+        shapes = {'char_input_projection': [(V, W)]}
+        for n in range(d):
+            bidi = n == 0 or self.deep_bidirectional_encoder
+            in_dim = W if n == 0 else (2 * W if (self.deep_bidirectional_encoder or n == 1) else W)
+            one = [(in_dim, 4 * W), (W, 4 * W), (4 * W,)]
+            shapes['encoder_lstm_%d' % (n + 1)] = one + one if bidi else one
+            if self.bridge_dense:
+                shapes['bridge_h_%d' % (n + 1)] = [(W, W), (W,)]
+                shapes['bridge_c_%d' % (n + 1)] = [(W, W), (W,)]
+        shapes['attention_dense'] = [(D, W)]
+        for n in range(d - 1):
+            shapes['decoder_lstm_%d' % (n + 1)] = [(W, 4 * W), (W, 4 * W), (4 * W,)]
+        shapes['decoder_lstm_%d' % d] = [(W, W), (W, 1), (W,), (1,), (W + D, 4 * W), (W, 4 * W), (4 * W,)]
+        return shapes
+
+    def _init_weights(self, rng):
+        """Keras default initialisers (seq2seq.py:240: embedding N(0, 0.001); glorot-uniform kernels;
+        orthogonal recurrent kernels; zero biases with unit forget gate)."""
+        W = int(self.width)
+
+        def glorot(shape):
+            lim = np.sqrt(6.0 / (shape[0] + shape[1]))
+            return rng.uniform(-lim, lim, size=shape).astype(np.float32)
+
+        def lstm(in_dim):
+            q, _ = np.linalg.qr(rng.standard_normal((4 * W, W)))
+            bias = np.zeros(4 * W, np.float32)
+            bias[W:2 * W] = 1.0
+            return [glorot((in_dim, 4 * W)), q.T.astype(np.float32), bias]
+
+        out = {}
+        for layer, shapes in self._layer_shapes().items():
+            if layer == 'char_input_projection':
+                out[layer] = [(rng.standard_normal(shapes[0]) * 0.001).astype(np.float32)]
+            elif layer == 'decoder_lstm_%d' % self.depth:
+                out[layer] = [glorot(shapes[0]), glorot(shapes[1]), np.zeros(shapes[2], np.float32),
+                              np.zeros(shapes[3], np.float32)] + lstm(shapes[4][0])
+            elif 'lstm' in layer:
+                out[layer] = sum((lstm(shapes[i][0]) for i in range(0, len(shapes), 3)), [])
+            elif len(shapes) == 2:      # bridge: Dense kernel + bias
+                out[layer] = [glorot(shapes[0]), np.zeros(shapes[1], np.float32)]
+            else:
+                out[layer] = [glorot(shapes[0])]
+        return out
+
+    def configure(self, batch_size=None):
+        '''Define encoder and decoder models for the configured parameters (seq2seq.py:190-489).
+
+        The Keras graphs become a weight store plus the CUDA engine; weights start from the
+        reference's initialisers and are normally replaced by ``load_weights``.'''
+        if batch_size:
+            self.batch_size = batch_size
+        self.logger.info('using B200 CUDA engine to compile %s model of depth %d width %d size %d with attention',
+                         'stateful' if self.stateful else 'stateless', self.depth, self.width, self.voc_size)
+        self._weights = self._init_weights(np.random.default_rng())
+        self._engine = None
+        names = list(self._layer_shapes())
+        enc = [n for n in names if n.startswith(('char_input', 'encoder_lstm', 'bridge'))]
+        self.encoder_decoder_model = _Model(self, 'encoder_decoder_model', names)
+        self.encoder_model = _Model(self, 'encoder_model', enc, predict=self._predict_encoder)
+        self.decoder_model = _Model(self, 'decoder_model', [n for n in names if n not in enc or n.startswith('char_input')])
+        self.graph = object()
+        self.status = 1
+
+    def _resync_decoder(self):
+        """The reference copies the attention layer into a second instance (:526-528); one weight store
+        makes this a no-op."""
+
+    # ------------------------------------------------------------------ engine
+    def _get_engine(self):
+        if self._engine is None:
+            from .engine import Engine
+            topo = dict(width=int(self.width), depth=int(self.depth), voc_size=int(self.voc_size),
+                        residual_connections=bool(self.residual_connections),
+                        deep_bidirectional_encoder=bool(self.deep_bidirectional_encoder),
+                        bridge_dense=bool(self.bridge_dense), lm_predict=bool(self.lm_predict), window_width=5)
+            eos = self.mapping[0].get('\n', 1)
+            self._engine = Engine(topo, self._weights, device=self.device, eos_index=eos, gemm_mode=self.gemm_mode)
+            self._engine_lm = bool(self.lm_predict)
+        elif self._engine_lm != bool(self.lm_predict):
+            self._engine = None
+            return self._get_engine()
+        return self._engine
+
+    # ------------------------------------------------------------------ model files
+    @staticmethod
+    def _weight_names(layer, count, depth):
+        """Dataset names the way Keras names the variables (loading is positional, names are cosmetic)."""
+        three = ['kernel:0', 'recurrent_kernel:0', 'bias:0']
+        if layer == 'char_input_projection':
+            return ['char_input_projection/kernel:0']
+        if layer == 'attention_dense':
+            return ['attention_dense/kernel:0']
+        if layer.startswith('bridge'):
+            return [layer + '/kernel:0', layer + '/bias:0']
+        if layer == 'decoder_lstm_%d' % depth:
+            return [layer + '/' + n for n in ['W_a:0', 'v_a:0', 'b_UW:0', 'b_v:0'] + three]
+        if count == 6:
+            return [layer + '/forward_' + layer + '/' + n for n in three] + \
+                   [layer + '/backward_' + layer + '/' + n for n in three]
+        return [layer + '/' + n for n in three]
+
+    def save(self, filename):
+        '''Save model weights and configuration parameters (seq2seq.py:1121-1141): Keras
+        ``save_weights`` layout plus the ``/config`` group.'''
+        assert self.status > 1  # already trained
+        self.logger.info('Saving model under "%s"', filename)
+        root = h5lite.Group()
+        names = list(self._layer_shapes())
+        root.attrs['layer_names'] = np.array([n.encode('utf8') for n in names])
+        root.attrs['backend'] = np.bytes_(b'tensorflow')
+        root.attrs['keras_version'] = np.bytes_(b'2.3.1')
+        for layer in names:
+            group = root.require_group(layer)
+            wnames = self._weight_names(layer, len(self._weights[layer]), self.depth)
+            group.attrs['weight_names'] = np.array([n.encode('utf8') for n in wnames])
+            for wname, arr in zip(wnames, self._weights[layer]):
+                parts = wname.split('/')
+                sub = group.require_group('/'.join(parts[:-1])) if len(parts) > 1 else group
+                sub[parts[-1]] = np.asarray(arr, np.float32)
+        config = root.require_group('config')
+        config['width'] = np.array(int(self.width))
+        config['depth'] = np.array(int(self.depth))
+        config['stateful'] = np.array(bool(self.stateful))
+        config['residual_connections'] = np.array(bool(self.residual_connections))
+        config['deep_bidirectional_encoder'] = np.array(bool(self.deep_bidirectional_encoder))
+        config['bridge_dense'] = np.array(bool(self.bridge_dense))
+        config['mapping'] = np.fromiter((ord(self.mapping[1][i]) if i in self.mapping[1] and self.mapping[1][i] else 0
+                                         for i in range(self.voc_size)), dtype=np.uint32)
+        h5lite.write(filename, root)
+
+    def load_config(self, filename):
+        '''Load parameters to prepare configuration/compilation (seq2seq.py:1143-1162).'''
+        config = h5lite.read(filename)['config']
+        self.width = int(config['width'][()])
+        self.depth = int(config['depth'][()])
+        self.stateful = bool(config['stateful'][()])
+        self.residual_connections = bool(config['residual_connections'][()]) \
+            if 'residual_connections' in config else False  # old default
+        self.deep_bidirectional_encoder = bool(config['deep_bidirectional_encoder'][()]) \
+            if 'deep_bidirectional_encoder' in config else False  # old default
+        self.bridge_dense = bool(config['bridge_dense'][()]) if 'bridge_dense' in config else False  # old default
+        c_i = dict((chr(c), i) if c > 0 else ('', 0) for i, c in enumerate(config['mapping'][()]))
+        i_c = dict((i, chr(c)) if c > 0 else (0, '') for i, c in enumerate(config['mapping'][()]))
+        self.mapping = (c_i, i_c)
+        self.voc_size = len(c_i)
+
+    @staticmethod
+    def _from_cudnn(weights, W):
+        """Keras ``_convert_rnn_weights`` CuDNNLSTM -> LSTM: a layer saved from a GPU-trained model has
+        bias length 8W and per-gate transposed kernels."""
+        out = []
+        for i in range(0, len(weights), 3):
+            k, r, b = weights[i:i + 3]
+            if b.shape != (8 * W,):
+                out += [k, r, b]
+                continue
+            k = np.hstack([g.T.reshape(g.shape, order='F') for g in np.hsplit(k, 4)])
+            r = np.hstack([g.T for g in np.hsplit(r, 4)])
+            out += [k, r, b.reshape((2, -1)).sum(axis=0)]
+        return out
+
+    def _read_layer_weights(self, root, by_name_only=True):
+        if 'layer_names' not in root.attrs and 'model_weights' in root:
+            root = root['model_weights']
+        found = {}
+        for raw in root.attrs.get('layer_names', []):
+            layer = raw.decode('utf8') if isinstance(raw, bytes) else str(raw)
+            if layer not in root:
+                continue
+            group = root[layer]
+            wnames = [n.decode('utf8') if isinstance(n, bytes) else str(n) for n in group.attrs.get('weight_names', [])]
+            if wnames:
+                found[layer] = [np.asarray(group.get_path(n), np.float32) for n in wnames]
+        return found
+
+    def load_weights(self, filename):
+        '''Load weights into the configured/compiled model (seq2seq.py:1164-1174): by layer name,
+        positional within the layer; layers of other shape raise like Keras does.'''
+        assert self.status > 0  # already compiled
+        self.logger.info('Loading model from "%s"', filename)
+        found = self._read_layer_weights(h5lite.read(filename))
+        W = int(self.width)
+        for layer, shapes in self._layer_shapes().items():
+            if layer not in found:
+                continue
+            ws = found[layer]
+            if 'lstm' in layer:
+                off = 4 if layer == 'decoder_lstm_%d' % self.depth else 0
+                ws = ws[:off] + self._from_cudnn(ws[off:], W)
+            if len(ws) != len(shapes):
+                raise ValueError('Layer %s expects %d weight(s), but the saved weights have %d element(s)'
+                                 % (layer, len(shapes), len(ws)))
+            for a, shape in zip(ws, shapes):
+                if tuple(a.shape) != tuple(shape):
+                    raise ValueError('Layer %s: weight shape %s incompatible with saved shape %s'
+                                     % (layer, shape, a.shape))
+            self._weights[layer] = [np.ascontiguousarray(a, np.float32) for a in ws]
+        self._engine = None
+        self._resync_decoder()
+        self.status = 2
+
+    def load_transfer_weights(self, filename):
+        '''Load weights from another model into the matching layers (seq2seq.py:1176-1213):
+        layers whose shapes do not match are skipped (``skip_mismatch=True``).'''
+        assert self.status > 0  # already compiled
+        assert self.depth > 1
+        root = h5lite.read(filename)
+        if 'config' in root:
+            config = root['config']
+            c_i = dict((chr(c), i) if c > 0 else ('', 0) for i, c in enumerate(config['mapping'][()]))
+            i_c = dict((i, chr(c)) if c > 0 else (0, '') for i, c in enumerate(config['mapping'][()]))
+            if len(c_i) != self.voc_size:
+                self.mapping, self.voc_size = (c_i, i_c), len(c_i)
+                self._weights.update({k: v for k, v in self._init_weights(np.random.default_rng()).items()
+                                      if k == 'char_input_projection'})
+            else:
+                self.mapping = (c_i, i_c)
+        self.logger.info('Transferring model from "%s"', filename)
+        found = self._read_layer_weights(root)
+        W = int(self.width)
+        for layer, shapes in self._layer_shapes().items():
+            if layer not in found:
+                continue
+            ws = found[layer]
+            off = 0
+            if layer == 'decoder_lstm_%d' % self.depth:
+                # the LM donor has no attention wrapper in its top layer: only the cell weights transfer
+                off = 4
+                ws = list(self._weights[layer][:4]) + (ws[4:] if len(ws) == 7 else ws)
+            if 'lstm' in layer:
+                ws = ws[:off] + self._from_cudnn(ws[off:], W)
+            if len(ws) != len(shapes) or any(tuple(a.shape) != tuple(s) for a, s in zip(ws, shapes)):
+                self.logger.warning('skipping layer %s due to mismatch', layer)
+                continue
+            self._weights[layer] = [np.ascontiguousarray(a, np.float32) for a in ws]
+        self._engine = None
+        self.status = 1
+
+    def train(self, filenames, val_filenames=None):
+        raise NotImplementedError('training is outside the B200 inference hot path (DESIGN.md: out of scope); '
+                                  'train with the reference and load the .h5 here')
+
+    def evaluate(self, filenames, fast=False, normalization='historic_latin', charmap=None, gt_level=1,
+                 confusion=10, histogram=True):
+        raise NotImplementedError('evaluate() needs the reference\'s alignment module (uniseg/rapidfuzz), which is '
+                                  'outside the neural hot path; use predict()/correct_lines() and score externally')
+
+    # ------------------------------------------------------------------ data
+    def gen_lines(self, filenames, repeat=True, split=None, train=False, unsupervised=False, charmap=None):
+        """Generate batches of lines from the given files (seq2seq.py:919-1018): text files with
+        ``source\\ttarget`` lines (or plain lines if ``unsupervised``), or pickled (source, target) pairs
+        with confidences; ``batch_size`` lines per batch in file order, the last one padded with ''."""
+        split_ratio = 0.2
+        if charmap:
+            charmap = str.maketrans(charmap)
+        while True:
+            lines_source, lines_sourceconf, lines_target, lines_filename = [], [], [], []
+            with_confidence = False
+            for filename in filenames:
+                with_confidence = filename.endswith('.pkl')
+                with open(filename, 'rb' if with_confidence else 'r') as file:
+                    if with_confidence:
+                        file = pickle.load(file)
+                    for line_no, line in enumerate(file):
+                        if isinstance(split, np.ndarray) and (split[line_no] < split_ratio) == train:
+                            continue
+                        if with_confidence:
+                            source_text, target_text = line
+                            if not source_text:
+                                source_text, source_conf = '', []
+                            elif type(source_text[0]) is tuple:     # prob line
+                                source_text, source_conf = map(list, zip(*source_text))
+                                source_text = ''.join(source_text)
+                            else:                                   # confmat
+                                source_conf = source_text
+                                source_text = ''.join(chunk[0][0] if chunk else '' for chunk in source_conf)
+                            if not source_text.endswith('\n'):
+                                source_conf = [[('\n', 1.0)]]
+                                source_text = '\n'
+                        elif unsupervised and '\t' not in line:
+                            source_text = target_text = line
+                        else:
+                            source_text, target_text = line.split('\t')
+                            source_text = source_text + '\n'
+                        if unsupervised:
+                            target_text = source_text
+                        if charmap:
+                            source_text = source_text.translate(charmap)
+                            target_text = target_text.translate(charmap)
+                        source_text = unicodedata.normalize('NFC', source_text)
+                        target_text = unicodedata.normalize('NFC', target_text)
+                        lines_source.append(source_text)
+                        lines_target.append(target_text)
+                        if with_confidence:
+                            lines_sourceconf.append(source_conf)
+                        lines_filename.append(filename)
+                        if len(lines_source) == self.batch_size:
+                            yield (lines_source, lines_sourceconf if with_confidence else None,
+                                   lines_target, lines_filename)
+                            lines_source, lines_sourceconf, lines_target, lines_filename = [], [], [], []
+            if repeat:
+                yield False
+            else:
+                if lines_source:
+                    pad = self.batch_size - len(lines_source)
+                    lines_source.extend(pad * [''])
+                    lines_target.extend(pad * [''])
+                    if with_confidence:
+                        lines_sourceconf.extend(pad * [[]])
+                    lines_filename.extend(pad * [None])
+                    yield (lines_source, lines_sourceconf if with_confidence else None,
+                           lines_target, lines_filename)
+                break
+
+    def predict(self, filenames, fast=False, greedy=False, charmap=None):
+        '''apply model on text files (seq2seq.py:756-780): yields (filenames, lines, scores) per batch.'''
+        assert self.status == 2
+        for batch in self.gen_lines(filenames, repeat=False, unsupervised=True, charmap=charmap):
+            lines_source, lines_sourceconf, _, lines_filename = batch
+            lines_result, _, scores_result, _ = self.correct_lines(lines_source, lines_sourceconf,
+                                                                   fast=fast, greedy=greedy)
+            yield (lines_filename, lines_result, scores_result)
+
+    def vectorize_lines(self, encoder_input_sequences, decoder_input_sequences, encoder_conf_sequences=None):
+        '''Convert a batch of source and target sequences to dense arrays (seq2seq.py:1020-1119).'''
+        assert len(encoder_input_sequences) == len(decoder_input_sequences)
+        batch_size = len(encoder_input_sequences)
+        idx, val = lines_to_sparse(self.mapping[0], encoder_input_sequences, encoder_conf_sequences, self.logger)
+        B, T, k = idx.shape
+        enc = np.zeros((batch_size, T, self.voc_size), dtype=np.float32 if encoder_conf_sequences else np.uint32)
+        for a in range(k):
+            b, t = np.nonzero(idx[:, :, a] >= 0)
+            enc[b, t, idx[b, t, a]] = 1 if val is None else val[b, t, a]
+        Td = max(map(len, decoder_input_sequences))
+        dec_in = np.zeros((batch_size, Td + 1, self.voc_size), dtype=np.uint32)
+        dec_out = np.zeros((batch_size, Td + 1, self.voc_size), dtype=np.uint32)
+        for i, dec_seq in enumerate(decoder_input_sequences):
+            for j, char in enumerate(dec_seq):
+                if char not in self.mapping[0]:
+                    if char != GAP:
+                        self.logger.error('unmapped character "%s" at decoder input sequence %d', char, i)
+                    v = 0
+                else:
+                    v = self.mapping[0][char]
+                dec_in[i, j + 1, v] = 1
+                dec_out[i, j, v] = 1
+        weights = np.ones(dec_out.shape[:-1], dtype=np.float32)
+        weights[np.all(dec_out == 0, axis=2)] = 0.
+        if self.lm_loss:
+            dec_out, weights = [dec_out, dec_out], [weights, weights]
+        return enc, dec_in, dec_out, weights
+
+    # ------------------------------------------------------------------ decoding
+    def _row_T(self, idx):
+        return np.full(idx.shape[0], idx.shape[1], np.int32)    # one call = one reference batch: T is its padded length
+
+    def _predict_encoder(self, encoder_input_data):
+        """encoder_model.predict_on_batch (seq2seq.py:403-406): [enc_out (B,T,D)] + [h_n, c_n]*depth + [a0 (B,T)]."""
+        import torch
+        eng = self._get_engine()
+        idx, val = dense_to_sparse(encoder_input_data)
+        dev = eng.device
+        enc_out, states = eng.encode(torch.as_tensor(idx, device=dev),
+                                     None if val is None else torch.as_tensor(val, device=dev),
+                                     torch.as_tensor(self._row_T(idx), device=dev))
+        out = [enc_out.permute(1, 0, 2).contiguous().cpu().numpy()]
+        out += [s.cpu().numpy() for s in states]
+        out.append(np.zeros(idx.shape[:2], np.float32))
+        return out
+
+    def _greedy_sparse(self, idx, val, want_align=True):
+        eng = self._get_engine()
+        chars, probs, scores, lens, align = eng.correct_greedy_host(idx, val, self._row_T(idx), want_align=want_align)
+        chars, probs, scores, lens = chars.numpy(), probs.numpy(), scores.numpy(), lens.numpy()
+        i2c = self.mapping[1]
+        B = idx.shape[0]
+        lines = [''.join(i2c[int(v)] for v in chars[j, :lens[j]]) for j in range(B)]
+        out_probs = [list(probs[j, :lens[j]]) for j in range(B)]
+        out_scores = [float(scores[j]) if lens[j] else 0. for j in range(B)]
+        if align is not None:
+            align = align.numpy()
+            alignments = [[align[s, j].copy() for s in range(lens[j])] for j in range(B)]
+        else:
+            alignments = [[] for _ in range(B)]
+        return lines, out_probs, out_scores, alignments
+
+    def correct_lines(self, lines, conf=None, fast=True, greedy=True):
+        '''apply correction model on text strings (seq2seq.py:782-842).
+
+        Return a 4-tuple of the corrected lines, probability lists, perplexity scores, and
+        input-output alignments.'''
+        assert not fast or greedy, "cannot decode in fast mode with beam search enabled"
+        if not lines:
+            return [], [], [], []
+        idx, val = lines_to_sparse(self.mapping[0], lines, conf, self.logger)
+        if fast:
+            return self._greedy_sparse(idx, val)
+        if greedy:
+            # decode_sequence_greedy per line (:817-819) picks the same characters as the batch decoder —
+            # "argmax, and if '' wins the argmax of the rest" == argmax over indices >= 1 — from the same
+            # batch encoding; only the score is accumulated in float32 there (:1312, :1343)
+            out_lines, out_probs, _, alignments = self._greedy_sparse(idx, val)
+            out_scores = []
+            for j, line in enumerate(lines):
+                if not line:
+                    out_lines[j], out_probs[j], alignments[j] = '', [], []
+                    out_scores.append(0)
+                    continue
+                total = np.float32(0)
+                for p in out_probs[j]:
+                    total = np.float32(total + -np.log(p))
+                out_scores.append(total / len(out_lines[j]) if out_lines[j] else 0)
+                out_lines[j] = out_lines[j].replace(GAP, '')
+            return out_lines, out_probs, out_scores, alignments
+        return self._beam_sparse(lines, idx, val)
+
+    def _beam_sparse(self, lines, idx, val, want_align=True):
+        eng = self._get_engine()
+        bp = eng.beam_params(batch_size=min(int(self.batch_size), 256), beam_width_in=self.beam_width_in,
+                             beam_threshold_in=self.beam_threshold_in, beam_width_out=self.beam_width_out,
+                             rejection_threshold=self.rejection_threshold)
+        chars, probs, scores, lens, align, stats = eng.correct_beam_host(
+            idx, val, self._row_T(idx), bp, want_align=want_align, budget_bytes=self.beam_budget_bytes)
+        chars, probs, scores, lens, stats = chars.numpy(), probs.numpy(), scores.numpy(), lens.numpy(), stats.numpy()
+        align = None if align is None else align.numpy()
+        i2c = self.mapping[1]
+        output_lines, output_probs, output_scores, alignments = [], [], [], []
+        for j, input_line in enumerate(lines):
+            if not input_line:
+                line, prob, score, alignment = '', [], 0, []
+            elif lens[j] > 0:
+                n = int(lens[j])
+                line = ''.join(i2c[int(v)] for v in chars[j, :n])
+                prob = list(probs[j, :n])
+                score = float(scores[j])
+                alignment = [align[j, s].copy() for s in range(n)] if align is not None else []
+            else:
+                # no final hypothesis: the reference's StopIteration fallback (:826-836)
+                self.logger.error('cannot beam-decode input line %d: "%s"', j, input_line)
+                if isinstance(input_line[0], tuple):
+                    line = ''.join(chunk[0] for chunk in input_line)
+                if isinstance(input_line[0], list):
+                    line = ''.join(chunk[0][0] if chunk else '' for chunk in input_line)
+                else:
+                    line = input_line
+                prob = [1.0] * len(line)
+                score = 0
+                alignment = np.eye(len(line)).tolist()
+            line = line.replace(GAP, '')
+            output_lines.append(line)
+            output_probs.append(prob)
+            output_scores.append(score)
+            alignments.append(alignment)
+        self.last_beam_stats = stats
+        return output_lines, output_probs, output_scores, alignments
+
+    def decode_batch_greedy(self, encoder_input_data):
+        '''Predict from one batch of lines array without alternatives (seq2seq.py:1215-1286).
+
+        Return a 5-tuple of the full output array (for training phase), output strings, output
+        probability lists, entropies, and soft alignments.'''
+        encoder_input_data = np.asarray(encoder_input_data)
+        B, T = encoder_input_data.shape[:2]
+        idx, val = dense_to_sparse(encoder_input_data)
+        lines, probs, scores, alignments = self._greedy_sparse(idx, val)
+        # the reference's first value is the uint32 cast of the fed-back softmax rows, i.e. all zero unless a
+        # probability reaches 1.0 (:1237, :1244); only scheduled-sampling training reads it
+        decoder_output_data = np.zeros((B, T * 2, self.voc_size), dtype=np.uint32)
+        return decoder_output_data, lines, probs, scores, alignments
+
+    def decode_sequence_greedy(self, source_seq=None, encoder_outputs=None):
+        '''Predict from one line vector without alternatives (seq2seq.py:1288-1354).
+
+        ``encoder_outputs`` (slices of an earlier batch encoding) cannot be re-imported into the engine;
+        pass ``source_seq`` padded to the batch length instead.'''
+        if source_seq is None:
+            raise NotImplementedError('decode_sequence_greedy needs source_seq (T,V) on the B200 engine')
+        idx, val = dense_to_sparse(np.asarray(source_seq)[None])
+        lines, probs, _, alignments = self._greedy_sparse(idx, val)
+        total = np.float32(0)
+        for p in probs[0]:
+            total = np.float32(total + -np.log(p))
+        return lines[0], probs[0], total / len(lines[0]), alignments[0]
+
+    def decode_sequence_beam(self, source_seq=None, encoder_outputs=None):
+        '''Predict from one line vector with alternatives (seq2seq.py:1356-1544).
+
+        Generator of (string, probabilities, entropy, alignments); the engine materialises the best
+        final hypothesis only, which is what every caller draws (``next()``, :823, repl.py:80).'''
+        if source_seq is None:
+            raise NotImplementedError('decode_sequence_beam needs source_seq (T,V) on the B200 engine')
+        idx, val = dense_to_sparse(np.asarray(source_seq)[None])
+        eng = self._get_engine()
+        bp = eng.beam_params(batch_size=min(int(self.batch_size), 256), beam_width_in=self.beam_width_in,
+                             beam_threshold_in=self.beam_threshold_in, beam_width_out=self.beam_width_out,
+                             rejection_threshold=self.rejection_threshold)
+        chars, probs, scores, lens, align, stats = eng.correct_beam_host(
+            idx, val, self._row_T(idx), bp, want_align=True, budget_bytes=self.beam_budget_bytes)
+        n = int(lens[0])
+        if n > 0:
+            i2c = self.mapping[1]
+            yield (''.join(i2c[int(v)] for v in chars[0, :n]), list(probs[0, :n].numpy()), float(scores[0]),
+                   [align[0, s].numpy().copy() for s in range(n)])

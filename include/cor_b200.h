@@ -74,8 +74,8 @@ int cor_abi_version(void);
 int cor_model_create(const cor_config* cfg, int device, cor_model** out);
 /* One Keras weight by layer name and position inside the layer (SURVEY.md A.5 order), in the
  * Keras (in, out) layout; the Keras -> kernel repack (transposition to K-major, gate
- * interleave, TF32 hi/lo split) happens here.  A CuDNN-format LSTM layer (bias 8W) is
- * detected by its bias length and converted as Keras does on load. */
+ * interleave, TF32 hi/lo split) happens here.  LSTM layers must be in LSTM (not CuDNNLSTM)
+ * format: the host class converts CuDNN-format layers (bias 8W) the way Keras does on load. */
 int cor_model_set_weight(cor_model* m, const char* keras_layer, int index,
                          const float* host, const int64_t* shape, int rank);
 int cor_model_finalize(cor_model* m);
@@ -128,6 +128,13 @@ int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines,
 int cor_beam_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
                              const cor_beam_params* bp, size_t budget_bytes, size_t* bytes);
 int cor_correct_beam_host(cor_model* m, const cor_lines* host_lines, const cor_beam_params* bp,
+                          void* workspace, size_t workspace_bytes,
+                          int32_t* out_chars, float* out_probs, double* out_scores,
+                          int32_t* out_len, float* out_align, int64_t* stats, void* stream);
+
+/* Same search with the line arrays and every result array in DEVICE memory (inputs resident in HBM);
+ * only the per-line overflow flags cross to the host between waves. */
+int cor_decode_beam_batch(cor_model* m, const cor_lines* device_lines, const cor_beam_params* bp,
                           void* workspace, size_t workspace_bytes,
                           int32_t* out_chars, float* out_probs, double* out_scores,
                           int32_t* out_len, float* out_align, int64_t* stats, void* stream);

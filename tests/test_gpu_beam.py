@@ -111,3 +111,26 @@ def test_beam_c2_size_degenerate_bracket():
     assert text == lines
     assert np.allclose(scores, np.log(2.0), atol=1e-6)
     assert (stats[:, 0] == 81).all() and (stats[:, 1] == 81).all() and (stats[:, 2] == 1).all()
+
+
+def test_beam_device_entry_matches_host_entry():
+    """cor_decode_beam_batch (device arrays) == cor_correct_beam_host, incl. the retry path."""
+    from cor_asv_ann_b200.vectorize import lines_to_sparse
+    name, n, length, seed, params = BEAM_CASES["c1_mix"]
+    topo, w, mapping = make_model(name)
+    lines = synthetic_lines(mapping, 6, 10, seed=92, min_length=4)
+    eng = _engine(topo, w, 1)
+    idx, val = lines_to_sparse(mapping[0], lines)
+    B, T, _ = idx.shape
+    bp = eng.beam_params(**params)
+    for budget in (2 << 30, 24 << 20):
+        h = eng.correct_beam_host(idx, val, np.full(B, T, np.int32), bp, budget_bytes=budget)
+        d = eng.beam_device(torch.as_tensor(idx, device="cuda"), None, torch.full((B,), T, dtype=torch.int32, device="cuda"),
+                            bp, budget_bytes=budget)
+        torch.cuda.synchronize()
+        assert (h[3].numpy() == d[3].cpu().numpy()).all()
+        assert (h[5].numpy() == d[5].cpu().numpy()).all()
+        for j in range(B):
+            nj = int(h[3][j])
+            assert (h[0][j, :nj].numpy() == d[0][j, :nj].cpu().numpy()).all()
+            assert np.allclose(h[1][j, :nj].numpy(), d[1][j, :nj].cpu().numpy(), atol=1e-6)
