@@ -2,6 +2,7 @@
 // encoder scan, one decoder timestep, greedy driver.
 #include "model.h"
 #include "epilogue.cuh"
+#include <cuda_fp16.h>
 #include <string.h>
 #include <math.h>
 #include <algorithm>
@@ -51,16 +52,20 @@ static void prof_end(cudaStream_t st, int M, const int* m_dev, int N, const Gemm
     g_prof.launches += 1;
 }
 
-// GEMM dispatch: tcgen05 3xTF32 when the model keeps split operands and the tile is worth it,
+// GEMM dispatch: tcgen05 3xFP16 when the model keeps split operands and the tile is worth it,
 // exact FFMA otherwise (small M).  Both consume the same operand representation.
+static bool tc_shape_ok(const GemmSeg* s, int n) {
+    for (int i = 0; i < n; ++i) if (s[i].K % 64 != 0 || s[i].lda % 8 != 0 || s[i].ldb % 8 != 0) return false;
+    return true;
+}
 static int gemm_store(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const StoreEpi& e) {
-    if (m->split && M >= m->tc_min_rows && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e);
+    if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e);
     return gemm_store_ffma(st, M, m_dev, N, s, n, e);
 }
 static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const LstmEpi& e) {
     prof_begin(st);
     int rc;
-    if (m->split && M >= m->tc_min_rows && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
+    if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
     else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
     prof_end(st, M, m_dev, N, s, n);
     return rc;
@@ -73,15 +78,15 @@ static int dev_alloc(cor_model* m, size_t bytes, void** out) {
     return 0;
 }
 
-static void host_split(const std::vector<float>& x, std::vector<float>& hi, std::vector<float>& lo) {
+// fp16 (hi, lo) split of a weight matrix on the host (same arithmetic as f16_split on the device)
+static int host_split(const std::vector<float>& x, std::vector<__half>& hi, std::vector<__half>& lo) {
     hi.resize(x.size()); lo.resize(x.size());
     for (size_t i = 0; i < x.size(); ++i) {
-        uint32_t b; memcpy(&b, &x[i], 4);
-        uint32_t r = (b + 0x1000u) & 0xFFFFE000u;
-        if ((b & 0x7F800000u) == 0x7F800000u || (r & 0x7F800000u) == 0x7F800000u) r = b & 0xFFFFE000u;
-        float h; memcpy(&h, &r, 4);
-        hi[i] = h; lo[i] = x[i] - h;
+        COR_CHECK(fabsf(x[i]) < 6.0e4f, "weight outside the fp16 operand range: use gemm_mode 1 (exact FFMA) for this model");
+        hi[i] = __float2half_rn(x[i]);
+        lo[i] = __float2half_rn(x[i] - __half2float(hi[i]));
     }
+    return 0;
 }
 
 // upload a K-major matrix [rows][ld]
@@ -89,11 +94,12 @@ static int upload_mat(cor_model* m, const std::vector<float>& data, int rows, in
     out->rows = rows; out->ld = ld;
     const size_t bytes = data.size() * sizeof(float);
     if (m->split) {
-        std::vector<float> hi, lo;
-        host_split(data, hi, lo);
-        if (dev_alloc(m, bytes, (void**)&out->hi) || dev_alloc(m, bytes, (void**)&out->lo)) return 1;
-        COR_CUDA(cudaMemcpy(out->hi, hi.data(), bytes, cudaMemcpyHostToDevice));
-        COR_CUDA(cudaMemcpy(out->lo, lo.data(), bytes, cudaMemcpyHostToDevice));
+        std::vector<__half> hi, lo;
+        if (host_split(data, hi, lo)) return 1;
+        const size_t hb = data.size() * sizeof(__half);
+        if (dev_alloc(m, hb, (void**)&out->hi) || dev_alloc(m, hb, (void**)&out->lo)) return 1;
+        COR_CUDA(cudaMemcpy(out->hi, hi.data(), hb, cudaMemcpyHostToDevice));
+        COR_CUDA(cudaMemcpy(out->lo, lo.data(), hb, cudaMemcpyHostToDevice));
     } else {
         if (dev_alloc(m, bytes, (void**)&out->hi)) return 1;
         COR_CUDA(cudaMemcpy(out->hi, data.data(), bytes, cudaMemcpyHostToDevice));
@@ -253,8 +259,12 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
             for (int dir = 0; dir < ndir; ++dir) {
                 const LstmW& lw = dir == 0 ? m->enc_fw[n] : m->enc_bw[n];
                 const size_t slab = (size_t)s * B * in_dim;
+                // split operands are __half arrays behind float* (epilogue.cuh): offset in bytes
+                const size_t sb = slab * (in_lo[dir] ? sizeof(__half) : sizeof(float));
+                const float* a_hi = reinterpret_cast<const float*>(reinterpret_cast<const char*>(in[dir]) + sb);
+                const float* a_lo = in_lo[dir] ? reinterpret_cast<const float*>(reinterpret_cast<const char*>(in_lo[dir]) + sb) : nullptr;
                 GemmSeg segs[2] = {
-                    {in[dir] + slab, in_dim, in_lo[dir] ? in_lo[dir] + slab : nullptr, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, in_dim},
+                    {a_hi, in_dim, a_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, in_dim},
                     {ws.eh[dir][cur], W, ws.eh_lo[dir][cur], lw.R.hi, lw.R.ld, lw.R.lo, W}};
                 LstmEpi e{};
                 e.bias = lw.bias; e.c_in = ws.ec[dir]; e.c_out = ws.ec[dir];
@@ -428,7 +438,7 @@ const char* cor_last_error(void) { return g_error.c_str(); }
 int cor_abi_version(void) { return 1; }
 int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launches = 0; return v; }
 
-// Test hook: C[M,N] = A[M,K] . B[N,K]^T through one of the two GEMM kernels (1 = FFMA, 2 = tcgen05 3xTF32).
+// Test hook: C[M,N] = A[M,K] . B[N,K]^T through one of the two GEMM kernels (1 = FFMA, 2 = tcgen05 3xFP16).
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     COR_CHECK(mode == 1 || mode == 2, "mode must be 1 (FFMA) or 2 (tcgen05)");
@@ -652,9 +662,11 @@ int cor_decode_step(cor_model* m, void* workspace, size_t workspace_bytes, int n
     const int R = n_hyp, W = m->W, d = m->d;
     const size_t RW = (size_t)R * W;
     // stage the caller's rows into the step buffers of the workspace (stride V -> Vp for p)
-    COR_CUDA(cudaMemsetAsync(ws.p, 0, (size_t)R * m->Vp * 4, st));
-    COR_CUDA(cudaMemcpy2DAsync(ws.p, (size_t)m->Vp * 4, p_in, (size_t)m->V * 4, (size_t)m->V * 4, R, cudaMemcpyDeviceToDevice, st));
-    if (ws.p_lo && launch_split(st, ws.p, ws.p, ws.p_lo, (size_t)R * m->Vp)) return 1;
+    // (staged through the logits buffer: the fp16 split must not run in place)
+    float* p_stage = ws.p_lo ? ws.logits : ws.p;
+    COR_CUDA(cudaMemsetAsync(p_stage, 0, (size_t)R * m->Vp * 4, st));
+    COR_CUDA(cudaMemcpy2DAsync(p_stage, (size_t)m->Vp * 4, p_in, (size_t)m->V * 4, (size_t)m->V * 4, R, cudaMemcpyDeviceToDevice, st));
+    if (ws.p_lo && launch_split(st, p_stage, ws.p, ws.p_lo, (size_t)R * m->Vp)) return 1;
     StepIO io{};
     io.R = R; io.row_line = row_line; io.first = false;
     io.p = ws.p; io.p_lo = ws.p_lo; io.x = ws.x; io.x_lo = ws.x_lo;

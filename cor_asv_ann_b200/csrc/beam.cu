@@ -223,11 +223,11 @@ __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) 
     for (int row = blockIdx.x; row < R; row += gridDim.x) {
         const int line = b.row_line[row];
         const uint32_t node = b.row_node[row];
-        float* p = b.p + (size_t)row * b.Vp;
-        float* p_lo = split ? b.p_lo + (size_t)row * b.Vp : nullptr;
+        float* p_lo = split ? b.p_lo : nullptr;       // split operands: base pointers + element offsets only
+        const size_t po = (size_t)row * b.Vp;
         float* a_in = b.a_in + (size_t)row * b.T;
         if (node == 0u) {          // root: zero feedback, encoder final states, zero alignment
-            for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) { p[v] = 0.f; if (p_lo) p_lo[v] = 0.f; }
+            for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) store_split(b.p, p_lo, po + v, 0.f);
             for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = 0.f;
             for (int n = 0; n < b.d; ++n)
                 for (int u = threadIdx.x; u < b.W; u += blockDim.x) {
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) 
         for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) {
             float x = rp[v];
             for (int q = 0; q < k; ++q) if (acc[q] == v) x = 0.f;     // better siblings were zeroed before the copy
-            store_split(p, p_lo, v, x);
+            store_split(b.p, p_lo, po + v, x);
         }
         const float* ra = b.rec_a + g * b.T;
         for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = ra[j];

@@ -1,36 +1,48 @@
 // epilogue.cuh — device-side epilogues shared by the FFMA and the tcgen05 GEMM kernels.
 #pragma once
 #include "engine.h"
+#include <cuda_fp16.h>
 
 namespace cor {
 
-// Round-to-nearest split of an fp32 value into a TF32-representable head and the exact residual.
-// hi has its 13 low mantissa bits clear, so the tensor core's own fp32->tf32 conversion is exact
-// on it whatever its rounding mode; lo = x - hi is exact in fp32 (|lo| <= 2^-11 |x|).
-__device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
-    uint32_t b = __float_as_uint(x);
-    uint32_t r = (b + 0x1000u) & 0xFFFFE000u;
-    // keep inf/nan and values whose rounding would overflow the exponent untouched
-    if ((b & 0x7F800000u) == 0x7F800000u || (r & 0x7F800000u) == 0x7F800000u) r = b & 0xFFFFE000u;
-    hi = __uint_as_float(r);
-    lo = x - hi;
+// Split of an fp32 value into an fp16 head and an fp16 residual: x ~= hi + lo with
+// |x - hi - lo| <= 2^-22 |x| as long as lo stays a normal fp16 number (|x| >~ 0.12); below that the
+// residual sits on the fp16 subnormal grid and the absolute error is <= 2^-25 (3e-8).  Both parts have
+// 11-bit significands — what a TF32 operand carries too — but run at the fp16 tensor rate (2x TF32)
+// and take half the bytes.  Operand range: |x| < 65504 (activations here are O(1), weights O(0.1)).
+//
+// Representation convention used by every kernel: an operand is a pair of pointers (hi_p, lo_p), both
+// declared float*.  lo_p == nullptr: hi_p holds plain fp32 values.  lo_p != nullptr: BOTH point to
+// __half arrays (same element offsets), holding the head and the residual.
+__device__ __forceinline__ void f16_split(float x, __half& hi, __half& lo) {
+    hi = __float2half_rn(x);
+    lo = __float2half_rn(x - __half2float(hi));
 }
 
 __device__ __forceinline__ void store_split(float* hi_p, float* lo_p, size_t off, float v) {
     if (lo_p) {
-        float hi, lo;
-        tf32_split(v, hi, lo);
-        hi_p[off] = hi;
-        lo_p[off] = lo;
+        __half hi, lo;
+        f16_split(v, hi, lo);
+        reinterpret_cast<__half*>(hi_p)[off] = hi;
+        reinterpret_cast<__half*>(lo_p)[off] = lo;
     } else {
         hi_p[off] = v;
     }
 }
 
 __device__ __forceinline__ float load_split(const float* hi_p, const float* lo_p, size_t off) {
-    float v = hi_p[off];
-    if (lo_p) v += lo_p[off];
-    return v;
+    if (lo_p) return __half2float(reinterpret_cast<const __half*>(hi_p)[off]) + __half2float(reinterpret_cast<const __half*>(lo_p)[off]);
+    return hi_p[off];
+}
+
+// 4 consecutive elements (off a multiple of 4)
+__device__ __forceinline__ float4 load_split4(const float* hi_p, const float* lo_p, size_t off) {
+    if (!lo_p) return *reinterpret_cast<const float4*>(hi_p + off);
+    const uint2 h = *reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(hi_p) + off);
+    const uint2 l = *reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(lo_p) + off);
+    const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&h.x)), h1 = __half22float2(*reinterpret_cast<const __half2*>(&h.y));
+    const float2 l0 = __half22float2(*reinterpret_cast<const __half2*>(&l.x)), l1 = __half22float2(*reinterpret_cast<const __half2*>(&l.y));
+    return make_float4(h0.x + l0.x, h0.y + l0.y, h1.x + l1.x, h1.y + l1.y);
 }
 
 __device__ __forceinline__ float sigmoidf_exact(float x) { return 1.0f / (1.0f + expf(-x)); }

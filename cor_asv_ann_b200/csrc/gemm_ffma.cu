@@ -3,8 +3,8 @@
 // Role: the small-batch path (an OCR-D page is 20-60 lines: fewer rows than one tcgen05
 // M=128 tile) and the bring-up / cross-check path for the tensor-core kernel in gemm_tc.cu.
 // C[M,N] = sum_s A_s[M,K_s] * B_s[N,K_s]^T; 128x128 tile, 256 threads, 8x8 register tile,
-// BK=16 double-buffered through shared memory.  Operands stored as TF32 (hi, lo) pairs are
-// re-joined on load (hi + lo is exact), so this kernel always computes in full fp32.
+// BK=16 double-buffered through shared memory.  Operands stored as fp16 (hi, lo) pairs are
+// re-joined on load (hi + lo is exact in fp32), so this kernel always accumulates in full fp32.
 #include "engine.h"
 #include "epilogue.cuh"
 
@@ -54,19 +54,9 @@ __global__ void __launch_bounds__(NT) gemm_ffma_kernel(FfmaParams p, Epi epi) {
         for (int h = 0; h < 2; ++h) {
             int r = min(m0 + lrow + 64 * h, M - 1);
             size_t off = (size_t)r * g.lda + k0 + lk;
-            float4 v = *reinterpret_cast<const float4*>(g.A + off);
-            if (g.A_lo) {
-                float4 w = *reinterpret_cast<const float4*>(g.A_lo + off);
-                v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
-            }
-            ra[h] = v;
+            ra[h] = load_split4(g.A, g.A_lo, off);
             size_t offb = (size_t)min(n0 + lrow + 64 * h, p.N - 1) * g.ldb + k0 + lk;
-            float4 b = *reinterpret_cast<const float4*>(g.B + offb);
-            if (g.B_lo) {
-                float4 w = *reinterpret_cast<const float4*>(g.B_lo + offb);
-                b.x += w.x; b.y += w.y; b.z += w.z; b.w += w.w;
-            }
-            rb[h] = b;
+            rb[h] = load_split4(g.B, g.B_lo, offb);
         }
     };
     auto stash = [&](int buf) {

@@ -116,11 +116,7 @@ __global__ void __launch_bounds__(128) attention_kernel(AttnArgs a) {
         for (int q = 0; q < nj; ++q) {
             const float w = e[q] / esum;
             const size_t off = ((size_t)jj[q] * a.L + line) * a.D + k;
-            float4 x = *reinterpret_cast<const float4*>(a.enc + off);
-            if (a.enc_lo) {
-                const float4 y = *reinterpret_cast<const float4*>(a.enc_lo + off);
-                x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
-            }
+            const float4 x = load_split4(a.enc, a.enc_lo, off);
             c.x = fmaf(w, x.x, c.x); c.y = fmaf(w, x.y, c.y);
             c.z = fmaf(w, x.z, c.z); c.w = fmaf(w, x.w, c.w);
         }
@@ -182,18 +178,13 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
 __global__ void split_kernel(const float* __restrict__ x, float* hi, float* lo, size_t n) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) {
-        float h, l;
-        tf32_split(x[i], h, l);
-        hi[i] = h;
-        lo[i] = l;
-    }
+    for (; i < n; i += stride) store_split(hi, lo, i, x[i]);
 }
 
 __global__ void join_kernel(const float* __restrict__ hi, const float* __restrict__ lo, float* out, size_t n) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) out[i] = hi[i] + lo[i];
+    for (; i < n; i += stride) out[i] = load_split(hi, lo, i);
 }
 
 __global__ void finish_scores_kernel(double* score_sum, const int32_t* len, int R) {
