@@ -4,6 +4,7 @@
 #include "epilogue.cuh"
 #include <cuda_fp16.h>
 #include <string.h>
+#include <stdlib.h>
 #include <math.h>
 #include <algorithm>
 
@@ -310,30 +311,30 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------ decoder step
-int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) {
-    const int W = m->W, d = m->d, D = m->D, R = io.R;
+// The feedback projection x = p . E (seq2seq.py:421-423) feeds only the first cell's kernel, so
+// with PE = E . Kx prepared at load time its product is one K-segment of that cell's GEMM.
+static int x_segment(cor_model* m, const StepIO& io, const LstmW& lw, cudaStream_t st, GemmSeg* seg, int* n) {
+    if (m->fuse_pe) {
+        if (!io.first) seg[(*n)++] = GemmSeg{io.p, m->Vp, io.p_lo, m->PE.hi, m->PE.ld, m->PE.lo, m->Vp};
+        return 0;                                   // first step: p == 0, the segment vanishes
+    }
+    const int W = m->W;
     if (io.first) {
-        COR_CUDA(cudaMemsetAsync(io.x, 0, (size_t)R * W * 4, st));
-        if (io.x_lo) COR_CUDA(cudaMemsetAsync(io.x_lo, 0, (size_t)R * W * 4, st));
+        COR_CUDA(cudaMemsetAsync(io.x, 0, (size_t)io.R * W * 4, st));
+        if (io.x_lo) COR_CUDA(cudaMemsetAsync(io.x_lo, 0, (size_t)io.R * W * 4, st));
     } else {
         GemmSeg s = {io.p, m->Vp, io.p_lo, m->Et.hi, m->Et.ld, m->Et.lo, m->Vp};
         StoreEpi e{io.x, W, io.x_lo, nullptr, 0};
-        if (gemm_store(m, st, R, io.r_dev, W, &s, 1, e)) return 1;
+        if (gemm_store(m, st, io.R, io.r_dev, W, &s, 1, e)) return 1;
     }
-    const float* x = io.x; const float* x_lo = io.x_lo;
-    for (int n = 0; n + 1 < d; ++n) {
-        const LstmW& lw = m->dec[n];
-        GemmSeg segs[2] = {{x, W, x_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, W},
-                           {io.h_in[n], W, io.h_in_lo[n], lw.R.hi, lw.R.ld, lw.R.lo, W}};
-        LstmEpi e{};
-        e.bias = lw.bias; e.c_in = io.c_in[n]; e.c_out = io.c_out[n];
-        e.h_prev = io.h_in[n]; e.h_prev_lo = io.h_in_lo[n]; e.h_out = io.h_out[n]; e.h_out_lo = io.h_out_lo[n];
-        e.W = W;
-        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, 2, e)) return 1;
-        x = io.h_out[n]; x_lo = io.h_out_lo[n];
-    }
+    seg[(*n)++] = GemmSeg{io.x, W, io.x_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, W};
+    return 0;
+}
+
+int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) {
+    const int W = m->W, d = m->d, D = m->D, R = io.R;
     const int top = d - 1;
-    {   // wq = h_prev . W_a + b_UW   (attention.py:539)
+    if (!io.wq_ready) {   // wq = h_prev . W_a + b_UW   (attention.py:539)
         GemmSeg s = {io.h_in[top], W, io.h_in_lo[top], m->Wa.hi, m->Wa.ld, m->Wa.lo, W};
         StoreEpi e{io.wq, W, nullptr, m->b_UW, 0};
         if (gemm_store(m, st, R, io.r_dev, W, &s, 1, e)) return 1;
@@ -345,19 +346,55 @@ int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) 
     a.align_log = io.align_log;
     a.R = R; a.r_dev = io.r_dev; a.L = ws.B; a.t_max = ws.T; a.W = W; a.D = D;
     a.window = m->cfg.window_width; a.inclusive = 1;
-    if (launch_attention(st, a)) return 1;
+    // The attention of this step depends on the previous step only (query, alignment); with lower
+    // cells in between it runs on the side stream, its HBM traffic under their tensor work.
+    const bool overlap = d >= 2 && m->side != nullptr;
+    if (overlap) COR_CUDA(cudaEventRecord(m->ev_fork, st));
+    else if (launch_attention(st, a)) return 1;
+
+    GemmSeg xs[1]; int nx = 0;
+    if (x_segment(m, io, m->dec[0], st, xs, &nx)) return 1;
+    const float* x = nullptr; const float* x_lo = nullptr;
+    for (int n = 0; n + 1 < d; ++n) {
+        const LstmW& lw = m->dec[n];
+        GemmSeg segs[2]; int ns = 0;
+        if (n == 0) { if (nx) segs[ns++] = xs[0]; }
+        else segs[ns++] = GemmSeg{x, W, x_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, W};
+        segs[ns++] = GemmSeg{io.h_in[n], W, io.h_in_lo[n], lw.R.hi, lw.R.ld, lw.R.lo, W};
+        LstmEpi e{};
+        e.bias = lw.bias; e.c_in = io.c_in[n]; e.c_out = io.c_out[n];
+        e.h_prev = io.h_in[n]; e.h_prev_lo = io.h_in_lo[n]; e.h_out = io.h_out[n]; e.h_out_lo = io.h_out_lo[n];
+        e.W = W;
+        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, ns, e)) return 1;
+        x = io.h_out[n]; x_lo = io.h_out_lo[n];
+        if (n == 0 && overlap) {
+            // submitted behind the persistent GEMM, so that its CTAs take their SMs first and the
+            // attention blocks fill the registers and warp slots left beside them
+            COR_CUDA(cudaStreamWaitEvent(m->side, m->ev_fork, 0));
+            if (launch_attention(m->side, a)) return 1;
+            COR_CUDA(cudaEventRecord(m->ev_join, m->side));
+        }
+    }
+    if (overlap) COR_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
     const LstmW& tw = m->dec[top];
+    GemmSeg tsegs[3]; int nt = 0;          // input segment(s) of the top cell, shared with the LM evaluation
+    if (d == 1) { if (nx) tsegs[nt++] = xs[0]; }
+    else tsegs[nt++] = GemmSeg{x, W, x_lo, tw.Kx.hi, tw.Kx.ld, tw.Kx.lo, W};
+    const int n_in = nt;
     {
-        GemmSeg segs[3] = {{x, W, x_lo, tw.Kx.hi, tw.Kx.ld, tw.Kx.lo, W},
-                           {io.ctx, D, io.ctx_lo, tw.Kc.hi, tw.Kc.ld, tw.Kc.lo, D},
-                           {io.h_in[top], W, io.h_in_lo[top], tw.R.hi, tw.R.ld, tw.R.lo, W}};
+        tsegs[nt++] = GemmSeg{io.ctx, D, io.ctx_lo, tw.Kc.hi, tw.Kc.ld, tw.Kc.lo, D};
+        tsegs[nt++] = GemmSeg{io.h_in[top], W, io.h_in_lo[top], tw.R.hi, tw.R.ld, tw.R.lo, W};
         LstmEpi e{};
         e.bias = tw.bias; e.c_in = io.c_in[top]; e.c_out = io.c_out[top];
         e.h_prev = io.h_in[top]; e.h_prev_lo = io.h_in_lo[top]; e.h_out = io.h_out[top]; e.h_out_lo = io.h_out_lo[top];
         e.W = W;
-        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, 3, e)) return 1;
+        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, tsegs, nt, e)) return 1;
     }
-    {   // logits = h . E^T  (tied output projection, seq2seq.py:379)
+    if (io.wq_next) {   // logits = h . E^T (tied output projection, seq2seq.py:379) | next query = h . W_a + b_UW
+        GemmSeg s = {io.h_out[top], W, io.h_out_lo[top], m->EWa.hi, m->EWa.ld, m->EWa.lo, W};
+        StoreEpi e{io.logits, m->Vp, nullptr, nullptr, 0, m->Vp, io.wq_next, W, m->b_UW};
+        if (gemm_store(m, st, R, io.r_dev, m->Vp + W, &s, 1, e)) return 1;
+    } else {
         GemmSeg s = {io.h_out[top], W, io.h_out_lo[top], m->E.hi, m->E.ld, m->E.lo, W};
         StoreEpi e{io.logits, m->Vp, nullptr, nullptr, 0};
         if (gemm_store(m, st, R, io.r_dev, m->Vp, &s, 1, e)) return 1;
@@ -365,13 +402,14 @@ int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) 
     if (m->cfg.lm_predict && io.logits_lm) {
         // second evaluation of the top cell with attended == u == 0: context is exactly zero
         // (seq2seq.py:464-469); its states are discarded.
-        GemmSeg segs[2] = {{x, W, x_lo, tw.Kx.hi, tw.Kx.ld, tw.Kx.lo, W},
-                           {io.h_in[top], W, io.h_in_lo[top], tw.R.hi, tw.R.ld, tw.R.lo, W}};
+        GemmSeg segs[2]; int ns = 0;
+        if (n_in) segs[ns++] = tsegs[0];
+        segs[ns++] = GemmSeg{io.h_in[top], W, io.h_in_lo[top], tw.R.hi, tw.R.ld, tw.R.lo, W};
         LstmEpi e{};
         e.bias = tw.bias; e.c_in = io.c_in[top]; e.c_out = io.c_lm;
         e.h_prev = io.h_in[top]; e.h_prev_lo = io.h_in_lo[top]; e.h_out = io.h_lm; e.h_out_lo = io.h_lm_lo;
         e.W = W;
-        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, 2, e)) return 1;
+        if (gemm_lstm(m, st, R, io.r_dev, 4 * W, segs, ns, e)) return 1;
         GemmSeg s = {io.h_lm, W, io.h_lm_lo, m->E.hi, m->E.ld, m->E.lo, W};
         StoreEpi e2{io.logits_lm, m->Vp, nullptr, nullptr, 0};
         if (gemm_store(m, st, R, io.r_dev, m->Vp, &s, 1, e2)) return 1;
@@ -417,6 +455,7 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         io.a_in = ws.a[cur]; io.a_out = ws.a[cur ^ 1];
         io.align_log = ws.o_align ? ws.o_align + (size_t)s * B * T : nullptr;
         io.wq = ws.wq; io.ctx = ws.ctx; io.ctx_lo = ws.ctx_lo; io.logits = ws.logits;
+        io.wq_ready = (s > 0); io.wq_next = ws.wq;
         if (decoder_core(m, ws, io, st)) return 1;
         GreedyArgs g{};
         g.logits = ws.logits; g.p = ws.p; g.p_lo = ws.p_lo; g.row_T = ws.row_T; g.live = ws.live;
@@ -566,6 +605,37 @@ int cor_model_finalize(cor_model* m) {
         if (upload_vec(m, (*w)[1].data, &m->v_a) || upload_vec(m, (*w)[2].data, &m->b_UW)) return 1;
         m->b_v = (*w)[3].data[0];
         if (build_lstm(m, &(*w)[4], W + D, W, &m->dec[d - 1], name + " cell")) return 1;
+        // E rows then W_a rows (both K-major over W): logits and the next step's query from one launch
+        const std::vector<float> wa = transpose_rows((*w)[0], 0, W);
+        const HostWeight& E = m->host["char_input_projection"][0];
+        std::vector<float> ewa((size_t)(Vp + W) * W, 0.f);
+        std::copy(E.data.begin(), E.data.begin() + (size_t)V * W, ewa.begin());
+        std::copy(wa.begin(), wa.end(), ewa.begin() + (size_t)Vp * W);
+        if (upload_mat(m, ewa, Vp + W, W, &m->EWa)) return 1;
+    }
+    m->fuse_pe = 3 * Vp <= 4 * W;
+    if (m->fuse_pe) {
+        // PE[n][v] = sum_u Kx[n][u] * E[v][u] for the first decoder cell (fp64 accumulation, one rounding)
+        const HostWeight& E = m->host["char_input_projection"][0];
+        const std::string name = "decoder_lstm_1";
+        const HostWeight& K = m->host[name][d == 1 ? 4 : 0];
+        const std::vector<float> kx = lstm_rows(K, W, 0, W);      // [4W][W]
+        std::vector<float> pe((size_t)4 * W * Vp, 0.f);
+        for (int n = 0; n < 4 * W; ++n) {
+            const float* kr = &kx[(size_t)n * W];
+            for (int v = 0; v < V; ++v) {
+                const float* er = &E.data[(size_t)v * W];
+                double s = 0.0;
+                for (int u = 0; u < W; ++u) s += (double)kr[u] * (double)er[u];
+                pe[(size_t)n * Vp + v] = (float)s;
+            }
+        }
+        if (upload_mat(m, pe, 4 * W, Vp, &m->PE)) return 1;
+    }
+    if (!m->side && !getenv("COR_NO_OVERLAP")) {     // (debug switch: attention on the main stream)
+        COR_CUDA(cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking));
+        COR_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
+        COR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
     }
     m->host.clear();
     m->finalized = true;
@@ -575,6 +645,9 @@ int cor_model_finalize(cor_model* m) {
 void cor_model_destroy(cor_model* m) {
     if (!m) return;
     cudaSetDevice(m->device);
+    if (m->side) { cudaStreamSynchronize(m->side); cudaStreamDestroy(m->side); }
+    if (m->ev_fork) cudaEventDestroy(m->ev_fork);
+    if (m->ev_join) cudaEventDestroy(m->ev_join);
     for (void* p : m->allocs) cudaFree(p);
     delete m;
 }

@@ -59,6 +59,8 @@ struct BeamDev {
     int32_t* counters;                     // [0] rows this iteration (r_dev), [1] active lines
     // per record g = line*quota_x + xid
     float *rec_p, *rec_h, *rec_c, *rec_a;  // [G][Vp], [G][d][W], [G][d][W], [G][T]
+    float* rec_wq;                         // [G][W] attention query of the children (h_top . W_a + b)
+    float* wq;                             // [Rcap][W] query rows of the current iteration
     double* rec_cur; uint8_t* rec_amax1; int32_t *rec_pos, *rec_len, *rec_nacc; uint32_t* rec_parent;
     int32_t* ch_v; float* ch_p; double* ch_cum; uint8_t* ch_rej;   // [G][KMAX]
     // per row of the current iteration
@@ -248,6 +250,8 @@ __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) 
         }
         const float* ra = b.rec_a + g * b.T;
         for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = ra[j];
+        const float* rq = b.rec_wq + g * b.W;
+        for (int u = threadIdx.x; u < b.W; u += blockDim.x) b.wq[(size_t)row * b.W + u] = rq[u];
         for (int n = 0; n < b.d; ++n) {
             const float* rh = b.rec_h + (g * b.d + n) * b.W;
             const float* rc = b.rec_c + (g * b.d + n) * b.W;
@@ -349,6 +353,8 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
         for (int v = tid; v < b.Vp; v += 128) rp[v] = sp[v];
         float* ra = b.rec_a + g * b.T;
         for (int j = tid; j < b.T; j += 128) ra[j] = al[j];
+        float* rq = b.rec_wq + g * b.W;
+        for (int u = tid; u < b.W; u += 128) rq[u] = b.wq[(size_t)row * b.W + u];
         for (int n = 0; n < b.d; ++n) {
             float* rh = b.rec_h + (g * b.d + n) * b.W;
             float* rc = b.rec_c + (g * b.d + n) * b.W;
@@ -579,7 +585,7 @@ size_t row_bytes(const cor_model* m, int T) {
     return b + 64;
 }
 size_t rec_bytes(const cor_model* m, int T) {
-    return (size_t)m->Vp * 4 + 2 * (size_t)m->d * m->W * 4 + (size_t)T * 4 + 8 + 1 + 4 * 4 + KMAX * (4 + 4 + 8 + 1) + 16;
+    return (size_t)m->Vp * 4 + (2 * (size_t)m->d + 1) * m->W * 4 + (size_t)T * 4 + 8 + 1 + 4 * 4 + KMAX * (4 + 4 + 8 + 1) + 16;
 }
 
 int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, int quota_x, int Rcap, int want_align,
@@ -611,6 +617,7 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     const size_t G = (size_t)L * quota_x;
     b->rec_p = c.take<float>(G * Vp); b->rec_h = c.take<float>(G * d * W); b->rec_c = c.take<float>(G * d * W);
     b->rec_a = c.take<float>(G * T);
+    b->rec_wq = c.take<float>(G * W);
     b->rec_cur = c.take<double>(G); b->rec_amax1 = c.take<uint8_t>(G); b->rec_pos = c.take<int32_t>(G);
     b->rec_len = c.take<int32_t>(G); b->rec_nacc = c.take<int32_t>(G); b->rec_parent = c.take<uint32_t>(G);
     b->ch_v = c.take<int32_t>(G * KMAX); b->ch_p = c.take<float>(G * KMAX); b->ch_cum = c.take<double>(G * KMAX);
@@ -625,6 +632,7 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     io->p = b->p; io->p_lo = b->p_lo;
     io->x = c.take<float>(R * W); io->x_lo = sp ? c.take<float>(R * W) : nullptr;
     io->wq = c.take<float>(R * W);
+    b->wq = io->wq; io->wq_next = io->wq;
     io->ctx = c.take<float>(R * D); io->ctx_lo = sp ? c.take<float>(R * D) : nullptr;
     io->logits = b->logits;
     io->a_in = b->a_in; io->a_out = b->a_out;
@@ -721,6 +729,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         beam_gather_kernel<<<row_grid, 128, 0, st>>>(b, split);
         g_launches += 2;
         COR_CUDA(cudaGetLastError());
+        io.wq_ready = it > 0;     // iteration 0 expands the roots: their query comes from the encoder state
         if (decoder_core(m, ws, io, st)) return 1;
         beam_expand_kernel<<<row_grid, 128, expand_smem, st>>>(b, split);
         beam_push_kernel<<<L, 256, push_smem, st>>>(b);

@@ -49,6 +49,11 @@ struct StoreEpi {
     float* C_lo;               // if set: C gets the TF32-hi part and C_lo the residual
     const float* bias;         // [N] or nullptr
     int act;                   // 0 none, 1 tanh
+    // optional second destination: columns >= n_split (a multiple of 32) go to C2[row][col - n_split]
+    // as plain fp32 with bias2 (two products of the same A in one launch, e.g. logits | attention query)
+    int n_split;               // 0 = off
+    float* C2; int ldc2;
+    const float* bias2;        // [N - n_split] or nullptr
 };
 
 // LSTM-cell epilogue.  N = 4W with columns interleaved n = 4*unit + gate (i,f,c~,o).

@@ -45,7 +45,15 @@ __device__ __forceinline__ float4 load_split4(const float* hi_p, const float* lo
     return make_float4(h0.x + l0.x, h0.y + l0.y, h1.x + l1.x, h1.y + l1.y);
 }
 
-__device__ __forceinline__ float sigmoidf_exact(float x) { return 1.0f / (1.0f + expf(-x)); }
+// Activation functions.  ex2.approx (2^-22 relative) and the fast reciprocal give an absolute error
+// below 3e-7 on outputs in [-1, 1] — the same grade as expf/tanhf (2 ulp near 1) and three orders
+// below the 1e-4 parity budget — at a fifth of the instructions: the LSTM epilogue evaluates five
+// of these per unit and has to hide under the MMA main loop of the next tile.
+__device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanhf_fast(float x) {
+    const float e = __expf(2.0f * x);                   // inf for x > 44: 2/inf = 0, result 1
+    return 1.0f - __fdividef(2.0f, e + 1.0f);
+}
 
 // One LSTM unit of one row.  z[0..3] = pre-activations i,f,c~,o WITHOUT bias.
 // Keras LSTMCell, implementation 2.  Returns the new h.
@@ -55,13 +63,13 @@ __device__ __forceinline__ float lstm_unit(const LstmEpi& e, int row, int unit, 
     const float zf = z[1] + e.bias[4 * unit + 1];
     const float zg = z[2] + e.bias[4 * unit + 2];
     const float zo = z[3] + e.bias[4 * unit + 3];
-    const float i = sigmoidf_exact(zi);
-    const float f = sigmoidf_exact(zf);
-    const float g = tanhf(zg);
-    const float o = sigmoidf_exact(zo);
+    const float i = sigmoidf_fast(zi);
+    const float f = sigmoidf_fast(zf);
+    const float g = tanhf_fast(zg);
+    const float o = sigmoidf_fast(zo);
     const float c = f * e.c_in[so] + i * g;
     e.c_out[so] = c;
-    return o * tanhf(c);
+    return o * tanhf_fast(c);
 }
 
 // Write the new h of `n` consecutive units [unit0, unit0+n) of one row (n even when cross_sum).
@@ -109,7 +117,26 @@ __device__ __forceinline__ void lstm_row_units(const LstmEpi& e, int row, int un
     }
 }
 
+// 4 consecutive elements (off a multiple of 4)
+__device__ __forceinline__ void store_split4(float* hi_p, float* lo_p, size_t off, float4 v) {
+    if (!lo_p) { *reinterpret_cast<float4*>(hi_p + off) = v; return; }
+    __half h[4], l[4];
+    f16_split(v.x, h[0], l[0]); f16_split(v.y, h[1], l[1]); f16_split(v.z, h[2], l[2]); f16_split(v.w, h[3], l[3]);
+    uint2 ph, pl;
+    ph.x = (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16);
+    ph.y = (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16);
+    pl.x = (uint32_t)__half_as_ushort(l[0]) | ((uint32_t)__half_as_ushort(l[1]) << 16);
+    pl.y = (uint32_t)__half_as_ushort(l[2]) | ((uint32_t)__half_as_ushort(l[3]) << 16);
+    *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(hi_p) + off) = ph;
+    *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(lo_p) + off) = pl;
+}
+
 __device__ __forceinline__ void store_elem(const StoreEpi& e, int row, int col, float acc) {
+    if (e.n_split && col >= e.n_split) {
+        const int c2 = col - e.n_split;
+        e.C2[(size_t)row * e.ldc2 + c2] = acc + (e.bias2 ? e.bias2[c2] : 0.0f);
+        return;
+    }
     float v = acc + (e.bias ? e.bias[col] : 0.0f);
     if (e.act == 1) v = tanhf(v);
     store_split(e.C, e.C_lo, (size_t)row * e.ldc + col, v);

@@ -159,12 +159,12 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, int row, int unit0, 
         for (int q = 0; q < 8; ++q) ld4(e.bias, (size_t)4 * unit0 + 4 * q, b + 4 * q);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float i = sigmoidf_exact(__uint_as_float(z[4 * k + 0]) + b[4 * k + 0]);
-            const float f = sigmoidf_exact(__uint_as_float(z[4 * k + 1]) + b[4 * k + 1]);
-            const float g = tanhf(__uint_as_float(z[4 * k + 2]) + b[4 * k + 2]);
-            const float o = sigmoidf_exact(__uint_as_float(z[4 * k + 3]) + b[4 * k + 3]);
+            const float i = sigmoidf_fast(__uint_as_float(z[4 * k + 0]) + b[4 * k + 0]);
+            const float f = sigmoidf_fast(__uint_as_float(z[4 * k + 1]) + b[4 * k + 1]);
+            const float g = tanhf_fast(__uint_as_float(z[4 * k + 2]) + b[4 * k + 2]);
+            const float o = sigmoidf_fast(__uint_as_float(z[4 * k + 3]) + b[4 * k + 3]);
             c[k] = f * c[k] + i * g;
-            h[k] = o * tanhf(c[k]);
+            h[k] = o * tanhf_fast(c[k]);
         }
         st4(e.c_out, so, c); st4(e.c_out, so + 4, c + 4);
     } else {
@@ -202,7 +202,16 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, int row, int unit0, 
 }
 
 __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0, int N, const uint32_t (&z)[32]) {
-    if (col0 + 32 <= N && (e.ldc & 3) == 0) {
+    if (e.n_split && col0 >= e.n_split && col0 + 32 <= N && (e.ldc2 & 3) == 0) {
+        const int c2 = col0 - e.n_split;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            float v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = __uint_as_float(z[4 * q + k]) + (e.bias2 ? e.bias2[c2 + 4 * q + k] : 0.0f);
+            st4(e.C2, (size_t)row * e.ldc2 + c2 + 4 * q, v);
+        }
+    } else if (col0 + 32 <= N && (e.ldc & 3) == 0 && !(e.n_split && col0 >= e.n_split)) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             float v[8];

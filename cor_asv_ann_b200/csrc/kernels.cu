@@ -61,9 +61,15 @@ __global__ void live_rows_kernel(const int32_t* __restrict__ idx, const float* _
 // ---------------------------------------------------------------- K5c-e: attention
 // attention.py:526-575 restricted to the window: positions outside |centre-j|<=w have e*0 = 0
 // exactly, so evaluating only the window gives the same sums.  One warp per hypothesis row.
-__global__ void __launch_bounds__(128) attention_kernel(AttnArgs a) {
+// HBM-bound (per row: <=13 positions x (W + D) x 4 B, each read once): the loads of all window
+// positions of a 128-column chunk are issued together, the energies stay in registers (static
+// indices only) and the normalised weights go through 16 floats of shared memory per warp.
+constexpr int MAXWIN = 13;       // 2*window_width+1 with window_width <= 6
+__global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
+    __shared__ float s_w[4][16];
     const int R = a.r_dev ? min(*a.r_dev, a.R) : a.R;
-    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int wid = threadIdx.x >> 5;
+    const int row = blockIdx.x * (blockDim.x >> 5) + wid;
     if (row >= R) return;
     const int lane = threadIdx.x & 31;
     const int line = a.row_line ? a.row_line[row] : row;
@@ -73,58 +79,80 @@ __global__ void __launch_bounds__(128) attention_kernel(AttnArgs a) {
     float part = 0.f;
     for (int j = lane; j < T; j += 32) part = fmaf(ap[j], (float)j, part);
     const float centre = warp_sum(part) + 1.0f;
-    // window bounds: all j with |centre - j| <= w (inclusive) or < w
-    int j_lo = max(0, (int)ceilf(centre - (float)a.window) - 1);
-    int j_hi = min(T - 1, (int)floorf(centre + (float)a.window) + 1);
-    float e[16];      // window_width <= 6 -> at most 2*6+3 candidate positions
-    int nj = 0, jj[16];
-    const float* wq = a.wq + (size_t)row * a.W;
-    for (int j = j_lo; j <= j_hi && nj < 16; ++j) {
+    // window: all j with |centre - j| <= w (inclusive) or < w — a contiguous range [j0, j0+nj)
+    const int j_lo = max(0, (int)ceilf(centre - (float)a.window) - 1);
+    const int j_hi = min(T - 1, (int)floorf(centre + (float)a.window) + 1);
+    int j0 = 0, nj = 0;
+    for (int j = j_lo; j <= j_hi && nj < MAXWIN; ++j) {
         const float dist = fabsf(centre - (float)j);
         const bool keep = a.inclusive ? (dist <= (float)a.window) : (dist < (float)a.window);
-        if (!keep) continue;
-        const float* up = a.u + ((size_t)j * a.L + line) * a.W;
-        float s = 0.f;
-        for (int k = lane * 4; k < a.W; k += 128) {
-            const float4 w4 = *reinterpret_cast<const float4*>(wq + k);
-            const float4 u4 = *reinterpret_cast<const float4*>(up + k);
-            const float4 v4 = *reinterpret_cast<const float4*>(a.v_a + k);
-            s = fmaf(tanhf(w4.x + u4.x), v4.x, s);
-            s = fmaf(tanhf(w4.y + u4.y), v4.y, s);
-            s = fmaf(tanhf(w4.z + u4.z), v4.z, s);
-            s = fmaf(tanhf(w4.w + u4.w), v4.w, s);
+        if (keep) { if (nj == 0) j0 = j; ++nj; }
+    }
+    const float* wq = a.wq + (size_t)row * a.W;
+    const size_t ustride = (size_t)a.L * a.W;
+    const float* ub = a.u + ((size_t)j0 * a.L + line) * a.W;
+    float s[MAXWIN];
+#pragma unroll
+    for (int q = 0; q < MAXWIN; ++q) s[q] = 0.f;
+    for (int k = lane * 4; k < a.W; k += 128) {
+        const float4 w4 = *reinterpret_cast<const float4*>(wq + k);
+        const float4 v4 = *reinterpret_cast<const float4*>(a.v_a + k);
+        // loads of four positions in flight per lane; small enough for 6 blocks (24 warps) per SM
+#pragma unroll
+        for (int q0 = 0; q0 < MAXWIN; q0 += 4) {
+            float4 u4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q0 + q < MAXWIN && q0 + q < nj) u4[q] = *reinterpret_cast<const float4*>(ub + (q0 + q) * ustride + k);
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q0 + q < MAXWIN && q0 + q < nj) {
+                    float t = s[q0 + q];
+                    t = fmaf(tanhf_fast(w4.x + u4[q].x), v4.x, t);
+                    t = fmaf(tanhf_fast(w4.y + u4[q].y), v4.y, t);
+                    t = fmaf(tanhf_fast(w4.z + u4[q].z), v4.z, t);
+                    t = fmaf(tanhf_fast(w4.w + u4[q].w), v4.w, t);
+                    s[q0 + q] = t;
+                }
         }
-        s = warp_sum(s);
-        e[nj] = expf(s + a.b_v);
-        jj[nj] = j;
-        ++nj;
     }
     float esum = 0.f;
-    for (int q = 0; q < nj; ++q) esum += e[q];
+#pragma unroll
+    for (int q = 0; q < MAXWIN; ++q)
+        if (q < nj) { s[q] = expf(warp_sum(s[q]) + a.b_v); esum += s[q]; }
+#pragma unroll
+    for (int q = 0; q < MAXWIN; ++q)
+        if (q < nj && lane == 0) s_w[wid][q] = s[q] / esum;
+    __syncwarp();
     // alignment row: zero everywhere, a_j = e_j / sum in the window
     float* ao = a.a_out + (size_t)row * a.t_max;
     float* al = a.align_log ? a.align_log + (size_t)row * a.t_max : nullptr;
     for (int j = lane; j < a.t_max; j += 32) {
-        float v = 0.f;
-        for (int q = 0; q < nj; ++q) if (jj[q] == j) v = e[q] / esum;
+        const int q = j - j0;
+        const float v = (q >= 0 && q < nj) ? s_w[wid][q] : 0.f;
         ao[j] = v;
         if (al) al[j] = v;
     }
     // context = sum_j a_j * enc_j
+    const size_t estride = (size_t)a.L * a.D;
+    const size_t eb = ((size_t)j0 * a.L + line) * a.D;
     for (int k = lane * 4; k < a.D; k += 128) {
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int q = 0; q < nj; ++q) {
-            const float w = e[q] / esum;
-            const size_t off = ((size_t)jj[q] * a.L + line) * a.D + k;
-            const float4 x = load_split4(a.enc, a.enc_lo, off);
-            c.x = fmaf(w, x.x, c.x); c.y = fmaf(w, x.y, c.y);
-            c.z = fmaf(w, x.z, c.z); c.w = fmaf(w, x.w, c.w);
+#pragma unroll
+        for (int q0 = 0; q0 < MAXWIN; q0 += 4) {
+            float4 x4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q0 + q < MAXWIN && q0 + q < nj) x4[q] = load_split4(a.enc, a.enc_lo, eb + (q0 + q) * estride + k);
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q0 + q < MAXWIN && q0 + q < nj) {
+                    const float w = s_w[wid][q0 + q];
+                    c.x = fmaf(w, x4[q].x, c.x); c.y = fmaf(w, x4[q].y, c.y);
+                    c.z = fmaf(w, x4[q].z, c.z); c.w = fmaf(w, x4[q].w, c.w);
+                }
         }
-        const size_t o = (size_t)row * a.D + k;
-        store_split(a.ctx, a.ctx_lo, o + 0, c.x);
-        store_split(a.ctx, a.ctx_lo, o + 1, c.y);
-        store_split(a.ctx, a.ctx_lo, o + 2, c.z);
-        store_split(a.ctx, a.ctx_lo, o + 3, c.w);
+        store_split4(a.ctx, a.ctx_lo, (size_t)row * a.D + k, c);
     }
 }
 

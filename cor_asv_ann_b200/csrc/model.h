@@ -44,6 +44,11 @@ struct cor_model {
     cor::Mat U;               // [W][D]
     std::vector<cor::LstmW> dec;   // d entries; the last one is the attention cell's LSTMCell
     cor::Mat Wa;              // [W][W]
+    cor::Mat EWa;             // [Vp+W][W]  rows of E then rows of W_a: logits | next query in one launch
+    cor::Mat PE;              // [4W][Vp]   (E . Kx) of the first decoder cell: z_x = p . PE without the round trip through x
+    bool fuse_pe = false;     // PE exists (3*Vp <= 4*W: the fused product is the cheaper one)
+    cudaStream_t side = nullptr;          // attention runs here, beside the lower-cell GEMMs
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     float* b_UW = nullptr;    // [W]
     float* v_a = nullptr;     // [W]
     float b_v = 0.f;
@@ -89,6 +94,8 @@ struct StepIO {
     const float* c_in[8] = {}; float* c_out[8] = {};
     const float* a_in = nullptr; float* a_out = nullptr; float* align_log = nullptr;
     float *wq = nullptr, *ctx = nullptr, *ctx_lo = nullptr, *logits = nullptr;
+    bool wq_ready = false;                   // wq already holds h_in[top].W_a + b (written by the previous step)
+    float* wq_next = nullptr;                // if set: the logits launch also writes h_out[top].W_a + b here
     float *h_lm = nullptr, *h_lm_lo = nullptr, *c_lm = nullptr, *logits_lm = nullptr;
 };
 // One decoder timestep up to the logits (seq2seq.py:416-470); enc_out/u come from `ws`.
