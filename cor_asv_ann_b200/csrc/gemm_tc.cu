@@ -18,6 +18,8 @@
 #include "engine.h"
 #include "epilogue.cuh"
 #include <cuda.h>
+#include <stdlib.h>
+#include <algorithm>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -26,12 +28,22 @@ namespace cor {
 
 namespace {
 
-constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 2;
+constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
 constexpr int ELT = 2;                          // bytes per operand element (fp16)
 constexpr int A_TILE = BM * BK * ELT;          // 16 KB
-constexpr int B_TILE = BN * BK * ELT;          // 32 KB
-constexpr int STAGE_BYTES = 2 * A_TILE + 2 * B_TILE;   // 96 KB
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+// NCTA = 1: one CTA per 128 x 256 tile, 2 stages of {A_hi, A_lo, B_hi, B_lo} = 96 KB.
+// NCTA = 2: a CTA pair (cta_group::2) per 256 x 256 tile; each CTA stages its own 128 rows of A and
+// HALF of the B tile (128 of the 256 columns), 64 KB per stage, 3 stages.  The pair reads 128 KB from
+// L2 per k-block for twice the math of the single CTA's 96 KB: the kernel sits on the L2->SM path
+// (LTS cap ~6.3 KB/clk chip-wide), so this is what lifts the tensor-pipe duty.
+template <int NCTA> struct Geo {
+    static constexpr int B_ROWS = BN / NCTA;
+    static constexpr int B_TILE = B_ROWS * BK * ELT;
+    static constexpr int STAGE_BYTES = 2 * A_TILE + 2 * B_TILE;
+    static constexpr int STAGES = NCTA == 1 ? 2 : 3;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * NCTA) >> 4) << 24);
+};
 constexpr int NTHREADS = 256;
 constexpr int TMEM_COLS = 512;
 
@@ -79,6 +91,29 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// pair variant: executed by both CTAs, the bytes are accounted on the LEADER's barrier (`bar` is a
+// shared::cluster address obtained with mapa)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -92,6 +127,20 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint6
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on the barrier at this smem offset in BOTH CTAs of the pair when the pair's MMAs retire
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -116,7 +165,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
 }
 // kind::f16, D = f32 (c_format 1 at [4,6)), A/B = f16 (format 0 at [7,10) / [10,13)), both K-major,
 // N at [17,23) >> 3, M at [24,29) >> 4
-constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// (Geo<NCTA>::IDESC; M = 256 for the pair)
 
 // ------------------------------------------------------------------ vectorised LSTM epilogue (8 units of one row)
 __device__ __forceinline__ void st4(float* p, size_t off, const float* v) {
@@ -230,12 +279,16 @@ __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0
 }
 
 // ------------------------------------------------------------------ the kernel
-template <int EPI, typename Epi>
+template <int EPI, int NCTA, typename Epi>
 __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams p, const Epi epi) {
+    using G = Geo<NCTA>;
+    constexpr int STAGES = G::STAGES, STAGE_BYTES = G::STAGE_BYTES, B_TILE = G::B_TILE;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // SWIZZLE_128B wants 1024-byte alignment
     const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
-    // barriers (8 bytes each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base slot
+    // barriers (8 bytes each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base slot.
+    // Pair: full[] and tmem_empty[] are used in the leader CTA only (both CTAs' loads and both CTAs'
+    // epilogues signal there); empty[] and tmem_full[] exist in both and are hit by multicast commits.
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -245,8 +298,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + STAGES * STAGE_BYTES + 8 * (2 * STAGES + 4));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = NCTA == 2 ? cluster_rank() : 0u;
+    const bool leader = rank == 0;
+    const int unit = blockIdx.x / NCTA, n_units = gridDim.x / NCTA;     // a unit = one CTA or one CTA pair
     const int M = p.m_dev ? min(*p.m_dev, p.M) : p.M;
-    const int tiles_m = (M + BM - 1) / BM;
+    const int tiles_m = (M + BM * NCTA - 1) / (BM * NCTA);
     const int num_tiles = tiles_m * p.tiles_n;
     int kb_total = 0;
     for (int s = 0; s < p.nseg; ++s) kb_total += p.kblocks[s];
@@ -259,45 +315,60 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 128); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4 * NCTA); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(TMEM_COLS) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (NCTA == 1) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (one per CTA) =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+            for (int tile = unit; tile < num_tiles; tile += n_units) {
+                const int m0 = (tile / p.tiles_n) * (BM * NCTA) + (int)rank * BM;
+                const int n0 = (tile % p.tiles_n) * BN + (int)rank * G::B_ROWS;
                 for (int s = 0; s < p.nseg; ++s) {
                     for (int kb = 0; kb < p.kblocks[s]; ++kb) {
                         mbar_wait(empty_bar(stage), phase ^ 1);
                         const uint32_t sa = smem_base + stage * STAGE_BYTES;
-                        mbar_expect_tx(full_bar(stage), STAGE_BYTES);
-                        tma_load_2d(sa, &p.a_hi[s], kb * BK, m0, full_bar(stage));
-                        tma_load_2d(sa + A_TILE, &p.a_lo[s], kb * BK, m0, full_bar(stage));
-                        tma_load_2d(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, full_bar(stage));
-                        tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
+                        if constexpr (NCTA == 1) {
+                            mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+                            tma_load_2d(sa, &p.a_hi[s], kb * BK, m0, full_bar(stage));
+                            tma_load_2d(sa + A_TILE, &p.a_lo[s], kb * BK, m0, full_bar(stage));
+                            tma_load_2d(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, full_bar(stage));
+                            tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
+                        } else {
+                            if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE_BYTES);    // both CTAs' bytes
+                            const uint32_t fb = map_to_cta(full_bar(stage), 0);
+                            tma_load_2d_pair(sa, &p.a_hi[s], kb * BK, m0, fb);
+                            tma_load_2d_pair(sa + A_TILE, &p.a_lo[s], kb * BK, m0, fb);
+                            tma_load_2d_pair(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, fb);
+                            tma_load_2d_pair(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, fb);
+                        }
                         if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
+        // ===== MMA issuer (the leader CTA's, for the pair) =====
+        if (lane == 0 && leader) {
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                mbar_wait(tempty_bar(acc), acc_phase ^ 1);      // epilogue has drained this accumulator
+            for (int tile = unit; tile < num_tiles; tile += n_units) {
+                mbar_wait(tempty_bar(acc), acc_phase ^ 1);      // epilogue(s) have drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < kb_total; ++kb) {
@@ -306,35 +377,40 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                     const uint32_t sa = smem_base + stage * STAGE_BYTES;
                     const uint64_t a_hi = make_smem_desc(sa), a_lo = make_smem_desc(sa + A_TILE);
                     const uint64_t b_hi = make_smem_desc(sa + 2 * A_TILE), b_lo = make_smem_desc(sa + 2 * A_TILE + B_TILE);
+                    auto mma = [&](uint64_t a, uint64_t b, uint32_t accum) {
+                        if constexpr (NCTA == 1) umma_f16(d_tmem, a, b, G::IDESC, accum);
+                        else umma_f16_pair(d_tmem, a, b, G::IDESC, accum);
+                    };
                     // small terms first: A_lo*B_hi, A_hi*B_lo, then A_hi*B_hi
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
-                        umma_f16(d_tmem, a_lo + adv, b_hi + adv, kIdesc, (kb | k) != 0);
+                        mma(a_lo + adv, b_hi + adv, (kb | k) != 0);
                     }
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
-                        umma_f16(d_tmem, a_hi + adv, b_lo + adv, kIdesc, 1);
+                        mma(a_hi + adv, b_lo + adv, 1);
                     }
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
-                        umma_f16(d_tmem, a_hi + adv, b_hi + adv, kIdesc, 1);
+                        mma(a_hi + adv, b_hi + adv, 1);
                     }
-                    umma_commit(empty_bar(stage));              // frees the smem stage when these MMAs retire
+                    // frees the smem stage (in both CTAs) when these MMAs retire
+                    if constexpr (NCTA == 1) umma_commit(empty_bar(stage)); else umma_commit_pair(empty_bar(stage));
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(tfull_bar(acc));                    // accumulator complete
+                if constexpr (NCTA == 1) umma_commit(tfull_bar(acc)); else umma_commit_pair(tfull_bar(acc));   // accumulator complete
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
     } else if (warp >= 4) {
-        // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 =====
+        // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 of its own CTA =====
         const int wq = warp - 4;
         int acc = 0; uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+        for (int tile = unit; tile < num_tiles; tile += n_units) {
+            const int m0 = (tile / p.tiles_n) * (BM * NCTA) + (int)rank * BM, n0 = (tile % p.tiles_n) * BN;
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             const int row = m0 + wq * 32 + lane;
@@ -351,15 +427,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                 }
             }
             tc_fence_before();
-            mbar_arrive(tempty_bar(acc));
+            __syncwarp();
+            if (lane == 0) {        // one arrival per epilogue warp, on the (leader's) barrier the MMA issuer waits on
+                if constexpr (NCTA == 1) mbar_arrive(tempty_bar(acc));
+                else mbar_arrive_cluster(map_to_cta(tempty_bar(acc), 0));
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
     tc_fence_before();
-    __syncthreads();
+    // pair: neither CTA may leave (or free TMEM) while its peer can still read its smem or signal its barriers
+    if constexpr (NCTA == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+        if constexpr (NCTA == 1)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
     }
 }
 
@@ -370,6 +454,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 EncodeTiledFn g_encode = nullptr;
 int g_tc_state = -1;        // -1 unknown, 0 unavailable, 1 ok
 int g_num_sms = 148;
+int g_max_pairs = 0;        // resident CTA pairs (0: pair kernel unusable)
 std::mutex g_mu;
 std::map<std::tuple<const void*, long long, long long, long long, int>, CUtensorMap> g_maps;
 
@@ -386,8 +471,22 @@ bool init_tc() {
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) return false;
     g_encode = (EncodeTiledFn)fn;
-    if (cudaFuncSetAttribute(gemm_tc_kernel<0, StoreEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) return false;
-    if (cudaFuncSetAttribute(gemm_tc_kernel<1, LstmEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(gemm_tc_kernel<0, 1, StoreEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<1>::SMEM_BYTES) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(gemm_tc_kernel<1, 1, LstmEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<1>::SMEM_BYTES) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(gemm_tc_kernel<0, 2, StoreEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<2>::SMEM_BYTES) != cudaSuccess) return false;
+    if (cudaFuncSetAttribute(gemm_tc_kernel<1, 2, LstmEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<2>::SMEM_BYTES) != cudaSuccess) return false;
+    {   // how many CTA pairs can be resident at once (a GPC with an odd SM count leaves one SM unpaired):
+        // a persistent grid must not exceed it, or the surplus pairs would run as a second wave
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(g_num_sms & ~1); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = Geo<2>::SMEM_BYTES;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, gemm_tc_kernel<1, 2, LstmEpi>, &cfg) == cudaSuccess && nc > 0) g_max_pairs = nc;
+        else { g_max_pairs = 0; (void)cudaGetLastError(); }
+        if (getenv("COR_NO_PAIR")) g_max_pairs = 0;     // debug switch: single-CTA kernel everywhere
+    }
     g_tc_state = 1;
     return true;
 }
@@ -415,7 +514,7 @@ int get_map(const float* ptr, long long rows, long long cols, long long ld, int 
     return 0;
 }
 
-int fill_params(int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, TcParams* p) {
+int fill_params(int ncta, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, TcParams* p) {
     COR_CHECK(nseg >= 1 && nseg <= kMaxSegs, "bad segment count");
     p->nseg = nseg; p->M = M; p->m_dev = m_dev; p->N = N;
     p->tiles_n = (N + BN - 1) / BN;
@@ -425,14 +524,35 @@ int fill_params(int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, T
         COR_CHECK(g.K > 0 && g.K % BK == 0, "K must be a positive multiple of 64");
         p->kblocks[s] = g.K / BK;
         if (get_map(g.A, M, g.K, g.lda, BM, &p->a_hi[s]) || get_map(g.A_lo, M, g.K, g.lda, BM, &p->a_lo[s]) ||
-            get_map(g.B, N, g.K, g.ldb, BN, &p->b_hi[s]) || get_map(g.B_lo, N, g.K, g.ldb, BN, &p->b_lo[s])) return 1;
+            get_map(g.B, N, g.K, g.ldb, BN / ncta, &p->b_hi[s]) || get_map(g.B_lo, N, g.K, g.ldb, BN / ncta, &p->b_lo[s])) return 1;
     }
     return 0;
 }
 
-int grid_for(int M, int N) {
-    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+// The pair kernel pays off once there are enough 256-row tiles to fill the resident pairs; below that
+// the single-CTA kernel has the finer granularity (128-row tiles on 148 CTAs).
+int pick_ncta(int M, int N) {
+    if (g_max_pairs <= 0) return 1;
+    const long long pair_tiles = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
+    return pair_tiles >= g_max_pairs ? 2 : 1;
+}
+int grid_for(int ncta, int M, int N) {
+    const long long tiles = (long long)((M + BM * ncta - 1) / (BM * ncta)) * ((N + BN - 1) / BN);
+    if (ncta == 2) return 2 * (int)std::min<long long>(tiles, g_max_pairs);
     return (int)std::min<long long>(tiles, g_num_sms);
+}
+
+template <int EPI, int NCTA, typename Epi>
+int launch_tc(cudaStream_t st, int M, int N, const TcParams& p, const Epi& epi) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid_for(NCTA, M, N)); cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = Geo<NCTA>::SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = NCTA; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    COR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, NCTA, Epi>, p, epi));
+    ++g_launches;
+    return 0;
 }
 
 }  // namespace
@@ -442,24 +562,20 @@ bool tc_available() { return init_tc(); }
 int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi) {
     if (M <= 0) return 0;
     COR_CHECK(init_tc(), "tcgen05 path unavailable on this device");
+    const int ncta = pick_ncta(M, N);
     TcParams p;
-    if (fill_params(M, m_dev, N, segs, nseg, &p)) return 1;
-    gemm_tc_kernel<0, StoreEpi><<<grid_for(M, N), NTHREADS, SMEM_BYTES, st>>>(p, epi);
-    ++g_launches;
-    COR_CUDA(cudaGetLastError());
-    return 0;
+    if (fill_params(ncta, M, m_dev, N, segs, nseg, &p)) return 1;
+    return ncta == 2 ? launch_tc<0, 2, StoreEpi>(st, M, N, p, epi) : launch_tc<0, 1, StoreEpi>(st, M, N, p, epi);
 }
 
 int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi) {
     if (M <= 0) return 0;
     COR_CHECK(init_tc(), "tcgen05 path unavailable on this device");
     COR_CHECK(N == 4 * epi.W && epi.W % 8 == 0, "LSTM epilogue needs N == 4W with W a multiple of 8");
+    const int ncta = pick_ncta(M, N);
     TcParams p;
-    if (fill_params(M, m_dev, N, segs, nseg, &p)) return 1;
-    gemm_tc_kernel<1, LstmEpi><<<grid_for(M, N), NTHREADS, SMEM_BYTES, st>>>(p, epi);
-    ++g_launches;
-    COR_CUDA(cudaGetLastError());
-    return 0;
+    if (fill_params(ncta, M, m_dev, N, segs, nseg, &p)) return 1;
+    return ncta == 2 ? launch_tc<1, 2, LstmEpi>(st, M, N, p, epi) : launch_tc<1, 1, LstmEpi>(st, M, N, p, epi);
 }
 
 }  // namespace cor

@@ -31,7 +31,9 @@ def test_ffma_gemm(shape):
 
 
 @pytest.mark.parametrize("shape", [(128, 256, 64), (128, 256, 128), (256, 512, 512), (1000, 2048, 1536),
-                                   (77, 128, 64), (333, 96, 192), (16384, 512, 512)])
+                                   (77, 128, 64), (333, 96, 192), (16384, 512, 512),
+                                   # enough 256-row tiles for the CTA-pair kernel (cta_group::2), with M and N tails
+                                   (18999, 2048, 1024), (9473, 768, 192), (40000, 96, 64)])
 def test_tcgen05_3xfp16_gemm(shape):
     """Relative to sum |a||b| the 3-pass fp16 hi/lo result must be fp32-grade (one fp16/TF32 pass is ~5e-4)."""
     err = _run(2, *shape)
