@@ -632,7 +632,7 @@ int cor_model_finalize(cor_model* m) {
         }
         if (upload_mat(m, pe, 4 * W, Vp, &m->PE)) return 1;
     }
-    if (!m->side && !getenv("COR_NO_OVERLAP")) {     // (debug switch: attention on the main stream)
+    if (!m->side && getenv("COR_OVERLAP")) {     // experiment switch: attention beside the lower-cell GEMM (no gain measured: DESIGN.md)
         COR_CUDA(cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking));
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));

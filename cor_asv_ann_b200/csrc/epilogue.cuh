@@ -49,10 +49,12 @@ __device__ __forceinline__ float4 load_split4(const float* hi_p, const float* lo
 // below 3e-7 on outputs in [-1, 1] — the same grade as expf/tanhf (2 ulp near 1) and three orders
 // below the 1e-4 parity budget — at a fifth of the instructions: the LSTM epilogue evaluates five
 // of these per unit and has to hide under the MMA main loop of the next tile.
-__device__ __forceinline__ float sigmoidf_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigmoidf_fast(float x) { return rcp_approx(1.0f + ex2_approx(-1.4426950408889634f * x)); }
 __device__ __forceinline__ float tanhf_fast(float x) {
-    const float e = __expf(2.0f * x);                   // inf for x > 44: 2/inf = 0, result 1
-    return 1.0f - __fdividef(2.0f, e + 1.0f);
+    // 1 - 2/(e^2x + 1); e = inf for large x gives rcp = 0 and the result 1, e = 0 gives -1
+    return fmaf(-2.0f, rcp_approx(ex2_approx(2.8853900817779268f * x) + 1.0f), 1.0f);
 }
 
 // One LSTM unit of one row.  z[0..3] = pre-activations i,f,c~,o WITHOUT bias.

@@ -240,7 +240,7 @@ int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int 
     return 0;
 }
 
-int launch_attention(cudaStream_t st, const AttnArgs& a) {
+int launch_attention_reg(cudaStream_t st, const AttnArgs& a) {
     COR_CHECK(a.window >= 0 && a.window <= 6, "window_width above 6 is not supported");
     COR_CHECK(a.W % 4 == 0 && a.D % 4 == 0, "W and D must be multiples of 4");
     if (a.R <= 0) return 0;
