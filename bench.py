@@ -293,7 +293,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "beam"), choices=["greedy", "beam"])
     ap.add_argument("--lines", type=int, default=int(os.environ.get("COR_BENCH_LINES", "16384")))
-    ap.add_argument("--beam-lines", type=int, default=8192)
+    ap.add_argument("--beam-lines", type=int, default=9472)  # 37 x 256 lines: the GEMM tile count is a whole number of waves on 74 CTA pairs
     ap.add_argument("--beam-budget-gb", type=float, default=72.0)
     ap.add_argument("--gemm-mode", type=int, default=0)
     ap.add_argument("--cpu-lines", type=int, default=None)

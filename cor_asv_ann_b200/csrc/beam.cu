@@ -221,44 +221,53 @@ __global__ void __launch_bounds__(256) beam_rowmap_kernel(BeamDev b) {
 // ------------------------------------------------------------------ gather: decoder-step inputs of every row
 // (seq2seq.py:1423-1429: vstack of node.scores / node.state)
 __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) {
+    // 128-bit accesses throughout: a record is ~12 KB (p, h, c, query) and is read exactly once
     const int R = b.counters[0];
+    const int W4 = b.W >> 2, V4 = b.Vp >> 2;
     for (int row = blockIdx.x; row < R; row += gridDim.x) {
         const int line = b.row_line[row];
         const uint32_t node = b.row_node[row];
         float* p_lo = split ? b.p_lo : nullptr;       // split operands: base pointers + element offsets only
         const size_t po = (size_t)row * b.Vp;
         float* a_in = b.a_in + (size_t)row * b.T;
-        if (node == 0u) {          // root: zero feedback, encoder final states, zero alignment
-            for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) store_split(b.p, p_lo, po + v, 0.f);
+        if (node == 0u) {          // root: zero feedback, encoder final states, zero alignment (query: decoder_core)
+            for (int v = threadIdx.x; v < V4; v += blockDim.x) store_split4(b.p, p_lo, po + 4 * v, make_float4(0.f, 0.f, 0.f, 0.f));
             for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = 0.f;
-            for (int n = 0; n < b.d; ++n)
-                for (int u = threadIdx.x; u < b.W; u += blockDim.x) {
-                    const size_t o = (size_t)row * b.W + u;
-                    store_split(b.h_in[n], split ? b.h_in_lo[n] : nullptr, o, b.st_h[n][(size_t)line * b.W + u]);
-                    b.c_in[n][o] = b.st_c[n][(size_t)line * b.W + u];
+            for (int n = 0; n < b.d; ++n) {
+                const float4* sh = reinterpret_cast<const float4*>(b.st_h[n] + (size_t)line * b.W);
+                const float4* sc = reinterpret_cast<const float4*>(b.st_c[n] + (size_t)line * b.W);
+                float4* ci = reinterpret_cast<float4*>(b.c_in[n] + (size_t)row * b.W);
+                for (int u = threadIdx.x; u < W4; u += blockDim.x) {
+                    store_split4(b.h_in[n], split ? b.h_in_lo[n] : nullptr, (size_t)row * b.W + 4 * u, sh[u]);
+                    ci[u] = sc[u];
                 }
+            }
             continue;
         }
         const int k = (int)((node - 1u) % KMAX);
         const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
-        const float* rp = b.rec_p + g * b.Vp;
+        const float4* rp = reinterpret_cast<const float4*>(b.rec_p + g * b.Vp);
         const int32_t* acc = b.ch_v + g * KMAX;
-        for (int v = threadIdx.x; v < b.Vp; v += blockDim.x) {
-            float x = rp[v];
-            for (int q = 0; q < k; ++q) if (acc[q] == v) x = 0.f;     // better siblings were zeroed before the copy
-            store_split(b.p, p_lo, po + v, x);
+        for (int v = threadIdx.x; v < V4; v += blockDim.x) {
+            float4 x = rp[v];
+            for (int q = 0; q < k; ++q) {                // better siblings were zeroed before the copy
+                const int z = acc[q] - 4 * v;
+                if (z == 0) x.x = 0.f; else if (z == 1) x.y = 0.f; else if (z == 2) x.z = 0.f; else if (z == 3) x.w = 0.f;
+            }
+            store_split4(b.p, p_lo, po + 4 * v, x);
         }
         const float* ra = b.rec_a + g * b.T;
         for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = ra[j];
-        const float* rq = b.rec_wq + g * b.W;
-        for (int u = threadIdx.x; u < b.W; u += blockDim.x) b.wq[(size_t)row * b.W + u] = rq[u];
+        const float4* rq = reinterpret_cast<const float4*>(b.rec_wq + g * b.W);
+        float4* wq = reinterpret_cast<float4*>(b.wq + (size_t)row * b.W);
+        for (int u = threadIdx.x; u < W4; u += blockDim.x) wq[u] = rq[u];
         for (int n = 0; n < b.d; ++n) {
-            const float* rh = b.rec_h + (g * b.d + n) * b.W;
-            const float* rc = b.rec_c + (g * b.d + n) * b.W;
-            for (int u = threadIdx.x; u < b.W; u += blockDim.x) {
-                const size_t o = (size_t)row * b.W + u;
-                store_split(b.h_in[n], split ? b.h_in_lo[n] : nullptr, o, rh[u]);
-                b.c_in[n][o] = rc[u];
+            const float4* rh = reinterpret_cast<const float4*>(b.rec_h + (g * b.d + n) * b.W);
+            const float4* rc = reinterpret_cast<const float4*>(b.rec_c + (g * b.d + n) * b.W);
+            float4* ci = reinterpret_cast<float4*>(b.c_in[n] + (size_t)row * b.W);
+            for (int u = threadIdx.x; u < W4; u += blockDim.x) {
+                store_split4(b.h_in[n], split ? b.h_in_lo[n] : nullptr, (size_t)row * b.W + 4 * u, rh[u]);
+                ci[u] = rc[u];
             }
         }
     }
@@ -349,19 +358,21 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
         if (rej >= 0 && tid == 0 && (double)sp[rej] < b.rej_thr) sp[rej] = (float)b.rej_thr;
         __syncthreads();
         // ---- record: scores after the overwrite, states, alignment
-        float* rp = b.rec_p + g * b.Vp;
-        for (int v = tid; v < b.Vp; v += 128) rp[v] = sp[v];
+        const int W4 = b.W >> 2;
+        float4* rp = reinterpret_cast<float4*>(b.rec_p + g * b.Vp);
+        for (int v = tid; v < (b.Vp >> 2); v += 128) rp[v] = reinterpret_cast<const float4*>(sp)[v];
         float* ra = b.rec_a + g * b.T;
         for (int j = tid; j < b.T; j += 128) ra[j] = al[j];
-        float* rq = b.rec_wq + g * b.W;
-        for (int u = tid; u < b.W; u += 128) rq[u] = b.wq[(size_t)row * b.W + u];
+        float4* rq = reinterpret_cast<float4*>(b.rec_wq + g * b.W);
+        const float4* wq = reinterpret_cast<const float4*>(b.wq + (size_t)row * b.W);
+        for (int u = tid; u < W4; u += 128) rq[u] = wq[u];
         for (int n = 0; n < b.d; ++n) {
-            float* rh = b.rec_h + (g * b.d + n) * b.W;
-            float* rc = b.rec_c + (g * b.d + n) * b.W;
-            for (int u = tid; u < b.W; u += 128) {
-                const size_t o = (size_t)row * b.W + u;
-                rh[u] = load_split(b.h_out[n], split ? b.h_out_lo[n] : nullptr, o);
-                rc[u] = b.c_out[n][o];
+            float4* rh = reinterpret_cast<float4*>(b.rec_h + (g * b.d + n) * b.W);
+            float4* rc = reinterpret_cast<float4*>(b.rec_c + (g * b.d + n) * b.W);
+            const float4* co = reinterpret_cast<const float4*>(b.c_out[n] + (size_t)row * b.W);
+            for (int u = tid; u < W4; u += 128) {
+                rh[u] = load_split4(b.h_out[n], split ? b.h_out_lo[n] : nullptr, (size_t)row * b.W + 4 * u);
+                rc[u] = co[u];
             }
         }
         // ---- beam width from the relative threshold (:1470-1478)
@@ -422,6 +433,164 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
             ++nacc;
         }
         if (tid == 0) {
+            b.rec_cur[g] = cur; b.rec_amax1[g] = amax == 1.0f ? 1 : 0; b.rec_pos[g] = pos;
+            b.rec_len[g] = len_node; b.rec_nacc[g] = nacc; b.rec_parent[g] = node;
+        }
+    }
+}
+
+// Warp-per-row variant for Vp <= 1024: the whole score row lives in registers (element lane + 32k in
+// slot k, the assignment softmax_kernel uses, so both decoders see bit-identical probabilities), every
+// reduction is a shuffle, and no block barrier is needed.  Same procedure as beam_expand_kernel.
+template <int NVL>
+__global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int split) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int R = b.counters[0];
+    const unsigned FULL = 0xffffffffu;
+    for (int row = blockIdx.x * 4 + wid; row < R; row += gridDim.x * 4) {
+        const int line = b.row_line[row];
+        const uint32_t node = b.row_node[row];
+        const int Tl = b.row_T[line];
+        const size_t g = (size_t)line * b.quota_x + b.row_xid[row];
+        // ---- softmax of the logits row (and of the LM logits)
+        float p[NVL], plm[NVL];
+        auto softmax_row = [&](const float* z, float (&out)[NVL]) {
+            float m = -INFINITY;
+#pragma unroll
+            for (int k = 0; k < NVL; ++k) {
+                const int v = lane + 32 * k;
+                out[k] = v < b.V ? z[v] : -INFINITY;
+                m = fmaxf(m, out[k]);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
+            float s = 0.f;
+#pragma unroll
+            for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) s += expf(out[k] - m);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+#pragma unroll
+            for (int k = 0; k < NVL; ++k) out[k] = lane + 32 * k < b.V ? expf(out[k] - m) / s : 0.f;
+        };
+        softmax_row(b.logits + (size_t)row * b.Vp, p);
+        if (b.lm) softmax_row(b.logits_lm + (size_t)row * b.Vp, plm);
+        // value of element v of a register row, delivered to every lane
+        auto fetch = [&](const float (&arr)[NVL], int v) {
+            float mine = 0.f;
+#pragma unroll
+            for (int k = 0; k < NVL; ++k) if (k == (v >> 5)) mine = arr[k];
+            return __shfl_sync(FULL, mine, v & 31);
+        };
+        // ---- alignment: expected source position in fp64, max == 1.0 test (:1443-1452)
+        const float* al = b.a_out + (size_t)row * b.T;
+        double cur = 0.0; float amax = 0.f;
+        for (int j = lane; j < Tl; j += 32) { const float a = al[j]; cur += (double)a * (double)j; amax = fmaxf(amax, a); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cur += __shfl_xor_sync(FULL, cur, o);
+            amax = fmaxf(amax, __shfl_xor_sync(FULL, amax, o));
+        }
+        // ---- the expanded node
+        int len_node = 1; double pcum = 0.0, prev = 0.0; bool onehot = false;
+        if (node != 0u) {
+            const int pk = (int)((node - 1u) % KMAX);
+            const size_t pg = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+            len_node = b.rec_len[pg] + 1;
+            pcum = b.ch_cum[pg * KMAX + pk];
+            const bool was_rej = b.ch_rej[pg * KMAX + pk] != 0;
+            onehot = was_rej || b.rec_amax1[pg] != 0;
+            prev = was_rej ? (double)b.rec_pos[pg] : b.rec_cur[pg];
+        }
+        int pos = 0; double mis = 0.0;
+        if (len_node > 1) {
+            mis = fabs(cur - prev - 1.0);
+            pos = onehot ? (int)prev + 1 : (int)rint(cur);
+        }
+        // ---- rejection candidate (:1454-1466); pos == T raises IndexError in the reference: no candidate here
+        int rej = -1;
+        if (b.rej_thr > 0.0 && (mis < 0.1 || onehot) && pos >= 0 && pos < b.T) {
+            const int r = b.rej_table[(size_t)line * b.T + pos];
+            if (r >= 0) rej = r;
+        }
+        float rej_p = 0.f;
+        if (rej >= 0) {
+            rej_p = fetch(p, rej);
+            if ((double)rej_p < b.rej_thr) {
+                rej_p = (float)b.rej_thr;
+#pragma unroll
+                for (int k = 0; k < NVL; ++k) if (lane + 32 * k == rej) p[k] = rej_p;
+            }
+        }
+        // ---- record: scores after the overwrite, states, alignment, query of the children
+        float* rp = b.rec_p + g * b.Vp;
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) rp[lane + 32 * k] = p[k];
+        float* ra = b.rec_a + g * b.T;
+        for (int j = lane; j < b.T; j += 32) ra[j] = al[j];
+        const int W4 = b.W >> 2;
+        float4* rq = reinterpret_cast<float4*>(b.rec_wq + g * b.W);
+        const float4* wq = reinterpret_cast<const float4*>(b.wq + (size_t)row * b.W);
+        for (int u = lane; u < W4; u += 32) rq[u] = wq[u];
+        for (int n = 0; n < b.d; ++n) {
+            float4* rh = reinterpret_cast<float4*>(b.rec_h + (g * b.d + n) * b.W);
+            float4* rc = reinterpret_cast<float4*>(b.rec_c + (g * b.d + n) * b.W);
+            const float4* co = reinterpret_cast<const float4*>(b.c_out[n] + (size_t)row * b.W);
+            for (int u = lane; u < W4; u += 32) {
+                rh[u] = load_split4(b.h_out[n], split ? b.h_out_lo[n] : nullptr, (size_t)row * b.W + 4 * u);
+                rc[u] = co[u];
+            }
+        }
+        // ---- beam width from the relative threshold (:1470-1478)
+        float hi = 0.f;
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) hi = fmaxf(hi, p[k]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) hi = fmaxf(hi, __shfl_xor_sync(FULL, hi, o));
+        const double bound = (double)hi * b.thr_in;
+        int cnt = 0;
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) cnt += ((double)p[k] >= bound);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULL, cnt, o);
+        const int beampos = min(cnt, b.width_in);
+        // ---- walk the candidates best first (:1480-1529)
+        int nacc = 0, pending = rej;
+        for (int rank = 1; rank <= beampos + 1; ++rank) {
+            int v; float pv; bool isrej;
+            if (rank <= beampos) {
+                ArgMax best{-1.f, -1};
+#pragma unroll
+                for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) best = better(best, ArgMax{p[k], lane + 32 * k});
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    ArgMax other{__shfl_xor_sync(FULL, best.v, o), __shfl_xor_sync(FULL, best.i, o)};
+                    best = better(best, other);
+                }
+                if (best.i < 0 || best.v < 0.f) break;
+                v = best.i; pv = best.v;
+#pragma unroll
+                for (int k = 0; k < NVL; ++k) if (lane + 32 * k == v) p[k] = -1.f;     // taken
+                isrej = (v == pending);
+                if (isrej) pending = -1;
+            } else {
+                // past the beam width only a still pending rejection candidate enters; `if rej_idx:` (:1498)
+                // treats index 0 as not pending
+                if (pending <= 0) break;
+                v = pending; pv = rej_p; isrej = true; pending = -1;
+            }
+            if (v == 0) continue;                       // '' (underspecification) is never a hypothesis (:1504-1507)
+            const float pc = b.lm ? fetch(plm, v) : pv; // LM rates the beam, the decoder enters it (:1486-1489)
+            const float cost = (float)(-log((double)pc));
+            if (cost != cost) continue;
+            if (lane == 0) {
+                b.ch_v[g * KMAX + nacc] = v;
+                b.ch_p[g * KMAX + nacc] = pv;
+                b.ch_cum[g * KMAX + nacc] = pcum + (double)cost;
+                b.ch_rej[g * KMAX + nacc] = isrej ? 1 : 0;
+            }
+            ++nacc;
+        }
+        if (lane == 0) {
             b.rec_cur[g] = cur; b.rec_amax1[g] = amax == 1.0f ? 1 : 0; b.rec_pos[g] = pos;
             b.rec_len[g] = len_node; b.rec_nacc[g] = nacc; b.rec_parent[g] = node;
         }
@@ -731,7 +900,14 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         COR_CUDA(cudaGetLastError());
         io.wq_ready = it > 0;     // iteration 0 expands the roots: their query comes from the encoder state
         if (decoder_core(m, ws, io, st)) return 1;
-        beam_expand_kernel<<<row_grid, 128, expand_smem, st>>>(b, split);
+        const int warp_grid = std::min((plan.Rcap + 3) / 4, 148 * 8);
+        switch (m->Vp) {        // score row in registers when it fits (32 values per lane at most)
+            case 128:  beam_expand_warp_kernel<4><<<warp_grid, 128, 0, st>>>(b, split); break;
+            case 256:  beam_expand_warp_kernel<8><<<warp_grid, 128, 0, st>>>(b, split); break;
+            case 512:  beam_expand_warp_kernel<16><<<warp_grid, 128, 0, st>>>(b, split); break;
+            case 1024: beam_expand_warp_kernel<32><<<warp_grid, 128, 0, st>>>(b, split); break;
+            default:   beam_expand_kernel<<<row_grid, 128, expand_smem, st>>>(b, split);
+        }
         beam_push_kernel<<<L, 256, push_smem, st>>>(b);
         g_launches += 2;
         COR_CUDA(cudaGetLastError());
