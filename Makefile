@@ -14,7 +14,7 @@ all: $(LIB)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 
 $(LIB): $(OBJS)
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart -lpthread
 
 clean:
 	rm -f $(OBJS) $(LIB)

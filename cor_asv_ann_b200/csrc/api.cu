@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <math.h>
 #include <algorithm>
+#include <thread>
 
 namespace cor {
 
@@ -38,11 +39,12 @@ static void prof_begin(cudaStream_t st) {
     }
     cudaEventRecord(g_prof.ev[g_prof.used], st);
 }
-static void prof_end(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n) {
+static void prof_end(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, int k_table) {
     if (!g_prof.on || g_prof.used + 2 > g_prof.ev.size()) return;
     cudaEventRecord(g_prof.ev[g_prof.used + 1], st);
     g_prof.used += 2;
-    double k = 0;
+    // algorithmic K: the segments plus the input term a table gather stands in for (SURVEY.md 8d counts x.Kx)
+    double k = k_table;
     for (int i = 0; i < n; ++i) k += s[i].K;
     if (m_dev && g_prof.rows && g_prof.per_row.size() < kMaxDeferred) {
         cudaMemcpyAsync(g_prof.rows + g_prof.per_row.size(), m_dev, 4, cudaMemcpyDeviceToHost, st);
@@ -68,7 +70,7 @@ static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int
     int rc;
     if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
     else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
-    prof_end(st, M, m_dev, N, s, n);
+    prof_end(st, M, m_dev, N, s, n, e.xtab ? e.W : 0);
     return rc;
 }
 
@@ -137,6 +139,32 @@ static std::vector<float> lstm_bias(const HostWeight& b, int W) {
     return t;
 }
 
+// out[a][b] = sum_u A[a][u] * B[b][u]  (fp64 accumulation, one rounding), rows of A spread over host threads
+static std::vector<float> product_f64(const float* A, int na, const float* B, int nb, int K, int ld_out) {
+    std::vector<float> out((size_t)na * ld_out, 0.f);
+    unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    if ((size_t)na * nb * K < (1u << 22)) nt = 1;
+    auto work = [&](int a0, int a1) {
+        for (int a = a0; a < a1; ++a) {
+            const float* ar = A + (size_t)a * K;
+            for (int b = 0; b < nb; ++b) {
+                const float* br = B + (size_t)b * K;
+                double s = 0.0;
+                for (int u = 0; u < K; ++u) s += (double)ar[u] * (double)br[u];
+                out[(size_t)a * ld_out + b] = (float)s;
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    const int per = (na + (int)nt - 1) / (int)nt;
+    for (unsigned t = 0; t < nt; ++t) {
+        const int a0 = (int)t * per, a1 = std::min(na, a0 + per);
+        if (a0 < a1) th.emplace_back(work, a0, a1);
+    }
+    for (auto& t : th) t.join();
+    return out;
+}
+
 static int need(cor_model* m, const std::string& layer, size_t count, const std::vector<HostWeight>** out) {
     auto it = m->host.find(layer);
     COR_CHECK(it != m->host.end(), ("missing weights for layer " + layer).c_str());
@@ -183,8 +211,10 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
     ws->val = c.take<float>(BT * k);
     ws->live = c.take<uint8_t>(B);
     ws->done = c.take<uint8_t>(B);
-    ws->X = c.take<float>(BT * W);   ws->X_lo = sp ? c.take<float>(BT * W) : nullptr;
-    ws->Xr = c.take<float>(BT * W);  ws->Xr_lo = sp ? c.take<float>(BT * W) : nullptr;
+    if (!m->use_xtab) {      // projected input sequences (the table path gathers E.Kx in the epilogue instead)
+        ws->X = c.take<float>(BT * W);   ws->X_lo = sp ? c.take<float>(BT * W) : nullptr;
+        ws->Xr = c.take<float>(BT * W);  ws->Xr_lo = sp ? c.take<float>(BT * W) : nullptr;
+    }
     ws->seq.assign(d, nullptr); ws->seq_lo.assign(d, nullptr); ws->seqr.assign(d, nullptr); ws->seqr_lo.assign(d, nullptr);
     for (int n = 0; n < d; ++n) {
         const size_t e = BT * m->enc_out_dim(n);
@@ -242,7 +272,7 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
     const int W = m->W, d = m->d, B = ws.B, T = ws.T;
     const bool deep = m->cfg.deep_bidirectional_encoder != 0;
     if (launch_live_rows(st, ws.idx, ws.val, B, T, ws.k, ws.live)) return 1;
-    if (launch_embed(st, ws.idx, ws.val, ws.row_T, B, T, ws.k, m->E_full, W, m->V, ws.X, ws.X_lo, ws.Xr, ws.Xr_lo)) return 1;
+    if (!m->use_xtab && launch_embed(st, ws.idx, ws.val, ws.row_T, B, T, ws.k, m->E_full, W, m->V, ws.X, ws.X_lo, ws.Xr, ws.Xr_lo)) return 1;
     const size_t BW = (size_t)B * W;
     for (int n = 0; n < d; ++n) {
         const bool bidi = m->layer_bidi(n);
@@ -264,10 +294,12 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
                 const size_t sb = slab * (in_lo[dir] ? sizeof(__half) : sizeof(float));
                 const float* a_hi = reinterpret_cast<const float*>(reinterpret_cast<const char*>(in[dir]) + sb);
                 const float* a_lo = in_lo[dir] ? reinterpret_cast<const float*>(reinterpret_cast<const char*>(in_lo[dir]) + sb) : nullptr;
-                GemmSeg segs[2] = {
-                    {a_hi, in_dim, a_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, in_dim},
-                    {ws.eh[dir][cur], W, ws.eh_lo[dir][cur], lw.R.hi, lw.R.ld, lw.R.lo, W}};
+                const bool tab = n == 0 && m->use_xtab;
+                GemmSeg segs[2]; int ns = 0;
+                if (!tab) segs[ns++] = GemmSeg{a_hi, in_dim, a_lo, lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, in_dim};
+                segs[ns++] = GemmSeg{ws.eh[dir][cur], W, ws.eh_lo[dir][cur], lw.R.hi, lw.R.ld, lw.R.lo, W};
                 LstmEpi e{};
+                if (tab) { e.xtab = m->xtab[dir]; e.x_idx = ws.idx; e.x_val = ws.val; e.x_k = ws.k; e.x_tmax = T; }
                 e.bias = lw.bias; e.c_in = ws.ec[dir]; e.c_out = ws.ec[dir];
                 e.h_prev = ws.eh[dir][cur]; e.h_prev_lo = ws.eh_lo[dir][cur];
                 e.h_out = ws.eh[dir][cur ^ 1]; e.h_out_lo = ws.eh_lo[dir][cur ^ 1];
@@ -279,7 +311,7 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
                 }
                 e.cross_sum = deep && n + 1 < d;
                 e.W = W;
-                if (gemm_lstm(m, st, B, nullptr, 4 * W, segs, 2, e)) return 1;
+                if (gemm_lstm(m, st, B, nullptr, 4 * W, segs, ns, e)) return 1;
             }
             cur ^= 1;
         }
@@ -620,17 +652,19 @@ int cor_model_finalize(cor_model* m) {
         const std::string name = "decoder_lstm_1";
         const HostWeight& K = m->host[name][d == 1 ? 4 : 0];
         const std::vector<float> kx = lstm_rows(K, W, 0, W);      // [4W][W]
-        std::vector<float> pe((size_t)4 * W * Vp, 0.f);
-        for (int n = 0; n < 4 * W; ++n) {
-            const float* kr = &kx[(size_t)n * W];
-            for (int v = 0; v < V; ++v) {
-                const float* er = &E.data[(size_t)v * W];
-                double s = 0.0;
-                for (int u = 0; u < W; ++u) s += (double)kr[u] * (double)er[u];
-                pe[(size_t)n * Vp + v] = (float)s;
-            }
-        }
+        const std::vector<float> pe = product_f64(kx.data(), 4 * W, E.data.data(), V, W, Vp);
         if (upload_mat(m, pe, 4 * W, Vp, &m->PE)) return 1;
+    }
+    m->use_xtab = V <= 4096 && !getenv("COR_NO_XTAB");
+    if (m->use_xtab) {
+        // first encoder layer: x_t . Kx as a gather from (E . Kx) [V][4W], one table per scan direction
+        const HostWeight& E = m->host["char_input_projection"][0];
+        const std::vector<HostWeight>& l1 = m->host["encoder_lstm_1"];
+        for (int dir = 0; dir < 2; ++dir) {
+            const std::vector<float> kx = lstm_rows(l1[3 * dir], W, 0, W);     // [4W][W], gate-interleaved rows
+            const std::vector<float> tab = product_f64(E.data.data(), V, kx.data(), 4 * W, W, 4 * W);
+            if (upload_vec(m, tab, &m->xtab[dir])) return 1;
+        }
     }
     if (!m->side && getenv("COR_OVERLAP")) {     // experiment switch: attention beside the lower-cell GEMM (no gain measured: DESIGN.md)
         COR_CUDA(cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking));

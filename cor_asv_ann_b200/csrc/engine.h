@@ -76,6 +76,11 @@ struct LstmEpi {
     const float* resid; const float* resid_lo; int resid_ld;         // residual add into seq_out
     int cross_sum;             // seq value = h[2k]+h[2k+1] for both members of a pair
     int W;
+    // optional input term taken from a table instead of a K-segment (first encoder layer): the layer
+    // input is x_t = sum_k val_k E[idx_k] (seq2seq.py:237-244), so x_t . Kx = sum_k val_k (E.Kx)[idx_k]
+    // with xtab = E.Kx [V][4W] prepared at load time.  idx/val are the call's lines [row][x_tmax][x_k].
+    const float* xtab;
+    const int32_t* x_idx; const float* x_val; int x_k; int x_tmax;
 };
 
 // m_dev != nullptr: the row count is read on the device (beam), M is then the capacity.

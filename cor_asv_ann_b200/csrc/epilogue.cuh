@@ -76,14 +76,38 @@ __device__ __forceinline__ float lstm_unit(const LstmEpi& e, int row, int unit, 
 
 // Write the new h of `n` consecutive units [unit0, unit0+n) of one row (n even when cross_sum).
 // Handles the inactive-row copy-through, the recurrent state, and the sequence outputs.
+// z[0..n) += sum_k val_k * xtab[idx_k][col0 .. col0+n)  for the row's input position t (n a multiple of 4)
+template <int N>
+__device__ __forceinline__ void xtab_add(const LstmEpi& e, int row, int t, int col0, float* z) {
+    const size_t o = ((size_t)row * e.x_tmax + t) * e.x_k;
+    for (int k = 0; k < e.x_k; ++k) {
+        const int v = e.x_idx[o + k];
+        if (v < 0) continue;
+        const float w = e.x_val ? e.x_val[o + k] : 1.0f;
+        const float4* src = reinterpret_cast<const float4*>(e.xtab + (size_t)v * 4 * e.W + col0);
+#pragma unroll
+        for (int q = 0; q < N / 4; ++q) {
+            const float4 x = src[q];
+            z[4 * q + 0] = fmaf(w, x.x, z[4 * q + 0]); z[4 * q + 1] = fmaf(w, x.y, z[4 * q + 1]);
+            z[4 * q + 2] = fmaf(w, x.z, z[4 * q + 2]); z[4 * q + 3] = fmaf(w, x.w, z[4 * q + 3]);
+        }
+    }
+}
+
 template <int NU>
 __device__ __forceinline__ void lstm_row_units(const LstmEpi& e, int row, int unit0, const float (*z)[4]) {
     int T = e.row_T ? e.row_T[row] : 0x7fffffff;
     const bool active = e.step < T;
     float h[NU];
     if (active) {
+        float zz[NU][4];
 #pragma unroll
-        for (int k = 0; k < NU; ++k) h[k] = lstm_unit(e, row, unit0 + k, z[k]);
+        for (int k = 0; k < NU; ++k)
+#pragma unroll
+            for (int g = 0; g < 4; ++g) zz[k][g] = z[k][g];
+        if (e.xtab) xtab_add<4 * NU>(e, row, e.reverse ? T - 1 - e.step : e.step, 4 * unit0, &zz[0][0]);
+#pragma unroll
+        for (int k = 0; k < NU; ++k) h[k] = lstm_unit(e, row, unit0 + k, zz[k]);
     } else {
 #pragma unroll
         for (int k = 0; k < NU; ++k) {

@@ -44,7 +44,8 @@ template <int NCTA> struct Geo {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
     static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * NCTA) >> 4) << 24);
 };
-constexpr int NTHREADS = 256;
+constexpr int EPI_WARPS = 8;                   // two per TMEM lane quarter: each takes half of the tile's columns
+constexpr int NTHREADS = 128 + 32 * EPI_WARPS;
 constexpr int TMEM_COLS = 512;
 
 struct TcParams {
@@ -206,6 +207,7 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, int row, int unit0, 
         ld4(e.c_in, so, c); ld4(e.c_in, so + 4, c + 4);
 #pragma unroll
         for (int q = 0; q < 8; ++q) ld4(e.bias, (size_t)4 * unit0 + 4 * q, b + 4 * q);
+        if (e.xtab) xtab_add<32>(e, row, e.reverse ? T - 1 - e.step : e.step, 4 * unit0, b);    // folded into the bias term
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const float i = sigmoidf_fast(__uint_as_float(z[4 * k + 0]) + b[4 * k + 0]);
@@ -315,7 +317,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4 * NCTA); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), EPI_WARPS * NCTA); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -407,7 +409,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
         }
     } else if (warp >= 4) {
         // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 of its own CTA =====
-        const int wq = warp - 4;
+        // the LSTM epilogue is a chain of MUFU and load latencies per row: two warps per scheduler hide them
+        const int wq = (warp - 4) & 3, half = (warp - 4) >> 2;
+        constexpr int CH_PER = (BN / 32) / (EPI_WARPS / 4);
         int acc = 0; uint32_t acc_phase = 0;
         for (int tile = unit; tile < num_tiles; tile += n_units) {
             const int m0 = (tile / p.tiles_n) * (BM * NCTA) + (int)rank * BM, n0 = (tile % p.tiles_n) * BN;
@@ -416,7 +420,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
             const int row = m0 + wq * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int ch = 0; ch < BN / 32; ++ch) {
+            for (int ch = half * CH_PER; ch < (half + 1) * CH_PER; ++ch) {
                 uint32_t z[32];
                 tmem_ld32(taddr + ch * 32, z);
                 tmem_ld_wait();

@@ -46,6 +46,8 @@ struct cor_model {
     cor::Mat Wa;              // [W][W]
     cor::Mat EWa;             // [Vp+W][W]  rows of E then rows of W_a: logits | next query in one launch
     cor::Mat PE;              // [4W][Vp]   (E . Kx) of the first decoder cell: z_x = p . PE without the round trip through x
+    float* xtab[2] = {nullptr, nullptr};   // [V][4W] (E . Kx) of the first encoder layer, forward / backward scan
+    bool use_xtab = false;
     bool fuse_pe = false;     // PE exists (3*Vp <= 4*W: the fused product is the cheaper one)
     cudaStream_t side = nullptr;          // attention runs here, beside the lower-cell GEMMs
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
