@@ -56,7 +56,8 @@ struct BeamDev {
     double* fr_key; uint32_t* fr_id;       // [2][L][cap]
     uint32_t* beam_nodes;                  // [L][batch]
     int32_t* rej_table;                    // [L][T]
-    int32_t* counters;                     // [0] rows this iteration (r_dev), [1] active lines
+    int32_t* counters;                     // [0] rows this iteration (r_dev), [1] active lines, [2] lines on the heavy push list
+    int32_t* heavy;                        // [L] lines whose new children do not fit one warp
     // per record g = line*quota_x + xid
     float *rec_p, *rec_h, *rec_c, *rec_a;  // [G][Vp], [G][d][W], [G][d][W], [G][T]
     float* rec_wq;                         // [G][W] attention query of the children (h_top . W_a + b)
@@ -108,61 +109,57 @@ __global__ void beam_init_kernel(BeamDev b) {
 }
 
 // ------------------------------------------------------------------ pop (seq2seq.py:1398-1420)
+// One warp per line: the fringe is sorted, so the pop is a prefix of it — walked 32 entries at a time
+// until batch_size open nodes have been seen (a few chunks at most, whatever the fringe length).
 __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
-    const int line = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    __shared__ int s_wsum[8];
-    __shared__ int s_first_final, s_first_open;
-    if (b.status[line] != ST_ACTIVE) { if (tid == 0) b.beam_count[line] = 0; return; }
+    const int lane = threadIdx.x & 31;
+    const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (line >= b.L) return;
+    if (b.status[line] != ST_ACTIVE) { if (lane == 0) b.beam_count[line] = 0; return; }
     const int Tl = b.row_T[line];
     const int len = b.fr_len[line];
     if (b.iter[line] >= 2 * Tl) {                    // max_batches reached (:1397-1398)
-        if (tid == 0) { b.status[line] = ST_DONE; b.beam_count[line] = 0; b.open_left[line] = len; }
+        if (lane == 0) { b.status[line] = ST_DONE; b.beam_count[line] = 0; b.open_left[line] = len; }
         return;
     }
     const int cur = b.fr_buf[line];
     const double* keys = b.fr_key + ((size_t)cur * b.L + line) * b.cap;
     const uint32_t* ids = b.fr_id + ((size_t)cur * b.L + line) * b.cap;
-    if (tid == 0) { s_first_final = 0x7fffffff; s_first_open = 0x7fffffff; }
-    __syncthreads();
+    int first_final = 0x7fffffff, first_open = 0x7fffffff;
     int open_total = 0, consumed = 0, nfin = 0;
-    for (int base = 0; base < len && open_total < b.batch; base += 256) {
-        const int i = base + tid;
+    for (int base = 0; base < len && open_total < b.batch; base += 32) {
+        const int i = base + lane;
         const bool valid = i < len;
         const uint32_t id = valid ? ids[i] : 0u;
         const bool fin = valid && (id & FINAL_BIT);
         const bool open = valid && !fin;
         const unsigned bal = __ballot_sync(0xffffffffu, open);
-        if (lane == 0) s_wsum[warp] = __popc(bal);
-        __syncthreads();
-        int excl = open_total + __popc(bal & ((1u << lane) - 1u));
-        int blk = 0;
-        for (int w = 0; w < 8; ++w) { if (w < warp) excl += s_wsum[w]; blk += s_wsum[w]; }
+        const int excl = open_total + __popc(bal & ((1u << lane) - 1u));
         // an entry is popped iff fewer than batch_size open nodes precede it (:1400-1415)
         const bool take = valid && excl < b.batch;
-        if (take && open) {
-            b.beam_nodes[(size_t)line * b.batch + excl] = id;
-            if (excl == 0) s_first_open = i;
-        }
-        if (take && fin) atomicMin(&s_first_final, i);
-        consumed += __syncthreads_count(take);
-        nfin += __syncthreads_count(take && fin);
-        open_total += blk;
+        if (take && open) b.beam_nodes[(size_t)line * b.batch + excl] = id;
+        const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
+        const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);
+        if (t_open && first_open == 0x7fffffff) first_open = base + __ffs(t_open) - 1;
+        if (t_fin && first_final == 0x7fffffff) first_final = base + __ffs(t_fin) - 1;
+        consumed += __popc(t_open | t_fin);
+        nfin += __popc(t_fin);
+        open_total += __popc(bal);
     }
-    __syncthreads();
-    if (tid != 0) return;
+    if (lane != 0) return;
     const int count = min(open_total, b.batch);
     int fc = b.finals_count[line] + nfin;
     double bk = b.best_key[line];
     if (nfin > 0) {
-        const double kf = keys[s_first_final];
-        if (kf < bk) { bk = kf; b.best_key[line] = kf; b.best_final[line] = (int32_t)(ids[s_first_final] & ~FINAL_BIT); }
+        const double kf = keys[first_final];
+        if (kf < bk) { bk = kf; b.best_key[line] = kf; b.best_final[line] = (int32_t)(ids[first_final] & ~FINAL_BIT); }
     }
     b.finals_count[line] = fc;
     b.fr_off[line] = consumed;
     int out = count;
     if (count == 0) {
         b.status[line] = ST_DONE; b.open_left[line] = len - consumed;
-    } else if (fc > b.width_out && bk < keys[s_first_open]) {       // :1418-1420
+    } else if (fc > b.width_out && bk < keys[first_open]) {       // :1418-1420
         b.status[line] = ST_DONE; b.open_left[line] = len - consumed; out = 0;
     } else if (b.x_count[line] + count > b.quota_x) {
         b.status[line] = ST_OVERFLOW; out = 0;
@@ -174,48 +171,55 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
 }
 
 // ------------------------------------------------------------------ scan: row offsets, row total, active lines
+// One block; thread t owns the consecutive lines [t*per, (t+1)*per): all loads are issued at once,
+// one block-wide scan of the per-thread sums, then the row bases.  Row order = line order.
 __global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b) {
     __shared__ int s_wsum[32];
     __shared__ int s_total, s_active;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { s_total = 0; s_active = 0; }
-    __syncthreads();
-    int running = 0;
-    for (int base = 0; base < b.L; base += 1024) {
-        const int line = base + tid;
-        int c = line < b.L ? b.beam_count[line] : 0;
-        int incl = c;
+    if (tid == 0) { s_total = 0; s_active = 0; b.counters[2] = 0; }
+    const int per = (b.L + 1023) / 1024;
+    const int l0 = tid * per, l1 = min(b.L, l0 + per);
+    int mine = 0;
+    for (int line = l0; line < l1; ++line) mine += b.beam_count[line];
+    int incl = mine;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-        if (lane == 31) s_wsum[warp] = incl;
-        __syncthreads();
-        int off = 0, blk = 0;
-        for (int w = 0; w < 32; ++w) { if (w < warp) off += s_wsum[w]; blk += s_wsum[w]; }
-        const int rb = running + off + incl - c;
-        if (line < b.L) {
-            if (c > 0 && rb + c > b.Rcap) { b.status[line] = ST_OVERFLOW; b.beam_count[line] = 0; c = 0; }
-            b.row_base[line] = rb;
-            if (c > 0) atomicMax(&s_total, rb + c);
-            if (b.status[line] == ST_ACTIVE) atomicAdd(&s_active, 1);
-        }
-        running += blk;
-        __syncthreads();
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    int off = 0;
+    for (int w = 0; w < warp; ++w) off += s_wsum[w];
+    int rb = off + incl - mine;
+    int total = 0, active = 0;
+    for (int line = l0; line < l1; ++line) {
+        int c = b.beam_count[line];
+        if (c > 0 && rb + c > b.Rcap) { b.status[line] = ST_OVERFLOW; b.beam_count[line] = 0; }
+        else if (c > 0) total = rb + c;
+        b.row_base[line] = rb;
+        rb += c;
+        if (b.status[line] == ST_ACTIVE) ++active;
     }
+    if (total) atomicMax(&s_total, total);
+    if (active) atomicAdd(&s_active, active);
+    __syncthreads();
     if (tid == 0) { b.counters[0] = s_total; b.counters[1] = s_active; }
 }
 
+// One warp per line: the rows of a line are its popped nodes in fringe order.
 __global__ void __launch_bounds__(256) beam_rowmap_kernel(BeamDev b) {
-    const int line = blockIdx.x, tid = threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (line >= b.L) return;
     const int c = b.beam_count[line];
     if (c <= 0) return;
     const int rb = b.row_base[line], xb = b.x_count[line];
-    if (tid < c) {
-        b.row_line[rb + tid] = line;
-        b.row_node[rb + tid] = b.beam_nodes[(size_t)line * b.batch + tid];
-        b.row_xid[rb + tid] = xb + tid;
+    for (int t = lane; t < c; t += 32) {
+        b.row_line[rb + t] = line;
+        b.row_node[rb + t] = b.beam_nodes[(size_t)line * b.batch + t];
+        b.row_xid[rb + t] = xb + t;
     }
-    __syncthreads();
-    if (tid == 0) { b.x_base[line] = xb; b.x_count[line] = xb + c; }
+    __syncwarp();
+    if (lane == 0) { b.x_base[line] = xb; b.x_count[line] = xb + c; }
 }
 
 // ------------------------------------------------------------------ gather: decoder-step inputs of every row
@@ -598,12 +602,8 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
 }
 
 // ------------------------------------------------------------------ push: insort of the new children (:1515-1532)
-__global__ void __launch_bounds__(256) beam_push_kernel(BeamDev b) {
-    extern __shared__ unsigned char smraw[];
-    double* skey = reinterpret_cast<double*>(smraw);                 // [npad]
-    uint32_t* sid = reinterpret_cast<uint32_t*>(skey + MAX_NEW);     // [npad]
-    __shared__ int s_wsum[8];
-    const int line = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+__device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = b.beam_count[line];
     if (c <= 0) return;
     const int Tl = b.row_T[line];
@@ -675,6 +675,89 @@ __global__ void __launch_bounds__(256) beam_push_kernel(BeamDev b) {
         b.fr_len[line] = min(n_old + n_new, b.cap);
         b.fr_off[line] = 0;
         b.fr_buf[line] = cur ^ 1;
+    }
+}
+
+// Small case, one warp per line: at most 32 new children (the common case once the rejection candidate
+// or a narrow beam prunes the expansion).  Lane t holds child t; its slot in the merged fringe is its rank
+// among the new children plus the number of old entries that precede it.  Lines with more children go on
+// the heavy list for beam_push_kernel.  Same total order as there: (key, id), first inserted first.
+__global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
+    __shared__ double s_key[8][32];
+    __shared__ uint32_t s_id[8][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int line = blockIdx.x * 8 + wid;
+    if (line >= b.L) return;
+    const int c = b.beam_count[line];
+    if (c <= 0) return;
+    const unsigned FULL = 0xffffffffu;
+    const int xb = b.x_base[line];
+    int n_new = 33;
+    int nj = 0, off = 0;
+    if (c <= 32) {
+        nj = lane < c ? b.rec_nacc[(size_t)line * b.quota_x + xb + lane] : 0;
+        int incl = nj;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += y; }
+        n_new = __shfl_sync(FULL, incl, 31);
+        off = incl - nj;
+    }
+    if (n_new > 32) {
+        if (lane == 0) b.heavy[atomicAdd(&b.counters[2], 1)] = line;
+        return;
+    }
+    const int Tl = b.row_T[line];
+    if (lane < c) {
+        const size_t g = (size_t)line * b.quota_x + xb + lane;
+        const int len_child = b.rec_len[g] + 1;
+        const double pen = 3.0 * fabs((double)(len_child - Tl));      // cost0 * |length - length0| (:1588-1595)
+        for (int q = 0; q < nj; ++q) {
+            s_key[wid][off + q] = b.ch_cum[g * KMAX + q] + pen;
+            s_id[wid][off + q] = (1u + (uint32_t)(xb + lane) * KMAX + q) | (b.ch_v[g * KMAX + q] == b.eos ? FINAL_BIT : 0u);
+        }
+    }
+    __syncwarp();
+    const int cur = b.fr_buf[line];
+    const int o_off = b.fr_off[line];
+    const int n_old = b.fr_len[line] - o_off;
+    const double* okey = b.fr_key + ((size_t)cur * b.L + line) * b.cap + o_off;
+    const uint32_t* oid = b.fr_id + ((size_t)cur * b.L + line) * b.cap + o_off;
+    double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
+    uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
+    if (lane < n_new) {
+        const double k = s_key[wid][lane]; const uint32_t id = s_id[wid][lane];
+        int rank = 0;
+        for (int t = 0; t < n_new; ++t) rank += key_less(s_key[wid][t], s_id[wid][t], k, id);
+        int lo = 0, hi = n_old;                   // old entries that precede this new one
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
+        const int pos = rank + lo;
+        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+    }
+    for (int i = lane; i < n_old; i += 32) {
+        const double k = okey[i]; const uint32_t id = oid[i];
+        int before = 0;                           // new entries that precede this old one
+        for (int t = 0; t < n_new; ++t) before += key_less(s_key[wid][t], s_id[wid][t], k, id);
+        const int pos = i + before;
+        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        b.fr_len[line] = min(n_old + n_new, b.cap);
+        b.fr_off[line] = 0;
+        b.fr_buf[line] = cur ^ 1;
+    }
+}
+
+// Lines on the heavy list (more than 32 new children), one block per line at a time.
+__global__ void __launch_bounds__(256) beam_push_kernel(BeamDev b) {
+    extern __shared__ unsigned char smraw[];
+    double* skey = reinterpret_cast<double*>(smraw);                 // [npad]
+    uint32_t* sid = reinterpret_cast<uint32_t*>(skey + MAX_NEW);     // [npad]
+    __shared__ int s_wsum[8];
+    const int n = b.counters[2];
+    for (int i = blockIdx.x; i < n; i += gridDim.x) {
+        push_line(b, b.heavy[i], skey, sid, s_wsum);
+        __syncthreads();
     }
 }
 
@@ -781,6 +864,7 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     b->beam_nodes = c.take<uint32_t>((size_t)L * bp->batch_size);
     b->rej_table = c.take<int32_t>((size_t)L * T);
     b->counters = c.take<int32_t>(4);
+    b->heavy = c.take<int32_t>(L);
     b->o_stats = c.take<long long>((size_t)L * 4);
     b->o_align = want_align ? c.take<float>((size_t)L * 2 * T * T) : nullptr;
     const size_t G = (size_t)L * quota_x;
@@ -885,7 +969,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const size_t push_smem = (size_t)MAX_NEW * 12;
     const int t_hi = T;      // every row_T is <= t_max
     for (int it = 0; it <= 2 * t_hi; ++it) {
-        beam_pop_kernel<<<L, 256, 0, st>>>(b);
+        beam_pop_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
         beam_scan_kernel<<<1, 1024, 0, st>>>(b);
         g_launches += 2;
         if (it % 8 == 7 || it == 2 * t_hi) {          // host check: has every line finished?
@@ -894,7 +978,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
             COR_CUDA(cudaStreamSynchronize(st));
             if (cnt[1] == 0 && cnt[0] == 0) break;
         }
-        beam_rowmap_kernel<<<L, 256, 0, st>>>(b);
+        beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
         beam_gather_kernel<<<row_grid, 128, 0, st>>>(b, split);
         g_launches += 2;
         COR_CUDA(cudaGetLastError());
@@ -908,8 +992,9 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
             case 1024: beam_expand_warp_kernel<32><<<warp_grid, 128, 0, st>>>(b, split); break;
             default:   beam_expand_kernel<<<row_grid, 128, expand_smem, st>>>(b, split);
         }
-        beam_push_kernel<<<L, 256, push_smem, st>>>(b);
-        g_launches += 2;
+        beam_push_small_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
+        beam_push_kernel<<<std::min(L, 148 * 4), 256, push_smem, st>>>(b);
+        g_launches += 3;
         COR_CUDA(cudaGetLastError());
     }
     // results: staged in the encoder workspace's output slots and the wave's own staging buffers
