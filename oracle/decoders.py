@@ -23,6 +23,17 @@ from .model import encode, decode_step
 GAP = '\a'
 LOG = logging.getLogger("oracle")
 
+# Scalar promotion rules the bookkeeping below follows.  "legacy" = numpy<1.24, the reference's
+# pinned environment (Dockerfile:38): ``python_float + np.float32`` -> float64.  "nep50" = numpy>=2
+# (this image): python scalars are weak, the result stays float32.  The switch exists so that
+# tests/ref_harness.py can run the reference's own decoder code under this image's numpy and
+# compare it with this restatement bit for bit; the product follows "legacy".
+PROMOTION = "legacy"
+
+
+def _nep50():
+    return PROMOTION == "nep50"
+
 
 # --------------------------------------------------------------------------- vectorisation
 
@@ -99,7 +110,10 @@ def decode_batch_greedy(topo, w, mapping, x_in, hoist_u=True, max_steps=None, tr
             v = int(best[j])
             text[j] += i2c[v]
             probs[j].append(p[j, v])
-            score[j] += float(nlog[j, v])     # python float + np.float32 -> float64 under numpy<1.24
+            if _nep50():
+                score[j] = np.float32(score[j]) + nlog[j, v]
+            else:
+                score[j] += float(nlog[j, v])     # python float + np.float32 -> float64 under numpy<1.24
             aligns[j].append(a[j])
     for j in range(B):
         if text[j]:
@@ -154,7 +168,10 @@ class Node:
         self.parent = parent
         self.state = state
         # float64 accumulation of the float32 -log p (legacy numpy promotion)
-        self.cum_cost = np.float64(parent.cum_cost) + np.float64(cost) if parent else np.float64(cost)
+        if _nep50():
+            self.cum_cost = np.float32(parent.cum_cost) + np.float32(cost) if parent else cost
+        else:
+            self.cum_cost = np.float64(parent.cum_cost) + np.float64(cost) if parent else np.float64(cost)
         self.length = 1 if parent is None else parent.length + 1
         self.length0 = length0 or (parent.length0 if parent else 1)
         self.cost0 = cost0 or (parent.cost0 if parent else 0)
@@ -264,11 +281,16 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
                     and (mis < 0.1 or np.max(node.alignment) == 1.0)
                     and np.any(src)):
                 rej = int(np.nanargmax(src))
-                if np.float64(sc[rej]) < rejection_threshold:
+                thr = sc.dtype.type(rejection_threshold) if _nep50() else rejection_threshold
+                if np.float64(sc[rej]) < thr:
                     sc[rej] = rejection_threshold
             order = np.argsort(sc)
-            hi = np.float64(sc[order[-1]])
-            beampos = V - int(np.searchsorted(sc[order].astype(np.float64), hi * beam_threshold_in))
+            if _nep50():
+                cut = sc[order[-1]] * sc.dtype.type(beam_threshold_in)
+                beampos = V - int(np.searchsorted(sc[order], cut))
+            else:
+                hi = np.float64(sc[order[-1]])
+                beampos = V - int(np.searchsorted(sc[order].astype(np.float64), hi * beam_threshold_in))
             beampos = min(beampos, beam_width_in)
             if stats is not None and V > 1 and sc[order[-1]] == sc[order[-2]]:
                 n_score_ties += 1
