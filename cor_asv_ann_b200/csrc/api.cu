@@ -841,4 +841,12 @@ int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines, void* wor
     return 0;
 }
 
+int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_row,
+                        int n_rows, int t_max, int s_max, const int32_t* in_len, const int32_t* out_len,
+                        double min_score, int32_t* out_path, int path_ld, double* out_dist, void* stream) {
+    COR_CHECK(align && in_len && out_len && out_path && out_dist, "null pointer");
+    return launch_alignment_paths((cudaStream_t)stream, align, stride_step, stride_row, n_rows, t_max, s_max,
+                                  in_len, out_len, min_score, out_path, path_ld, out_dist);
+}
+
 }  // extern "C"

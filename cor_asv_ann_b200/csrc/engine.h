@@ -127,4 +127,11 @@ int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, s
 int launch_finish_scores(cudaStream_t st, double* score_sum, const int32_t* len, int R);
 int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int n_rows, int t_max, int k_alt, uint8_t* live);
 
+
+// ------------------------------------------------------------------ alignpath.cu
+// Viterbi re-alignment path per line (wrapper/transcode.py:279-349); a(row,j,i) = align[j*stride_j + row*stride_row + i]
+int launch_alignment_paths(cudaStream_t st, const float* align, long long stride_j, long long stride_row,
+                           int n_rows, int t_cap, int s_cap, const int32_t* i_max, const int32_t* j_max,
+                           double min_score, int32_t* path, int path_ld, double* dist);
+
 }  // namespace cor

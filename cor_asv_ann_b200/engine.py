@@ -204,6 +204,30 @@ class Engine:
                                                  _ptr(stats), self._stream()))
         return out
 
+    # ------------------------------------------------------------------ Viterbi re-alignment (row N1)
+    def alignment_paths(self, align, layout, in_len, out_len, min_score=None):
+        """Hard path per line from a DEVICE alignment tensor (wrapper/transcode.py:279-349).
+        layout "greedy": align [S,B,T] (greedy()/cor_decode_greedy_batch); "beam": align [B,S,T].
+        in_len/out_len int32 [B] (device or host); out_len < 0 = identity matrix of that size.
+        Returns (path int32 [B,T+1] with -1 for "no key", dist float64 [B]) as device tensors."""
+        assert align.is_cuda and align.dtype == torch.float32 and align.is_contiguous()
+        if layout == "greedy":
+            S, B, T = align.shape
+            stride_step, stride_row = B * T, T
+        else:
+            B, S, T = align.shape
+            stride_step, stride_row = T, S * T
+        dev = self.device
+        in_len = torch.as_tensor(in_len, dtype=torch.int32).to(dev).contiguous()
+        out_len = torch.as_tensor(out_len, dtype=torch.int32).to(dev).contiguous()
+        path = torch.empty((B, T + 1), dtype=torch.int32, device=dev)
+        dist = torch.empty((B,), dtype=torch.float64, device=dev)
+        ms = 1.0 / self.V if min_score is None else float(min_score)
+        with torch.cuda.device(dev):
+            check(self.lib.cor_alignment_paths(_ptr(align), stride_step, stride_row, B, T, S, _ptr(in_len),
+                                               _ptr(out_len), ms, _ptr(path), T + 1, _ptr(dist), self._stream()))
+        return path, dist
+
     def prof_enable(self, on=True):
         check(self.lib.cor_prof_enable(int(on)))
 

@@ -537,6 +537,94 @@ class Sequence2Sequence(object):
             return out_lines, out_probs, out_scores, alignments
         return self._beam_sparse(lines, idx, val)
 
+    def correct_lines_paths(self, lines, conf=None, fast=True, greedy=True, input_lens=None):
+        '''correct_lines plus the hard re-alignment path of every line, made on the device.
+
+        Replaces the pair "correct_lines, then per line _alignment2path(alignment, input_line_len,
+        len(output_line), 1. / voc_size)" of the OCR-D wrapper (wrapper/transcode.py:111-127,
+        279-349): the soft alignments never leave the GPU; only T+1 ints and a float per line do.
+        `input_lens`: input_line_len per line (transcode.py:123; default: number of input positions).
+        Return a 5-tuple: lines, probability lists, scores, realignment dicts {input pos: output pos},
+        distances — the first three exactly as correct_lines returns them.'''
+        import torch
+        assert not fast or greedy, "cannot decode in fast mode with beam search enabled"
+        if not lines:
+            return [], [], [], [], []
+        eng = self._get_engine()
+        dev = eng.device
+        idx, val = lines_to_sparse(self.mapping[0], lines, conf, self.logger)
+        B, T, _ = idx.shape
+        d_idx = torch.as_tensor(idx, device=dev)
+        d_val = None if val is None else torch.as_tensor(val, device=dev)
+        d_T = torch.as_tensor(self._row_T(idx), device=dev)
+        i2c = self.mapping[1]
+        if input_lens is None:
+            input_lens = [len(line) for line in lines]
+        if greedy:
+            eng.encode(d_idx, d_val, d_T, want_align=True)
+            chars, probs, scores, lens, align = eng.greedy()
+            layout = "greedy"
+        else:
+            bp = eng.beam_params(batch_size=min(int(self.batch_size), 256), beam_width_in=self.beam_width_in,
+                                 beam_threshold_in=self.beam_threshold_in, beam_width_out=self.beam_width_out,
+                                 rejection_threshold=self.rejection_threshold)
+            out = (torch.empty((B, 2 * T), dtype=torch.int32, device=dev), torch.empty((B, 2 * T), dtype=torch.float32, device=dev),
+                   torch.empty((B,), dtype=torch.float64, device=dev), torch.empty((B,), dtype=torch.int32, device=dev),
+                   torch.empty((B, 2 * T, T), dtype=torch.float32, device=dev), torch.empty((B, 4), dtype=torch.int64, device=dev))
+            chars, probs, scores, lens, align, stats = eng.beam_device(d_idx, d_val, d_T, bp,
+                                                                       budget_bytes=self.beam_budget_bytes, out=out)
+            self.last_beam_stats = stats.cpu().numpy()
+            layout = "beam"
+        chars, probs, scores, lens = chars.cpu().numpy(), probs.cpu().numpy(), scores.cpu().numpy(), lens.cpu().numpy()
+        out_lines, out_probs, out_scores, out_len = [], [], [], []
+        for j, input_line in enumerate(lines):
+            n = int(lens[j])
+            if not input_line:
+                line, prob, score, jl = '', [], 0, 0
+            elif n > 0:
+                line = ''.join(i2c[int(v)] for v in chars[j, :n])
+                prob = list(probs[j, :n])
+                if fast or not greedy:
+                    score = float(scores[j])
+                else:                       # decode_sequence_greedy accumulates in float32 (:1312, :1343)
+                    total = np.float32(0)
+                    for p in prob:
+                        total = np.float32(total + -np.log(p))
+                    score = total / len(line)
+                if not fast:
+                    line = line.replace(GAP, '')
+                jl = len(line)
+            else:                           # beam fallback (:826-836): input returned, identity alignment
+                self.logger.error('cannot beam-decode input line %d: "%s"', j, input_line)
+                if isinstance(input_line[0], tuple):
+                    line = ''.join(chunk[0] for chunk in input_line)
+                if isinstance(input_line[0], list):
+                    line = ''.join(chunk[0][0] if chunk else '' for chunk in input_line)
+                else:
+                    line = input_line
+                prob, score = [1.0] * len(line), 0
+                line = line.replace(GAP, '')
+                jl = -len(prob)
+            out_lines.append(line)
+            out_probs.append(prob)
+            out_scores.append(score)
+            out_len.append(jl)
+        path, dist = eng.alignment_paths(align, layout, np.asarray(input_lens, np.int32),
+                                         np.asarray(out_len, np.int32), 1. / self.voc_size)
+        path, dist = path.cpu().numpy(), dist.cpu().numpy()
+        realignments = []
+        for j in range(B):
+            i_max = int(input_lens[j])
+            if i_max < 1 or out_len[j] == 0:
+                realignments.append({})
+                continue
+            row = path[j, :i_max + 1]
+            d = {i_max: int(row[i_max])}                      # same insertion order as the reference's dict
+            d.update({int(i): int(row[i]) for i in range(i_max - 1, 0, -1) if row[i] >= 0})
+            d[0] = 0
+            realignments.append(d)
+        return out_lines, out_probs, out_scores, realignments, [float(x) for x in dist]
+
     def _beam_sparse(self, lines, idx, val, want_align=True):
         eng = self._get_engine()
         bp = eng.beam_params(batch_size=min(int(self.batch_size), 256), beam_width_in=self.beam_width_in,

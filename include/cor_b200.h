@@ -139,6 +139,23 @@ int cor_decode_beam_batch(cor_model* m, const cor_lines* device_lines, const cor
                           int32_t* out_chars, float* out_probs, double* out_scores,
                           int32_t* out_len, float* out_align, int64_t* stats, void* stream);
 
+/* ---- hard re-alignment path per line: replaces the per-line Python call
+ * `_alignment2path(alignment, input_line_len, len(output_line), 1./voc_size)` of the OCR-D wrapper
+ * (wrapper/transcode.py:279-349, called at :126) — the only consumer of the decoders' alignments —
+ * so that (t_max+1) ints and one double per line cross to the host instead of S*T floats.
+ * `align` is the DEVICE alignment array of cor_decode_greedy_batch (stride_step = n_rows*t_max,
+ * stride_row = t_max) or of cor_decode_beam_batch (stride_step = t_max, stride_row = 2*t_max*t_max):
+ * a(row, step j, position i) = align[j*stride_step + row*stride_row + i].
+ * in_len[row] = input_line_len (<= t_max), out_len[row] = len(output_line) (<= s_max); a negative
+ * out_len means "identity matrix of that size" (the beam fallback of correct_lines, seq2seq.py:835).
+ * min_score is compared in double, like np.float32 > python float under the reference's numpy.
+ * out_path int32 [n_rows][path_ld], path_ld >= t_max+1: out_path[row][i] = output position of input
+ * position i, -1 where the reference's dict has no key; entry [in_len] = out_len, entry [0] = 0.
+ * out_dist double [n_rows] = sum of (1 - score) along the path.  All pointers DEVICE. */
+int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_row,
+                        int n_rows, int t_max, int s_max, const int32_t* in_len, const int32_t* out_len,
+                        double min_score, int32_t* out_path, int path_ld, double* out_dist, void* stream);
+
 /* ---- instrumentation for bench.py: kernels launched since the last reset, and device
  * time accumulated by the GEMM kernels between cor_prof_enable(1) and cor_prof_enable(0). */
 int64_t cor_launch_count(int reset);

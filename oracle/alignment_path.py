@@ -30,7 +30,10 @@ def forward_table(alignment, i_max, j_max, min_score):
     table = np.zeros((i_max, j_max), np.float32)
     if i_max == 0 or j_max == 0:
         return table
-    todo = a > np.float32(min_score)
+    if _dec.PROMOTION == "nep50":
+        todo = a > np.float32(min_score)
+    else:
+        todo = a.astype(np.float64) > float(min_score)   # np.float32 > python float compares in float64 (numpy<1.24)
     todo[0, 0] = True                               # the walk starts at (0,0) unconditionally
     for j in range(j_max):
         for i in np.flatnonzero(todo[j]):
