@@ -31,12 +31,12 @@ extern int64_t g_launches;   // kernels launched (bench.py's gpu_launches)
 
 // ------------------------------------------------------------------ GEMM
 // C[M,N] = sum_s A_s[M,K_s] * B_s[N,K_s]^T   (A row-major, B "K-major": one row per output column)
-// Every B operand is a weight prepared at load time; `B_lo` is the TF32 residual of B
-// (B = hi + lo with hi = B rounded to TF32), used only by the tcgen05 3xTF32 path, which also
+// Every B operand is a weight prepared at load time; `B_lo` is the fp16 residual of B
+// (B = hi + lo with hi = B rounded to fp16; both stored as packed halves behind the float* type), used only by the tcgen05 3-pass path, which also
 // wants A split the same way (A = A_hi + A_lo, produced by the epilogue that wrote A).
 struct GemmSeg {
-    const float* A;  int lda;      // fp32 (FFMA path) or TF32-hi part (tensor path)
-    const float* A_lo;             // TF32 residual or nullptr
+    const float* A;  int lda;      // fp32 (FFMA path) or fp16 head (tensor path)
+    const float* A_lo;             // fp16 residual or nullptr
     const float* B;  int ldb;
     const float* B_lo;
     int K;
@@ -46,7 +46,7 @@ constexpr int kMaxSegs = 3;
 // plain epilogue: C = act(acc + bias)
 struct StoreEpi {
     float* C; int ldc;
-    float* C_lo;               // if set: C gets the TF32-hi part and C_lo the residual
+    float* C_lo;               // if set: C gets the fp16 head and C_lo the residual
     const float* bias;         // [N] or nullptr
     int act;                   // 0 none, 1 tanh
     // optional second destination: columns >= n_split (a multiple of 32) go to C2[row][col - n_split]
@@ -66,7 +66,7 @@ struct LstmEpi {
     const float* h_prev;       // [M][W] (copied through for inactive rows)
     const float* h_prev_lo;
     float* h_out;              // [M][W]
-    float* h_out_lo;           // TF32 residual of h_out or nullptr
+    float* h_out_lo;           // fp16 residual of h_out or nullptr
     const int32_t* row_T;
     int step;
     int reverse;

@@ -41,7 +41,7 @@ typedef struct cor_config {
     int32_t lm_predict;
     int32_t window_width;      /* 5 in the reference (seq2seq.py:347,452) */
     int32_t eos_index;         /* index of '\n' in the mapping (1 when built by map_files, seq2seq.py:580-586) */
-    int32_t gemm_mode;         /* 0 auto, 1 force FFMA fp32, 2 force tcgen05 3xTF32 */
+    int32_t gemm_mode;         /* 0 auto, 1 force FFMA fp32, 2 force tcgen05 3-pass fp16 hi/lo */
 } cor_config;
 
 /* Input lines of one call — replaces the dense (B,T,V) array of
@@ -74,7 +74,7 @@ int cor_abi_version(void);
 int cor_model_create(const cor_config* cfg, int device, cor_model** out);
 /* One Keras weight by layer name and position inside the layer (SURVEY.md A.5 order), in the
  * Keras (in, out) layout; the Keras -> kernel repack (transposition to K-major, gate
- * interleave, TF32 hi/lo split) happens here.  LSTM layers must be in LSTM (not CuDNNLSTM)
+ * interleave, fp16 hi/lo split) happens here.  LSTM layers must be in LSTM (not CuDNNLSTM)
  * format: the host class converts CuDNN-format layers (bias 8W) the way Keras does on load. */
 int cor_model_set_weight(cor_model* m, const char* keras_layer, int index,
                          const float* host, const int64_t* shape, int rank);
@@ -159,7 +159,7 @@ int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_
 /* ---- instrumentation for bench.py: kernels launched since the last reset, and device
  * time accumulated by the GEMM kernels between cor_prof_enable(1) and cor_prof_enable(0). */
 int64_t cor_launch_count(int reset);
-/* test hook: C[M,N] = A[M,K] . B[N,K]^T (device fp32) through one GEMM kernel: 1 = FFMA, 2 = tcgen05 3xTF32 */
+/* test hook: C[M,N] = A[M,K] . B[N,K]^T (device fp32) through one GEMM kernel: 1 = FFMA, 2 = tcgen05 3-pass fp16 hi/lo */
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream);
 int cor_prof_enable(int on);   /* on: reset and start bracketing every LSTM-GEMM launch with events */
 int cor_prof_read(double* total_ms, int64_t* launches, double* flops);   /* synchronizes the device */
