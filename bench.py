@@ -129,6 +129,9 @@ def run_reference(args):
     if rank != 0:
         return
     cores = host_threads()
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm is meant to use every host thread
+    from threadpoolctl import threadpool_limits
+    threadpool_limits(limits=cores)
     total = args.steps + args.warmup
     probe_lines = 8 if args.workload == "greedy" else 4
     rate, _ = cpu_oracle_rate(args.workload, probe_lines)
@@ -260,8 +263,21 @@ def measure(args, eng, workload, rank, world, local, sample_clocks):
             "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra}
 
 
+def measured_traffic(workload, rows):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/traffic.json), or None when no capture exists for this workload at this row count."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(workload)
+    except (OSError, ValueError):
+        return None, None
+    if not t or t.get("rows") != rows:
+        return None, None
+    return t["bytes_per_launch"], t["source"]
+
+
 def bench_line(args, r, workload, world, peaks):
     peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    traffic, traffic_src = measured_traffic(workload, r["L"])
     peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1400 (of fallback)"
     achieved = r["k_flops"] / (r["k_ms"] * 1e-3) / 1e12 if r["k_ms"] > 0 else 0.0
     line = {
@@ -274,7 +290,7 @@ def bench_line(args, r, workload, world, peaks):
         "gpu_launches": r["launches"],
         "clocks": r["clocks"],
         "roofline": {"bound": "tensor", "kernel": "GEMM + fused LSTM-cell epilogue", "achieved": achieved,
-                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
+                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": peak_src, "launches": r["k_n"], "kernel_ms_per_step": r["k_ms"] / args.steps,
                      "kernel_share_of_step": r["k_ms"] / r["ms"] if r["ms"] else None,
                      "precision": "fp32 via FFMA" if args.gemm_mode == 1 else "fp32-grade (see DESIGN.md)"},
@@ -314,6 +330,11 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    # stdout carries exactly one JSON line: anything libraries print while we measure (NCCL's version
+    # banner under NCCL_DEBUG=VERSION, for one) goes to stderr instead
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     topo, w, mapping = build_model()
@@ -322,6 +343,11 @@ def main():
     main_r = measure(args, eng, args.workload, rank, world, local, sample_clocks=(rank == 0))
     other_r = None if args.only else measure(args, eng, other, rank, world, local, sample_clocks=(rank == 0))
 
+    if world > 1:
+        dist.barrier()
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    os.close(saved_stdout)
     if rank == 0:
         peaks = {}
         try:
@@ -335,6 +361,8 @@ def main():
                                                "clocks", "roofline", "algorithmic_gflop_per_line", "whole_step_tflops")}
         if world == 1 and not args.no_cpu:
             cores = host_threads()
+            from threadpoolctl import threadpool_limits
+            threadpool_limits(limits=cores)
             n_cpu = args.cpu_lines or (128 if args.workload == "greedy" else 48)
             v, dt = cpu_oracle_rate(args.workload, n_cpu)
             line["cpu_baseline"] = {"value": v, "unit": "chars/s", "cores": cores, "kind": "port",

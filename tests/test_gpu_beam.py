@@ -134,3 +134,29 @@ def test_beam_device_entry_matches_host_entry():
             nj = int(h[3][j])
             assert (h[0][j, :nj].numpy() == d[0][j, :nj].cpu().numpy()).all()
             assert np.allclose(h[1][j, :nj].numpy(), d[1][j, :nj].cpu().numpy(), atol=1e-6)
+
+
+def test_beam_c4_full_size():
+    """BASELINE config 4 at full size (depth 3 / width 768 / V 512, deep bidirectional encoder, residual
+    connections, LM-rated beam; D = 1536): default beam on a few lines against the oracle run live, plus
+    a low-rejection case with competing hypotheses."""
+    from oracle.model import Topology, init_weights
+    from tests.common import synthetic_alphabet
+    topo = Topology(width=768, depth=3, voc_size=512, deep_bidirectional_encoder=True,
+                    residual_connections=True, lm_predict=True)
+    w, mapping = init_weights(topo, 7, "U"), synthetic_alphabet(512)
+    eng = _engine(topo, w, 0)
+    for lines, params in ((synthetic_lines(mapping, 5, 40, seed=1004, min_length=30), dict(rejection_threshold=0.3)),
+                          (synthetic_lines(mapping, 3, 7, seed=1005, min_length=5),
+                           dict(rejection_threshold=0.004, beam_width_in=3, batch_size=32))):
+        st = {}
+        r_text, r_probs, r_score, _ = od.correct_lines(topo, w, mapping, lines, fast=False, greedy=False,
+                                                       beam_params=params, stats=st)
+        text, probs, scores, lens, _, stats = _run_beam(eng, mapping, lines, params, budget=8 << 30)
+        for j, line in enumerate(lines):
+            got = text[j] if lens[j] > 0 else line
+            assert got == r_text[j]
+            assert stats[j, 0] == st["lines"][j]["iterations"] and stats[j, 1] == st["lines"][j]["hypothesis_steps"]
+            if lens[j] > 0:
+                assert abs(scores[j] - r_score[j]) < 1e-4
+                assert np.abs(probs[j, :lens[j]] - np.asarray(r_probs[j], np.float32)).max() < 1e-4
