@@ -275,6 +275,30 @@ def measured_traffic(workload, rows):
     return t["bytes_per_launch"], t["source"]
 
 
+def measure_page(args, eng, n_lines):
+    """The small-batch regime (one OCR-D page per call, wrapper/transcode.py:111): fast greedy decode of
+    `n_lines` lines through the host entry point; latency per call and per decoder timestep."""
+    import torch
+    T = LINE_LEN + 1
+    idx = [torch.as_tensor(make_indices(n_lines, 2000 + s)).pin_memory() for s in range(4)]
+    host_T = torch.full((n_lines,), T, dtype=torch.int32).pin_memory()
+    out = eng.host_outputs(n_lines, T)
+    for s in range(3):
+        eng.correct_greedy_host(idx[s % 4], None, host_T, out=out)
+    torch.cuda.synchronize()
+    eng.launch_count(reset=True)
+    reps = 10
+    t0 = time.perf_counter()
+    for s in range(reps):
+        eng.correct_greedy_host(idx[s % 4], None, host_T, out=out)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / reps
+    return {"lines": n_lines, "ms_per_call": dt * 1e3, "us_per_decoder_timestep": dt * 1e6 / (2 * T + T),
+            "timesteps_per_call": 3 * T, "chars_per_s": LINE_LEN * n_lines / dt,
+            "gpu_launches_per_call": eng.launch_count() / reps,
+            "api": "cor_correct_greedy_host (pinned host buffers), T encoder + 2T decoder timesteps"}
+
+
 def bench_line(args, r, workload, world, peaks):
     peak = peaks.get("bf16_tflops_sustained", 1400.0)
     traffic, traffic_src = measured_traffic(workload, r["L"])
@@ -314,6 +338,8 @@ def main():
     ap.add_argument("--gemm-mode", type=int, default=0)
     ap.add_argument("--cpu-lines", type=int, default=None)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--page-lines", type=int, default=32, help="lines of the small-batch (one page) latency leg; 0 = skip")
+    ap.add_argument("--page-only", action="store_true", help="run just the small-batch latency leg")
     ap.add_argument("--only", action="store_true", help="measure only --workload (skip the other decoder)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -339,9 +365,15 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     topo, w, mapping = build_model()
     eng = Engine(topo_dict(topo), w, device=local, eos_index=1, gemm_mode=args.gemm_mode)
+    if args.page_only:
+        print_page = measure_page(args, eng, args.page_lines)
+        sys.stdout.flush(); os.dup2(saved_stdout, 1)
+        print(json.dumps({"page": print_page}))
+        return
     other = "greedy" if args.workload == "beam" else "beam"
     main_r = measure(args, eng, args.workload, rank, world, local, sample_clocks=(rank == 0))
     other_r = None if args.only else measure(args, eng, other, rank, world, local, sample_clocks=(rank == 0))
+    page_r = measure_page(args, eng, args.page_lines) if (rank == 0 and args.page_lines > 0 and not args.only) else None
 
     if world > 1:
         dist.barrier()
@@ -359,6 +391,8 @@ def main():
             o = bench_line(args, other_r, other, world, peaks)
             line["also"] = {k: o[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "gpu_launches",
                                                "clocks", "roofline", "algorithmic_gflop_per_line", "whole_step_tflops")}
+        if page_r is not None:
+            line["page"] = page_r
         if world == 1 and not args.no_cpu:
             cores = host_threads()
             from threadpoolctl import threadpool_limits

@@ -55,8 +55,9 @@ static void prof_end(cudaStream_t st, int M, const int* m_dev, int N, const Gemm
     g_prof.launches += 1;
 }
 
-// GEMM dispatch: tcgen05 3xFP16 when the model keeps split operands and the tile is worth it,
-// exact FFMA otherwise (small M).  Both consume the same operand representation.
+// GEMM dispatch: tcgen05 3xFP16 whenever the model keeps split operands and the shape is TMA-aligned
+// (gemm_tc.cu picks pair / single / narrow tiles from M and N), the exact FFMA kernel otherwise.
+// Both consume the same operand representation.
 static bool tc_shape_ok(const GemmSeg* s, int n) {
     for (int i = 0; i < n; ++i) if (s[i].K % 64 != 0 || s[i].lda % 8 != 0 || s[i].ldb % 8 != 0) return false;
     return true;
@@ -512,7 +513,7 @@ int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launc
 // Test hook: C[M,N] = A[M,K] . B[N,K]^T through one of the two GEMM kernels (1 = FFMA, 2 = tcgen05 3xFP16).
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    COR_CHECK(mode == 1 || mode == 2, "mode must be 1 (FFMA) or 2 (tcgen05)");
+    COR_CHECK(mode >= 1 && mode <= 3, "mode must be 1 (FFMA), 2 (tcgen05, tile shape picked from M and N) or 3 (tcgen05, 128x32 tiles forced)");
     StoreEpi e{C, N, nullptr, nullptr, 0};
     if (mode == 1) {
         GemmSeg s{A, K, nullptr, B, K, nullptr, K};
@@ -525,7 +526,9 @@ int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B
     int rc = launch_split(st, A, a_hi, a_lo, na) || launch_split(st, B, b_hi, b_lo, nb);
     if (!rc) {
         GemmSeg s{a_hi, K, a_lo, b_hi, K, b_lo, K};
+        tc_force_narrow(mode == 3);
         rc = gemm_store_tc(st, M, nullptr, N, &s, 1, e);
+        tc_force_narrow(false);
     }
     cudaError_t err = cudaStreamSynchronize(st);
     cudaFree(a_hi); cudaFree(a_lo); cudaFree(b_hi); cudaFree(b_lo);
@@ -572,7 +575,8 @@ int cor_model_create(const cor_config* cfg, int device, cor_model** out) {
     m->W = cfg->width; m->d = cfg->depth; m->V = cfg->voc_size; m->Vp = (cfg->voc_size + 127) & ~127;
     m->D = (cfg->depth == 1 || cfg->deep_bidirectional_encoder) ? 2 * cfg->width : cfg->width;
     m->split = cfg->gemm_mode == 2 || (cfg->gemm_mode == 0 && tc_available());
-    m->tc_min_rows = cfg->gemm_mode == 2 ? 1 : 64;   // below one half tile the exact FFMA kernel is used
+    m->tc_min_rows = 1;     // page-sized batches run the narrow-tile tcgen05 kernel (8 rows: 19 ms per page call against 110 ms on the FFMA kernel)
+    if (const char* v = getenv("COR_TC_MIN_ROWS")) m->tc_min_rows = atoi(v);
     *out = m;
     return 0;
 }

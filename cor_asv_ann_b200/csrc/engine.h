@@ -89,6 +89,7 @@ int gemm_lstm_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSe
 int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi);
 int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi);
 bool tc_available();
+void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape
 
 // ------------------------------------------------------------------ small kernels (kernels.cu)
 // X[t][r][:] = sum_k val*E[idx]; Xr[T_r-1-t][r][:] = same (reversed copy for backward scans)

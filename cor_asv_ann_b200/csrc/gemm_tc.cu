@@ -28,7 +28,8 @@ namespace cor {
 
 namespace {
 
-constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int BN_WIDE = 256, BN_NARROW = 32;   // tile widths: full tiles / page-sized M (see pick_bn)
 constexpr int ELT = 2;                          // bytes per operand element (fp16)
 constexpr int A_TILE = BM * BK * ELT;          // 16 KB
 // NCTA = 1: one CTA per 128 x 256 tile, 2 stages of {A_hi, A_lo, B_hi, B_lo} = 96 KB.
@@ -36,11 +37,14 @@ constexpr int A_TILE = BM * BK * ELT;          // 16 KB
 // HALF of the B tile (128 of the 256 columns), 64 KB per stage, 3 stages.  The pair reads 128 KB from
 // L2 per k-block for twice the math of the single CTA's 96 KB: the kernel sits on the L2->SM path
 // (LTS cap ~6.3 KB/clk chip-wide), so this is what lifts the tensor-pipe duty.
-template <int NCTA> struct Geo {
+// BN = 32 (NCTA = 1 only): the page-sized regime (one OCR-D page per call, M of a few dozen rows).  There a
+// launch is bound by how fast ONE SM can pull its share of the weights out of L2, so the columns are
+// spread over 8x as many CTAs (64 at N = 2048) with 5 stages of 40 KB in flight per CTA.
+template <int NCTA, int BN> struct Geo {
     static constexpr int B_ROWS = BN / NCTA;
     static constexpr int B_TILE = B_ROWS * BK * ELT;
     static constexpr int STAGE_BYTES = 2 * A_TILE + 2 * B_TILE;
-    static constexpr int STAGES = NCTA == 1 ? 2 : 3;
+    static constexpr int STAGES = NCTA == 2 ? 3 : (BN == BN_WIDE ? 2 : 5);
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
     static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * NCTA) >> 4) << 24);
 };
@@ -166,7 +170,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
 }
 // kind::f16, D = f32 (c_format 1 at [4,6)), A/B = f16 (format 0 at [7,10) / [10,13)), both K-major,
 // N at [17,23) >> 3, M at [24,29) >> 4
-// (Geo<NCTA>::IDESC; M = 256 for the pair)
+// (Geo<NCTA, BN>::IDESC; M = 256 for the pair)
 
 // ------------------------------------------------------------------ vectorised LSTM epilogue (8 units of one row)
 __device__ __forceinline__ void st4(float* p, size_t off, const float* v) {
@@ -281,9 +285,9 @@ __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0
 }
 
 // ------------------------------------------------------------------ the kernel
-template <int EPI, int NCTA, typename Epi>
+template <int EPI, int NCTA, int BN, typename Epi>
 __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams p, const Epi epi) {
-    using G = Geo<NCTA>;
+    using G = Geo<NCTA, BN>;
     constexpr int STAGES = G::STAGES, STAGE_BYTES = G::STAGE_BYTES, B_TILE = G::B_TILE;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // SWIZZLE_128B wants 1024-byte alignment
@@ -411,7 +415,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
         // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 of its own CTA =====
         // the LSTM epilogue is a chain of MUFU and load latencies per row: two warps per scheduler hide them
         const int wq = (warp - 4) & 3, half = (warp - 4) >> 2;
-        constexpr int CH_PER = (BN / 32) / (EPI_WARPS / 4);
         int acc = 0; uint32_t acc_phase = 0;
         for (int tile = unit; tile < num_tiles; tile += n_units) {
             const int m0 = (tile / p.tiles_n) * (BM * NCTA) + (int)rank * BM, n0 = (tile % p.tiles_n) * BN;
@@ -420,7 +423,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
             const int row = m0 + wq * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int ch = half * CH_PER; ch < (half + 1) * CH_PER; ++ch) {
+            for (int ch = half; ch < BN / 32; ch += EPI_WARPS / 4) {
                 uint32_t z[32];
                 tmem_ld32(taddr + ch * 32, z);
                 tmem_ld_wait();
@@ -475,19 +478,19 @@ bool init_tc() {
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) return false;
     g_encode = (EncodeTiledFn)fn;
-    if (cudaFuncSetAttribute(gemm_tc_kernel<0, 1, StoreEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<1>::SMEM_BYTES) != cudaSuccess) return false;
-    if (cudaFuncSetAttribute(gemm_tc_kernel<1, 1, LstmEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<1>::SMEM_BYTES) != cudaSuccess) return false;
-    if (cudaFuncSetAttribute(gemm_tc_kernel<0, 2, StoreEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<2>::SMEM_BYTES) != cudaSuccess) return false;
-    if (cudaFuncSetAttribute(gemm_tc_kernel<1, 2, LstmEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<2>::SMEM_BYTES) != cudaSuccess) return false;
+    auto opt_in = [](auto kern, int bytes) { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess; };
+    if (!opt_in(gemm_tc_kernel<0, 1, BN_WIDE, StoreEpi>, Geo<1, BN_WIDE>::SMEM_BYTES) || !opt_in(gemm_tc_kernel<1, 1, BN_WIDE, LstmEpi>, Geo<1, BN_WIDE>::SMEM_BYTES) ||
+        !opt_in(gemm_tc_kernel<0, 1, BN_NARROW, StoreEpi>, Geo<1, BN_NARROW>::SMEM_BYTES) || !opt_in(gemm_tc_kernel<1, 1, BN_NARROW, LstmEpi>, Geo<1, BN_NARROW>::SMEM_BYTES) ||
+        !opt_in(gemm_tc_kernel<0, 2, BN_WIDE, StoreEpi>, Geo<2, BN_WIDE>::SMEM_BYTES) || !opt_in(gemm_tc_kernel<1, 2, BN_WIDE, LstmEpi>, Geo<2, BN_WIDE>::SMEM_BYTES)) return false;
     {   // how many CTA pairs can be resident at once (a GPC with an odd SM count leaves one SM unpaired):
         // a persistent grid must not exceed it, or the surplus pairs would run as a second wave
         cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3(g_num_sms & ~1); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = Geo<2>::SMEM_BYTES;
+        cfg.gridDim = dim3(g_num_sms & ~1); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = Geo<2, BN_WIDE>::SMEM_BYTES;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
         int nc = 0;
-        if (cudaOccupancyMaxActiveClusters(&nc, gemm_tc_kernel<1, 2, LstmEpi>, &cfg) == cudaSuccess && nc > 0) g_max_pairs = nc;
+        if (cudaOccupancyMaxActiveClusters(&nc, gemm_tc_kernel<1, 2, BN_WIDE, LstmEpi>, &cfg) == cudaSuccess && nc > 0) g_max_pairs = nc;
         else { g_max_pairs = 0; (void)cudaGetLastError(); }
         if (getenv("COR_NO_PAIR")) g_max_pairs = 0;     // debug switch: single-CTA kernel everywhere
     }
@@ -518,68 +521,79 @@ int get_map(const float* ptr, long long rows, long long cols, long long ld, int 
     return 0;
 }
 
-int fill_params(int ncta, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, TcParams* p) {
+int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, TcParams* p) {
     COR_CHECK(nseg >= 1 && nseg <= kMaxSegs, "bad segment count");
     p->nseg = nseg; p->M = M; p->m_dev = m_dev; p->N = N;
-    p->tiles_n = (N + BN - 1) / BN;
+    p->tiles_n = (N + bn - 1) / bn;
     for (int s = 0; s < nseg; ++s) {
         const GemmSeg& g = segs[s];
         COR_CHECK(g.A_lo && g.B_lo, "tcgen05 path needs split (hi, lo) operands");
         COR_CHECK(g.K > 0 && g.K % BK == 0, "K must be a positive multiple of 64");
         p->kblocks[s] = g.K / BK;
         if (get_map(g.A, M, g.K, g.lda, BM, &p->a_hi[s]) || get_map(g.A_lo, M, g.K, g.lda, BM, &p->a_lo[s]) ||
-            get_map(g.B, N, g.K, g.ldb, BN / ncta, &p->b_hi[s]) || get_map(g.B_lo, N, g.K, g.ldb, BN / ncta, &p->b_lo[s])) return 1;
+            get_map(g.B, N, g.K, g.ldb, bn / ncta, &p->b_hi[s]) || get_map(g.B_lo, N, g.K, g.ldb, bn / ncta, &p->b_lo[s])) return 1;
     }
     return 0;
 }
 
-// The pair kernel pays off once there are enough 256-row tiles to fill the resident pairs; below that
-// the single-CTA kernel has the finer granularity (128-row tiles on 148 CTAs).
-int pick_ncta(int M, int N) {
-    if (g_max_pairs <= 0) return 1;
-    const long long pair_tiles = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
-    return pair_tiles >= g_max_pairs ? 2 : 1;
+int g_force_bn = 0;      // test hook (cor_debug_gemm mode 3): force the narrow tile
+
+// Tile shape.  The pair kernel pays off once there are enough 256-row tiles to fill the resident pairs;
+// below that the single-CTA kernel has the finer granularity (128-row tiles on 148 CTAs); and while the
+// 32-column tiles still fit in ONE wave (a page of lines: M <= 256 rows at N = 2048 is <= 128 tiles)
+// they spread the weight stream over 8x as many SMs as the wide tiles would.
+void pick_shape(int M, int N, int* ncta, int* bn) {
+    const long long tiles_m = (M + BM - 1) / BM, narrow = tiles_m * ((N + BN_NARROW - 1) / BN_NARROW);
+    if (g_force_bn == BN_NARROW || (narrow <= g_num_sms && !getenv("COR_NO_NARROW"))) { *ncta = 1; *bn = BN_NARROW; return; }
+    *bn = BN_WIDE;
+    const long long pair_tiles = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + BN_WIDE - 1) / BN_WIDE);
+    *ncta = (g_max_pairs > 0 && pair_tiles >= g_max_pairs) ? 2 : 1;
 }
-int grid_for(int ncta, int M, int N) {
-    const long long tiles = (long long)((M + BM * ncta - 1) / (BM * ncta)) * ((N + BN - 1) / BN);
+int grid_for(int ncta, int bn, int M, int N) {
+    const long long tiles = (long long)((M + BM * ncta - 1) / (BM * ncta)) * ((N + bn - 1) / bn);
     if (ncta == 2) return 2 * (int)std::min<long long>(tiles, g_max_pairs);
     return (int)std::min<long long>(tiles, g_num_sms);
 }
 
-template <int EPI, int NCTA, typename Epi>
+template <int EPI, int NCTA, int BN, typename Epi>
 int launch_tc(cudaStream_t st, int M, int N, const TcParams& p, const Epi& epi) {
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid_for(NCTA, M, N)); cfg.blockDim = dim3(NTHREADS);
-    cfg.dynamicSmemBytes = Geo<NCTA>::SMEM_BYTES; cfg.stream = st;
+    cfg.gridDim = dim3(grid_for(NCTA, BN, M, N)); cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = Geo<NCTA, BN>::SMEM_BYTES; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = NCTA; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    COR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, NCTA, Epi>, p, epi));
+    COR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, NCTA, BN, Epi>, p, epi));
     ++g_launches;
     return 0;
+}
+
+template <int EPI, typename Epi>
+int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const Epi& epi) {
+    int ncta, bn;
+    pick_shape(M, N, &ncta, &bn);
+    TcParams p;
+    if (fill_params(ncta, bn, M, m_dev, N, segs, nseg, &p)) return 1;
+    if (bn == BN_NARROW) return launch_tc<EPI, 1, BN_NARROW, Epi>(st, M, N, p, epi);
+    return ncta == 2 ? launch_tc<EPI, 2, BN_WIDE, Epi>(st, M, N, p, epi) : launch_tc<EPI, 1, BN_WIDE, Epi>(st, M, N, p, epi);
 }
 
 }  // namespace
 
 bool tc_available() { return init_tc(); }
+void tc_force_narrow(bool on) { g_force_bn = on ? BN_NARROW : 0; }
 
 int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi) {
     if (M <= 0) return 0;
     COR_CHECK(init_tc(), "tcgen05 path unavailable on this device");
-    const int ncta = pick_ncta(M, N);
-    TcParams p;
-    if (fill_params(ncta, M, m_dev, N, segs, nseg, &p)) return 1;
-    return ncta == 2 ? launch_tc<0, 2, StoreEpi>(st, M, N, p, epi) : launch_tc<0, 1, StoreEpi>(st, M, N, p, epi);
+    return dispatch_tc<0, StoreEpi>(st, M, m_dev, N, segs, nseg, epi);
 }
 
 int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi) {
     if (M <= 0) return 0;
     COR_CHECK(init_tc(), "tcgen05 path unavailable on this device");
     COR_CHECK(N == 4 * epi.W && epi.W % 8 == 0, "LSTM epilogue needs N == 4W with W a multiple of 8");
-    const int ncta = pick_ncta(M, N);
-    TcParams p;
-    if (fill_params(ncta, M, m_dev, N, segs, nseg, &p)) return 1;
-    return ncta == 2 ? launch_tc<1, 2, LstmEpi>(st, M, N, p, epi) : launch_tc<1, 1, LstmEpi>(st, M, N, p, epi);
+    return dispatch_tc<1, LstmEpi>(st, M, m_dev, N, segs, nseg, epi);
 }
 
 }  // namespace cor

@@ -30,7 +30,7 @@ struct cor_model {
     int device = 0;
     int W = 0, d = 0, V = 0, Vp = 0, D = 0;
     bool split = false;       // activations and weights kept as TF32 (hi, lo) pairs for the tcgen05 path
-    int tc_min_rows = 64;
+    int tc_min_rows = 1;
     bool finalized = false;
     std::map<std::string, std::vector<cor::HostWeight>> host;   // until finalize
     std::vector<void*> allocs;

@@ -159,7 +159,7 @@ int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_
 /* ---- instrumentation for bench.py: kernels launched since the last reset, and device
  * time accumulated by the GEMM kernels between cor_prof_enable(1) and cor_prof_enable(0). */
 int64_t cor_launch_count(int reset);
-/* test hook: C[M,N] = A[M,K] . B[N,K]^T (device fp32) through one GEMM kernel: 1 = FFMA, 2 = tcgen05 3-pass fp16 hi/lo */
+/* test hook: C[M,N] = A[M,K] . B[N,K]^T (device fp32) through one GEMM kernel: 1 = FFMA, 2 = tcgen05 3-pass fp16 hi/lo, 3 = the same with the page-sized 128x32 tiles forced */
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream);
 int cor_prof_enable(int on);   /* on: reset and start bracketing every LSTM-GEMM launch with events */
 int cor_prof_read(double* total_ms, int64_t* launches, double* flops);   /* synchronizes the device */

@@ -1,4 +1,4 @@
-"""The two GEMM kernels against a float64 matmul, through the C-ABI test hook cor_debug_gemm."""
+"""The three GEMM kernels against a float64 matmul, through the C-ABI test hook cor_debug_gemm."""
 import ctypes as C
 
 import numpy as np
@@ -28,6 +28,15 @@ def test_ffma_gemm(shape):
     err = _run(1, *shape)
     print("ffma %s: %.3g" % (shape, err))
     assert err < 1e-6
+
+
+@pytest.mark.parametrize("shape", [(1, 16, 64), (8, 512, 512), (32, 2048, 1536), (33, 1024, 576), (64, 2048, 1024),
+                                   (61, 40, 128), (130, 48, 64), (300, 2048, 512)])
+def test_tc_narrow_gemm(shape):
+    """The page-sized (small M) 128x32-tile variant of the tcgen05 kernel, with row and column tails."""
+    err = _run(3, *shape)
+    print("narrow %s: %.3g" % (shape, err))
+    assert err < 2e-6
 
 
 @pytest.mark.parametrize("shape", [(128, 256, 64), (128, 256, 128), (256, 512, 512), (1000, 2048, 1536),
