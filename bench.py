@@ -299,6 +299,40 @@ def measure_page(args, eng, n_lines):
             "api": "cor_correct_greedy_host (pinned host buffers), T encoder + 2T decoder timesteps"}
 
 
+def measure_predict(args, topo, w, mapping, device, n_lines):
+    """Row N2, the call a user of the reference makes (scripts/proc.py:62): Sequence2Sequence.predict on a
+    text file, fast mode, strings in -> strings + scores out; 64 reference batches per engine call with
+    the next super-batch read and encoded in a worker thread, against the reference's one-batch loop."""
+    import tempfile
+    from cor_asv_ann_b200.seq2seq import Sequence2Sequence
+    s = Sequence2Sequence()
+    s.width, s.depth, s.voc_size, s.mapping = topo.width, topo.depth, topo.voc_size, mapping
+    s.device = device
+    s.configure()
+    for layer, arrs in w.items():
+        s.encoder_decoder_model.get_layer(layer).set_weights(arrs)
+    s.status = 2
+    i2c = np.array([ord(mapping[1][i]) if mapping[1][i] else 0 for i in range(VOC)], dtype=np.uint32)
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        def run(n, superbatch, seed):
+            path = os.path.join(tmp, "lines_%d_%d.txt" % (n, superbatch))
+            idx = make_indices(n, seed)[:, :, 0]
+            with open(path, "w", encoding="utf-8") as f:
+                f.write(i2c[idx].tobytes().decode("utf-32-le"))
+            s.superbatch = superbatch
+            t0 = time.perf_counter()
+            n_out = sum(len(lines) for _, lines, _ in s.predict([path], fast=True, greedy=True))
+            dt = time.perf_counter() - t0
+            assert n_out == n
+            return LINE_LEN * n / dt
+        run(4 * REF_BATCH, 4, 3000)                       # warm-up (engine creation, workspaces)
+        out["chars_per_s"] = run(n_lines, 64, 3001)
+        out["chars_per_s_one_batch_per_call"] = run(min(n_lines, 8 * REF_BATCH), 1, 3002)
+    out.update({"lines": n_lines, "superbatch": 64, "api": "Sequence2Sequence.predict(text file, fast=True), file read + encode + decode + strings"})
+    return out
+
+
 def bench_line(args, r, workload, world, peaks):
     peak = peaks.get("bf16_tflops_sustained", 1400.0)
     traffic, traffic_src = measured_traffic(workload, r["L"])
@@ -340,6 +374,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--page-lines", type=int, default=32, help="lines of the small-batch (one page) latency leg; 0 = skip")
     ap.add_argument("--page-only", action="store_true", help="run just the small-batch latency leg")
+    ap.add_argument("--predict-lines", type=int, default=65536, help="lines of the Sequence2Sequence.predict leg; 0 = skip")
+    ap.add_argument("--predict-only", action="store_true", help="run just the predict leg")
     ap.add_argument("--only", action="store_true", help="measure only --workload (skip the other decoder)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -365,6 +401,11 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     topo, w, mapping = build_model()
     eng = Engine(topo_dict(topo), w, device=local, eos_index=1, gemm_mode=args.gemm_mode)
+    if args.predict_only:
+        r = measure_predict(args, topo, w, mapping, local, args.predict_lines)
+        sys.stdout.flush(); os.dup2(saved_stdout, 1)
+        print(json.dumps({"predict": r}))
+        return
     if args.page_only:
         print_page = measure_page(args, eng, args.page_lines)
         sys.stdout.flush(); os.dup2(saved_stdout, 1)
@@ -374,6 +415,7 @@ def main():
     main_r = measure(args, eng, args.workload, rank, world, local, sample_clocks=(rank == 0))
     other_r = None if args.only else measure(args, eng, other, rank, world, local, sample_clocks=(rank == 0))
     page_r = measure_page(args, eng, args.page_lines) if (rank == 0 and args.page_lines > 0 and not args.only) else None
+    predict_r = measure_predict(args, topo, w, mapping, local, args.predict_lines) if (rank == 0 and world == 1 and args.predict_lines > 0 and not args.only) else None
 
     if world > 1:
         dist.barrier()
@@ -393,6 +435,8 @@ def main():
                                                "clocks", "roofline", "algorithmic_gflop_per_line", "whole_step_tflops")}
         if page_r is not None:
             line["page"] = page_r
+        if predict_r is not None:
+            line["predict"] = predict_r
         if world == 1 and not args.no_cpu:
             cores = host_threads()
             from threadpoolctl import threadpool_limits

@@ -17,6 +17,7 @@ import numpy as np
 
 from . import h5lite
 from .vectorize import lines_to_sparse, dense_to_sparse
+from .pipeline import StringTable, Prefetcher, chunked, float32_mean_neglog, merge_batches
 
 GAP = '\a'  # reserved for gap in input (seq2seq.py:29)
 
@@ -100,6 +101,8 @@ class Sequence2Sequence(object):
         self.device = 0
         self.gemm_mode = 0
         self.beam_budget_bytes = 8 << 30
+        self.superbatch = 64     # reference batches per engine call in predict() (16 384 lines at batch_size 256)
+        self.prefetch = True     # read + encode the next super-batch in a worker thread
         self._weights = {}
         self._engine = None
 
@@ -436,13 +439,20 @@ class Sequence2Sequence(object):
                 break
 
     def predict(self, filenames, fast=False, greedy=False, charmap=None):
-        '''apply model on text files (seq2seq.py:756-780): yields (filenames, lines, scores) per batch.'''
+        '''apply model on text files (seq2seq.py:756-780): yields (filenames, lines, scores) per batch.
+
+        Same batches, same order and same results as the reference's loop, but `superbatch` reference
+        batches share one engine call (correct_batches) and the next super-batch is read and encoded in
+        a worker thread while the GPU decodes the current one.'''
         assert self.status == 2
-        for batch in self.gen_lines(filenames, repeat=False, unsupervised=True, charmap=charmap):
-            lines_source, lines_sourceconf, _, lines_filename = batch
-            lines_result, _, scores_result, _ = self.correct_lines(lines_source, lines_sourceconf,
-                                                                   fast=fast, greedy=greedy)
-            yield (lines_filename, lines_result, scores_result)
+        batches = self.gen_lines(filenames, repeat=False, unsupervised=True, charmap=charmap)
+        groups = chunked(batches, max(int(self.superbatch), 1))
+        if self.prefetch:
+            groups = Prefetcher(groups, depth=2)
+        for group in groups:
+            results = self.correct_batches([(b[0], b[1]) for b in group], fast=fast, greedy=greedy, want_probs=False)
+            for batch, (lines_result, _, scores_result, _) in zip(group, results):
+                yield (batch[3], lines_result, scores_result)
 
     def vectorize_lines(self, encoder_input_sequences, decoder_input_sequences, encoder_conf_sequences=None):
         '''Convert a batch of source and target sequences to dense arrays (seq2seq.py:1020-1119).'''
@@ -491,18 +501,27 @@ class Sequence2Sequence(object):
         out.append(np.zeros(idx.shape[:2], np.float32))
         return out
 
-    def _greedy_sparse(self, idx, val, want_align=True):
+    def _strings(self, chars, lens):
+        table = getattr(self, '_string_table', None)
+        if table is None or table.i2c is not self.mapping[1]:
+            table = self._string_table = StringTable(self.mapping[1], self.voc_size)
+        return table.strings(chars, lens)
+
+    def _greedy_sparse(self, idx, val, want_align=True, row_T=None, want_probs=True):
         eng = self._get_engine()
-        chars, probs, scores, lens, align = eng.correct_greedy_host(idx, val, self._row_T(idx), want_align=want_align)
+        if row_T is None:
+            row_T = self._row_T(idx)
+        chars, probs, scores, lens, align = eng.correct_greedy_host(idx, val, row_T, want_align=want_align)
         chars, probs, scores, lens = chars.numpy(), probs.numpy(), scores.numpy(), lens.numpy()
-        i2c = self.mapping[1]
         B = idx.shape[0]
-        lines = [''.join(i2c[int(v)] for v in chars[j, :lens[j]]) for j in range(B)]
-        out_probs = [list(probs[j, :lens[j]]) for j in range(B)]
-        out_scores = [float(scores[j]) if lens[j] else 0. for j in range(B)]
+        lines = self._strings(chars, lens)
+        # predict() drops the probabilities: hand out array rows then instead of 2T Python floats per line
+        out_probs = [list(probs[j, :lens[j]]) for j in range(B)] if want_probs else [probs[j, :lens[j]] for j in range(B)]
+        out_scores = np.where(lens > 0, scores, 0.).tolist()
         if align is not None:
             align = align.numpy()
-            alignments = [[align[s, j].copy() for s in range(lens[j])] for j in range(B)]
+            # one copy per line, then S row views of it (the reference returns a list of S arrays (T,))
+            alignments = [list(np.ascontiguousarray(align[:lens[j], j, :row_T[j]])) for j in range(B)]
         else:
             alignments = [[] for _ in range(B)]
         return lines, out_probs, out_scores, alignments
@@ -516,26 +535,49 @@ class Sequence2Sequence(object):
         if not lines:
             return [], [], [], []
         idx, val = lines_to_sparse(self.mapping[0], lines, conf, self.logger)
+        return self._correct_sparse(lines, idx, val, None, fast, greedy, True)
+
+    def _correct_sparse(self, lines, idx, val, row_T, fast, greedy, want_align, want_probs=True):
         if fast:
-            return self._greedy_sparse(idx, val)
+            return self._greedy_sparse(idx, val, want_align, row_T, want_probs)
         if greedy:
             # decode_sequence_greedy per line (:817-819) picks the same characters as the batch decoder —
             # "argmax, and if '' wins the argmax of the rest" == argmax over indices >= 1 — from the same
             # batch encoding; only the score is accumulated in float32 there (:1312, :1343)
-            out_lines, out_probs, _, alignments = self._greedy_sparse(idx, val)
+            out_lines, out_probs, _, alignments = self._greedy_sparse(idx, val, want_align, row_T, want_probs)
             out_scores = []
             for j, line in enumerate(lines):
                 if not line:
                     out_lines[j], out_probs[j], alignments[j] = '', [], []
                     out_scores.append(0)
                     continue
-                total = np.float32(0)
-                for p in out_probs[j]:
-                    total = np.float32(total + -np.log(p))
-                out_scores.append(total / len(out_lines[j]) if out_lines[j] else 0)
+                out_scores.append(float32_mean_neglog(out_probs[j]) if out_lines[j] else 0)
                 out_lines[j] = out_lines[j].replace(GAP, '')
             return out_lines, out_probs, out_scores, alignments
-        return self._beam_sparse(lines, idx, val)
+        return self._beam_sparse(lines, idx, val, want_align, row_T)
+
+    def correct_batches(self, batches, fast=True, greedy=True, want_align=False, want_probs=True):
+        '''correct_lines over several reference batches in ONE engine call.
+
+        `batches`: list of (lines, conf) pairs, each what one correct_lines call would get (e.g. the
+        256-line batches of gen_lines, or the pages of a document).  Every line is decoded with the
+        padded length of ITS batch (the reference does not mask padding, so T is part of the input),
+        hence the result of batch b equals correct_lines(*batches[b]) — without the soft alignments
+        unless `want_align`; with `want_probs=False` the probability entries are float32 array rows
+        rather than lists.  Return a list of 4-tuples, one per batch.'''
+        assert not fast or greedy, "cannot decode in fast mode with beam search enabled"
+        todo = [(b, lines, conf) for b, (lines, conf) in enumerate(batches) if lines]
+        results = [([], [], [], []) for _ in batches]
+        if not todo:
+            return results
+        encoded = [lines_to_sparse(self.mapping[0], lines, conf, self.logger) for _, lines, conf in todo]
+        idx, val, row_T, offsets = merge_batches(encoded)
+        all_lines = [line for _, lines, _ in todo for line in lines]
+        merged = self._correct_sparse(all_lines, idx, val, row_T, fast, greedy, want_align, want_probs)
+        for n, (b, _, _) in enumerate(todo):
+            lo, hi = offsets[n], offsets[n + 1]
+            results[b] = tuple(part[lo:hi] for part in merged)
+        return results
 
     def correct_lines_paths(self, lines, conf=None, fast=True, greedy=True, input_lens=None):
         '''correct_lines plus the hard re-alignment path of every line, made on the device.
@@ -625,26 +667,28 @@ class Sequence2Sequence(object):
             realignments.append(d)
         return out_lines, out_probs, out_scores, realignments, [float(x) for x in dist]
 
-    def _beam_sparse(self, lines, idx, val, want_align=True):
+    def _beam_sparse(self, lines, idx, val, want_align=True, row_T=None):
         eng = self._get_engine()
+        if row_T is None:
+            row_T = self._row_T(idx)
         bp = eng.beam_params(batch_size=min(int(self.batch_size), 256), beam_width_in=self.beam_width_in,
                              beam_threshold_in=self.beam_threshold_in, beam_width_out=self.beam_width_out,
                              rejection_threshold=self.rejection_threshold)
         chars, probs, scores, lens, align, stats = eng.correct_beam_host(
-            idx, val, self._row_T(idx), bp, want_align=want_align, budget_bytes=self.beam_budget_bytes)
+            idx, val, row_T, bp, want_align=want_align, budget_bytes=self.beam_budget_bytes)
         chars, probs, scores, lens, stats = chars.numpy(), probs.numpy(), scores.numpy(), lens.numpy(), stats.numpy()
         align = None if align is None else align.numpy()
-        i2c = self.mapping[1]
+        decoded = self._strings(chars, lens)
         output_lines, output_probs, output_scores, alignments = [], [], [], []
         for j, input_line in enumerate(lines):
             if not input_line:
                 line, prob, score, alignment = '', [], 0, []
             elif lens[j] > 0:
                 n = int(lens[j])
-                line = ''.join(i2c[int(v)] for v in chars[j, :n])
+                line = decoded[j]
                 prob = list(probs[j, :n])
                 score = float(scores[j])
-                alignment = [align[j, s].copy() for s in range(n)] if align is not None else []
+                alignment = list(np.ascontiguousarray(align[j, :n, :row_T[j]])) if align is not None else []
             else:
                 # no final hypothesis: the reference's StopIteration fallback (:826-836)
                 self.logger.error('cannot beam-decode input line %d: "%s"', j, input_line)

@@ -10,10 +10,25 @@ import numpy as np
 GAP = '\a'
 
 
+_TABLES = {}
+
+
 def _lookup_table(c2i):
-    keys = np.array(sorted(ord(c) for c in c2i if c), dtype=np.int64)
-    vals = np.array([c2i[chr(k)] for k in keys], dtype=np.int32)
-    return keys, vals
+    """Code point -> index as one dense array (-1 = unmapped), cached per mapping object.  Alphabets
+    are a few hundred code points of the BMP; the table is capped at the full Unicode range."""
+    key = (id(c2i), len(c2i))
+    hit = _TABLES.get(key)
+    if hit is not None and hit[0] is c2i:
+        return hit[1]
+    cps = [ord(c) for c in c2i if len(c) == 1]
+    table = np.full(max(cps + [0]) + 2, -1, dtype=np.int32)      # last slot: everything beyond the alphabet
+    for c, i in c2i.items():
+        if len(c) == 1:
+            table[ord(c)] = i
+    if len(_TABLES) > 16:
+        _TABLES.clear()
+    _TABLES[key] = (c2i, table)
+    return table
 
 
 def strings_to_sparse(c2i, lines, logger=None):
@@ -25,16 +40,19 @@ def strings_to_sparse(c2i, lines, logger=None):
     if T == 0:
         return idx[:, :0], None
     text = ''.join(lines)
-    cps = np.frombuffer(text.encode('utf-32-le'), dtype=np.uint32).astype(np.int64)
-    keys, vals = _lookup_table(c2i)
-    pos = np.searchsorted(keys, cps)
-    pos[pos >= len(keys)] = 0
-    hit = keys[pos] == cps if len(keys) else np.zeros(len(cps), bool)
-    mapped = np.where(hit, vals[pos] if len(keys) else 0, 0).astype(np.int32)
-    if logger is not None and not hit.all():
-        for cp in np.unique(cps[~hit]):
-            if chr(cp) != GAP:
-                logger.error('unmapped character "%s" in encoder input', chr(cp))
+    cps = np.frombuffer(text.encode('utf-32-le'), dtype=np.uint32)
+    table = _lookup_table(c2i)
+    mapped = table[np.minimum(cps, len(table) - 1)]
+    hit = mapped >= 0
+    if not hit.all():
+        if logger is not None:
+            for cp in np.unique(cps[~hit]):
+                if chr(cp) != GAP:
+                    logger.error('unmapped character "%s" in encoder input', chr(cp))
+        mapped = np.where(hit, mapped, 0).astype(np.int32)
+    if (lens == T).all():
+        idx[:, :, 0] = mapped.reshape(B, T)
+        return idx, None
     rows = np.repeat(np.arange(B), lens)
     cols = np.arange(len(cps)) - np.repeat(np.cumsum(lens) - lens, lens)
     idx[rows, cols, 0] = mapped

@@ -99,3 +99,35 @@ def test_beam_fallback_returns_input(tmp_path):
                            beam_params=dict(rejection_threshold=0, batch_size=32, beam_width_in=5))
     assert out[0] == ref[0] == lines
     assert out[1][0] == [1.0] * len(lines[0]) and out[2] == [0, 0]
+
+
+@pytest.mark.parametrize("mode", ["fast", "greedy", "beam"])
+def test_predict_superbatches_equal_per_batch_calls(tmp_path, mode):
+    """Row N2: predict() over text files with several reference batches per engine call (each row
+    carrying its own batch's padded T) returns exactly what the reference's batch-by-batch loop does,
+    and what the oracle returns for those batches."""
+    topo, w, mapping = make_model("c2s")
+    s = _loaded(topo, w, mapping, tmp_path)
+    s.batch_size = 8
+    s.rejection_threshold, s.beam_width_in = 0.03, 5
+    lines = synthetic_lines(mapping, 29, 18, seed=77, min_length=3)
+    lines[8:16] = synthetic_lines(mapping, 8, 7, seed=78, min_length=2)      # a batch with a much shorter T
+    lines = [l.replace('\t', ' ') for l in lines]
+    f1, f2 = tmp_path / 'one.txt', tmp_path / 'two.txt'
+    f1.write_text(''.join(lines[:13]))
+    f2.write_text(''.join(lines[13:]))
+    fast, greedy = mode == "fast", mode != "beam"
+    s.superbatch, s.prefetch = 1, False
+    want = list(s.predict([str(f1), str(f2)], fast=fast, greedy=greedy))
+    s.superbatch, s.prefetch = 3, True
+    got = list(s.predict([str(f1), str(f2)], fast=fast, greedy=greedy))
+    assert len(got) == len(want) == 4
+    params = dict(rejection_threshold=0.03, batch_size=8, beam_width_in=5)
+    for b, ((names, out, scores), (names_w, out_w, scores_w)) in enumerate(zip(got, want)):
+        assert names == names_w and out == out_w
+        assert np.allclose(np.array(scores, np.float64), np.array(scores_w, np.float64), atol=1e-6)
+        chunk = lines[8 * b:8 * b + 8]
+        chunk = chunk + [''] * (8 - len(chunk))
+        ref = od.correct_lines(topo, w, mapping, chunk, fast=fast, greedy=greedy, beam_params=params)
+        assert out == ref[0]
+        assert np.allclose(np.array(scores, np.float64), np.array(ref[2], np.float64), atol=1e-4)
