@@ -63,13 +63,13 @@ static bool tc_shape_ok(const GemmSeg* s, int n) {
     return true;
 }
 static int gemm_store(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const StoreEpi& e) {
-    if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e);
+    if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) return gemm_store_tc(st, M, m_dev, N, s, n, e, m->passes);
     return gemm_store_ffma(st, M, m_dev, N, s, n, e);
 }
 static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, const LstmEpi& e) {
     prof_begin(st);
     int rc;
-    if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e);
+    if (m->split && M >= m->tc_min_rows && tc_shape_ok(s, n) && tc_available()) rc = gemm_lstm_tc(st, M, m_dev, N, s, n, e, m->passes);
     else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
     prof_end(st, M, m_dev, N, s, n, e.xtab ? e.W : 0);
     return rc;
@@ -513,7 +513,7 @@ int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launc
 // Test hook: C[M,N] = A[M,K] . B[N,K]^T through one of the two GEMM kernels (1 = FFMA, 2 = tcgen05 3xFP16).
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    COR_CHECK(mode >= 1 && mode <= 3, "mode must be 1 (FFMA), 2 (tcgen05, tile shape picked from M and N) or 3 (tcgen05, 128x32 tiles forced)");
+    COR_CHECK(mode >= 1 && mode <= 4, "mode must be 1 (FFMA), 2 (tcgen05, tile shape picked from M and N), 3 (tcgen05, 128x32 tiles forced) or 4 (tcgen05, fp16 heads only)");
     StoreEpi e{C, N, nullptr, nullptr, 0};
     if (mode == 1) {
         GemmSeg s{A, K, nullptr, B, K, nullptr, K};
@@ -527,7 +527,7 @@ int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B
     if (!rc) {
         GemmSeg s{a_hi, K, a_lo, b_hi, K, b_lo, K};
         tc_force_narrow(mode == 3);
-        rc = gemm_store_tc(st, M, nullptr, N, &s, 1, e);
+        rc = gemm_store_tc(st, M, nullptr, N, &s, 1, e, mode == 4 ? 1 : 3);
         tc_force_narrow(false);
     }
     cudaError_t err = cudaStreamSynchronize(st);
@@ -574,7 +574,9 @@ int cor_model_create(const cor_config* cfg, int device, cor_model** out) {
     m->cfg = *cfg; m->device = device;
     m->W = cfg->width; m->d = cfg->depth; m->V = cfg->voc_size; m->Vp = (cfg->voc_size + 127) & ~127;
     m->D = (cfg->depth == 1 || cfg->deep_bidirectional_encoder) ? 2 * cfg->width : cfg->width;
-    m->split = cfg->gemm_mode == 2 || (cfg->gemm_mode == 0 && tc_available());
+    COR_CHECK(cfg->gemm_mode >= 0 && cfg->gemm_mode <= 3, "gemm_mode must be 0..3");
+    m->split = cfg->gemm_mode >= 2 || (cfg->gemm_mode == 0 && tc_available());
+    m->passes = cfg->gemm_mode == 3 ? 1 : 3;
     m->tc_min_rows = 1;     // page-sized batches run the narrow-tile tcgen05 kernel (8 rows: 19 ms per page call against 110 ms on the FFMA kernel)
     if (const char* v = getenv("COR_TC_MIN_ROWS")) m->tc_min_rows = atoi(v);
     *out = m;

@@ -86,8 +86,9 @@ struct LstmEpi {
 // m_dev != nullptr: the row count is read on the device (beam), M is then the capacity.
 int gemm_store_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi);
 int gemm_lstm_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi);
-int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi);
-int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi);
+// passes: 3 = hi/lo three-pass product (fp32 grade), 1 = fp16 heads only (one pass, ~5e-4 relative per product)
+int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi, int passes = 3);
+int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi, int passes = 3);
 bool tc_available();
 void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape
 

@@ -58,6 +58,7 @@ struct TcParams {
     int nseg;
     int M; const int* m_dev; int N;
     int tiles_n;
+    int passes;     // 3: fp32-grade hi/lo product (the product path); 1: heads only (gemm_mode 3, stated looser tolerance)
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -172,6 +173,23 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
 // N at [17,23) >> 3, M at [24,29) >> 4
 // (Geo<NCTA, BN>::IDESC; M = 256 for the pair)
 
+// 256-bit global accesses (sm_100): the epilogue is "one row per lane", so every warp-wide access touches 32
+// different lines and costs 32 L1 wavefronts whatever its width -- the LSU pipe, not the MUFU or the tensor
+// pipe, bounded the K = 512 launches (ncu: 129 us against 66 us of MMA time).  32-byte accesses halve the
+// instruction count of the 16-byte version.
+__device__ __forceinline__ void ld8(const float* p, float* v) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
+}
+__device__ __forceinline__ void ld8_nc(const float* p, float* v) {      // read-only data (bias, tables)
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
+}
+__device__ __forceinline__ void st8(float* p, const float* v) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
+
 // ------------------------------------------------------------------ vectorised LSTM epilogue (8 units of one row)
 __device__ __forceinline__ void st4(float* p, size_t off, const float* v) {
     *reinterpret_cast<float4*>(p + off) = make_float4(v[0], v[1], v[2], v[3]);
@@ -187,6 +205,8 @@ __device__ __forceinline__ void store8_split(float* hi_p, float* lo_p, size_t of
         for (int k = 0; k < 8; ++k) f16_split(v[k], hi[k], lo[k]);
         *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(hi_p) + off) = *reinterpret_cast<const uint4*>(hi);
         *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(lo_p) + off) = *reinterpret_cast<const uint4*>(lo);
+    } else if ((((uintptr_t)(hi_p + off)) & 31) == 0) {
+        st8(hi_p + off, v);
     } else {
         st4(hi_p, off, v); st4(hi_p, off + 4, v + 4);
     }
@@ -200,18 +220,68 @@ __device__ __forceinline__ void load8_split(const float* hi_p, const float* lo_p
     }
 }
 
+// Per-row constants of a tile's LSTM epilogue, loaded BEFORE the wait on the accumulator: the padded length,
+// the sequence position and the first table index of the row (three dependent global loads that used to sit
+// inside every 32-column chunk).
+struct RowCtx {
+    int T; bool active; int t;
+    int idx0; float w0;        // first alternative of the row's input position (xtab); idx0 < 0: none
+    size_t xo;                 // offset of the row's alternatives in x_idx / x_val
+};
+__device__ __forceinline__ RowCtx lstm_row_begin(const LstmEpi& e, int row, bool valid) {
+    RowCtx rc;
+    rc.T = (valid && e.row_T) ? e.row_T[row] : 0x7fffffff;
+    rc.active = e.step < rc.T;
+    rc.t = e.reverse ? rc.T - 1 - e.step : e.step;
+    rc.idx0 = -1; rc.w0 = 1.0f; rc.xo = 0;
+    if (valid && rc.active && e.xtab) {
+        rc.xo = ((size_t)row * e.x_tmax + rc.t) * e.x_k;
+        rc.idx0 = e.x_idx[rc.xo];
+        if (e.x_val) rc.w0 = e.x_val[rc.xo];
+    }
+    return rc;
+}
+// Operands of one chunk that do not depend on the accumulator: b = bias (+ the table rows of the input term),
+// c = the cell state.  Issued before the TMEM load so that their latency overlaps it.
+__device__ __forceinline__ void lstm_chunk_operands(const LstmEpi& e, const RowCtx& rc, int row, int unit0, float (&b)[32], float (&c)[8]) {
+    ld8(e.c_in + (size_t)row * e.W + unit0, c);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) ld8_nc(e.bias + (size_t)4 * unit0 + 8 * q, b + 8 * q);
+    if (e.xtab) {
+        if (rc.idx0 >= 0) {
+            const float* src = e.xtab + (size_t)rc.idx0 * 4 * e.W + 4 * unit0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float x[8];
+                ld8_nc(src + 8 * q, x);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) b[8 * q + k] = fmaf(rc.w0, x[k], b[8 * q + k]);
+            }
+        }
+        for (int a = 1; a < e.x_k; ++a) {           // further alternatives (confusion networks): rare
+            const int v = e.x_idx[rc.xo + a];
+            if (v < 0) continue;
+            const float w = e.x_val ? e.x_val[rc.xo + a] : 1.0f;
+            const float* src = e.xtab + (size_t)v * 4 * e.W + 4 * unit0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float x[8];
+                ld8_nc(src + 8 * q, x);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) b[8 * q + k] = fmaf(w, x[k], b[8 * q + k]);
+            }
+        }
+    }
+}
+
 // z = 32 accumulator columns = units [unit0, unit0+8) x gates (i,f,c~,o) of one row
-__device__ __forceinline__ void lstm_row8(const LstmEpi& e, int row, int unit0, const uint32_t (&z)[32]) {
-    const int T = e.row_T ? e.row_T[row] : 0x7fffffff;
-    const bool active = e.step < T;
+__device__ __forceinline__ void lstm_row8(const LstmEpi& e, const RowCtx& rc, int row, int unit0, const uint32_t (&z)[32],
+                                          const float (&b)[32], float (&c)[8]) {
+    const int T = rc.T;
+    const bool active = rc.active;
     const size_t so = (size_t)row * e.W + unit0;
     float h[8];
     if (active) {
-        float c[8], b[32];
-        ld4(e.c_in, so, c); ld4(e.c_in, so + 4, c + 4);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) ld4(e.bias, (size_t)4 * unit0 + 4 * q, b + 4 * q);
-        if (e.xtab) xtab_add<32>(e, row, e.reverse ? T - 1 - e.step : e.step, 4 * unit0, b);    // folded into the bias term
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const float i = sigmoidf_fast(__uint_as_float(z[4 * k + 0]) + b[4 * k + 0]);
@@ -221,18 +291,18 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, int row, int unit0, 
             c[k] = f * c[k] + i * g;
             h[k] = o * tanhf_fast(c[k]);
         }
-        st4(e.c_out, so, c); st4(e.c_out, so + 4, c + 4);
+        st8(e.c_out + so, c);
     } else {
         load8_split(e.h_prev, e.h_prev_lo, so, h);
         if (e.c_out != e.c_in) {
-            float c[8];
-            ld4(e.c_in, so, c); ld4(e.c_in, so + 4, c + 4);
-            st4(e.c_out, so, c); st4(e.c_out, so + 4, c + 4);
+            float cc[8];
+            ld8(e.c_in + so, cc);
+            st8(e.c_out + so, cc);
         }
     }
     store8_split(e.h_out, e.h_out_lo, so, h);
     if (!active || (!e.seq_out && !e.seq_rev)) return;
-    const int t = e.reverse ? T - 1 - e.step : e.step;
+    const int t = rc.t;
     float y[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) y[k] = h[k];
@@ -259,12 +329,14 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, int row, int unit0, 
 __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0, int N, const uint32_t (&z)[32]) {
     if (e.n_split && col0 >= e.n_split && col0 + 32 <= N && (e.ldc2 & 3) == 0) {
         const int c2 = col0 - e.n_split;
+        const bool wide = (e.ldc2 & 7) == 0 && ((uintptr_t)e.C2 & 31) == 0;     // 32-byte stores (see ld8/st8)
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            float v[4];
+        for (int q = 0; q < 4; ++q) {
+            float v[8];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) v[k] = __uint_as_float(z[4 * q + k]) + (e.bias2 ? e.bias2[c2 + 4 * q + k] : 0.0f);
-            st4(e.C2, (size_t)row * e.ldc2 + c2 + 4 * q, v);
+            for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(z[8 * q + k]) + (e.bias2 ? e.bias2[c2 + 8 * q + k] : 0.0f);
+            float* dst = e.C2 + (size_t)row * e.ldc2 + c2 + 8 * q;
+            if (wide) st8(dst, v); else { st4(dst, 0, v); st4(dst, 4, v + 4); }
         }
     } else if (col0 + 32 <= N && (e.ldc & 3) == 0 && !(e.n_split && col0 >= e.n_split)) {
 #pragma unroll
@@ -349,19 +421,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                     for (int kb = 0; kb < p.kblocks[s]; ++kb) {
                         mbar_wait(empty_bar(stage), phase ^ 1);
                         const uint32_t sa = smem_base + stage * STAGE_BYTES;
+                        const bool lo = p.passes == 3;          // heads-only mode leaves the residual tiles out
+                        const uint32_t bytes = lo ? STAGE_BYTES : A_TILE + B_TILE;
                         if constexpr (NCTA == 1) {
-                            mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+                            mbar_expect_tx(full_bar(stage), bytes);
                             tma_load_2d(sa, &p.a_hi[s], kb * BK, m0, full_bar(stage));
-                            tma_load_2d(sa + A_TILE, &p.a_lo[s], kb * BK, m0, full_bar(stage));
+                            if (lo) tma_load_2d(sa + A_TILE, &p.a_lo[s], kb * BK, m0, full_bar(stage));
                             tma_load_2d(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, full_bar(stage));
-                            tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
+                            if (lo) tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
                         } else {
-                            if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE_BYTES);    // both CTAs' bytes
+                            if (leader) mbar_expect_tx(full_bar(stage), 2 * bytes);    // both CTAs' bytes
                             const uint32_t fb = map_to_cta(full_bar(stage), 0);
                             tma_load_2d_pair(sa, &p.a_hi[s], kb * BK, m0, fb);
-                            tma_load_2d_pair(sa + A_TILE, &p.a_lo[s], kb * BK, m0, fb);
+                            if (lo) tma_load_2d_pair(sa + A_TILE, &p.a_lo[s], kb * BK, m0, fb);
                             tma_load_2d_pair(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, fb);
-                            tma_load_2d_pair(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, fb);
+                            if (lo) tma_load_2d_pair(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, fb);
                         }
                         if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
@@ -388,20 +462,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                         else umma_f16_pair(d_tmem, a, b, G::IDESC, accum);
                     };
                     // small terms first: A_lo*B_hi, A_hi*B_lo, then A_hi*B_hi
+                    const bool lo = p.passes == 3;
+                    if (lo) {
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
-                        mma(a_lo + adv, b_hi + adv, (kb | k) != 0);
+                        for (int k = 0; k < BK / UMMA_K; ++k) {
+                            const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
+                            mma(a_lo + adv, b_hi + adv, (kb | k) != 0);
+                        }
+#pragma unroll
+                        for (int k = 0; k < BK / UMMA_K; ++k) {
+                            const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
+                            mma(a_hi + adv, b_lo + adv, 1);
+                        }
                     }
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
-                        mma(a_hi + adv, b_lo + adv, 1);
-                    }
-#pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
-                        mma(a_hi + adv, b_hi + adv, 1);
+                        mma(a_hi + adv, b_hi + adv, lo || (kb | k) != 0);
                     }
                     // frees the smem stage (in both CTAs) when these MMAs retire
                     if constexpr (NCTA == 1) umma_commit(empty_bar(stage)); else umma_commit_pair(empty_bar(stage));
@@ -418,19 +495,35 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
         int acc = 0; uint32_t acc_phase = 0;
         for (int tile = unit; tile < num_tiles; tile += n_units) {
             const int m0 = (tile / p.tiles_n) * (BM * NCTA) + (int)rank * BM, n0 = (tile % p.tiles_n) * BN;
-            mbar_wait(tfull_bar(acc), acc_phase);
-            tc_fence_after();
             const int row = m0 + wq * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
+            if constexpr (EPI == 1) {
+                // everything that does not depend on the accumulator is fetched before waiting for it
+                const RowCtx rc = lstm_row_begin(epi, row, row < M);
+                bool waited = false;
 #pragma unroll 1
-            for (int ch = half; ch < BN / 32; ch += EPI_WARPS / 4) {
-                uint32_t z[32];
-                tmem_ld32(taddr + ch * 32, z);
-                tmem_ld_wait();
-                const int col0 = n0 + ch * 32;
-                if (row < M && col0 < p.N) {
-                    if constexpr (EPI == 0) store_row32(epi, row, col0, p.N, z);
-                    else lstm_row8(epi, row, col0 >> 2, z);
+                for (int ch = half; ch < BN / 32; ch += EPI_WARPS / 4) {
+                    const int col0 = n0 + ch * 32;
+                    const bool live = row < M && col0 < p.N;
+                    float b[32], c[8];
+                    if (live && rc.active) lstm_chunk_operands(epi, rc, row, col0 >> 2, b, c);
+                    if (!waited) { mbar_wait(tfull_bar(acc), acc_phase); tc_fence_after(); waited = true; }
+                    uint32_t z[32];
+                    tmem_ld32(taddr + ch * 32, z);
+                    tmem_ld_wait();
+                    if (live) lstm_row8(epi, rc, row, col0 >> 2, z, b, c);
+                }
+                if (!waited) { mbar_wait(tfull_bar(acc), acc_phase); tc_fence_after(); }
+            } else {
+                mbar_wait(tfull_bar(acc), acc_phase);
+                tc_fence_after();
+#pragma unroll 1
+                for (int ch = half; ch < BN / 32; ch += EPI_WARPS / 4) {
+                    uint32_t z[32];
+                    tmem_ld32(taddr + ch * 32, z);
+                    tmem_ld_wait();
+                    const int col0 = n0 + ch * 32;
+                    if (row < M && col0 < p.N) store_row32(epi, row, col0, p.N, z);
                 }
             }
             tc_fence_before();
@@ -521,9 +614,10 @@ int get_map(const float* ptr, long long rows, long long cols, long long ld, int 
     return 0;
 }
 
-int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, TcParams* p) {
+int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, int passes, TcParams* p) {
     COR_CHECK(nseg >= 1 && nseg <= kMaxSegs, "bad segment count");
-    p->nseg = nseg; p->M = M; p->m_dev = m_dev; p->N = N;
+    COR_CHECK(passes == 1 || passes == 3, "passes must be 1 or 3");
+    p->passes = passes; p->nseg = nseg; p->M = M; p->m_dev = m_dev; p->N = N;
     p->tiles_n = (N + bn - 1) / bn;
     for (int s = 0; s < nseg; ++s) {
         const GemmSeg& g = segs[s];
@@ -569,11 +663,11 @@ int launch_tc(cudaStream_t st, int M, int N, const TcParams& p, const Epi& epi) 
 }
 
 template <int EPI, typename Epi>
-int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const Epi& epi) {
+int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, int passes, const Epi& epi) {
     int ncta, bn;
     pick_shape(M, N, &ncta, &bn);
     TcParams p;
-    if (fill_params(ncta, bn, M, m_dev, N, segs, nseg, &p)) return 1;
+    if (fill_params(ncta, bn, M, m_dev, N, segs, nseg, passes, &p)) return 1;
     if (bn == BN_NARROW) return launch_tc<EPI, 1, BN_NARROW, Epi>(st, M, N, p, epi);
     return ncta == 2 ? launch_tc<EPI, 2, BN_WIDE, Epi>(st, M, N, p, epi) : launch_tc<EPI, 1, BN_WIDE, Epi>(st, M, N, p, epi);
 }
@@ -583,17 +677,17 @@ int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* 
 bool tc_available() { return init_tc(); }
 void tc_force_narrow(bool on) { g_force_bn = on ? BN_NARROW : 0; }
 
-int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi) {
+int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi, int passes) {
     if (M <= 0) return 0;
     COR_CHECK(init_tc(), "tcgen05 path unavailable on this device");
-    return dispatch_tc<0, StoreEpi>(st, M, m_dev, N, segs, nseg, epi);
+    return dispatch_tc<0, StoreEpi>(st, M, m_dev, N, segs, nseg, passes, epi);
 }
 
-int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi) {
+int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi, int passes) {
     if (M <= 0) return 0;
     COR_CHECK(init_tc(), "tcgen05 path unavailable on this device");
     COR_CHECK(N == 4 * epi.W && epi.W % 8 == 0, "LSTM epilogue needs N == 4W with W a multiple of 8");
-    return dispatch_tc<1, LstmEpi>(st, M, m_dev, N, segs, nseg, epi);
+    return dispatch_tc<1, LstmEpi>(st, M, m_dev, N, segs, nseg, passes, epi);
 }
 
 }  // namespace cor

@@ -31,6 +31,7 @@ struct cor_model {
     int W = 0, d = 0, V = 0, Vp = 0, D = 0;
     bool split = false;       // activations and weights kept as TF32 (hi, lo) pairs for the tcgen05 path
     int tc_min_rows = 1;
+    int passes = 3;           // tcgen05 passes per product: 3 = fp32 grade; 1 = fp16 heads only (gemm_mode 3)
     bool finalized = false;
     std::map<std::string, std::vector<cor::HostWeight>> host;   // until finalize
     std::vector<void*> allocs;

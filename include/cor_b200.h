@@ -41,7 +41,8 @@ typedef struct cor_config {
     int32_t lm_predict;
     int32_t window_width;      /* 5 in the reference (seq2seq.py:347,452) */
     int32_t eos_index;         /* index of '\n' in the mapping (1 when built by map_files, seq2seq.py:580-586) */
-    int32_t gemm_mode;         /* 0 auto, 1 force FFMA fp32, 2 force tcgen05 3-pass fp16 hi/lo */
+    int32_t gemm_mode;         /* 0 auto, 1 force FFMA fp32, 2 force tcgen05 3-pass fp16 hi/lo (fp32 grade), 3 tcgen05 single-pass fp16
+                                * (the north star's reduced-precision variant: looser stated tolerance, never picked by 0) */
 } cor_config;
 
 /* Input lines of one call — replaces the dense (B,T,V) array of

@@ -178,3 +178,37 @@ def test_two_reference_batches_in_one_call():
     got = [''.join(mapping[1][int(v)] for v in chars[j, :lens[j]]) for j in range(len(a) + len(b))]
     assert got == ra[0] + rb[0]
     assert np.allclose(scores, np.array(ra[2] + rb[2]), atol=1e-4)
+
+
+# Stated tolerance of the reduced-precision variant (gemm_mode 3, single-pass fp16 tensor products; the north
+# star's "bf16 GEMM variants get a stated looser tolerance").  Measured on 2 048 lines by scripts/measure_mode3.py
+# (profiles/r01_mode3_drift.json: 99.1 % identical strings, max |dp| 3.9e-7 where strings agree, score drift 3.8e-5 --
+# with random-init weights the probabilities themselves are ~1/V, so this is ~2e-4 relative).
+TOL_P_SINGLE_PASS = 1e-5
+
+
+def test_single_pass_variant_stated_tolerance():
+    """gemm_mode 3 against the fp32-grade product path (gemm_mode 2, itself checked against the oracle above)
+    at the C2/C3 topology: per-character probabilities within TOL_P_SINGLE_PASS up to the first differing
+    character, and the two paths are really different kernels (the drift is not zero)."""
+    topo, w, mapping = make_model("c2")
+    lines = synthetic_lines(mapping, 256, 80, seed=4242)
+    idx, val = _sparse(mapping, lines)
+    B, T, _ = idx.shape
+    res = {}
+    for mode in (2, 3):
+        eng = _engine(topo, w, mode)
+        chars, probs, scores, lens, _ = eng.correct_greedy_host(idx, val, np.full(B, T, np.int32), want_align=False)
+        res[mode] = tuple(t.numpy().copy() for t in (chars, probs, lens))
+    (c2, p2, l2), (c3, p3, l3) = res[2], res[3]
+    worst, identical = 0.0, 0
+    for j in range(B):
+        n = int(min(l2[j], l3[j]))
+        d = np.nonzero(c2[j, :n] != c3[j, :n])[0]
+        k = int(d[0]) if len(d) else n
+        identical += int(len(d) == 0 and l2[j] == l3[j])
+        if k:
+            worst = max(worst, float(np.abs(p2[j, :k] - p3[j, :k]).max()))
+    print("single pass: %d of %d strings identical, max |dp| on common prefixes %.3g" % (identical, B, worst))
+    assert 0.0 < worst < TOL_P_SINGLE_PASS
+    assert identical >= (B * 19) // 20

@@ -65,3 +65,12 @@ def test_tcgen05_small_magnitudes():
     err = (Cm.double() - A.double() @ B.double().T).abs().max().item()
     print("abs err %.3g" % err)
     assert err < 2e-7
+
+
+@pytest.mark.parametrize("shape", [(256, 512, 512), (77, 128, 64), (18999, 2048, 1024), (32, 2048, 1536)])
+def test_tcgen05_single_pass_gemm(shape):
+    """gemm_mode 3 (fp16 heads only, one tensor pass): the error of ONE rounding of each operand to 11
+    significand bits, two to three orders above the three-pass product and well inside 1e-3."""
+    err1, err3 = _run(4, *shape), _run(2, *shape)
+    print("tcgen05 1xFP16 %s: %.3g (three-pass %.3g)" % (shape, err1, err3))
+    assert err3 < 1e-5 < err1 < 1e-3, (err1, err3)
