@@ -200,6 +200,12 @@ struct Carver {
     }
 };
 
+// Page-sized calls reserve room for the persistent recurrence.  Must be a pure function of (model, B): the
+// workspace size is computed without a device (and before the first launch).
+static bool recur_layout(const cor_model* m, int B) {
+    return m->split && m->passes == 3 && B <= kRecurMaxRows && m->W % 16 == 0 && m->W <= 768 && !getenv("COR_NO_RECUR");
+}
+
 int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, Ws* ws) {
     COR_CHECK(B > 0 && T > 0 && k > 0, "empty call geometry");
     Carver c{(char*)base};
@@ -227,6 +233,10 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
         }
     }
     ws->u = c.take<float>(BT * W);
+    if (recur_layout(m, B)) {    // persistent recurrence (recur.cu): the upper layers' input term for all timesteps
+        ws->zx[0] = c.take<float>(BT * 4 * W);
+        ws->zx[1] = (m->cfg.deep_bidirectional_encoder || !m->use_xtab) ? c.take<float>(BT * 4 * W) : nullptr;
+    } else { ws->zx[0] = ws->zx[1] = nullptr; }
     const size_t BW = (size_t)B * W;
     for (int dir = 0; dir < 2; ++dir) {
         for (int q = 0; q < 2; ++q) {
@@ -287,6 +297,41 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
             COR_CUDA(cudaMemsetAsync(ws.ec[dir], 0, BW * 4, st));
         }
         int cur = 0;
+        const bool tab0 = n == 0 && m->use_xtab;
+        // a bidirectional layer too wide for one grid runs its directions one after the other
+        const int per_launch = (ws.zx[0] && lstm_recur_supported(W, B, ndir)) ? ndir : 1;
+        if (ws.zx[0] && (tab0 || ws.zx[ndir - 1]) && lstm_recur_supported(W, B, per_launch)) {
+            // ---- page-sized batch: one persistent launch per layer (recur.cu)
+            for (int d0 = 0; d0 < ndir; d0 += per_launch) {
+                RecurArgs ra{};
+                ra.ndir = per_launch; ra.W = W; ra.B = B; ra.T = T; ra.barrier = m->grid_bar;
+                for (int q = 0; q < per_launch; ++q) {
+                    const int dir = d0 + q;
+                    const LstmW& lw = dir == 0 ? m->enc_fw[n] : m->enc_bw[n];
+                    if (!tab0) {    // input term of every timestep from ONE GEMM over the (t,row) pairs
+                        GemmSeg sx = {in[dir], in_dim, in_lo[dir], lw.Kx.hi, lw.Kx.ld, lw.Kx.lo, in_dim};
+                        StoreEpi ex{ws.zx[dir], 4 * W, nullptr, nullptr, 0};
+                        if (gemm_store(m, st, T * B, nullptr, 4 * W, &sx, 1, ex)) return 1;
+                    }
+                    ra.R_hi[q] = lw.R.hi; ra.R_lo[q] = lw.R.lo; ra.ldr = lw.R.ld;
+                    ra.zx[q] = tab0 ? nullptr : ws.zx[dir];
+                    for (int pp = 0; pp < 2; ++pp) { ra.h[q][pp] = ws.eh[dir][pp]; ra.h_lo[q][pp] = ws.eh_lo[dir][pp]; }
+                    LstmEpi& e = ra.epi[q];
+                    if (tab0) { e.xtab = m->xtab[dir]; e.x_idx = ws.idx; e.x_val = ws.val; e.x_k = ws.k; e.x_tmax = T; }
+                    e.bias = lw.bias; e.c_in = ws.ec[dir]; e.c_out = ws.ec[dir];
+                    e.row_T = ws.row_T; e.reverse = dir; e.rows_total = B;
+                    e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W;
+                    e.seq_rev = ws.seqr[n]; e.seq_rev_lo = ws.seqr_lo[n];
+                    if (m->cfg.residual_connections && !bidi && n >= 2) {
+                        e.resid = ws.seq[n - 1]; e.resid_lo = ws.seq_lo[n - 1]; e.resid_ld = m->enc_out_dim(n - 1);
+                    }
+                    e.cross_sum = deep && n + 1 < d;
+                    e.W = W;
+                }
+                if (launch_lstm_recur(st, ra)) return 1;
+            }
+            cur = T & 1;
+        } else
         for (int s = 0; s < T; ++s) {
             for (int dir = 0; dir < ndir; ++dir) {
                 const LstmW& lw = dir == 0 ? m->enc_fw[n] : m->enc_bw[n];
@@ -677,6 +722,7 @@ int cor_model_finalize(cor_model* m) {
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
     }
+    { void* gb = nullptr; if (dev_alloc(m, 256, &gb)) return 1; m->grid_bar = (unsigned*)gb; }
     m->host.clear();
     m->finalized = true;
     return 0;

@@ -92,6 +92,21 @@ int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg*
 bool tc_available();
 void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape
 
+// ------------------------------------------------------------------ persistent recurrence (recur.cu)
+// One launch = all T timesteps of one LSTM layer (both directions side by side) for a page-sized batch:
+// recurrent weights resident in shared memory, grid-wide barrier between timesteps.
+constexpr int kRecurMaxRows = 32;
+struct RecurArgs {
+    int ndir, W, B, T;
+    const float* R_hi[2]; const float* R_lo[2]; int ldr;   // recurrent kernels [4W][ldr] (fp16 head / residual)
+    LstmEpi epi[2];              // per direction; step and the h pointers are filled in by the kernel
+    float* h[2][2]; float* h_lo[2][2];                     // [dir][ping-pong]: step s reads [s & 1], writes [(s & 1) ^ 1]
+    const float* zx[2];          // non-recurrent input term [T][B][4W] (fp32) or nullptr (table gather / none)
+    unsigned* barrier;           // one counter in global memory (zeroed by the launcher)
+};
+bool lstm_recur_supported(int W, int B, int ndir);
+int launch_lstm_recur(cudaStream_t st, const RecurArgs& a);
+
 // ------------------------------------------------------------------ small kernels (kernels.cu)
 // X[t][r][:] = sum_k val*E[idx]; Xr[T_r-1-t][r][:] = same (reversed copy for backward scans)
 int launch_embed(cudaStream_t st, const int32_t* idx, const float* val, const int32_t* row_T,

@@ -163,14 +163,16 @@ def test_batch_greedy_c2_size():
         assert bad == 0, "gemm_mode %d: %d of %d strings differ" % (mode, bad, B)
 
 
-def test_two_reference_batches_in_one_call():
-    """Rows of reference batches with different padded T share one call (row_T)."""
+@pytest.mark.parametrize("gemm_mode", [1, 2])
+def test_two_reference_batches_in_one_call(gemm_mode):
+    """Rows of reference batches with different padded T share one call (row_T); gemm_mode 2 with <= 32 rows
+    runs the encoder as the persistent recurrence (recur.cu)."""
     topo, w, mapping = make_model("c2s")
     a = synthetic_lines(mapping, 5, 14, seed=21, min_length=4)
     b = synthetic_lines(mapping, 4, 25, seed=22, min_length=9)
     ra = od.correct_lines(topo, w, mapping, a, fast=True)
     rb = od.correct_lines(topo, w, mapping, b, fast=True)
-    eng = _engine(topo, w, 1)
+    eng = _engine(topo, w, gemm_mode)
     idx, _ = _sparse(mapping, a + b)
     Ta, Tb = max(map(len, a)), max(map(len, b))
     row_T = np.array([Ta] * len(a) + [Tb] * len(b), np.int32)
@@ -212,3 +214,13 @@ def test_single_pass_variant_stated_tolerance():
     print("single pass: %d of %d strings identical, max |dp| on common prefixes %.3g" % (identical, B, worst))
     assert 0.0 < worst < TOL_P_SINGLE_PASS
     assert identical >= (B * 19) // 20
+
+
+@pytest.mark.parametrize("n_lines", [1, 16, 17, 32])
+def test_page_sized_batches_c2(n_lines):
+    """Page-sized calls at the C2/C3 topology (<= 32 rows: persistent encoder recurrence with the weights
+    resident in shared memory, one launch per layer) against the oracle: strings, probabilities, alignments."""
+    topo, w, mapping = make_model("c2")
+    lines = synthetic_lines(mapping, n_lines, 40, seed=900 + n_lines, min_length=12)
+    bad, B = _greedy_compare("c2", lines, 2)
+    assert bad == 0, "%d of %d strings differ" % (bad, B)
