@@ -237,6 +237,11 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
         ws->zx[0] = c.take<float>(BT * 4 * W);
         ws->zx[1] = (m->cfg.deep_bidirectional_encoder || !m->use_xtab) ? c.take<float>(BT * 4 * W) : nullptr;
     } else { ws->zx[0] = ws->zx[1] = nullptr; }
+    for (int q = 0; q < 8; ++q) ws->pgA[q] = nullptr;
+    if (recur_layout(m, B) && m->LowCat.hi) {     // operand rows of the persistent page decoder (fp16: 2 bytes per element)
+        for (int q = 0; q < 4; ++q) ws->pgA[q] = reinterpret_cast<float*>(c.take<uint16_t>((size_t)kRecurMaxRows * (m->Vp + W)));
+        for (int q = 4; q < 8; ++q) ws->pgA[q] = reinterpret_cast<float*>(c.take<uint16_t>((size_t)kRecurMaxRows * (2 * W + D)));
+    }
     const size_t BW = (size_t)B * W;
     for (int dir = 0; dir < 2; ++dir) {
         for (int q = 0; q < 2; ++q) {
@@ -521,6 +526,35 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
     COR_CUDA(cudaMemsetAsync(ws.o_probs, 0, (size_t)B * 2 * T * 4, st));
     int cur = 0;
     const int S = 2 * T;
+    if (ws.pgA[0] && page_decoder_supported(W, m->D, m->Vp, B)) {
+        // ---- page-sized batch: the whole loop is one persistent launch (decpage.cu)
+        const int top = d - 1;
+        {   // query of step 0: wq = h_0 . W_a + b_UW  (attention.py:539)
+            GemmSeg sq = {ws.dh[0][top], W, ws.dh_lo[0][top], m->Wa.hi, m->Wa.ld, m->Wa.lo, W};
+            StoreEpi eq{ws.wq, W, nullptr, m->b_UW, 0};
+            if (gemm_store(m, st, B, nullptr, W, &sq, 1, eq)) return 1;
+        }
+        PageDecArgs pa{};
+        pa.B = B; pa.T = T; pa.S = S; pa.W = W; pa.D = m->D; pa.V = m->V; pa.Vp = m->Vp;
+        pa.window = m->cfg.window_width; pa.eos = m->cfg.eos_index; pa.b_v = m->b_v;
+        pa.low_hi = (const __half*)m->LowCat.hi; pa.low_lo = (const __half*)m->LowCat.lo;
+        pa.top_hi = (const __half*)m->TopCat.hi; pa.top_lo = (const __half*)m->TopCat.lo;
+        pa.ewa_hi = (const __half*)m->EWa.hi; pa.ewa_lo = (const __half*)m->EWa.lo; pa.ewa_ld = m->EWa.ld;
+        pa.bias_low = m->dec[0].bias; pa.bias_top = m->dec[1].bias; pa.b_UW = m->b_UW; pa.v_a = m->v_a;
+        for (int q = 0; q < 2; ++q) {
+            pa.lowA_hi[q] = (__half*)ws.pgA[2 * q]; pa.lowA_lo[q] = (__half*)ws.pgA[2 * q + 1];
+            pa.topA_hi[q] = (__half*)ws.pgA[4 + 2 * q]; pa.topA_lo[q] = (__half*)ws.pgA[4 + 2 * q + 1];
+            pa.h0_hi[q] = (const __half*)ws.dh[0][q]; pa.h0_lo[q] = (const __half*)ws.dh_lo[0][q];
+            pa.c[q] = ws.dc[q]; pa.a[q] = ws.a[q];
+        }
+        pa.logits = ws.logits; pa.wq = ws.wq; pa.o_align = ws.o_align;
+        pa.u = ws.u; pa.enc = ws.enc_out(); pa.enc_lo = ws.enc_out_lo();
+        pa.line_T = ws.row_T; pa.live = ws.live; pa.done = ws.done;
+        pa.out_chars = ws.o_chars; pa.out_probs = ws.o_probs; pa.score_sum = ws.o_score; pa.out_len = ws.o_len;
+        pa.barrier = m->grid_bar;
+        if (launch_page_decoder(st, pa)) return 1;
+        return launch_finish_scores(st, ws.o_score, ws.o_len, B);
+    }
     for (int s = 0; s < S; ++s) {
         StepIO io{};
         io.R = B; io.first = (s == 0);
@@ -723,6 +757,24 @@ int cor_model_finalize(cor_model* m) {
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
     }
     { void* gb = nullptr; if (dev_alloc(m, 256, &gb)) return 1; m->grid_bar = (unsigned*)gb; }
+    if (m->split && m->passes == 3 && d == 2 && m->fuse_pe && !m->cfg.lm_predict) {
+        // page decoder: the two cells' kernels concatenated along K, so that a CTA's K-slice is one contiguous range
+        const LstmW& lo_w = m->dec[0]; const LstmW& tw = m->dec[1];
+        const int K_low = Vp + W, K_top = 2 * W + D;
+        m->LowCat.rows = 4 * W; m->LowCat.ld = K_low; m->TopCat.rows = 4 * W; m->TopCat.ld = K_top;
+        if (dev_alloc(m, (size_t)4 * W * K_low * 2, (void**)&m->LowCat.hi) || dev_alloc(m, (size_t)4 * W * K_low * 2, (void**)&m->LowCat.lo) ||
+            dev_alloc(m, (size_t)4 * W * K_top * 2, (void**)&m->TopCat.hi) || dev_alloc(m, (size_t)4 * W * K_top * 2, (void**)&m->TopCat.lo)) return 1;
+        auto put = [&](const Mat& dst, int k0, const Mat& src, int k) -> int {
+            for (int part = 0; part < 2; ++part) {
+                char* d_ = reinterpret_cast<char*>(part ? dst.lo : dst.hi) + (size_t)k0 * 2;
+                const char* s_ = reinterpret_cast<const char*>(part ? src.lo : src.hi);
+                COR_CUDA(cudaMemcpy2D(d_, (size_t)dst.ld * 2, s_, (size_t)src.ld * 2, (size_t)k * 2, 4 * W, cudaMemcpyDeviceToDevice));
+            }
+            return 0;
+        };
+        if (put(m->LowCat, 0, m->PE, Vp) || put(m->LowCat, Vp, lo_w.R, W) ||
+            put(m->TopCat, 0, tw.Kx, W) || put(m->TopCat, W, tw.Kc, D) || put(m->TopCat, W + D, tw.R, W)) return 1;
+    }
     m->host.clear();
     m->finalized = true;
     return 0;

@@ -1,6 +1,7 @@
 // engine.h — internal interfaces shared by the .cu files of libcor_b200.so
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stddef.h>
 #include <string>
@@ -106,6 +107,32 @@ struct RecurArgs {
 };
 bool lstm_recur_supported(int W, int B, int ndir);
 int launch_lstm_recur(cudaStream_t st, const RecurArgs& a);
+
+// ------------------------------------------------------------------ persistent page decoder (decpage.cu)
+// The whole fast batch-greedy decode of a page (<= 32 lines, depth 2) in one launch; weights resident in
+// shared memory, K split over the 8 CTAs of a cluster, partial sums reduced through distributed shared memory.
+struct PageDecArgs {
+    int B, T, S, W, D, V, Vp, window, eos;
+    float b_v;
+    const __half *low_hi, *low_lo;       // [4W][Vp+W]   = [E.Kx | R] of the lower cell
+    const __half *top_hi, *top_lo;       // [4W][2W+D]   = [Kx | Kc | R] of the attention cell
+    const __half *ewa_hi, *ewa_lo; int ewa_ld;   // [Vp+W][W] = [E ; W_a]
+    const float *bias_low, *bias_top, *b_UW, *v_a;
+    __half *lowA_hi[2], *lowA_lo[2];     // [32][Vp+W]   operand rows [p | h1], ping-pong
+    __half *topA_hi[2], *topA_lo[2];     // [32][2W+D]   operand rows [h1' | ctx | h2]
+    const __half *h0_hi[2], *h0_lo[2];   // initial h of the two cells [B][W]
+    float* c[2];                         // cell states [B][W]
+    float *logits, *wq;                  // [B][Vp], [B][W] (wq of step 0 prepared by the caller)
+    float* a[2];                         // alignment rows [B][T], ping-pong; a[0] zeroed by the caller
+    float* o_align;                      // optional alignment history [S][B][T]
+    const float *u, *enc, *enc_lo;       // [T][B][W], [T][B][D] (hi/lo)
+    const int32_t* line_T;
+    const uint8_t* live; uint8_t* done;
+    int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len;
+    unsigned* barrier;
+};
+bool page_decoder_supported(int W, int D, int Vp, int B);
+int launch_page_decoder(cudaStream_t st, const PageDecArgs& a);
 
 // ------------------------------------------------------------------ small kernels (kernels.cu)
 // X[t][r][:] = sum_k val*E[idx]; Xr[T_r-1-t][r][:] = same (reversed copy for backward scans)

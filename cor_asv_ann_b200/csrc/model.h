@@ -52,6 +52,7 @@ struct cor_model {
     bool fuse_pe = false;     // PE exists (3*Vp <= 4*W: the fused product is the cheaper one)
     cudaStream_t side = nullptr;          // attention runs here, beside the lower-cell GEMMs
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cor::Mat LowCat, TopCat;  // page decoder (decpage.cu): [E.Kx | R] and [Kx | Kc | R] concatenated along K (depth 2 only)
     unsigned* grid_bar = nullptr;         // grid barrier counter of the persistent recurrence (recur.cu)
     float* b_UW = nullptr;    // [W]
     float* v_a = nullptr;     // [W]
@@ -73,6 +74,7 @@ struct Ws {
     float *X = nullptr, *X_lo = nullptr, *Xr = nullptr, *Xr_lo = nullptr;
     std::vector<float*> seq, seq_lo, seqr, seqr_lo;     // per encoder layer [T][B][Dn]
     float* u = nullptr;                                  // [T][B][W]
+    float* pgA[8] = {};                                  // page decoder operand rows: lowA hi/lo x2, topA hi/lo x2
     float* zx[2] = {nullptr, nullptr};                   // page-sized calls: input term of a layer for all timesteps [T][B][4W]
     float *eh[2][2] = {}, *eh_lo[2][2] = {}, *ec[2] = {};
     std::vector<float*> st_h, st_c;                      // encoder final states per layer [B][W]
