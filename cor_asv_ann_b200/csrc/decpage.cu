@@ -32,6 +32,8 @@
 #include <math.h>
 #include <stdlib.h>
 #include <algorithm>
+#include <stdio.h>
+#include <vector>
 
 namespace cor {
 
@@ -66,6 +68,15 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned target) {
         }
     }
     __syncthreads();
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// optional phase stamps (COR_PD_TIMING): CTA 0 records the time at which it LEAVES each barrier
+__device__ __forceinline__ void stamp(const PageDecArgs& a, int s, int phase) {
+    if (a.timing && blockIdx.x == 0 && threadIdx.x == 0) a.timing[(size_t)s * 4 + phase] = globaltimer_ns();
 }
 __device__ __forceinline__ void cluster_sync() {
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -334,6 +345,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) page_decoder_kernel(const PageD
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);
         if (s == a.S) break;
+        stamp(a, s, 0);
 
         // ================= P1: lower cell  [p | h1] -> h1', c1'
         load_tile_async(a_hi, a.lowA_hi[cur], K_low, 0, B, rank * KS_low, KS_low);
@@ -361,6 +373,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) page_decoder_kernel(const PageD
             }
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);
+        stamp(a, s, 1);
 
         // ================= P2: attention cell  [h1' | ctx | h2] -> h2', c2'
         load_tile_async(a_hi, a.topA_hi[cur], K_top, 0, B, rank * KS_top, KS_top);
@@ -387,6 +400,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) page_decoder_kernel(const PageD
             }
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);
+        stamp(a, s, 2);
 
         // ================= P3: [logits | next query] = h2' . [E ; W_a]^T
         load_tile_async(a_hi, a.topA_hi[nxt] + W + a.D, K_top, 0, B, rank * KS_e, KS_e);
@@ -411,6 +425,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) page_decoder_kernel(const PageD
             }
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);     // logits and query complete before the next P0
+        stamp(a, s, 3);
     }
     cluster_sync();     // no CTA leaves while a peer may still read its shared memory
 }
@@ -457,8 +472,33 @@ bool page_decoder_supported(int W, int D, int Vp, int B) {
     return g_pd_state == 1 && n_clusters <= g_pd_max_clusters;       // the grid barrier needs every cluster resident
 }
 
-int launch_page_decoder(cudaStream_t st, const PageDecArgs& a) {
+// COR_PD_TIMING=<file>: per-phase times of the LAST call (ns between CTA 0 leaving consecutive grid barriers,
+// averaged over the timesteps) are appended to <file>; a measurement aid, off by default.
+static void report_timing(const unsigned long long* dev, int S, cudaStream_t st, const char* path, int B) {
+    std::vector<unsigned long long> h((size_t)S * 4);
+    if (cudaStreamSynchronize(st) != cudaSuccess) return;
+    if (cudaMemcpy(h.data(), dev, h.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    double ph[4] = {0, 0, 0, 0};
+    for (int s = 1; s < S; ++s) {
+        ph[0] += (double)(h[(size_t)s * 4 + 0] - h[(size_t)(s - 1) * 4 + 3]);       // P0: softmax || attention
+        for (int k = 1; k < 4; ++k) ph[k] += (double)(h[(size_t)s * 4 + k] - h[(size_t)s * 4 + k - 1]);
+    }
+    if (FILE* f = fopen(path, "a")) {
+        fprintf(f, "{\"rows\": %d, \"steps\": %d, \"ns_P0_softmax_attention\": %.0f, \"ns_P1_lower_cell\": %.0f, \"ns_P2_attention_cell\": %.0f, \"ns_P3_logits_query\": %.0f}\n",
+                B, S, ph[0] / (S - 1), ph[1] / (S - 1), ph[2] / (S - 1), ph[3] / (S - 1));
+        fclose(f);
+    }
+}
+
+int launch_page_decoder(cudaStream_t st, const PageDecArgs& a_in) {
+    PageDecArgs a = a_in;
     COR_CHECK(page_decoder_supported(a.W, a.D, a.Vp, a.B), "persistent page decoder not available for this shape");
+    const char* tpath = getenv("COR_PD_TIMING");
+    static unsigned long long* t_buf = nullptr; static int t_cap = 0;
+    if (tpath) {
+        if (t_cap < a.S) { if (t_buf) cudaFree(t_buf); COR_CUDA(cudaMalloc(&t_buf, (size_t)a.S * 4 * 8)); t_cap = a.S; }
+        a.timing = t_buf;
+    }
     COR_CUDA(cudaMemsetAsync(a.barrier, 0, sizeof(unsigned), st));
     const int n_clusters = 4 * a.W / PD_NCOL;
     cudaLaunchConfig_t cfg{};
@@ -467,7 +507,8 @@ int launch_page_decoder(cudaStream_t st, const PageDecArgs& a) {
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = PD_CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
-    cfg.attrs = at; cfg.numAttrs = 2;
+    // COR_PD_NOCOOP: plain cluster launch (ncu cannot replay the cooperative one); co-residency then rests on the occupancy check alone
+    cfg.attrs = at; cfg.numAttrs = getenv("COR_PD_NOCOOP") ? 1 : 2;
     cudaError_t err = cudaLaunchKernelEx(&cfg, page_decoder_kernel, a);
     if (err != cudaSuccess) {       // cooperative + cluster refused: the occupancy check above already guarantees co-residency
         (void)cudaGetLastError();
@@ -476,6 +517,7 @@ int launch_page_decoder(cudaStream_t st, const PageDecArgs& a) {
     }
     COR_CUDA(err);
     ++g_launches;
+    if (tpath) report_timing(t_buf, a.S, st, tpath, a.B);
     return 0;
 }
 

@@ -130,6 +130,7 @@ struct PageDecArgs {
     const uint8_t* live; uint8_t* done;
     int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len;
     unsigned* barrier;
+    unsigned long long* timing;          // optional [S][4] phase stamps (COR_PD_TIMING), else nullptr
 };
 bool page_decoder_supported(int W, int D, int Vp, int B);
 int launch_page_decoder(cudaStream_t st, const PageDecArgs& a);

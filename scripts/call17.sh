@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_gpu_core.py -m gpu -x -q -k "page_sized or c2_size or two_reference" 2>&1 | tail -5 | tee gpurun_out/gpu_tests_page.log
+for n in 8 32; do timeout 300 python bench.py --page-only --page-lines $n > gpurun_out/page7_$n.json 2> gpurun_out/page7.err; cat gpurun_out/page7_$n.json; done
+tail -3 gpurun_out/page7.err
