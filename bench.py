@@ -293,10 +293,26 @@ def measure_page(args, eng, n_lines):
         eng.correct_greedy_host(idx[s % 4], None, host_T, out=out)
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / reps
-    return {"lines": n_lines, "ms_per_call": dt * 1e3, "us_per_decoder_timestep": dt * 1e6 / (2 * T + T),
+    page = {"lines": n_lines, "ms_per_call": dt * 1e3, "us_per_decoder_timestep": dt * 1e6 / (2 * T + T),
             "timesteps_per_call": 3 * T, "chars_per_s": LINE_LEN * n_lines / dt,
             "gpu_launches_per_call": eng.launch_count() / reps,
             "api": "cor_correct_greedy_host (pinned host buffers), T encoder + 2T decoder timesteps"}
+    # the OCR-D processor's default mode (fast_mode false, ocrd-tool.json:55-58) is the beamed decoder: same page,
+    # config-2 beam parameters (random-init weights: T iterations of one hypothesis per line)
+    bp = eng.beam_params(**BEAM)
+    b_out = None
+    for s in range(2):
+        b_out = eng.correct_beam_host(idx[s % 4], None, host_T, bp, budget_bytes=2 << 30, out=b_out)
+    torch.cuda.synchronize()
+    eng.launch_count(reset=True)
+    t0 = time.perf_counter()
+    for s in range(reps):
+        b_out = eng.correct_beam_host(idx[s % 4], None, host_T, bp, budget_bytes=2 << 30, out=b_out)
+    torch.cuda.synchronize()
+    db = (time.perf_counter() - t0) / reps
+    page["beam"] = {"ms_per_call": db * 1e3, "chars_per_s": LINE_LEN * n_lines / db, "gpu_launches_per_call": eng.launch_count() / reps,
+                    "api": "cor_correct_beam_host (pinned host buffers), persistent encoder recurrence + per-iteration beam kernels"}
+    return page
 
 
 def measure_predict(args, topo, w, mapping, device, n_lines):
@@ -441,7 +457,7 @@ def main():
             cores = host_threads()
             from threadpoolctl import threadpool_limits
             threadpool_limits(limits=cores)
-            n_cpu = args.cpu_lines or (128 if args.workload == "greedy" else 48)
+            n_cpu = args.cpu_lines or (256 if args.workload == "greedy" else 384)   # ~10-20 s of CPU work
             v, dt = cpu_oracle_rate(args.workload, n_cpu)
             line["cpu_baseline"] = {"value": v, "unit": "chars/s", "cores": cores, "kind": "port",
                                     "sample": "%d lines of the same workload, numpy oracle (Keras/TF unavailable), %.1f s"
