@@ -531,11 +531,61 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
         for (int k = 0; k < NVL; ++k) rp[lane + 32 * k] = p[k];
         float* ra = b.rec_a + g * b.T;
         for (int j = lane; j < b.T; j += 32) ra[j] = al[j];
+        // The copy is a chain of memory round trips if every array waits for the previous one's stores (the
+        // long-scoreboard stalls of the ncu capture): all loads of a 128-float4 block -- query, h (hi, lo) and c
+        // of the first two layers -- are issued together, then stored.
         const int W4 = b.W >> 2;
         float4* rq = reinterpret_cast<float4*>(b.rec_wq + g * b.W);
         const float4* wq = reinterpret_cast<const float4*>(b.wq + (size_t)row * b.W);
-        for (int u = lane; u < W4; u += 32) rq[u] = wq[u];
-        for (int n = 0; n < b.d; ++n) {
+        const int nl = min(b.d, 2);
+        for (int u0 = lane; u0 < W4; u0 += 128) {
+            float4 tq[4], tc[2][4];
+            uint2 th[2][4], tl[2][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = u0 + 32 * i;
+                if (u < W4) {
+                    tq[i] = wq[u];
+#pragma unroll
+                    for (int n = 0; n < 2; ++n) {
+                        if (n < nl) {
+                            tc[n][i] = reinterpret_cast<const float4*>(b.c_out[n] + (size_t)row * b.W)[u];
+                            if (split) {
+                                th[n][i] = *reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(b.h_out[n]) + (size_t)row * b.W + 4 * u);
+                                tl[n][i] = *reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(b.h_out_lo[n]) + (size_t)row * b.W + 4 * u);
+                            } else {
+                                const float4 hv = reinterpret_cast<const float4*>(b.h_out[n] + (size_t)row * b.W)[u];
+                                th[n][i] = make_uint2(__float_as_uint(hv.x), __float_as_uint(hv.y));
+                                tl[n][i] = make_uint2(__float_as_uint(hv.z), __float_as_uint(hv.w));
+                            }
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = u0 + 32 * i;
+                if (u < W4) {
+                    rq[u] = tq[i];
+#pragma unroll
+                    for (int n = 0; n < 2; ++n) {
+                        if (n < nl) {
+                            float4 hv;
+                            if (split) {
+                                const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&th[n][i].x)), h1 = __half22float2(*reinterpret_cast<const __half2*>(&th[n][i].y));
+                                const float2 l0 = __half22float2(*reinterpret_cast<const __half2*>(&tl[n][i].x)), l1 = __half22float2(*reinterpret_cast<const __half2*>(&tl[n][i].y));
+                                hv = make_float4(h0.x + l0.x, h0.y + l0.y, h1.x + l1.x, h1.y + l1.y);
+                            } else {
+                                hv = make_float4(__uint_as_float(th[n][i].x), __uint_as_float(th[n][i].y), __uint_as_float(tl[n][i].x), __uint_as_float(tl[n][i].y));
+                            }
+                            reinterpret_cast<float4*>(b.rec_h + (g * b.d + n) * b.W)[u] = hv;
+                            reinterpret_cast<float4*>(b.rec_c + (g * b.d + n) * b.W)[u] = tc[n][i];
+                        }
+                    }
+                }
+            }
+        }
+        for (int n = 2; n < b.d; ++n) {
             float4* rh = reinterpret_cast<float4*>(b.rec_h + (g * b.d + n) * b.W);
             float4* rc = reinterpret_cast<float4*>(b.rec_c + (g * b.d + n) * b.W);
             const float4* co = reinterpret_cast<const float4*>(b.c_out[n] + (size_t)row * b.W);
