@@ -252,20 +252,47 @@ __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) 
         const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
         const float4* rp = reinterpret_cast<const float4*>(b.rec_p + g * b.Vp);
         const int32_t* acc = b.ch_v + g * KMAX;
-        for (int v = threadIdx.x; v < V4; v += blockDim.x) {
-            float4 x = rp[v];
-            for (int q = 0; q < k; ++q) {                // better siblings were zeroed before the copy
-                const int z = acc[q] - 4 * v;
-                if (z == 0) x.x = 0.f; else if (z == 1) x.y = 0.f; else if (z == 2) x.z = 0.f; else if (z == 3) x.w = 0.f;
-            }
-            store_split4(b.p, p_lo, po + 4 * v, x);
-        }
         const float* ra = b.rec_a + g * b.T;
-        for (int j = threadIdx.x; j < b.T; j += blockDim.x) a_in[j] = ra[j];
         const float4* rq = reinterpret_cast<const float4*>(b.rec_wq + g * b.W);
         float4* wq = reinterpret_cast<float4*>(b.wq + (size_t)row * b.W);
-        for (int u = threadIdx.x; u < W4; u += blockDim.x) wq[u] = rq[u];
-        for (int n = 0; n < b.d; ++n) {
+        const int nl = min(b.d, 2);
+        // every load of a 128-wide block of the record (scores, alignment, query, h and c of the first two layers)
+        // is issued before the first store: one memory round trip per block instead of one per array
+        const int span = max(max(V4, W4), b.T);
+        for (int base = 0; base < span; base += blockDim.x) {
+            const int i = base + threadIdx.x;
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f), tq = x, th[2], tc[2];
+            float ta = 0.f;
+            if (i < V4) x = rp[i];
+            if (i < b.T) ta = ra[i];
+            if (i < W4) {
+                tq = rq[i];
+#pragma unroll
+                for (int n = 0; n < 2; ++n)
+                    if (n < nl) {
+                        th[n] = reinterpret_cast<const float4*>(b.rec_h + (g * b.d + n) * b.W)[i];
+                        tc[n] = reinterpret_cast<const float4*>(b.rec_c + (g * b.d + n) * b.W)[i];
+                    }
+            }
+            if (i < V4) {
+                for (int q = 0; q < k; ++q) {                // better siblings were zeroed before the copy
+                    const int z = acc[q] - 4 * i;
+                    if (z == 0) x.x = 0.f; else if (z == 1) x.y = 0.f; else if (z == 2) x.z = 0.f; else if (z == 3) x.w = 0.f;
+                }
+                store_split4(b.p, p_lo, po + 4 * i, x);
+            }
+            if (i < b.T) a_in[i] = ta;
+            if (i < W4) {
+                wq[i] = tq;
+#pragma unroll
+                for (int n = 0; n < 2; ++n)
+                    if (n < nl) {
+                        store_split4(b.h_in[n], split ? b.h_in_lo[n] : nullptr, (size_t)row * b.W + 4 * i, th[n]);
+                        reinterpret_cast<float4*>(b.c_in[n] + (size_t)row * b.W)[i] = tc[n];
+                    }
+            }
+        }
+        for (int n = 2; n < b.d; ++n) {
             const float4* rh = reinterpret_cast<const float4*>(b.rec_h + (g * b.d + n) * b.W);
             const float4* rc = reinterpret_cast<const float4*>(b.rec_c + (g * b.d + n) * b.W);
             float4* ci = reinterpret_cast<float4*>(b.c_in[n] + (size_t)row * b.W);
