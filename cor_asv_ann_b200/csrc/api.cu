@@ -326,6 +326,7 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
                     e.bias = lw.bias; e.c_in = ws.ec[dir]; e.c_out = ws.ec[dir];
                     e.row_T = ws.row_T; e.reverse = dir; e.rows_total = B;
                     e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W;
+                    if (n == d - 1) { e.seq_tm = 1; e.seq_rm = T; }      // enc_out is line-major (attention gathers windows)
                     e.seq_rev = ws.seqr[n]; e.seq_rev_lo = ws.seqr_lo[n];
                     if (m->cfg.residual_connections && !bidi && n >= 2) {
                         e.resid = ws.seq[n - 1]; e.resid_lo = ws.seq_lo[n - 1]; e.resid_ld = m->enc_out_dim(n - 1);
@@ -356,6 +357,7 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
                 e.h_out = ws.eh[dir][cur ^ 1]; e.h_out_lo = ws.eh_lo[dir][cur ^ 1];
                 e.row_T = ws.row_T; e.step = s; e.reverse = dir; e.rows_total = B;
                 e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W;
+                if (n == d - 1) { e.seq_tm = 1; e.seq_rm = T; }          // enc_out is line-major (attention gathers windows)
                 e.seq_rev = ws.seqr[n]; e.seq_rev_lo = ws.seqr_lo[n];
                 if (m->cfg.residual_connections && !bidi && n >= 2) {
                     e.resid = ws.seq[n - 1]; e.resid_lo = ws.seq_lo[n - 1]; e.resid_ld = m->enc_out_dim(n - 1);
@@ -853,7 +855,8 @@ int cor_encode(cor_model* m, const cor_lines* lines, void* workspace, size_t wor
     if (!lines->val) ws.val = nullptr;
     if (run_encoder(m, ws, st)) return 1;
     const size_t BW = (size_t)ws.B * m->W;
-    if (enc_out && copy_out(st, ws.enc_out(), ws.enc_out_lo(), enc_out, (size_t)ws.T * ws.B * m->D)) return 1;
+    // the internal enc_out is line-major; the C ABI returns the reference's (T, B, D) enumeration
+    if (enc_out && launch_join_lt(st, ws.enc_out(), ws.enc_out_lo(), enc_out, ws.B, ws.T, m->D)) return 1;
     if (states)
         for (int n = 0; n < m->d; ++n) {
             COR_CUDA(cudaMemcpyAsync(states + (2 * n) * BW, ws.st_h[n], BW * 4, cudaMemcpyDeviceToDevice, st));

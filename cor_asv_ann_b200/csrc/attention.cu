@@ -88,25 +88,27 @@ __global__ void __launch_bounds__(512, 1) attention_tma_kernel(AttnArgs a, SlabG
     };
     // the two bursts of a row (issued by the group's first warp): query + keys u_j on bar_u,
     // annotations enc_j (hi, lo) on bar_e
+    // u and enc are line-major ([L][t_max][.]): the window rows of a line are ONE contiguous block per array,
+    // fetched by a single bulk copy (two for hi/lo) instead of one 1-2 KB copy per position
     auto issue_u = [&](int row, int line, int j0, int nj) {
         if (lane == 0) {
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_u), "r"(u_row * (uint32_t)(1 + nj)) : "memory");
             bulk_g2s(slab_s + g.wq_off, a.wq + (size_t)row * a.W, u_row, bar_u);
+            if (nj > 0) bulk_g2s(slab_s + g.u_off, a.u + ((size_t)line * a.t_max + j0) * a.W, u_row * (uint32_t)nj, bar_u);
         }
         __syncwarp();
-        if (lane < nj)
-            bulk_g2s(slab_s + g.u_off + lane * u_row, a.u + ((size_t)(j0 + lane) * a.L + line) * a.W, u_row, bar_u);
     };
     auto issue_e = [&](int line, int j0, int nj) {
-        if (lane == 0)
+        if (lane == 0) {
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_e), "r"((uint32_t)nj * e_row * (a.enc_lo ? 2u : 1u)) : "memory");
-        __syncwarp();
-        if (lane < nj) {
-            const size_t pos = (size_t)(j0 + lane) * a.L + line;
-            bulk_g2s(slab_s + g.e_hi_off + lane * e_row, reinterpret_cast<const uint8_t*>(a.enc) + pos * e_row, e_row, bar_e);
-            if (a.enc_lo)
-                bulk_g2s(slab_s + g.e_lo_off + lane * e_row, reinterpret_cast<const uint8_t*>(a.enc_lo) + pos * e_row, e_row, bar_e);
+            if (nj > 0) {
+                const size_t pos = (size_t)line * a.t_max + j0;
+                bulk_g2s(slab_s + g.e_hi_off, reinterpret_cast<const uint8_t*>(a.enc) + pos * e_row, e_row * (uint32_t)nj, bar_e);
+                if (a.enc_lo)
+                    bulk_g2s(slab_s + g.e_lo_off, reinterpret_cast<const uint8_t*>(a.enc_lo) + pos * e_row, e_row * (uint32_t)nj, bar_e);
+            }
         }
+        __syncwarp();
     };
     auto wait = [&](uint32_t bar, uint32_t parity) {
         if (mbar_try(bar, parity)) return;

@@ -202,7 +202,7 @@ __device__ void attention_row_cta(const PageDecArgs& a, int row, const float* a_
     }
     const float* wq = a.wq + (size_t)row * a.W;
     for (int qq = warp; qq < nj; qq += PD_THREADS / 32) {      // one warp per window position
-        const float* u = a.u + ((size_t)(j0 + qq) * a.B + row) * a.W;
+        const float* u = a.u + ((size_t)row * a.T + j0 + qq) * a.W;
         float t = 0.f;
         for (int k = lane * 4; k < a.W; k += 128) {
             const float4 w4 = *reinterpret_cast<const float4*>(wq + k);
@@ -229,7 +229,7 @@ __device__ void attention_row_cta(const PageDecArgs& a, int row, const float* a_
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int qq = 0; qq < nj; ++qq) {
             const float w = s_scr[qq] / esum;
-            const float4 x = load_split4(a.enc, a.enc_lo, ((size_t)(j0 + qq) * a.B + row) * a.D + k);
+            const float4 x = load_split4(a.enc, a.enc_lo, ((size_t)row * a.T + j0 + qq) * a.D + k);
             c.x = fmaf(w, x.x, c.x); c.y = fmaf(w, x.y, c.y); c.z = fmaf(w, x.z, c.z); c.w = fmaf(w, x.w, c.w);
         }
         store_h(ctx_hi, ctx_lo, k + 0, c.x); store_h(ctx_hi, ctx_lo, k + 1, c.y);

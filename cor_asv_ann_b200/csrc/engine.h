@@ -73,6 +73,11 @@ struct LstmEpi {
     int reverse;
     int rows_total;            // B: row stride of the time-major sequence buffers
     float* seq_out;  float* seq_out_lo;  int seq_ld; int seq_col;   // seq_out[t][r][seq_col+u]
+    // position of (t, r) in seq_out, in rows of seq_ld elements: t * seq_tm + r * seq_rm.  Time-major (tm = B, rm = 1)
+    // for layers that feed another layer's per-timestep GEMM; LINE-major (tm = 1, rm = t_max) for the last layer, whose
+    // output is only gathered by window (attention): a line's window is then one contiguous block for the bulk copies.
+    // Both 0 = time-major with rows_total.
+    int seq_tm, seq_rm;
     float* seq_rev;  float* seq_rev_lo;                              // seq_rev[T-1-t][r][seq_col+u]
     const float* resid; const float* resid_lo; int resid_ld;         // residual add into seq_out
     int cross_sum;             // seq value = h[2k]+h[2k+1] for both members of a pair
@@ -125,7 +130,7 @@ struct PageDecArgs {
     float *logits, *wq;                  // [B][Vp], [B][W] (wq of step 0 prepared by the caller)
     float* a[2];                         // alignment rows [B][T], ping-pong; a[0] zeroed by the caller
     float* o_align;                      // optional alignment history [S][B][T]
-    const float *u, *enc, *enc_lo;       // [T][B][W], [T][B][D] (hi/lo)
+    const float *u, *enc, *enc_lo;       // [B][T][W], [B][T][D] (hi/lo), line-major
     const int32_t* line_T;
     const uint8_t* live; uint8_t* done;
     int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len;
@@ -143,8 +148,8 @@ int launch_embed(cudaStream_t st, const int32_t* idx, const float* val, const in
 
 struct AttnArgs {
     const float* wq;           // [R][W]  = h_prev*W_a + b_UW
-    const float* u;            // [T][L][W]
-    const float* enc;          // [T][L][D]  (hi part when enc_lo set)
+    const float* u;            // [L][t_max][W]   line-major: a line's window rows are contiguous
+    const float* enc;          // [L][t_max][D]  (hi part when enc_lo set)
     const float* enc_lo;
     const float* a_prev;       // [R][t_max]
     const int32_t* row_line;   // [R] or nullptr
@@ -169,6 +174,7 @@ int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a);
 int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, int R, const int* r_dev, int V);
 int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n);
 int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, size_t n);
+int launch_join_lt(cudaStream_t st, const float* hi, const float* lo, float* out, int L, int T, int D);   // line-major (hi, lo) -> time-major fp32
 int launch_finish_scores(cudaStream_t st, double* score_sum, const int32_t* len, int R);
 int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int n_rows, int t_max, int k_alt, uint8_t* live);
 

@@ -57,6 +57,11 @@ __device__ __forceinline__ float tanhf_fast(float x) {
     return fmaf(-2.0f, rcp_approx(ex2_approx(2.8853900817779268f * x) + 1.0f), 1.0f);
 }
 
+// row index of sequence position (t, row) in seq_out / seq_rev (see LstmEpi::seq_tm)
+__device__ __forceinline__ size_t seq_pos(const LstmEpi& e, int t, int row) {
+    return e.seq_tm ? (size_t)t * e.seq_tm + (size_t)row * e.seq_rm : (size_t)t * e.rows_total + row;
+}
+
 // One LSTM unit of one row.  z[0..3] = pre-activations i,f,c~,o WITHOUT bias.
 // Keras LSTMCell, implementation 2.  Returns the new h.
 __device__ __forceinline__ float lstm_unit(const LstmEpi& e, int row, int unit, const float z[4]) {
@@ -128,7 +133,7 @@ __device__ __forceinline__ void lstm_row_units(const LstmEpi& e, int row, int un
         for (int k = 0; k + 1 < NU; k += 2) { float s = h[k] + h[k + 1]; y[k] = s; y[k + 1] = s; }
     }
     if (e.seq_out) {
-        const size_t base = ((size_t)t * e.rows_total + row) * e.seq_ld + e.seq_col + unit0;
+        const size_t base = seq_pos(e, t, row) * e.seq_ld + e.seq_col + unit0;
 #pragma unroll
         for (int k = 0; k < NU; ++k) {
             float v = y[k];
@@ -137,7 +142,7 @@ __device__ __forceinline__ void lstm_row_units(const LstmEpi& e, int row, int un
         }
     }
     if (e.seq_rev) {
-        const size_t base = ((size_t)(T - 1 - t) * e.rows_total + row) * e.seq_ld + e.seq_col + unit0;
+        const size_t base = seq_pos(e, T - 1 - t, row) * e.seq_ld + e.seq_col + unit0;
 #pragma unroll
         for (int k = 0; k < NU; ++k) store_split(e.seq_rev, e.seq_rev_lo, base + k, y[k]);
     }

@@ -320,10 +320,10 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, const RowCtx& rc, in
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] += r[k];
         }
-        store8_split(e.seq_out, e.seq_out_lo, ((size_t)t * e.rows_total + row) * e.seq_ld + e.seq_col + unit0, v);
+        store8_split(e.seq_out, e.seq_out_lo, seq_pos(e, t, row) * e.seq_ld + e.seq_col + unit0, v);
     }
     if (e.seq_rev)
-        store8_split(e.seq_rev, e.seq_rev_lo, ((size_t)(T - 1 - t) * e.rows_total + row) * e.seq_ld + e.seq_col + unit0, y);
+        store8_split(e.seq_rev, e.seq_rev_lo, seq_pos(e, T - 1 - t, row) * e.seq_ld + e.seq_col + unit0, y);
 }
 
 __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0, int N, const uint32_t (&z)[32]) {

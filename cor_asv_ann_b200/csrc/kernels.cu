@@ -89,8 +89,8 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
         if (keep) { if (nj == 0) j0 = j; ++nj; }
     }
     const float* wq = a.wq + (size_t)row * a.W;
-    const size_t ustride = (size_t)a.L * a.W;
-    const float* ub = a.u + ((size_t)j0 * a.L + line) * a.W;
+    const size_t ustride = (size_t)a.W;                          // line-major: [L][t_max][W]
+    const float* ub = a.u + ((size_t)line * a.t_max + j0) * a.W;
     float s[MAXWIN];
 #pragma unroll
     for (int q = 0; q < MAXWIN; ++q) s[q] = 0.f;
@@ -134,8 +134,8 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
         if (al) al[j] = v;
     }
     // context = sum_j a_j * enc_j
-    const size_t estride = (size_t)a.L * a.D;
-    const size_t eb = ((size_t)j0 * a.L + line) * a.D;
+    const size_t estride = (size_t)a.D;
+    const size_t eb = ((size_t)line * a.t_max + j0) * a.D;
     for (int k = lane * 4; k < a.D; k += 128) {
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -215,6 +215,15 @@ __global__ void join_kernel(const float* __restrict__ hi, const float* __restric
     for (; i < n; i += stride) out[i] = load_split(hi, lo, i);
 }
 
+// out[t][l][:] (fp32, time-major: the C-ABI layout of cor_encode) = hi/lo[l][t][:] (line-major, internal)
+__global__ void join_lt_kernel(const float* __restrict__ hi, const float* __restrict__ lo, float* out, int L, int T, int D) {
+    const size_t n = (size_t)L * T * D;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int dd = (int)(i % D); const size_t lt = i / D; const int t = (int)(lt % T), l = (int)(lt / T);
+        out[((size_t)t * L + l) * D + dd] = load_split(hi, lo, i);
+    }
+}
+
 __global__ void finish_scores_kernel(double* score_sum, const int32_t* len, int R) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < R && len[r] > 0) score_sum[r] /= (double)len[r];
@@ -283,6 +292,16 @@ int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, s
     int blocks = (int)((n + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     join_kernel<<<blocks, 256, 0, st>>>(hi, lo, out, n);
+    ++g_launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_join_lt(cudaStream_t st, const float* hi, const float* lo, float* out, int L, int T, int D) {
+    const size_t n = (size_t)L * T * D;
+    if (!n) return 0;
+    int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+    join_lt_kernel<<<blocks, 256, 0, st>>>(hi, lo, out, L, T, D);
     ++g_launches;
     COR_CUDA(cudaGetLastError());
     return 0;
