@@ -6,8 +6,9 @@
 // each byte used once, nothing shared between rows — an HBM-bound gather.  One group of warps per row:
 //   1. centre and window from the previous alignment row (attention.py:551-557),
 //   2. two bursts of bulk async copies (cp.async.bulk, the 1-D TMA path) into the group's shared-memory
-//      slab, each counted on its own mbarrier: the query row + every window row of u, and every window
-//      row of enc (hi, lo) — ~45 KB in flight per row without holding a register,
+//      slab, each counted on its own mbarrier: the query row + the window block of u, and the window
+//      blocks of enc (hi, lo) — u and enc are line-major, so a window is one contiguous block per array;
+//      ~45 KB in flight per row without holding a register,
 //   3. energies e_j = exp(v . tanh(wq + u_j) + b_v) and the context sum_j a_j enc_j from shared memory.
 // Positions outside the window have e*0 = 0 exactly in the reference (mask multiply, :557-566), so
 // evaluating only the window gives the same sums.

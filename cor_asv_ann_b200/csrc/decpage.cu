@@ -181,24 +181,35 @@ __device__ __forceinline__ void store_h(__half* hi, __half* lo, size_t off, floa
 
 // Attention of one line by one CTA (attention.py:526-575 restricted to the window; the arithmetic and its
 // order follow attention_kernel in kernels.cu: per-lane fmaf chains over k, butterfly sums, weights in window order).
-__device__ void attention_row_cta(const PageDecArgs& a, int row, const float* a_prev, float* a_out, float* align_log,
+__device__ void attention_row_cta(const PageDecArgs& a, int row, bool first, float* a_out, float* align_log,
                                   __half* ctx_hi, __half* ctx_lo, float* s_scr) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int T = a.line_T[row];
-    const float* ap = a_prev + (size_t)row * a.T;
-    if (warp == 0) {    // centre = sum_j a_prev[j]*j + 1
-        float part = 0.f;
-        for (int j = lane; j < T; j += 32) part = fmaf(ap[j], (float)j, part);
-        const float centre = warp_sum(part) + 1.0f;
-        if (lane == 0) s_scr[31] = centre;
-    }
-    __syncthreads();
-    const float centre = s_scr[31];
+    // centre = sum_j a_prev[j]*j + 1 (attention.py:551-553).  The previous alignment row was produced by THIS
+    // CTA one timestep ago, so the centre is carried in shared memory (s_scr[30], computed at the end of the
+    // previous call with the reference kernel's lane assignment and summation order) instead of re-reading the
+    // row from global memory; the first step has a_prev == 0.
+    const float centre = first ? 1.0f : s_scr[30];
     const int j_lo = max(0, (int)ceilf(centre - (float)a.window) - 1);
     const int j_hi = min(T - 1, (int)floorf(centre + (float)a.window) + 1);
     int j0 = 0, nj = 0;
     for (int j = j_lo; j <= j_hi && nj < 13; ++j) {
         if (fabsf(centre - (float)j) <= (float)a.window) { if (nj == 0) j0 = j; ++nj; }
+    }
+    // the annotation rows of the window do not depend on the energies: their loads are issued first and wait in
+    // registers (one memory round trip for keys and annotations together)
+    const int kx = threadIdx.x * 4;
+    const bool has_x = kx < a.D && a.D <= PD_THREADS * 4 && a.enc_lo != nullptr;
+    uint2 xh[13], xl[13];
+    if (has_x) {
+        const __half* eh = reinterpret_cast<const __half*>(a.enc) + ((size_t)row * a.T + j0) * a.D + kx;
+        const __half* el = reinterpret_cast<const __half*>(a.enc_lo) + ((size_t)row * a.T + j0) * a.D + kx;
+#pragma unroll
+        for (int qq = 0; qq < 13; ++qq)
+            if (qq < nj) {
+                xh[qq] = *reinterpret_cast<const uint2*>(eh + (size_t)qq * a.D);
+                xl[qq] = *reinterpret_cast<const uint2*>(el + (size_t)qq * a.D);
+            }
     }
     const float* wq = a.wq + (size_t)row * a.W;
     for (int qq = warp; qq < nj; qq += PD_THREADS / 32) {      // one warp per window position
@@ -225,17 +236,41 @@ __device__ void attention_row_cta(const PageDecArgs& a, int row, const float* a_
         a_out[(size_t)row * a.T + j] = v;
         if (align_log) align_log[(size_t)row * a.T + j] = v;
     }
-    for (int k = threadIdx.x * 4; k < a.D; k += PD_THREADS * 4) {
-        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int qq = 0; qq < nj; ++qq) {
-            const float w = s_scr[qq] / esum;
-            const float4 x = load_split4(a.enc, a.enc_lo, ((size_t)row * a.T + j0 + qq) * a.D + k);
-            c.x = fmaf(w, x.x, c.x); c.y = fmaf(w, x.y, c.y); c.z = fmaf(w, x.z, c.z); c.w = fmaf(w, x.w, c.w);
+    float next_centre = 0.f;
+    if (warp == 0) {    // lane l owns the positions j = l (mod 32); the window has at most one of them, the rest are zeros
+        float part = 0.f;
+        for (int j = lane; j < T; j += 32) {
+            const int qq = j - j0;
+            if (qq >= 0 && qq < nj) part = fmaf(s_scr[qq] / esum, (float)j, part);
         }
-        store_h(ctx_hi, ctx_lo, k + 0, c.x); store_h(ctx_hi, ctx_lo, k + 1, c.y);
-        store_h(ctx_hi, ctx_lo, k + 2, c.z); store_h(ctx_hi, ctx_lo, k + 3, c.w);
+        next_centre = warp_sum(part) + 1.0f;
     }
-    __syncthreads();
+    if (has_x) {
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int qq = 0; qq < 13; ++qq)
+            if (qq < nj) {
+                const float w = s_scr[qq] / esum;
+                const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&xh[qq].x)), h1 = __half22float2(*reinterpret_cast<const __half2*>(&xh[qq].y));
+                const float2 l0 = __half22float2(*reinterpret_cast<const __half2*>(&xl[qq].x)), l1 = __half22float2(*reinterpret_cast<const __half2*>(&xl[qq].y));
+                c.x = fmaf(w, h0.x + l0.x, c.x); c.y = fmaf(w, h0.y + l0.y, c.y); c.z = fmaf(w, h1.x + l1.x, c.z); c.w = fmaf(w, h1.y + l1.y, c.w);
+            }
+        store_h(ctx_hi, ctx_lo, kx + 0, c.x); store_h(ctx_hi, ctx_lo, kx + 1, c.y);
+        store_h(ctx_hi, ctx_lo, kx + 2, c.z); store_h(ctx_hi, ctx_lo, kx + 3, c.w);
+    } else if (!(a.D <= PD_THREADS * 4 && a.enc_lo != nullptr)) {
+        for (int k = threadIdx.x * 4; k < a.D; k += PD_THREADS * 4) {
+            float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int qq = 0; qq < nj; ++qq) {
+                const float w = s_scr[qq] / esum;
+                const float4 x = load_split4(a.enc, a.enc_lo, ((size_t)row * a.T + j0 + qq) * a.D + k);
+                c.x = fmaf(w, x.x, c.x); c.y = fmaf(w, x.y, c.y); c.z = fmaf(w, x.z, c.z); c.w = fmaf(w, x.w, c.w);
+            }
+            store_h(ctx_hi, ctx_lo, k + 0, c.x); store_h(ctx_hi, ctx_lo, k + 1, c.y);
+            store_h(ctx_hi, ctx_lo, k + 2, c.z); store_h(ctx_hi, ctx_lo, k + 3, c.w);
+        }
+    }
+    __syncthreads();                                   // everyone is done with the energies in s_scr
+    if (warp == 0 && lane == 0) s_scr[30] = next_centre;
 }
 
 // softmax of one line's logits + greedy bookkeeping (decode_batch_greedy, seq2seq.py:1250-1260) by one warp;
@@ -340,7 +375,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) page_decoder_kernel(const PageD
         if (s < a.S) {
             const int row = (int)gridDim.x - 1 - (int)blockIdx.x;       // attention rows on the other end of the grid
             if (row < B)
-                attention_row_cta(a, row, a.a[cur], a.a[nxt], a.o_align ? a.o_align + (size_t)s * B * a.T : nullptr,
+                attention_row_cta(a, row, s == 0, a.a[nxt], a.o_align ? a.o_align + (size_t)s * B * a.T : nullptr,
                                   a.topA_hi[cur] + (size_t)row * K_top + W, a.topA_lo[cur] + (size_t)row * K_top + W, s_scr);
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);

@@ -72,8 +72,8 @@ struct Ws {
     size_t bytes = 0;
     int32_t* row_T = nullptr; int32_t* idx = nullptr; float* val = nullptr; uint8_t* live = nullptr; uint8_t* done = nullptr;
     float *X = nullptr, *X_lo = nullptr, *Xr = nullptr, *Xr_lo = nullptr;
-    std::vector<float*> seq, seq_lo, seqr, seqr_lo;     // per encoder layer [T][B][Dn]
-    float* u = nullptr;                                  // [T][B][W]
+    std::vector<float*> seq, seq_lo, seqr, seqr_lo;     // per encoder layer [T][B][Dn]; the LAST layer (enc_out) is line-major [B][T][D]
+    float* u = nullptr;                                  // [B][T][W] (line-major, like enc_out)
     float* pgA[8] = {};                                  // page decoder operand rows: lowA hi/lo x2, topA hi/lo x2
     float* zx[2] = {nullptr, nullptr};                   // page-sized calls: input term of a layer for all timesteps [T][B][4W]
     float *eh[2][2] = {}, *eh_lo[2][2] = {}, *ec[2] = {};

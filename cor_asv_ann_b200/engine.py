@@ -82,14 +82,16 @@ class Engine:
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     # ------------------------------------------------------------------ encoder
-    def encode(self, idx, val, row_T, want_align=False):
+    def encode(self, idx, val, row_T, want_align=False, want_outputs=True):
         """idx int32 [B,T,k] (device), val float32 [B,T,k] or None, row_T int32 [B].
-        Returns (enc_out [T,B,D], states [2d,B,W]); the encoded lines stay in the workspace."""
+        Returns (enc_out [T,B,D], states [2d,B,W]); the encoded lines stay in the workspace.
+        want_outputs=False skips the two copies (the decoders read the workspace, not these): enc_out alone is
+        T*B*D*4 bytes -- 2.7 GB for 16 384 lines -- and returns (None, None)."""
         B, T, k = idx.shape
         ws = self._workspace(self.workspace_bytes(B, T, k, want_align))
         lines = CorLines(B, T, k, _ptr(row_T), _ptr(idx), _ptr(val))
-        enc_out = torch.empty((T, B, self.D), dtype=torch.float32, device=self.device)
-        states = torch.empty((2 * self.d, B, self.W), dtype=torch.float32, device=self.device)
+        enc_out = torch.empty((T, B, self.D), dtype=torch.float32, device=self.device) if want_outputs else None
+        states = torch.empty((2 * self.d, B, self.W), dtype=torch.float32, device=self.device) if want_outputs else None
         with torch.cuda.device(self.device):
             check(self.lib.cor_encode(self.handle, C.byref(lines), _ptr(ws), ws.numel(),
                                       _ptr(enc_out), _ptr(states), self._stream()))
