@@ -1,4 +1,4 @@
-// decpage.cu — persistent fused decoder for page-sized batches (fast batch-greedy decode, <= 32 lines).
+// decpage.cu — persistent fused decoder for page-sized batches (fast batch-greedy decode, <= 64 lines, in blocks of 32 rows).
 //
 // North star item (3): "one fused decoder-step kernel that performs the LSTM cell, the local monotonic
 // additive attention cell, the tied-weight softmax and the direct softmax feedback".  For a page of lines
@@ -39,7 +39,7 @@ namespace cor {
 
 namespace {
 
-constexpr int PD_ROWS = kRecurMaxRows;   // 32
+constexpr int PD_ROWS = 32;              // rows per pass (two m16 tiles); a call has up to kRecurMaxRows rows, taken in blocks
 constexpr int PD_CS = 4;                 // CTAs per cluster = K-slices (B200 fits 33 clusters of 4 one-CTA-per-SM blocks, but only 15 of 8)
 constexpr int PD_NCOL = 64;              // gate columns per cluster (16 LSTM units): one n-tile per warp
 constexpr int PD_THREADS = 256;
@@ -382,74 +382,84 @@ __global__ void __launch_bounds__(PD_THREADS, 1) page_decoder_kernel(const PageD
         if (s == a.S) break;
         stamp(a, s, 0);
 
-        // ================= P1: lower cell  [p | h1] -> h1', c1'
-        load_tile_async(a_hi, a.lowA_hi[cur], K_low, 0, B, rank * KS_low, KS_low);
-        load_tile_async(a_lo, a.lowA_lo[cur], K_low, 0, B, rank * KS_low, KS_low);
-        cp_async_wait_all();
-        __syncthreads();
-        partial_product(part, a_hi, a_lo, wl_hi, wl_lo, KS_low, PD_NCOL, B);
-        cluster_sync();
-        if (tid < PD_ROWS * 4) {
-            const int row = tid >> 2, u = tid & 3;
-            if (row < B) {
-                const int unit = (col0 >> 2) + 4 * rank + u;
-                float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-                const float* src = part + row * PART_LD + 16 * rank + 4 * u;
+        // ================= P1: lower cell  [p | h1] -> h1', c1'   (rows in blocks of 32 over the resident weights)
+        for (int r0 = 0; r0 < B; r0 += PD_ROWS) {
+            const int Bb = min(PD_ROWS, B - r0);
+            if (r0 > 0) cluster_sync();                  // the peers are done with this CTA's partial sums of the previous block
+            load_tile_async(a_hi, a.lowA_hi[cur], K_low, r0, Bb, rank * KS_low, KS_low);
+            load_tile_async(a_lo, a.lowA_lo[cur], K_low, r0, Bb, rank * KS_low, KS_low);
+            cp_async_wait_all();
+            __syncthreads();
+            partial_product(part, a_hi, a_lo, wl_hi, wl_lo, KS_low, PD_NCOL, Bb);
+            cluster_sync();
+            if (tid < PD_ROWS * 4) {
+                const int rl = tid >> 2, u = tid & 3, row = r0 + rl;
+                if (rl < Bb) {
+                    const int unit = (col0 >> 2) + 4 * rank + u;
+                    float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float* src = part + rl * PART_LD + 16 * rank + 4 * u;
 #pragma unroll
-                for (uint32_t r = 0; r < PD_CS; ++r) { const float4 v = ld_dsmem4(src, r); z.x += v.x; z.y += v.y; z.z += v.z; z.w += v.w; }
-                const float4 b = *reinterpret_cast<const float4*>(a.bias_low + 4 * unit);
-                const float ig = sigmoidf_fast(z.x + b.x), fg = sigmoidf_fast(z.y + b.y), gg = tanhf_fast(z.z + b.z), og = sigmoidf_fast(z.w + b.w);
-                const size_t so = (size_t)row * W + unit;
-                const float c = fg * a.c[0][so] + ig * gg;
-                a.c[0][so] = c;
-                const float h = og * tanhf_fast(c);
-                store_h(a.topA_hi[cur], a.topA_lo[cur], (size_t)row * K_top + unit, h);                 // input of this step's attention cell
-                store_h(a.lowA_hi[nxt], a.lowA_lo[nxt], (size_t)row * K_low + a.Vp + unit, h);          // recurrent input of the next step
+                    for (uint32_t r = 0; r < PD_CS; ++r) { const float4 v = ld_dsmem4(src, r); z.x += v.x; z.y += v.y; z.z += v.z; z.w += v.w; }
+                    const float4 b = *reinterpret_cast<const float4*>(a.bias_low + 4 * unit);
+                    const float ig = sigmoidf_fast(z.x + b.x), fg = sigmoidf_fast(z.y + b.y), gg = tanhf_fast(z.z + b.z), og = sigmoidf_fast(z.w + b.w);
+                    const size_t so = (size_t)row * W + unit;
+                    const float c = fg * a.c[0][so] + ig * gg;
+                    a.c[0][so] = c;
+                    const float h = og * tanhf_fast(c);
+                    store_h(a.topA_hi[cur], a.topA_lo[cur], (size_t)row * K_top + unit, h);                 // input of this step's attention cell
+                    store_h(a.lowA_hi[nxt], a.lowA_lo[nxt], (size_t)row * K_low + a.Vp + unit, h);          // recurrent input of the next step
+                }
             }
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);
         stamp(a, s, 1);
 
         // ================= P2: attention cell  [h1' | ctx | h2] -> h2', c2'
-        load_tile_async(a_hi, a.topA_hi[cur], K_top, 0, B, rank * KS_top, KS_top);
-        load_tile_async(a_lo, a.topA_lo[cur], K_top, 0, B, rank * KS_top, KS_top);
-        cp_async_wait_all();
-        __syncthreads();
-        partial_product(part, a_hi, a_lo, wt_hi, wt_lo, KS_top, PD_NCOL, B);
-        cluster_sync();
-        if (tid < PD_ROWS * 4) {
-            const int row = tid >> 2, u = tid & 3;
-            if (row < B) {
-                const int unit = (col0 >> 2) + 4 * rank + u;
-                float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-                const float* src = part + row * PART_LD + 16 * rank + 4 * u;
+        for (int r0 = 0; r0 < B; r0 += PD_ROWS) {
+            const int Bb = min(PD_ROWS, B - r0);
+            if (r0 > 0) cluster_sync();
+            load_tile_async(a_hi, a.topA_hi[cur], K_top, r0, Bb, rank * KS_top, KS_top);
+            load_tile_async(a_lo, a.topA_lo[cur], K_top, r0, Bb, rank * KS_top, KS_top);
+            cp_async_wait_all();
+            __syncthreads();
+            partial_product(part, a_hi, a_lo, wt_hi, wt_lo, KS_top, PD_NCOL, Bb);
+            cluster_sync();
+            if (tid < PD_ROWS * 4) {
+                const int rl = tid >> 2, u = tid & 3, row = r0 + rl;
+                if (rl < Bb) {
+                    const int unit = (col0 >> 2) + 4 * rank + u;
+                    float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float* src = part + rl * PART_LD + 16 * rank + 4 * u;
 #pragma unroll
-                for (uint32_t r = 0; r < PD_CS; ++r) { const float4 v = ld_dsmem4(src, r); z.x += v.x; z.y += v.y; z.z += v.z; z.w += v.w; }
-                const float4 b = *reinterpret_cast<const float4*>(a.bias_top + 4 * unit);
-                const float ig = sigmoidf_fast(z.x + b.x), fg = sigmoidf_fast(z.y + b.y), gg = tanhf_fast(z.z + b.z), og = sigmoidf_fast(z.w + b.w);
-                const size_t so = (size_t)row * W + unit;
-                const float c = fg * a.c[1][so] + ig * gg;
-                a.c[1][so] = c;
-                const float h = og * tanhf_fast(c);
-                store_h(a.topA_hi[nxt], a.topA_lo[nxt], (size_t)row * K_top + W + a.D + unit, h);       // h2 of the next step (and of P3)
+                    for (uint32_t r = 0; r < PD_CS; ++r) { const float4 v = ld_dsmem4(src, r); z.x += v.x; z.y += v.y; z.z += v.z; z.w += v.w; }
+                    const float4 b = *reinterpret_cast<const float4*>(a.bias_top + 4 * unit);
+                    const float ig = sigmoidf_fast(z.x + b.x), fg = sigmoidf_fast(z.y + b.y), gg = tanhf_fast(z.z + b.z), og = sigmoidf_fast(z.w + b.w);
+                    const size_t so = (size_t)row * W + unit;
+                    const float c = fg * a.c[1][so] + ig * gg;
+                    a.c[1][so] = c;
+                    const float h = og * tanhf_fast(c);
+                    store_h(a.topA_hi[nxt], a.topA_lo[nxt], (size_t)row * K_top + W + a.D + unit, h);       // h2 of the next step (and of P3)
+                }
             }
         }
         grid_sync(a.barrier, gridDim.x * ++epoch);
         stamp(a, s, 2);
 
         // ================= P3: [logits | next query] = h2' . [E ; W_a]^T
-        load_tile_async(a_hi, a.topA_hi[nxt] + W + a.D, K_top, 0, B, rank * KS_e, KS_e);
-        load_tile_async(a_lo, a.topA_lo[nxt] + W + a.D, K_top, 0, B, rank * KS_e, KS_e);
-        cp_async_wait_all();
-        __syncthreads();
-        partial_product(part, a_hi, a_lo, we_hi, we_lo, KS_e, NE, B);
-        cluster_sync();
-        {
+        for (int r0 = 0; r0 < B; r0 += PD_ROWS) {
+            const int Bb = min(PD_ROWS, B - r0);
+            if (r0 > 0) cluster_sync();
+            load_tile_async(a_hi, a.topA_hi[nxt] + W + a.D, K_top, r0, Bb, rank * KS_e, KS_e);
+            load_tile_async(a_lo, a.topA_lo[nxt] + W + a.D, K_top, r0, Bb, rank * KS_e, KS_e);
+            cp_async_wait_all();
+            __syncthreads();
+            partial_product(part, a_hi, a_lo, we_hi, we_lo, KS_e, NE, Bb);
+            cluster_sync();
             const int per = NE / PD_CS;              // output columns finalised by this CTA
             for (int i = tid; i < PD_ROWS * per; i += PD_THREADS) {
-                const int row = i / per, cc = i % per;
-                if (row < B) {
-                    const float* src = part + row * PART_LD + per * rank + cc;
+                const int rl = i / per, cc = i % per, row = r0 + rl;
+                if (rl < Bb) {
+                    const float* src = part + rl * PART_LD + per * rank + cc;
                     float z = 0.f;
 #pragma unroll
                     for (uint32_t r = 0; r < PD_CS; ++r) z += ld_dsmem1(src, r);
@@ -480,7 +490,7 @@ int g_pd_max_clusters = 0;
 }  // namespace
 
 bool page_decoder_supported(int W, int D, int Vp, int B) {
-    if (B < 1 || B > PD_ROWS) return false;
+    if (B < 1 || B > kRecurMaxRows) return false;
     const int K_low = Vp + W, K_top = 2 * W + D;
     if (K_low % (PD_CS * 64) || K_top % (PD_CS * 64) || W % (PD_CS * 64)) return false;     // swizzle: K-slices in 64-element blocks
     if ((4 * W) % PD_NCOL) return false;

@@ -101,7 +101,7 @@ void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape
 // ------------------------------------------------------------------ persistent recurrence (recur.cu)
 // One launch = all T timesteps of one LSTM layer (both directions side by side) for a page-sized batch:
 // recurrent weights resident in shared memory, grid-wide barrier between timesteps.
-constexpr int kRecurMaxRows = 32;
+constexpr int kRecurMaxRows = 64;        // lines per page-sized call (processed in blocks of 32 rows)
 struct RecurArgs {
     int ndir, W, B, T;
     const float* R_hi[2]; const float* R_lo[2]; int ldr;   // recurrent kernels [4W][ldr] (fp16 head / residual)
@@ -114,7 +114,7 @@ bool lstm_recur_supported(int W, int B, int ndir);
 int launch_lstm_recur(cudaStream_t st, const RecurArgs& a);
 
 // ------------------------------------------------------------------ persistent page decoder (decpage.cu)
-// The whole fast batch-greedy decode of a page (<= 32 lines, depth 2) in one launch; weights resident in
+// The whole fast batch-greedy decode of a page (<= 64 lines, depth 2) in one launch; weights resident in
 // shared memory, K split over the 8 CTAs of a cluster, partial sums reduced through distributed shared memory.
 struct PageDecArgs {
     int B, T, S, W, D, V, Vp, window, eos;

@@ -1,4 +1,4 @@
-// recur.cu — persistent LSTM recurrence for page-sized batches (one OCR-D page per call, <= 32 lines).
+// recur.cu — persistent LSTM recurrence for page-sized batches (one OCR-D page per call, <= 64 lines, in blocks of 32 rows).
 //
 // North star item (2): "persistent recurrence kernels for the bidirectional bottom encoder layer and the
 // stacked forward LSTMs, with recurrent weights held in shared memory across timesteps".  With a few dozen
@@ -29,7 +29,7 @@ namespace cor {
 
 namespace {
 
-constexpr int RC_ROWS = kRecurMaxRows;   // 32: two m16 tiles
+constexpr int RC_ROWS = 32;              // rows per pass: two m16 tiles (a call has up to kRecurMaxRows rows)
 constexpr int RC_COLS = 32;              // gate columns per CTA = 8 units
 constexpr int RC_THREADS = 256;
 constexpr int ZLD = RC_COLS + 1;
@@ -102,61 +102,67 @@ __global__ void __launch_bounds__(RC_THREADS, 1) lstm_recur_kernel(const RecurAr
     const __half* al = Alo + (mt * 16 + g) * LD + 2 * q;
     const __half* bh = Whi + (nt * 8 + g) * LD + 2 * q;
     const __half* bl = Wlo + (nt * 8 + g) * LD + 2 * q;
-    const bool tile_live = mt * 16 < B;              // the second row tile is empty for B <= 16
 
     for (int s = 0; s < a.T; ++s) {
         const int cur = s & 1;
         if (s > 0) grid_sync(a.barrier, gridDim.x * (unsigned)s);
-        {
-            const __half* hp = reinterpret_cast<const __half*>(a.h[dir][cur]);
-            const __half* hl = reinterpret_cast<const __half*>(a.h_lo[dir][cur]);
-            for (int i = tid; i < B * chunks; i += RC_THREADS) {
-                const int r = i / chunks, c8 = i % chunks;
-                cp_async16(Ahi + r * LD + c8 * 8, hp + (size_t)r * W + c8 * 8);
-                cp_async16(Alo + r * LD + c8 * 8, hl + (size_t)r * W + c8 * 8);
-            }
-            cp_async_wait_all();
-        }
-        __syncthreads();
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        if (tile_live) {
-#pragma unroll 4
-            for (int k0 = 0; k0 < W; k0 += 16) {
-                const uint32_t a_h[4] = {lds32(ah + k0), lds32(ah + 8 * LD + k0), lds32(ah + k0 + 8), lds32(ah + 8 * LD + k0 + 8)};
-                const uint32_t a_l[4] = {lds32(al + k0), lds32(al + 8 * LD + k0), lds32(al + k0 + 8), lds32(al + 8 * LD + k0 + 8)};
-                const uint32_t b_h[2] = {lds32(bh + k0), lds32(bh + k0 + 8)};
-                const uint32_t b_l[2] = {lds32(bl + k0), lds32(bl + k0 + 8)};
-                mma16816(acc, a_l, b_h);             // small terms first, like the tcgen05 kernel
-                mma16816(acc, a_h, b_l);
-                mma16816(acc, a_h, b_h);
-            }
-        }
-        {
-            float* z0 = zs + (mt * 16 + g) * ZLD + nt * 8 + 2 * q;
-            z0[0] = acc[0]; z0[1] = acc[1];
-            z0[8 * ZLD] = acc[2]; z0[8 * ZLD + 1] = acc[3];
-        }
-        __syncthreads();
-        if (tid < RC_ROWS * 4) {                     // (row, pair of units): the cross-sum couples units 2k, 2k+1
-            const int row = tid >> 2, up = tid & 3;
-            if (row < B) {
-                float z[2][4];
-#pragma unroll
-                for (int k = 0; k < 2; ++k)
-#pragma unroll
-                    for (int gate = 0; gate < 4; ++gate) z[k][gate] = zs[row * ZLD + 8 * up + 4 * k + gate];
-                if (a.zx[dir]) {
-                    const float4* x = reinterpret_cast<const float4*>(a.zx[dir] + ((size_t)s * B + row) * 4 * W + col0 + 8 * up);
-#pragma unroll
-                    for (int k = 0; k < 2; ++k) {
-                        const float4 v = x[k];
-                        z[k][0] += v.x; z[k][1] += v.y; z[k][2] += v.z; z[k][3] += v.w;
-                    }
+        // rows in blocks of 32 (two m16 tiles): a page of up to kRecurMaxRows lines takes one or two passes over the
+        // resident weights per timestep, still with ONE grid barrier
+        for (int r0 = 0; r0 < B; r0 += RC_ROWS) {
+            const int Bb = min(RC_ROWS, B - r0);
+            const bool tile_live = mt * 16 < Bb;         // the second row tile is empty for <= 16 rows
+            if (r0 > 0) __syncthreads();                 // the previous block's epilogue is done with zs, its MMAs with A
+            {
+                const __half* hp = reinterpret_cast<const __half*>(a.h[dir][cur]) + (size_t)r0 * W;
+                const __half* hl = reinterpret_cast<const __half*>(a.h_lo[dir][cur]) + (size_t)r0 * W;
+                for (int i = tid; i < Bb * chunks; i += RC_THREADS) {
+                    const int r = i / chunks, c8 = i % chunks;
+                    cp_async16(Ahi + r * LD + c8 * 8, hp + (size_t)r * W + c8 * 8);
+                    cp_async16(Alo + r * LD + c8 * 8, hl + (size_t)r * W + c8 * 8);
                 }
-                e.step = s;
-                e.h_prev = a.h[dir][cur]; e.h_prev_lo = a.h_lo[dir][cur];
-                e.h_out = a.h[dir][cur ^ 1]; e.h_out_lo = a.h_lo[dir][cur ^ 1];
-                lstm_row_units<2>(e, row, cd * 8 + 2 * up, z);
+                cp_async_wait_all();
+            }
+            __syncthreads();
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            if (tile_live) {
+#pragma unroll 4
+                for (int k0 = 0; k0 < W; k0 += 16) {
+                    const uint32_t a_h[4] = {lds32(ah + k0), lds32(ah + 8 * LD + k0), lds32(ah + k0 + 8), lds32(ah + 8 * LD + k0 + 8)};
+                    const uint32_t a_l[4] = {lds32(al + k0), lds32(al + 8 * LD + k0), lds32(al + k0 + 8), lds32(al + 8 * LD + k0 + 8)};
+                    const uint32_t b_h[2] = {lds32(bh + k0), lds32(bh + k0 + 8)};
+                    const uint32_t b_l[2] = {lds32(bl + k0), lds32(bl + k0 + 8)};
+                    mma16816(acc, a_l, b_h);             // small terms first, like the tcgen05 kernel
+                    mma16816(acc, a_h, b_l);
+                    mma16816(acc, a_h, b_h);
+                }
+            }
+            {
+                float* z0 = zs + (mt * 16 + g) * ZLD + nt * 8 + 2 * q;
+                z0[0] = acc[0]; z0[1] = acc[1];
+                z0[8 * ZLD] = acc[2]; z0[8 * ZLD + 1] = acc[3];
+            }
+            __syncthreads();
+            if (tid < RC_ROWS * 4) {                     // (row, pair of units): the cross-sum couples units 2k, 2k+1
+                const int rl = tid >> 2, up = tid & 3, row = r0 + rl;
+                if (rl < Bb) {
+                    float z[2][4];
+#pragma unroll
+                    for (int k = 0; k < 2; ++k)
+#pragma unroll
+                        for (int gate = 0; gate < 4; ++gate) z[k][gate] = zs[rl * ZLD + 8 * up + 4 * k + gate];
+                    if (a.zx[dir]) {
+                        const float4* x = reinterpret_cast<const float4*>(a.zx[dir] + ((size_t)s * B + row) * 4 * W + col0 + 8 * up);
+#pragma unroll
+                        for (int k = 0; k < 2; ++k) {
+                            const float4 v = x[k];
+                            z[k][0] += v.x; z[k][1] += v.y; z[k][2] += v.z; z[k][3] += v.w;
+                        }
+                    }
+                    e.step = s;
+                    e.h_prev = a.h[dir][cur]; e.h_prev_lo = a.h_lo[dir][cur];
+                    e.h_out = a.h[dir][cur ^ 1]; e.h_out_lo = a.h_lo[dir][cur ^ 1];
+                    lstm_row_units<2>(e, row, cd * 8 + 2 * up, z);
+                }
             }
         }
         // the next step's grid_sync starts with __syncthreads: zs and A are not touched before everyone is here
@@ -186,7 +192,7 @@ bool lstm_recur_supported(int W, int B, int ndir) {
         (void)cudaGetLastError();
     }
     if (g_recur_state != 1) return false;
-    return B >= 1 && B <= RC_ROWS && W % 16 == 0 && ndir * (W / 8) <= g_recur_sms && recur_smem_bytes(W) <= 227 * 1024;
+    return B >= 1 && B <= kRecurMaxRows && W % 16 == 0 && ndir * (W / 8) <= g_recur_sms && recur_smem_bytes(W) <= 227 * 1024;
 }
 
 int launch_lstm_recur(cudaStream_t st, const RecurArgs& a) {

@@ -216,9 +216,9 @@ def test_single_pass_variant_stated_tolerance():
     assert identical >= (B * 19) // 20
 
 
-@pytest.mark.parametrize("n_lines", [1, 16, 17, 32])
+@pytest.mark.parametrize("n_lines", [1, 16, 17, 32, 33, 48, 64])
 def test_page_sized_batches_c2(n_lines):
-    """Page-sized calls at the C2/C3 topology (<= 32 rows: persistent encoder recurrence with the weights
+    """Page-sized calls at the C2/C3 topology (<= 64 rows in blocks of 32: persistent encoder recurrence with the weights
     resident in shared memory, one launch per layer) against the oracle: strings, probabilities, alignments."""
     topo, w, mapping = make_model("c2")
     lines = synthetic_lines(mapping, n_lines, 40, seed=900 + n_lines, min_length=12)
