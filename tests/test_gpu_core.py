@@ -224,3 +224,29 @@ def test_page_sized_batches_c2(n_lines):
     lines = synthetic_lines(mapping, n_lines, 40, seed=900 + n_lines, min_length=12)
     bad, B = _greedy_compare("c2", lines, 2)
     assert bad == 0, "%d of %d strings differ" % (bad, B)
+
+
+def test_page_path_agrees_with_large_batch_path():
+    """Two kernel families, one answer: 512 lines decoded in ONE call (tcgen05 GEMM per timestep) and the same lines
+    in 16 page-sized calls (persistent recurrence + fused page decoder, mma.sync, different summation orders).
+    Both are fp32-grade, so the strings agree except at near-ties and the probabilities within the parity budget."""
+    topo, w, mapping = make_model("c2")
+    lines = synthetic_lines(mapping, 512, 60, seed=777, min_length=60)
+    idx, val = _sparse(mapping, lines)
+    B, T, _ = idx.shape
+    eng = _engine(topo, w, 2)
+    row_T = np.full(B, T, np.int32)
+    big = [t.numpy().copy() for t in eng.correct_greedy_host(idx, val, row_T)[:4]]
+    same, worst = 0, 0.0
+    for b0 in range(0, B, 32):
+        sl = slice(b0, b0 + 32)
+        chars, probs, scores, lens = [t.numpy() for t in eng.correct_greedy_host(idx[sl], None if val is None else val[sl], row_T[sl])[:4]]
+        for j in range(32):
+            n = int(lens[j])
+            if n == big[3][b0 + j] and (chars[j, :n] == big[0][b0 + j, :n]).all():
+                same += 1
+                if n:
+                    worst = max(worst, float(np.abs(probs[j, :n] - big[1][b0 + j, :n]).max()))
+    print("page path vs large-batch path: %d of %d strings identical, max |dp| %.3g" % (same, B, worst))
+    assert same >= B - 5, same
+    assert worst < TOL_P
