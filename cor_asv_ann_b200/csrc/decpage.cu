@@ -484,9 +484,6 @@ size_t pagedec_smem_bytes(int W, int D, int Vp) {
     return (size_t)2 * 2 * (PD_NCOL * KS_low + PD_NCOL * KS_top + NE * KS_e + PD_ROWS * KS_max) + 32 * 4 + 16;
 }
 
-int g_pd_state = -1;
-int g_pd_max_clusters = 0;
-
 }  // namespace
 
 bool page_decoder_supported(int W, int D, int Vp, int B) {
@@ -500,21 +497,25 @@ bool page_decoder_supported(int W, int D, int Vp, int B) {
     if (NE > PD_NCOL || (size_t)PD_ROWS * PART_LD * 4 > (size_t)2 * 2 * PD_ROWS * (W / PD_CS)) return false;
     const size_t smem = pagedec_smem_bytes(W, D, Vp);
     if (smem > 227 * 1024) return false;
-    if (g_pd_state < 0) {
-        g_pd_state = 0;
-        if (!getenv("COR_NO_PAGEDEC") &&
-            cudaFuncSetAttribute(page_decoder_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) == cudaSuccess) {
+    if (getenv("COR_NO_PAGEDEC")) return false;
+    // the grid barrier needs every cluster resident: ask the occupancy calculator (per device and footprint)
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    static int c_dev = -1, c_clusters = 0; static size_t c_smem = 0;
+    if (c_dev != dev || c_smem != smem) {
+        c_dev = dev; c_smem = smem; c_clusters = 0;
+        if (cudaFuncSetAttribute(page_decoder_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) == cudaSuccess) {
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3(n_clusters * PD_CS); cfg.blockDim = dim3(PD_THREADS); cfg.dynamicSmemBytes = smem;
             cudaLaunchAttribute at[1];
             at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = PD_CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
             cfg.attrs = at; cfg.numAttrs = 1;
             int nc = 0;
-            if (cudaOccupancyMaxActiveClusters(&nc, page_decoder_kernel, &cfg) == cudaSuccess) { g_pd_max_clusters = nc; g_pd_state = 1; }
+            if (cudaOccupancyMaxActiveClusters(&nc, page_decoder_kernel, &cfg) == cudaSuccess) c_clusters = nc;
         }
         (void)cudaGetLastError();
     }
-    return g_pd_state == 1 && n_clusters <= g_pd_max_clusters;       // the grid barrier needs every cluster resident
+    return n_clusters <= c_clusters;
 }
 
 // COR_PD_TIMING=<file>: per-phase times of the LAST call (ns between CTA 0 leaving consecutive grid barriers,

@@ -173,26 +173,23 @@ size_t recur_smem_bytes(int W) {
     return (size_t)(2 * RC_COLS + 2 * RC_ROWS) * (W + 8) * sizeof(__half) + (size_t)RC_ROWS * ZLD * sizeof(float);
 }
 
-int g_recur_state = -1;     // -1 unknown, 0 unusable, 1 ok
-int g_recur_sms = 0;
-
 }  // namespace
 
 bool lstm_recur_supported(int W, int B, int ndir) {
-    if (g_recur_state < 0) {
-        g_recur_state = 0;
-        int dev = 0, coop = 0, sms = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess &&
-            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && coop &&
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
-            cudaFuncSetAttribute(lstm_recur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) == cudaSuccess) {
-            g_recur_sms = sms;
-            g_recur_state = getenv("COR_NO_RECUR") ? 0 : 1;
-        }
+    if (getenv("COR_NO_RECUR")) return false;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    static int c_dev = -1, c_ok = 0, c_sms = 0;
+    if (c_dev != dev) {         // per device: cooperative launch support, SM count, shared-memory opt-in
+        c_dev = dev; c_ok = 0;
+        int coop = 0;
+        if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && coop &&
+            cudaDeviceGetAttribute(&c_sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+            cudaFuncSetAttribute(lstm_recur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) == cudaSuccess)
+            c_ok = 1;
         (void)cudaGetLastError();
     }
-    if (g_recur_state != 1) return false;
-    return B >= 1 && B <= kRecurMaxRows && W % 16 == 0 && ndir * (W / 8) <= g_recur_sms && recur_smem_bytes(W) <= 227 * 1024;
+    return c_ok && B >= 1 && B <= kRecurMaxRows && W % 16 == 0 && ndir * (W / 8) <= c_sms && recur_smem_bytes(W) <= 227 * 1024;
 }
 
 int launch_lstm_recur(cudaStream_t st, const RecurArgs& a) {

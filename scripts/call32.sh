@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 | tee gpurun_out/gpu_tests.log
+timeout 600 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1 | tee gpurun_out/smoke.log
+timeout 900 python bench.py > gpurun_out/bench_p32.json 2> gpurun_out/bench_p32.err; cut -c1-160 gpurun_out/bench_p32.json
