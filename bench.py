@@ -346,6 +346,18 @@ def measure_predict(args, topo, w, mapping, device, n_lines):
         out["chars_per_s"] = run(n_lines, 64, 3001)
         out["chars_per_s_one_batch_per_call"] = run(min(n_lines, 8 * REF_BATCH), 1, 3002)
     out.update({"lines": n_lines, "superbatch": 64, "api": "Sequence2Sequence.predict(text file, fast=True), file read + encode + decode + strings"})
+    # one OCR-D page through the class the wrapper calls (wrapper/transcode.py:111-115): strings in -> strings,
+    # probabilities, scores, alignments out, fast greedy mode and the default beamed mode
+    page = [i2c[make_indices(1, 5000 + j)[0, :, 0]].tobytes().decode("utf-32-le") for j in range(32)]
+    s.rejection_threshold, s.beam_width_in = BEAM["rejection_threshold"], BEAM["beam_width_in"]
+    for fast in (True, False):
+        for _ in range(2):
+            s.correct_lines(page, None, fast=fast, greedy=fast)
+        t0 = time.perf_counter()
+        for _ in range(5):
+            res = s.correct_lines(page, None, fast=fast, greedy=fast)
+        assert len(res[0]) == len(page)
+        out["page32_correct_lines_ms_%s" % ("fast" if fast else "beam")] = (time.perf_counter() - t0) / 5 * 1e3
     return out
 
 
