@@ -276,23 +276,37 @@ __device__ void attention_row_cta(const PageDecArgs& a, int row, bool first, flo
 // softmax of one line's logits + greedy bookkeeping (decode_batch_greedy, seq2seq.py:1250-1260) by one warp;
 // same arithmetic as softmax_kernel<true> in kernels.cu.  p goes to the [p | h1] operand rows (hi/lo).
 __device__ void softmax_greedy_row(const PageDecArgs& a, int row, int step, __half* p_hi, __half* p_lo) {
+    // One pass over the logits (kept in registers) and ONE expf per element: softmax_kernel evaluates
+    // expf(z - m) twice with identical results, so the bits are the same, but this warp's chain of loads, expf
+    // and divisions is the critical path of the phase (~6 us as three passes).  Vp <= 32 * VL (checked on the host).
+    constexpr int VL = 16;
     const int lane = threadIdx.x & 31;
     const float* z = a.logits + (size_t)row * a.Vp;
+    float e[VL];
     float m = -INFINITY;
-    for (int v = lane; v < a.V; v += 32) m = fmaxf(m, z[v]);
+#pragma unroll
+    for (int k = 0; k < VL; ++k) {
+        const int v = lane + 32 * k;
+        e[k] = v < a.V ? z[v] : -INFINITY;
+    }
+#pragma unroll
+    for (int k = 0; k < VL; ++k) m = fmaxf(m, e[k]);
     m = warp_max(m);
     float s = 0.f;
-    for (int v = lane; v < a.V; v += 32) s += expf(z[v] - m);
+#pragma unroll
+    for (int k = 0; k < VL; ++k)
+        if (lane + 32 * k < a.V) { e[k] = expf(e[k] - m); s += e[k]; } else e[k] = 0.f;
     s = warp_sum(s);
     float best = -INFINITY;
     int best_v = 0x7fffffff;
-    for (int v = lane; v < a.Vp; v += 32) {
-        float pv = 0.f;
-        if (v < a.V) {
-            pv = expf(z[v] - m) / s;
-            if (v >= 1 && pv > best) { best = pv; best_v = v; }
+#pragma unroll
+    for (int k = 0; k < VL; ++k) {
+        const int v = lane + 32 * k;
+        if (v < a.Vp) {
+            const float pv = v < a.V ? e[k] / s : 0.f;
+            if (v < a.V && v >= 1 && pv > best) { best = pv; best_v = v; }
+            store_h(p_hi, p_lo, v, pv);
         }
-        store_h(p_hi, p_lo, v, pv);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -487,7 +501,7 @@ size_t pagedec_smem_bytes(int W, int D, int Vp) {
 }  // namespace
 
 bool page_decoder_supported(int W, int D, int Vp, int B) {
-    if (B < 1 || B > kRecurMaxRows) return false;
+    if (B < 1 || B > kRecurMaxRows || Vp > 512) return false;     // softmax_greedy_row keeps a row in 16 registers per lane
     const int K_low = Vp + W, K_top = 2 * W + D;
     if (K_low % (PD_CS * 64) || K_top % (PD_CS * 64) || W % (PD_CS * 64)) return false;     // swizzle: K-slices in 64-element blocks
     if ((4 * W) % PD_NCOL) return false;
