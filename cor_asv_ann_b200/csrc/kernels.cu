@@ -159,7 +159,9 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
 // ---------------------------------------------------------------- K5g softmax (+K6 greedy)
 // softmax(h.E^T) (seq2seq.py:379); greedy bookkeeping of decode_batch_greedy (:1250-1260).
 // One warp per row.  The row stride of logits / p is V rounded up to 128; the pad stays zero.
-template <bool GREEDY>
+// NVL > 0: Vp == 32 * NVL and the row lives in registers (one pass over the logits, one expf per element --
+// the same values the generic path computes twice, so the bits are identical); NVL == 0: generic path.
+template <bool GREEDY, int NVL>
 __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r_dev) {
     const int R = r_dev ? min(*r_dev, g.R) : g.R;
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -167,21 +169,43 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
     const int lane = threadIdx.x & 31;
     const int ld = (g.V + 127) & ~127;
     const float* z = g.logits + (size_t)row * ld;
-    float m = -INFINITY;
-    for (int v = lane; v < g.V; v += 32) m = fmaxf(m, z[v]);
-    m = warp_max(m);
-    float s = 0.f;
-    for (int v = lane; v < g.V; v += 32) s += expf(z[v] - m);
-    s = warp_sum(s);
     float best = -INFINITY;
     int best_v = 0x7fffffff;
-    for (int v = lane; v < ld; v += 32) {
-        float pv = 0.f;
-        if (v < g.V) {
-            pv = expf(z[v] - m) / s;
-            if (GREEDY && v >= 1 && pv > best) { best = pv; best_v = v; }   // first maximum among v>=1
+    if constexpr (NVL > 0) {
+        float e[NVL];
+        float m = -INFINITY;
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) { const int v = lane + 32 * k; e[k] = v < g.V ? z[v] : -INFINITY; }
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) m = fmaxf(m, e[k]);
+        m = warp_max(m);
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < NVL; ++k)
+            if (lane + 32 * k < g.V) { e[k] = expf(e[k] - m); s += e[k]; } else e[k] = 0.f;
+        s = warp_sum(s);
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) {
+            const int v = lane + 32 * k;
+            const float pv = v < g.V ? e[k] / s : 0.f;
+            if (GREEDY && v < g.V && v >= 1 && pv > best) { best = pv; best_v = v; }   // first maximum among v>=1
+            store_split(g.p, g.p_lo, (size_t)row * ld + v, pv);
         }
-        store_split(g.p, g.p_lo, (size_t)row * ld + v, pv);
+    } else {
+        float m = -INFINITY;
+        for (int v = lane; v < g.V; v += 32) m = fmaxf(m, z[v]);
+        m = warp_max(m);
+        float s = 0.f;
+        for (int v = lane; v < g.V; v += 32) s += expf(z[v] - m);
+        s = warp_sum(s);
+        for (int v = lane; v < ld; v += 32) {
+            float pv = 0.f;
+            if (v < g.V) {
+                pv = expf(z[v] - m) / s;
+                if (GREEDY && v >= 1 && pv > best) { best = pv; best_v = v; }   // first maximum among v>=1
+            }
+            store_split(g.p, g.p_lo, (size_t)row * ld + v, pv);
+        }
     }
     if (!GREEDY) return;
 #pragma unroll
@@ -261,7 +285,10 @@ int launch_attention_reg(cudaStream_t st, const AttnArgs& a) {
 
 int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a) {
     if (a.R <= 0) return 0;
-    softmax_kernel<true><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
+    const int ld = (a.V + 127) & ~127;
+    if (ld == 512) softmax_kernel<true, 16><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
+    else if (ld == 128) softmax_kernel<true, 4><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
+    else softmax_kernel<true, 0><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
     ++g_launches;
     COR_CUDA(cudaGetLastError());
     return 0;
@@ -271,7 +298,10 @@ int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, 
     if (R <= 0) return 0;
     GreedyArgs g{};
     g.logits = logits; g.p = p; g.p_lo = p_lo; g.R = R; g.V = V;
-    softmax_kernel<false><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
+    const int ld = (V + 127) & ~127;
+    if (ld == 512) softmax_kernel<false, 16><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
+    else if (ld == 128) softmax_kernel<false, 4><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
+    else softmax_kernel<false, 0><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
     ++g_launches;
     COR_CUDA(cudaGetLastError());
     return 0;
