@@ -497,11 +497,12 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
             for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
             float s = 0.f;
 #pragma unroll
-            for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) s += expf(out[k] - m);
+            for (int k = 0; k < NVL; ++k)      // one expf per element: the value is reused for the quotient (same bits)
+                if (lane + 32 * k < b.V) { out[k] = expf(out[k] - m); s += out[k]; } else out[k] = 0.f;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
 #pragma unroll
-            for (int k = 0; k < NVL; ++k) out[k] = lane + 32 * k < b.V ? expf(out[k] - m) / s : 0.f;
+            for (int k = 0; k < NVL; ++k) out[k] = lane + 32 * k < b.V ? out[k] / s : 0.f;
         };
         softmax_row(b.logits + (size_t)row * b.Vp, p);
         if (b.lm) softmax_row(b.logits_lm + (size_t)row * b.Vp, plm);
