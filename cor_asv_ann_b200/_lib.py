@@ -35,19 +35,20 @@ PROTOTYPES = {
     "cor_model_finalize": (C.c_int, [C.c_void_p]),
     "cor_model_destroy": (None, [C.c_void_p]),
     "cor_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
-    "cor_encode": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cor_encode": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cor_decode_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p] + [C.c_void_p] * 9 + [C.c_void_p]),
-    "cor_decode_greedy_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t] + [C.c_void_p] * 5 + [C.c_void_p]),
-    "cor_correct_greedy_host": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.c_void_p, C.c_size_t] + [C.c_void_p] * 5 + [C.c_void_p]),
+    "cor_decode_greedy_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),
+    "cor_correct_greedy_host": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),
     "cor_beam_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(CorBeamParams), C.c_size_t, C.POINTER(C.c_size_t)]),
     "cor_correct_beam_host": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.POINTER(CorBeamParams), C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),
     "cor_decode_beam_batch": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.POINTER(CorBeamParams), C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),
     "cor_alignment_paths": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                       C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
-    "cor_launch_count": (C.c_int64, [C.c_int]),
+    "cor_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
+    "cor_debug_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_int]),
     "cor_debug_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "cor_prof_enable": (C.c_int, [C.c_int]),
-    "cor_prof_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),
+    "cor_prof_enable": (C.c_int, [C.c_void_p, C.c_int]),
+    "cor_prof_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),
 }
 
 _lib = None

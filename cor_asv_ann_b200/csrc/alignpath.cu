@@ -163,7 +163,7 @@ int launch_alignment_paths(cudaStream_t st, const float* align, long long stride
         COR_CUDA(cudaFuncSetAttribute(alignment_path_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     PathArgs p{align, stride_j, stride_row, i_max, j_max, min_score, path, path_ld, dist, t_cap, s_cap};
     alignment_path_kernel<<<n_rows, 128, smem, st>>>(p);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }

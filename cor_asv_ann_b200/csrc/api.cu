@@ -12,47 +12,42 @@
 namespace cor {
 
 static thread_local std::string g_error;
-int64_t g_launches = 0;
 void set_error(const std::string& msg) { g_error = msg; }
 
-// ------------------------------------------------------------------ per-launch timing (bench.py roofline)
-// When enabled, every LSTM-GEMM launch (the dominant kernel) is bracketed by two events on the
-// launching stream; cor_prof_read sums the elapsed times after a synchronize.
-struct Prof {
-    bool on = false;
-    std::vector<cudaEvent_t> ev;     // pairs
-    size_t used = 0;
-    double flops = 0;                // launches whose row count is known on the host
-    int64_t launches = 0;
-    // launches whose row count lives on the device (beam): the count is copied into pinned memory
-    // right behind the kernel, and the flops are added up in cor_prof_read
-    int32_t* rows = nullptr;         // pinned [kMaxDeferred]
-    std::vector<double> per_row;     // 2*N*K of the deferred launch
-} g_prof;
+// ------------------------------------------------------------------ per-handle state (engine.h)
+static Ctx g_default_ctx;                       // handle-free test hooks only
+static thread_local Ctx* t_ctx = nullptr;
+Ctx& ctx() { return t_ctx ? *t_ctx : g_default_ctx; }
+CtxScope::CtxScope(Ctx* c) : prev(t_ctx) { t_ctx = c; }
+CtxScope::~CtxScope() { t_ctx = prev; }
+
+// ------------------------------------------------------------------ per-launch timing (bench.py roofline pass)
 constexpr size_t kMaxDeferred = 65536;
+static Prof g_no_prof;
+static Prof& prof() { return ctx().prof ? *static_cast<Prof*>(ctx().prof) : g_no_prof; }
 
 static void prof_begin(cudaStream_t st) {
-    if (!g_prof.on) return;
-    if (g_prof.used + 2 > g_prof.ev.size()) {
-        if (g_prof.ev.size() >= 60000) return;
-        for (int i = 0; i < 2; ++i) { cudaEvent_t e; cudaEventCreate(&e); g_prof.ev.push_back(e); }
+    if (!prof().on) return;
+    if (prof().used + 2 > prof().ev.size()) {
+        if (prof().ev.size() >= 60000) return;
+        for (int i = 0; i < 2; ++i) { cudaEvent_t e; cudaEventCreate(&e); prof().ev.push_back(e); }
     }
-    cudaEventRecord(g_prof.ev[g_prof.used], st);
+    cudaEventRecord(prof().ev[prof().used], st);
 }
 static void prof_end(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* s, int n, int k_table) {
-    if (!g_prof.on || g_prof.used + 2 > g_prof.ev.size()) return;
-    cudaEventRecord(g_prof.ev[g_prof.used + 1], st);
-    g_prof.used += 2;
+    if (!prof().on || prof().used + 2 > prof().ev.size()) return;
+    cudaEventRecord(prof().ev[prof().used + 1], st);
+    prof().used += 2;
     // algorithmic K: the segments plus the input term a table gather stands in for (SURVEY.md 8d counts x.Kx)
     double k = k_table;
     for (int i = 0; i < n; ++i) k += s[i].K;
-    if (m_dev && g_prof.rows && g_prof.per_row.size() < kMaxDeferred) {
-        cudaMemcpyAsync(g_prof.rows + g_prof.per_row.size(), m_dev, 4, cudaMemcpyDeviceToHost, st);
-        g_prof.per_row.push_back(2.0 * N * k);
+    if (m_dev && prof().rows && prof().per_row.size() < kMaxDeferred) {
+        cudaMemcpyAsync(prof().rows + prof().per_row.size(), m_dev, 4, cudaMemcpyDeviceToHost, st);
+        prof().per_row.push_back(2.0 * N * k);
     } else {
-        g_prof.flops += 2.0 * M * N * k;
+        prof().flops += 2.0 * M * N * k;
     }
-    g_prof.launches += 1;
+    prof().launches += 1;
 }
 
 // GEMM dispatch: tcgen05 3xFP16 whenever the model keeps split operands and the shape is TMA-aligned
@@ -277,6 +272,7 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
     ws->o_probs = c.take<float>(B * S);
     ws->o_score = c.take<double>(B);
     ws->o_len = c.take<int32_t>(B);
+    ws->o_ties = c.take<int32_t>(B);
     ws->o_align = want_align ? c.take<float>(S * BT) : nullptr;
     ws->bytes = (c.off + 255) & ~size_t(255);
     return 0;
@@ -523,6 +519,7 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
     COR_CUDA(cudaMemsetAsync(ws.a[0], 0, (size_t)B * T * 4, st));
     COR_CUDA(cudaMemsetAsync(ws.done, 0, B, st));
     COR_CUDA(cudaMemsetAsync(ws.o_len, 0, (size_t)B * 4, st));
+    COR_CUDA(cudaMemsetAsync(ws.o_ties, 0, (size_t)B * 4, st));
     COR_CUDA(cudaMemsetAsync(ws.o_score, 0, (size_t)B * 8, st));
     COR_CUDA(cudaMemsetAsync(ws.o_chars, 0, (size_t)B * 2 * T * 4, st));
     COR_CUDA(cudaMemsetAsync(ws.o_probs, 0, (size_t)B * 2 * T * 4, st));
@@ -553,9 +550,12 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         pa.u = ws.u; pa.enc = ws.enc_out(); pa.enc_lo = ws.enc_out_lo();
         pa.line_T = ws.row_T; pa.live = ws.live; pa.done = ws.done;
         pa.out_chars = ws.o_chars; pa.out_probs = ws.o_probs; pa.score_sum = ws.o_score; pa.out_len = ws.o_len;
+        pa.out_ties = ws.o_ties;
         pa.barrier = m->grid_bar;
-        if (launch_page_decoder(st, pa)) return 1;
-        return launch_finish_scores(st, ws.o_score, ws.o_len, B);
+        const int rc = launch_page_decoder(st, pa);
+        if (rc == 1) return 1;
+        if (rc == 0) return launch_finish_scores(st, ws.o_score, ws.o_len, B);
+        // rc == 2: the cooperative launch was refused and nothing ran -- per-timestep launches below
     }
     for (int s = 0; s < S; ++s) {
         StepIO io{};
@@ -574,6 +574,7 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         GreedyArgs g{};
         g.logits = ws.logits; g.p = ws.p; g.p_lo = ws.p_lo; g.row_T = ws.row_T; g.live = ws.live;
         g.out_chars = ws.o_chars; g.out_probs = ws.o_probs; g.score_sum = ws.o_score; g.out_len = ws.o_len; g.done = ws.done;
+        g.out_ties = ws.o_ties;
         g.R = B; g.V = m->V; g.step = s; g.s_max = S; g.eos = m->cfg.eos_index;
         if (launch_softmax_greedy(st, g)) return 1;
         cur ^= 1;
@@ -588,8 +589,20 @@ using namespace cor;
 extern "C" {
 
 const char* cor_last_error(void) { return g_error.c_str(); }
-int cor_abi_version(void) { return 1; }
-int64_t cor_launch_count(int reset) { int64_t v = g_launches; if (reset) g_launches = 0; return v; }
+int cor_abi_version(void) { return 2; }
+int64_t cor_launch_count(cor_model* m, int reset) {
+    if (!m) return -1;
+    const int64_t v = m->ctx.launches;
+    if (reset) m->ctx.launches = 0;
+    return v;
+}
+int cor_debug_counters(cor_model* m, int64_t* out, int reset) {
+    COR_CHECK(m && out, "null argument");
+    for (int e = 0; e < 2; ++e) for (int k = 0; k < 3; ++k) out[3 * e + k] = m->ctx.tc_kind[e][k];
+    out[6] = m->ctx.ffma_kind[0]; out[7] = m->ctx.ffma_kind[1];
+    if (reset) { memset(m->ctx.tc_kind, 0, sizeof(m->ctx.tc_kind)); memset(m->ctx.ffma_kind, 0, sizeof(m->ctx.ffma_kind)); }
+    return 0;
+}
 
 // Test hook: C[M,N] = A[M,K] . B[N,K]^T through one of the two GEMM kernels (1 = FFMA, 2 = tcgen05 3xFP16).
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream) {
@@ -617,26 +630,32 @@ int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B
     return rc;
 }
 
-int cor_prof_enable(int on) {
-    g_prof.on = on != 0;
+int cor_prof_enable(cor_model* m, int on) {
+    COR_CHECK(m, "null argument");
+    CtxScope scope(&m->ctx);
+    COR_CUDA(cudaSetDevice(m->device));
+    prof().on = on != 0;
     if (on) {
-        g_prof.used = 0; g_prof.flops = 0; g_prof.launches = 0; g_prof.per_row.clear();
-        if (!g_prof.rows) COR_CUDA(cudaMallocHost((void**)&g_prof.rows, kMaxDeferred * 4));
+        prof().used = 0; prof().flops = 0; prof().launches = 0; prof().per_row.clear();
+        if (!prof().rows) COR_CUDA(cudaMallocHost((void**)&prof().rows, kMaxDeferred * 4));
     }
     return 0;
 }
-int cor_prof_read(double* total_ms, int64_t* launches, double* flops) {
+int cor_prof_read(cor_model* m, double* total_ms, int64_t* launches, double* flops) {
+    COR_CHECK(m, "null argument");
+    CtxScope scope(&m->ctx);
+    COR_CUDA(cudaSetDevice(m->device));
     COR_CUDA(cudaDeviceSynchronize());
     double ms = 0;
-    for (size_t i = 0; i + 1 < g_prof.used; i += 2) {
+    for (size_t i = 0; i + 1 < prof().used; i += 2) {
         float t = 0;
-        COR_CUDA(cudaEventElapsedTime(&t, g_prof.ev[i], g_prof.ev[i + 1]));
+        COR_CUDA(cudaEventElapsedTime(&t, prof().ev[i], prof().ev[i + 1]));
         ms += t;
     }
-    double fl = g_prof.flops;
-    for (size_t i = 0; i < g_prof.per_row.size(); ++i) fl += g_prof.per_row[i] * (double)g_prof.rows[i];
+    double fl = prof().flops;
+    for (size_t i = 0; i < prof().per_row.size(); ++i) fl += prof().per_row[i] * (double)prof().rows[i];
     if (total_ms) *total_ms = ms;
-    if (launches) *launches = g_prof.launches;
+    if (launches) *launches = prof().launches;
     if (flops) *flops = fl;
     return 0;
 }
@@ -652,6 +671,7 @@ int cor_model_create(const cor_config* cfg, int device, cor_model** out) {
     COR_CHECK(device >= 0 && device < ndev, "no such CUDA device");
     COR_CUDA(cudaSetDevice(device));
     cor_model* m = new cor_model();
+    m->ctx.prof = &m->prof;
     m->cfg = *cfg; m->device = device;
     m->W = cfg->width; m->d = cfg->depth; m->V = cfg->voc_size; m->Vp = (cfg->voc_size + 127) & ~127;
     m->D = (cfg->depth == 1 || cfg->deep_bidirectional_encoder) ? 2 * cfg->width : cfg->width;
@@ -680,6 +700,7 @@ int cor_model_set_weight(cor_model* m, const char* layer, int index, const float
 
 int cor_model_finalize(cor_model* m) {
     COR_CHECK(m && !m->finalized, "bad model state");
+    CtxScope scope(&m->ctx);
     COR_CUDA(cudaSetDevice(m->device));
     const int W = m->W, d = m->d, V = m->V, Vp = m->Vp, D = m->D;
     const std::vector<HostWeight>* w;
@@ -789,6 +810,9 @@ void cor_model_destroy(cor_model* m) {
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);
     for (void* p : m->allocs) cudaFree(p);
+    for (cudaEvent_t e : m->prof.ev) cudaEventDestroy(e);
+    if (m->prof.rows) cudaFreeHost(m->prof.rows);
+    tc_ctx_release(&m->ctx);
     delete m;
 }
 
@@ -840,16 +864,14 @@ static int read_header(cor_model* m, void* workspace, size_t bytes, Ws* ws, int*
     return 0;
 }
 
-int cor_encode(cor_model* m, const cor_lines* lines, void* workspace, size_t workspace_bytes,
+int cor_encode(cor_model* m, const cor_lines* lines, int want_alignments, void* workspace, size_t workspace_bytes,
                float* enc_out, float* states, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     Ws ws;
-    // alignments are decided at encode time: the header records whether room was reserved
-    size_t need_plain = 0, need_align = 0;
     if (!m || !lines) { set_error("null argument"); return 1; }
-    if (cor_workspace_bytes(m, lines->n_rows, lines->t_max, lines->k_alt, 0, &need_plain)) return 1;
-    if (cor_workspace_bytes(m, lines->n_rows, lines->t_max, lines->k_alt, 1, &need_align)) return 1;
-    const int align = workspace_bytes >= need_align;
+    CtxScope scope(&m->ctx);
+    // alignments are decided at encode time, by the caller: the header records whether room was reserved
+    const int align = want_alignments != 0;
     if (bind(m, lines, workspace, workspace_bytes, align, &ws)) return 1;
     if (stage_lines(ws, lines, cudaMemcpyDeviceToDevice, st)) return 1;
     if (!lines->val) ws.val = nullptr;
@@ -870,6 +892,8 @@ int cor_decode_step(cor_model* m, void* workspace, size_t workspace_bytes, int n
                     float* p_out, float* lm_out, float* h_out, float* c_out, float* a_out, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     Ws ws;
+    COR_CHECK(m, "null argument");
+    CtxScope scope(&m->ctx);
     if (read_header(m, workspace, workspace_bytes, &ws, nullptr, st)) return 1;
     COR_CHECK(n_hyp > 0 && n_hyp <= ws.B, "hypothesis count must be in 1..n_rows of the encoded call");
     COR_CHECK(p_in && h_in && c_in && a_in && p_out && h_out && c_out && a_out, "null argument");
@@ -908,12 +932,13 @@ int cor_decode_step(cor_model* m, void* workspace, size_t workspace_bytes, int n
 }
 
 static int greedy_results(const Ws& ws, int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len,
-                          float* out_align, cudaMemcpyKind kind, cudaStream_t st) {
+                          int32_t* out_ties, float* out_align, cudaMemcpyKind kind, cudaStream_t st) {
     const size_t BS = (size_t)ws.B * 2 * ws.T;
     if (out_chars) COR_CUDA(cudaMemcpyAsync(out_chars, ws.o_chars, BS * 4, kind, st));
     if (out_probs) COR_CUDA(cudaMemcpyAsync(out_probs, ws.o_probs, BS * 4, kind, st));
     if (out_scores) COR_CUDA(cudaMemcpyAsync(out_scores, ws.o_score, (size_t)ws.B * 8, kind, st));
     if (out_len) COR_CUDA(cudaMemcpyAsync(out_len, ws.o_len, (size_t)ws.B * 4, kind, st));
+    if (out_ties) COR_CUDA(cudaMemcpyAsync(out_ties, ws.o_ties, (size_t)ws.B * 4, kind, st));
     if (out_align) {
         COR_CHECK(ws.o_align, "alignments were not reserved in this workspace");
         COR_CUDA(cudaMemcpyAsync(out_align, ws.o_align, BS * ws.T * 4, kind, st));
@@ -923,27 +948,31 @@ static int greedy_results(const Ws& ws, int32_t* out_chars, float* out_probs, do
 
 int cor_decode_greedy_batch(cor_model* m, void* workspace, size_t workspace_bytes,
                             int32_t* out_chars, float* out_probs, double* out_scores,
-                            int32_t* out_len, float* out_align, void* stream) {
+                            int32_t* out_len, int32_t* out_ties, float* out_align, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     Ws ws;
+    COR_CHECK(m, "null argument");
+    CtxScope scope(&m->ctx);
     if (read_header(m, workspace, workspace_bytes, &ws, nullptr, st)) return 1;
     COR_CHECK(!m->cfg.lm_predict, "fast mode with lm_predict is undefined in the reference (seq2seq.py:1248)");
     if (greedy_loop(m, ws, st)) return 1;
-    return greedy_results(ws, out_chars, out_probs, out_scores, out_len, out_align, cudaMemcpyDeviceToDevice, st);
+    return greedy_results(ws, out_chars, out_probs, out_scores, out_len, out_ties, out_align, cudaMemcpyDeviceToDevice, st);
 }
 
 int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines, void* workspace, size_t workspace_bytes,
                             int32_t* out_chars, float* out_probs, double* out_scores,
-                            int32_t* out_len, float* out_align, void* stream) {
+                            int32_t* out_len, int32_t* out_ties, float* out_align, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     Ws ws;
+    COR_CHECK(m, "null argument");
+    CtxScope scope(&m->ctx);
     if (bind(m, host_lines, workspace, workspace_bytes, out_align != nullptr, &ws)) return 1;
     COR_CHECK(!m->cfg.lm_predict, "fast mode with lm_predict is undefined in the reference (seq2seq.py:1248)");
     if (stage_lines(ws, host_lines, cudaMemcpyHostToDevice, st)) return 1;
     if (!host_lines->val) ws.val = nullptr;
     if (run_encoder(m, ws, st)) return 1;
     if (greedy_loop(m, ws, st)) return 1;
-    if (greedy_results(ws, out_chars, out_probs, out_scores, out_len, out_align, cudaMemcpyDeviceToHost, st)) return 1;
+    if (greedy_results(ws, out_chars, out_probs, out_scores, out_len, out_ties, out_align, cudaMemcpyDeviceToHost, st)) return 1;
     COR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }

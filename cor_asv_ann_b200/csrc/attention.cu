@@ -274,7 +274,7 @@ int launch_attention(cudaStream_t st, const AttnArgs& a) {
     const size_t smem = 128 + (size_t)v_bytes + (size_t)groups * g.bytes;
     const int blocks = std::min((a.R + groups - 1) / groups, n_sms);
     attention_tma_kernel<<<blocks, groups * GW * 32, smem, st>>>(a, g, v_bytes);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }

@@ -39,6 +39,7 @@ constexpr int KMAX = 16;             // children per expansion: beam_width_in (<
 constexpr int MAX_NEW = 4096;        // batch_size (<= 256) * KMAX
 constexpr int ST_ACTIVE = 0, ST_DONE = 1, ST_OVERFLOW = 2, ST_EMPTY = 3;
 constexpr uint32_t FINAL_BIT = 0x80000000u;
+constexpr int kStats = 8;            // int64 statistics per line (include/cor_b200.h)
 
 struct BeamDev {
     // geometry and parameters
@@ -53,6 +54,9 @@ struct BeamDev {
     int32_t *status, *iter, *x_count, *x_base, *beam_count, *row_base, *fr_len, *fr_off, *fr_buf;
     int32_t *finals_count, *best_final, *open_left;
     double* best_key; long long* hyp_steps;
+    // diagnostics per line (stats[4..7]): exact top-2 score ties, near-tie ordering decisions, order-sensitive checksum of
+    // the popped hypotheses, peak fringe length
+    long long *score_ties, *near_ties; unsigned long long* pop_sum; int32_t* fr_peak;
     double* fr_key; uint32_t* fr_id;       // [2][L][cap]
     uint32_t* beam_nodes;                  // [L][batch]
     int32_t* rej_table;                    // [L][T]
@@ -103,6 +107,7 @@ __global__ void beam_init_kernel(BeamDev b) {
         b.fr_len[line] = 1; b.fr_off[line] = 0; b.fr_buf[line] = 0;
         b.finals_count[line] = 0; b.best_final[line] = -1; b.open_left[line] = 0;
         b.best_key[line] = INFINITY; b.hyp_steps[line] = 0;
+        b.score_ties[line] = 0; b.near_ties[line] = 0; b.pop_sum[line] = 0ull; b.fr_peak[line] = 1;
         b.fr_key[(size_t)line * b.cap] = 3.0 * fabs(1.0 - (double)Tl);
         b.fr_id[(size_t)line * b.cap] = 0u;
     }
@@ -127,6 +132,10 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     const uint32_t* ids = b.fr_id + ((size_t)cur * b.L + line) * b.cap;
     int first_final = 0x7fffffff, first_open = 0x7fffffff;
     int open_total = 0, consumed = 0, nfin = 0;
+    // order-sensitive checksum of the popped open hypotheses: sum over pops of (length << 16 | char + 1) * odd(pop index),
+    // pop index counted per line over the whole search -- what the oracle computes from its own beam lists
+    const unsigned long long pop0 = (unsigned long long)b.hyp_steps[line];
+    unsigned long long csum = 0ull;
     for (int base = 0; base < len && open_total < b.batch; base += 32) {
         const int i = base + lane;
         const bool valid = i < len;
@@ -137,7 +146,15 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
         const int excl = open_total + __popc(bal & ((1u << lane) - 1u));
         // an entry is popped iff fewer than batch_size open nodes precede it (:1400-1415)
         const bool take = valid && excl < b.batch;
-        if (take && open) b.beam_nodes[(size_t)line * b.batch + excl] = id;
+        if (take && open) {
+            b.beam_nodes[(size_t)line * b.batch + excl] = id;
+            unsigned long long x = (1ull << 16) + 1ull;            // root: length 1, no character
+            if (id != 0u) {
+                const size_t pg = (size_t)line * b.quota_x + (id - 1u) / KMAX;
+                x = ((unsigned long long)(b.rec_len[pg] + 1) << 16) + (unsigned long long)b.ch_v[pg * KMAX + (id - 1u) % KMAX] + 1ull;
+            }
+            csum += x * (2ull * (pop0 + (unsigned long long)excl) + 1ull) * 0x9E3779B97F4A7C15ull;
+        }
         const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
         const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);
         if (t_open && first_open == 0x7fffffff) first_open = base + __ffs(t_open) - 1;
@@ -146,6 +163,8 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
         nfin += __popc(t_fin);
         open_total += __popc(bal);
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, o);
     if (lane != 0) return;
     const int count = min(open_total, b.batch);
     int fc = b.finals_count[line] + nfin;
@@ -166,6 +185,9 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     } else {
         b.iter[line] += 1;
         b.hyp_steps[line] += count;
+        b.pop_sum[line] += csum;
+        // near-tie at the pop boundary: which of two hypotheses enters this batch hangs on the last bits of their keys
+        if (consumed < len && consumed > 0 && fabs(keys[consumed] - keys[consumed - 1]) <= 1e-6 * fmax(1.0, fabs(keys[consumed]))) b.near_ties[line] += 1;
     }
     b.beam_count[line] = out;
 }
@@ -416,12 +438,20 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
         hi = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
         const double bound = (double)hi * b.thr_in;
         int cnt = 0;
-        for (int v = tid; v < b.V; v += 128) cnt += ((double)sp[v] >= bound);
+        // packed counters: [0,10) scores >= bound, [10,20) scores equal to the maximum, [20,30) scores within the tie margin of the bound
+        for (int v = tid; v < b.V; v += 128) {
+            const double x = (double)sp[v];
+            cnt += (x >= bound) + ((sp[v] == hi) << 10) + ((fabs(x - bound) <= (double)kTieMargin * bound) << 20);
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
         if (lane == 0) s_cnt[warp] = cnt;
         __syncthreads();
-        const int beampos = min(s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3], b.width_in);
+        const int cnt_all = s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3];
+        const int beampos = min(cnt_all & 1023, b.width_in);
+        const bool score_tie = ((cnt_all >> 10) & 1023) >= 2;
+        bool near_tie = ((cnt_all >> 20) & 1023) > 0;
+        float walked_prev = -1.f;
         // ---- walk the candidates best first (:1480-1529)
         int nacc = 0, pending = rej;
         const float rej_p = rej >= 0 ? sp[rej] : 0.f;
@@ -441,6 +471,8 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
                 __syncthreads();
                 if (best.i < 0 || best.v < 0.f) break;
                 v = best.i; pv = best.v;
+                if (walked_prev >= 0.f && walked_prev - pv <= kTieMargin * walked_prev) near_tie = true;
+                walked_prev = pv;
                 if (tid == 0) sp[v] = -1.f;            // taken
                 __syncthreads();
                 isrej = (v == pending);
@@ -463,9 +495,22 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
             }
             ++nacc;
         }
+        if (walked_prev >= 0.f) {       // the first candidate LEFT OUT against the last one taken (see the warp variant)
+            float rest = -1.f;
+            for (int q = tid; q < b.V; q += 128) rest = fmaxf(rest, sp[q]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) rest = fmaxf(rest, __shfl_xor_sync(0xffffffffu, rest, o));
+            __syncthreads();
+            if (lane == 0) s_red[warp] = rest;
+            __syncthreads();
+            rest = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+            if (rest >= 0.f && walked_prev - rest <= kTieMargin * walked_prev) near_tie = true;
+        }
         if (tid == 0) {
             b.rec_cur[g] = cur; b.rec_amax1[g] = amax == 1.0f ? 1 : 0; b.rec_pos[g] = pos;
             b.rec_len[g] = len_node; b.rec_nacc[g] = nacc; b.rec_parent[g] = node;
+            if (score_tie) atomicAdd((unsigned long long*)&b.score_ties[line], 1ull);
+            if (near_tie) atomicAdd((unsigned long long*)&b.near_ties[line], 1ull);
         }
     }
 }
@@ -630,11 +675,19 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
         for (int o = 16; o > 0; o >>= 1) hi = fmaxf(hi, __shfl_xor_sync(FULL, hi, o));
         const double bound = (double)hi * b.thr_in;
         int cnt = 0;
+        // packed counters: [0,10) scores >= bound, [10,20) scores equal to the maximum, [20,30) scores within the tie margin of the bound
 #pragma unroll
-        for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) cnt += ((double)p[k] >= bound);
+        for (int k = 0; k < NVL; ++k)
+            if (lane + 32 * k < b.V) {
+                const double x = (double)p[k];
+                cnt += (x >= bound) + ((p[k] == hi) << 10) + ((fabs(x - bound) <= (double)kTieMargin * bound) << 20);
+            }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULL, cnt, o);
-        const int beampos = min(cnt, b.width_in);
+        const int beampos = min(cnt & 1023, b.width_in);
+        const bool score_tie = ((cnt >> 10) & 1023) >= 2;
+        bool near_tie = ((cnt >> 20) & 1023) > 0;
+        float walked_prev = -1.f;
         // ---- walk the candidates best first (:1480-1529)
         int nacc = 0, pending = rej;
         for (int rank = 1; rank <= beampos + 1; ++rank) {
@@ -650,6 +703,8 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
                 }
                 if (best.i < 0 || best.v < 0.f) break;
                 v = best.i; pv = best.v;
+                if (walked_prev >= 0.f && walked_prev - pv <= kTieMargin * walked_prev) near_tie = true;
+                walked_prev = pv;
 #pragma unroll
                 for (int k = 0; k < NVL; ++k) if (lane + 32 * k == v) p[k] = -1.f;     // taken
                 isrej = (v == pending);
@@ -672,9 +727,19 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
             }
             ++nacc;
         }
+        if (walked_prev >= 0.f) {       // the first candidate LEFT OUT against the last one taken: a near-tie there changes the children
+            float rest = -1.f;
+#pragma unroll
+            for (int k = 0; k < NVL; ++k) if (lane + 32 * k < b.V) rest = fmaxf(rest, p[k]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) rest = fmaxf(rest, __shfl_xor_sync(FULL, rest, o));
+            if (rest >= 0.f && walked_prev - rest <= kTieMargin * walked_prev) near_tie = true;
+        }
         if (lane == 0) {
             b.rec_cur[g] = cur; b.rec_amax1[g] = amax == 1.0f ? 1 : 0; b.rec_pos[g] = pos;
             b.rec_len[g] = len_node; b.rec_nacc[g] = nacc; b.rec_parent[g] = node;
+            if (score_tie) atomicAdd((unsigned long long*)&b.score_ties[line], 1ull);
+            if (near_tie) atomicAdd((unsigned long long*)&b.near_ties[line], 1ull);
         }
     }
 }
@@ -734,25 +799,29 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
     const uint32_t* oid = b.fr_id + ((size_t)cur * b.L + line) * b.cap + o_off;
     double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
+    // truncation to the best max_batches * batch_size = 2T * batch_size of THIS line's reference batch (seq2seq.py:1397, 1531)
+    const int keep = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);
     for (int i = tid; i < n_old; i += 256) {
         const double k = okey[i]; const uint32_t id = oid[i];
         int lo = 0, hi = n_new;                   // new entries that precede this old one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = i + lo;
-        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+        if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
     for (int j = tid; j < n_new; j += 256) {
         const double k = skey[j]; const uint32_t id = sid[j];
         int lo = 0, hi = n_old;                   // old entries that precede this new one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = j + lo;
-        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+        if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
     __syncthreads();
     if (tid == 0) {
-        b.fr_len[line] = min(n_old + n_new, b.cap);
+        const int nl = min(n_old + n_new, keep);
+        b.fr_len[line] = nl;
         b.fr_off[line] = 0;
         b.fr_buf[line] = cur ^ 1;
+        if (nl > b.fr_peak[line]) b.fr_peak[line] = nl;
     }
 }
 
@@ -802,6 +871,7 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
     const uint32_t* oid = b.fr_id + ((size_t)cur * b.L + line) * b.cap + o_off;
     double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
+    const int keep = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);     // see push_line
     if (lane < n_new) {
         const double k = s_key[wid][lane]; const uint32_t id = s_id[wid][lane];
         int rank = 0;
@@ -809,20 +879,22 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
         int lo = 0, hi = n_old;                   // old entries that precede this new one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = rank + lo;
-        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+        if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
     for (int i = lane; i < n_old; i += 32) {
         const double k = okey[i]; const uint32_t id = oid[i];
         int before = 0;                           // new entries that precede this old one
         for (int t = 0; t < n_new; ++t) before += key_less(s_key[wid][t], s_id[wid][t], k, id);
         const int pos = i + before;
-        if (pos < b.cap) { nkey[pos] = k; nid[pos] = id; }
+        if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
     __syncwarp();
     if (lane == 0) {
-        b.fr_len[line] = min(n_old + n_new, b.cap);
+        const int nl = min(n_old + n_new, keep);
+        b.fr_len[line] = nl;
         b.fr_off[line] = 0;
         b.fr_buf[line] = cur ^ 1;
+        if (nl > b.fr_peak[line]) b.fr_peak[line] = nl;
     }
 }
 
@@ -873,10 +945,15 @@ __global__ void __launch_bounds__(128) beam_finish_kernel(BeamDev b, int32_t* o_
         }
         o_len[line] = n;
         s_n = n;
-        o_stats[(size_t)line * 4 + 0] = st == ST_OVERFLOW ? -1 : (st == ST_EMPTY ? -2 : b.iter[line]);
-        o_stats[(size_t)line * 4 + 1] = b.hyp_steps[line];
-        o_stats[(size_t)line * 4 + 2] = b.finals_count[line];
-        o_stats[(size_t)line * 4 + 3] = st == ST_ACTIVE ? b.fr_len[line] : b.open_left[line];
+        long long* os = o_stats + (size_t)line * kStats;
+        os[0] = st == ST_OVERFLOW ? -1 : (st == ST_EMPTY ? -2 : b.iter[line]);
+        os[1] = b.hyp_steps[line];
+        os[2] = b.finals_count[line];
+        os[3] = st == ST_ACTIVE ? b.fr_len[line] : b.open_left[line];
+        os[4] = b.score_ties[line];
+        os[5] = b.near_ties[line];
+        os[6] = (long long)b.pop_sum[line];
+        os[7] = b.fr_peak[line];
     }
     __syncthreads();
     if (!o_align) return;
@@ -938,12 +1015,14 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     b->fr_off = c.take<int32_t>(L); b->fr_buf = c.take<int32_t>(L); b->finals_count = c.take<int32_t>(L);
     b->best_final = c.take<int32_t>(L); b->open_left = c.take<int32_t>(L);
     b->best_key = c.take<double>(L); b->hyp_steps = c.take<long long>(L);
+    b->score_ties = c.take<long long>(L); b->near_ties = c.take<long long>(L); b->pop_sum = c.take<unsigned long long>(L);
+    b->fr_peak = c.take<int32_t>(L);
     b->fr_key = c.take<double>((size_t)2 * L * cap); b->fr_id = c.take<uint32_t>((size_t)2 * L * cap);
     b->beam_nodes = c.take<uint32_t>((size_t)L * bp->batch_size);
     b->rej_table = c.take<int32_t>((size_t)L * T);
     b->counters = c.take<int32_t>(4);
     b->heavy = c.take<int32_t>(L);
-    b->o_stats = c.take<long long>((size_t)L * 4);
+    b->o_stats = c.take<long long>((size_t)L * kStats);
     b->o_align = want_align ? c.take<float>((size_t)L * 2 * T * T) : nullptr;
     const size_t G = (size_t)L * quota_x;
     b->rec_p = c.take<float>(G * Vp); b->rec_h = c.take<float>(G * d * W); b->rec_c = c.take<float>(G * d * W);
@@ -1027,7 +1106,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
              const cor_beam_params* bp, const Plan& plan, void* workspace,
              int32_t* o_chars, float* o_probs, double* o_scores, int32_t* o_len, float* o_align, int64_t* o_stats,
              bool on_device, int64_t* host_stats, cudaStream_t st) {
-    // on_device: the line arrays and the result arrays are DEVICE memory; host_stats (always HOST, [L][4])
+    // on_device: the line arrays and the result arrays are DEVICE memory; host_stats (always HOST, [L][kStats])
     // additionally receives the statistics, which carry the per-line overflow flag the retry loop needs
     const cudaMemcpyKind kin = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     const cudaMemcpyKind kout = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
@@ -1039,7 +1118,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     if (h_val) COR_CUDA(cudaMemcpyAsync(ws.val, h_val, n * 4, kin, st));
     else { ws.val = nullptr; b.val = nullptr; }
     if (run_encoder(m, ws, st)) return 1;
-    beam_init_kernel<<<L, 128, 0, st>>>(b); ++g_launches;
+    beam_init_kernel<<<L, 128, 0, st>>>(b); ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     const int split = m->split ? 1 : 0;
     const int row_grid = std::min(plan.Rcap, 148 * 8);
@@ -1049,7 +1128,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     for (int it = 0; it <= 2 * t_hi; ++it) {
         beam_pop_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
         beam_scan_kernel<<<1, 1024, 0, st>>>(b);
-        g_launches += 2;
+        ctx().launches += 2;
         if (it % 8 == 7 || it == 2 * t_hi) {          // host check: has every line finished?
             int32_t cnt[2] = {0, 0};
             COR_CUDA(cudaMemcpyAsync(cnt, b.counters, 8, cudaMemcpyDeviceToHost, st));
@@ -1058,7 +1137,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         }
         beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
         beam_gather_kernel<<<row_grid, 128, 0, st>>>(b, split);
-        g_launches += 2;
+        ctx().launches += 2;
         COR_CUDA(cudaGetLastError());
         io.wq_ready = it > 0;     // iteration 0 expands the roots: their query comes from the encoder state
         if (decoder_core(m, ws, io, st)) return 1;
@@ -1072,7 +1151,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         }
         beam_push_small_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
         beam_push_kernel<<<std::min(L, 148 * 4), 256, push_smem, st>>>(b);
-        g_launches += 3;
+        ctx().launches += 3;
         COR_CUDA(cudaGetLastError());
     }
     // results: staged in the encoder workspace's output slots and the wave's own staging buffers
@@ -1082,14 +1161,14 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     COR_CUDA(cudaMemsetAsync(d_chars, 0, (size_t)L * S * 4, st));
     COR_CUDA(cudaMemsetAsync(d_probs, 0, (size_t)L * S * 4, st));
     beam_finish_kernel<<<L, 128, 0, st>>>(b, d_chars, d_probs, d_score, d_len, d_align, b.o_stats);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     COR_CUDA(cudaMemcpyAsync(o_chars, d_chars, (size_t)L * S * 4, kout, st));
     COR_CUDA(cudaMemcpyAsync(o_probs, d_probs, (size_t)L * S * 4, kout, st));
     COR_CUDA(cudaMemcpyAsync(o_scores, d_score, (size_t)L * 8, kout, st));
     COR_CUDA(cudaMemcpyAsync(o_len, d_len, (size_t)L * 4, kout, st));
-    COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * 32, kout, st));
-    COR_CUDA(cudaMemcpyAsync(host_stats, b.o_stats, (size_t)L * 32, cudaMemcpyDeviceToHost, st));
+    COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * kStats * 8, kout, st));
+    COR_CUDA(cudaMemcpyAsync(host_stats, b.o_stats, (size_t)L * kStats * 8, cudaMemcpyDeviceToHost, st));
     if (o_align) COR_CUDA(cudaMemcpyAsync(o_align, d_align, (size_t)L * S * T * 4, kout, st));
     COR_CUDA(cudaStreamSynchronize(st));
     return 0;
@@ -1135,6 +1214,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                         size_t workspace_bytes, int32_t* out_chars, float* out_probs, double* out_scores, int32_t* out_len,
                         float* out_align, int64_t* stats, cudaStream_t st) {
     if (check_params(m, bp)) return 1;
+    CtxScope scope(&m->ctx);
     COR_CHECK(hl && workspace && out_chars && out_probs && out_scores && out_len && stats, "null argument");
     COR_CHECK(hl->n_rows > 0 && hl->t_max > 0 && hl->k_alt > 0, "empty call geometry");
     COR_CUDA(cudaSetDevice(m->device));
@@ -1168,7 +1248,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                 float* vl = hl->val ? (float*)stage.take((size_t)L * tk * 4) : nullptr;
                 w_chars = (int32_t*)stage.take((size_t)L * S * 4); w_probs = (float*)stage.take((size_t)L * S * 4);
                 w_scores = (double*)stage.take((size_t)L * 8); w_len = (int32_t*)stage.take((size_t)L * 4);
-                w_stats = (int64_t*)stage.take((size_t)L * 32);
+                w_stats = (int64_t*)stage.take((size_t)L * kStats * 8);
                 w_align = out_align ? (float*)stage.take((size_t)L * S * T * 4) : nullptr;
                 COR_CHECK(rT && ix && (vl || !hl->val) && w_chars && w_probs && w_scores && w_len && w_stats && (w_align || !out_align),
                           "out of memory for beam retry staging");
@@ -1181,17 +1261,17 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
             }
             Plan wp = plan;
             if (L != plan.L && make_plan(m, L, T, k, bp, out_align != nullptr, workspace_bytes, &wp)) return 1;
-            hstats.assign((size_t)L * 4, 0);
+            hstats.assign((size_t)L * kStats, 0);
             if (run_wave(m, L, T, k, w_T, w_idx, w_val, bp, wp, workspace, w_chars, w_probs, w_scores, w_len, w_align, w_stats,
                          on_device, hstats.data(), st)) return 1;
             for (int j = 0; j < L; ++j) {
                 const int dst = pending[p0 + j];
-                if (hstats[(size_t)j * 4] == -1) { failed.push_back(dst); continue; }
+                if (hstats[(size_t)j * kStats] == -1) { failed.push_back(dst); continue; }
                 if (direct) continue;
                 if (xcopy(out_chars + (size_t)dst * S, w_chars + (size_t)j * S, S * 4) ||
                     xcopy(out_probs + (size_t)dst * S, w_probs + (size_t)j * S, S * 4) ||
                     xcopy(out_scores + dst, w_scores + j, 8) || xcopy(out_len + dst, w_len + j, 4) ||
-                    xcopy(stats + (size_t)dst * 4, w_stats + (size_t)j * 4, 32)) return 1;
+                    xcopy(stats + (size_t)dst * kStats, w_stats + (size_t)j * kStats, kStats * 8)) return 1;
                 if (out_align && xcopy(out_align + (size_t)dst * S * T, w_align + (size_t)j * S * T, S * T * 4)) return 1;
             }
             if (on_device) COR_CUDA(cudaStreamSynchronize(st));      // staging is freed at the end of this scope

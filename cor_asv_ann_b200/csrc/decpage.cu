@@ -275,6 +275,20 @@ __device__ void attention_row_cta(const PageDecArgs& a, int row, bool first, flo
 
 // softmax of one line's logits + greedy bookkeeping (decode_batch_greedy, seq2seq.py:1250-1260) by one warp;
 // same arithmetic as softmax_kernel<true> in kernels.cu.  p goes to the [p | h1] operand rows (hi/lo).
+// best and second-best probability over v >= 1 of one lane's elements, merged across the warp: the runner-up
+// is only used to LOG near-ties (north star: "excluding exact-tie argmaxes, which are logged")
+__device__ __forceinline__ void top2_merge(float& best, int& best_v, float& second) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+        const float os = __shfl_xor_sync(0xffffffffu, second, o);
+        const bool take = ob > best || (ob == best && ov < best_v);
+        const float loser = take ? best : ob;
+        second = fmaxf(fmaxf(second, os), loser);
+        if (take) { best = ob; best_v = ov; }
+    }
+}
 __device__ void softmax_greedy_row(const PageDecArgs& a, int row, int step, __half* p_hi, __half* p_lo) {
     // One pass over the logits (kept in registers) and ONE expf per element: softmax_kernel evaluates
     // expf(z - m) twice with identical results, so the bits are the same, but this warp's chain of loads, expf
@@ -297,23 +311,21 @@ __device__ void softmax_greedy_row(const PageDecArgs& a, int row, int step, __ha
     for (int k = 0; k < VL; ++k)
         if (lane + 32 * k < a.V) { e[k] = expf(e[k] - m); s += e[k]; } else e[k] = 0.f;
     s = warp_sum(s);
-    float best = -INFINITY;
+    float best = -INFINITY, second = -INFINITY;
     int best_v = 0x7fffffff;
 #pragma unroll
     for (int k = 0; k < VL; ++k) {
         const int v = lane + 32 * k;
         if (v < a.Vp) {
             const float pv = v < a.V ? e[k] / s : 0.f;
-            if (v < a.V && v >= 1 && pv > best) { best = pv; best_v = v; }
+            if (v < a.V && v >= 1) {
+                if (pv > best) { second = best; best = pv; best_v = v; }
+                else second = fmaxf(second, pv);
+            }
             store_h(p_hi, p_lo, v, pv);
         }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-        const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
-        if (ob > best || (ob == best && ov < best_v)) { best = ob; best_v = ov; }
-    }
+    top2_merge(best, best_v, second);
     if (lane == 0) {
         const bool alive = !a.done[row] && a.live[row] && step < 2 * a.line_T[row];
         if (alive) {
@@ -323,6 +335,7 @@ __device__ void softmax_greedy_row(const PageDecArgs& a, int row, int step, __ha
             a.score_sum[row] += (double)(-logf(best));
             a.out_len[row] = n + 1;
             if (best_v == a.eos) a.done[row] = 1;
+            if (a.out_ties && best - second <= kTieMargin * best) a.out_ties[row] += 1;
         }
     }
 }
@@ -570,13 +583,16 @@ int launch_page_decoder(cudaStream_t st, const PageDecArgs& a_in) {
     // COR_PD_NOCOOP: plain cluster launch (ncu cannot replay the cooperative one); co-residency then rests on the occupancy check alone
     cfg.attrs = at; cfg.numAttrs = getenv("COR_PD_NOCOOP") ? 1 : 2;
     cudaError_t err = cudaLaunchKernelEx(&cfg, page_decoder_kernel, a);
-    if (err != cudaSuccess) {       // cooperative + cluster refused: the occupancy check above already guarantees co-residency
+    if (err != cudaSuccess && cfg.numAttrs == 2) {
+        // cooperative + cluster launch refused.  The occupancy check does not guarantee co-residency when another kernel
+        // holds SMs (side stream, other process, MPS), and the hand-rolled grid barrier would then spin into its trap:
+        // tell the caller to take the per-timestep launches instead (return 2).  COR_PD_NOCOOP (above) stays a profiling
+        // switch only (ncu cannot replay a cooperative launch) and is unsafe outside an otherwise idle GPU.
         (void)cudaGetLastError();
-        cfg.numAttrs = 1;
-        err = cudaLaunchKernelEx(&cfg, page_decoder_kernel, a);
+        return 2;
     }
     COR_CUDA(err);
-    ++g_launches;
+    ++ctx().launches;
     if (tpath) report_timing(t_buf, a.S, st, tpath, a.B);
     return 0;
 }

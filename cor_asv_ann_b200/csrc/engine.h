@@ -28,7 +28,26 @@ void set_error(const std::string& msg);
         }                                                                      \
     } while (0)
 
-extern int64_t g_launches;   // kernels launched (bench.py's gpu_launches)
+// ------------------------------------------------------------------ per-handle engine state
+// Counters, the tensor-map cache and the test switches belong to ONE cor_model: two handles in a process (two
+// models, or one model per GPU) never share them.  A C-ABI entry point installs its handle's Ctx for the duration
+// of the call (CtxScope, thread-local); handle-free test hooks (cor_debug_gemm) run on a default Ctx.
+struct Ctx {
+    int64_t launches = 0;          // kernels launched (bench.py's gpu_launches)
+    // tcgen05 launches by [epilogue: 0 store, 1 LSTM][tile: 0 = 128x32, 1 = 128x256, 2 = CTA pair 256x256], then FFMA [store, LSTM]
+    int64_t tc_kind[2][3] = {};
+    int64_t ffma_kind[2] = {};
+    int force_bn = 0;              // test hook (cor_debug_gemm mode 3): force the narrow tile
+    void* tc_maps = nullptr;       // tensor-map cache (gemm_tc.cu owns the type)
+    void* prof = nullptr;          // per-launch event bracketing (api.cu owns the type)
+};
+Ctx& ctx();
+struct CtxScope {
+    Ctx* prev;
+    explicit CtxScope(Ctx* c);
+    ~CtxScope();
+};
+void tc_ctx_release(Ctx* c);       // frees the tensor-map cache
 
 // ------------------------------------------------------------------ GEMM
 // C[M,N] = sum_s A_s[M,K_s] * B_s[N,K_s]^T   (A row-major, B "K-major": one row per output column)
@@ -96,7 +115,7 @@ int gemm_lstm_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSe
 int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi, int passes = 3);
 int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi, int passes = 3);
 bool tc_available();
-void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape
+void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape (current Ctx)
 
 // ------------------------------------------------------------------ persistent recurrence (recur.cu)
 // One launch = all T timesteps of one LSTM layer (both directions side by side) for a page-sized batch:
@@ -134,11 +153,12 @@ struct PageDecArgs {
     const int32_t* line_T;
     const uint8_t* live; uint8_t* done;
     int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len;
+    int32_t* out_ties;                   // optional [B] near-tie counter (see GreedyArgs)
     unsigned* barrier;
     unsigned long long* timing;          // optional [S][4] phase stamps (COR_PD_TIMING), else nullptr
 };
 bool page_decoder_supported(int W, int D, int Vp, int B);
-int launch_page_decoder(cudaStream_t st, const PageDecArgs& a);
+int launch_page_decoder(cudaStream_t st, const PageDecArgs& a);   // 0 ok, 1 error, 2 cooperative launch refused (nothing ran: use the per-timestep path)
 
 // ------------------------------------------------------------------ small kernels (kernels.cu)
 // X[t][r][:] = sum_k val*E[idx]; Xr[T_r-1-t][r][:] = same (reversed copy for backward scans)
@@ -168,8 +188,12 @@ struct GreedyArgs {
     const int32_t* row_T;
     const uint8_t* live;       // [R] line has any input
     int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len; uint8_t* done;
+    int32_t* out_ties;         // [R] or nullptr: emitted characters whose runner-up is within kTieMargin (relative)
     int R; int V; int step; int s_max; int eos;
 };
+// An argmax whose runner-up lies within this relative margin is logged as a near-tie: fp32-grade implementations
+// (this one, Keras/TF, the numpy oracle) may legitimately pick either, so parity tests report such lines separately.
+constexpr float kTieMargin = 1e-6f;
 int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a);
 int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, int R, const int* r_dev, int V);
 int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n);

@@ -130,7 +130,7 @@ int gemm_store_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmS
     p.nseg = nseg; p.M = M; p.m_dev = m_dev; p.N = N;
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
     gemm_ffma_kernel<0, StoreEpi><<<grid, NT, 0, st>>>(p, epi);
-    ++g_launches;
+    ++ctx().launches; ++ctx().ffma_kind[0];
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -144,7 +144,7 @@ int gemm_lstm_ffma(cudaStream_t st, int M, const int* m_dev, int N, const GemmSe
     p.nseg = nseg; p.M = M; p.m_dev = m_dev; p.N = N;
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
     gemm_ffma_kernel<1, LstmEpi><<<grid, NT, 0, st>>>(p, epi);
-    ++g_launches;
+    ++ctx().launches; ++ctx().ffma_kind[1];
     COR_CUDA(cudaGetLastError());
     return 0;
 }

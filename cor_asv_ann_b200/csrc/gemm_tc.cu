@@ -556,7 +556,12 @@ int g_tc_state = -1;        // -1 unknown, 0 unavailable, 1 ok
 int g_num_sms = 148;
 int g_max_pairs = 0;        // resident CTA pairs (0: pair kernel unusable)
 std::mutex g_mu;
-std::map<std::tuple<const void*, long long, long long, long long, int>, CUtensorMap> g_maps;
+// tensor maps are cached per handle (Ctx::tc_maps), keyed by pointer and geometry; a handle is used by one thread at a time
+using MapCache = std::map<std::tuple<const void*, long long, long long, long long, int>, CUtensorMap>;
+MapCache& maps_of(Ctx& c) {
+    if (!c.tc_maps) c.tc_maps = new MapCache();
+    return *static_cast<MapCache*>(c.tc_maps);
+}
 
 bool init_tc() {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -594,10 +599,10 @@ bool init_tc() {
 // 2-D fp16 row-major [rows][cols] with leading dimension ld (elements); box = 64 columns x box_rows
 int get_map(const float* ptr, long long rows, long long cols, long long ld, int box_rows, CUtensorMap* out) {
     auto key = std::make_tuple((const void*)ptr, rows, cols, ld, box_rows);
+    MapCache& maps = maps_of(ctx());
     {
-        std::lock_guard<std::mutex> lk(g_mu);
-        auto it = g_maps.find(key);
-        if (it != g_maps.end()) { *out = it->second; return 0; }
+        auto it = maps.find(key);
+        if (it != maps.end()) { *out = it->second; return 0; }
     }
     COR_CHECK(((uintptr_t)ptr & 15) == 0 && (ld * ELT) % 16 == 0, "TMA operand must be 16-byte aligned with a 16-byte multiple pitch");
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -608,9 +613,8 @@ int get_map(const float* ptr, long long rows, long long cols, long long ld, int 
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     COR_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
-    std::lock_guard<std::mutex> lk(g_mu);
-    if (g_maps.size() > 4096) g_maps.clear();
-    g_maps[key] = *out;
+    if (maps.size() > 4096) maps.clear();
+    maps[key] = *out;
     return 0;
 }
 
@@ -630,15 +634,13 @@ int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg*
     return 0;
 }
 
-int g_force_bn = 0;      // test hook (cor_debug_gemm mode 3): force the narrow tile
-
 // Tile shape.  The pair kernel pays off once there are enough 256-row tiles to fill the resident pairs;
 // below that the single-CTA kernel has the finer granularity (128-row tiles on 148 CTAs); and while the
 // 32-column tiles still fit in ONE wave (a page of lines: M <= 256 rows at N = 2048 is <= 128 tiles)
 // they spread the weight stream over 8x as many SMs as the wide tiles would.
 void pick_shape(int M, int N, int* ncta, int* bn) {
     const long long tiles_m = (M + BM - 1) / BM, narrow = tiles_m * ((N + BN_NARROW - 1) / BN_NARROW);
-    if (g_force_bn == BN_NARROW || (narrow <= g_num_sms && !getenv("COR_NO_NARROW"))) { *ncta = 1; *bn = BN_NARROW; return; }
+    if (ctx().force_bn == BN_NARROW || (narrow <= g_num_sms && !getenv("COR_NO_NARROW"))) { *ncta = 1; *bn = BN_NARROW; return; }
     *bn = BN_WIDE;
     const long long pair_tiles = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + BN_WIDE - 1) / BN_WIDE);
     *ncta = (g_max_pairs > 0 && pair_tiles >= g_max_pairs) ? 2 : 1;
@@ -658,7 +660,7 @@ int launch_tc(cudaStream_t st, int M, int N, const TcParams& p, const Epi& epi) 
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = NCTA; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     COR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, NCTA, BN, Epi>, p, epi));
-    ++g_launches;
+    ++ctx().launches; ++ctx().tc_kind[EPI][NCTA == 2 ? 2 : (BN == BN_WIDE ? 1 : 0)];
     return 0;
 }
 
@@ -675,7 +677,10 @@ int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* 
 }  // namespace
 
 bool tc_available() { return init_tc(); }
-void tc_force_narrow(bool on) { g_force_bn = on ? BN_NARROW : 0; }
+void tc_force_narrow(bool on) { ctx().force_bn = on ? BN_NARROW : 0; }
+void tc_ctx_release(Ctx* c) {
+    if (c && c->tc_maps) { delete static_cast<MapCache*>(c->tc_maps); c->tc_maps = nullptr; }
+}
 
 int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const StoreEpi& epi, int passes) {
     if (M <= 0) return 0;

@@ -161,6 +161,20 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
 // One warp per row.  The row stride of logits / p is V rounded up to 128; the pad stays zero.
 // NVL > 0: Vp == 32 * NVL and the row lives in registers (one pass over the logits, one expf per element --
 // the same values the generic path computes twice, so the bits are identical); NVL == 0: generic path.
+// best and second-best probability over v >= 1 of one lane's elements, merged across the warp: the runner-up
+// is only used to LOG near-ties (north star: "excluding exact-tie argmaxes, which are logged")
+__device__ __forceinline__ void top2_merge(float& best, int& best_v, float& second) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+        const float os = __shfl_xor_sync(0xffffffffu, second, o);
+        const bool take = ob > best || (ob == best && ov < best_v);
+        const float loser = take ? best : ob;
+        second = fmaxf(fmaxf(second, os), loser);
+        if (take) { best = ob; best_v = ov; }
+    }
+}
 template <bool GREEDY, int NVL>
 __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r_dev) {
     const int R = r_dev ? min(*r_dev, g.R) : g.R;
@@ -169,7 +183,7 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
     const int lane = threadIdx.x & 31;
     const int ld = (g.V + 127) & ~127;
     const float* z = g.logits + (size_t)row * ld;
-    float best = -INFINITY;
+    float best = -INFINITY, second = -INFINITY;
     int best_v = 0x7fffffff;
     if constexpr (NVL > 0) {
         float e[NVL];
@@ -188,7 +202,10 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
         for (int k = 0; k < NVL; ++k) {
             const int v = lane + 32 * k;
             const float pv = v < g.V ? e[k] / s : 0.f;
-            if (GREEDY && v < g.V && v >= 1 && pv > best) { best = pv; best_v = v; }   // first maximum among v>=1
+            if (GREEDY && v < g.V && v >= 1) {
+                if (pv > best) { second = best; best = pv; best_v = v; }   // first maximum among v>=1
+                else second = fmaxf(second, pv);
+            }
             store_split(g.p, g.p_lo, (size_t)row * ld + v, pv);
         }
     } else {
@@ -202,18 +219,16 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
             float pv = 0.f;
             if (v < g.V) {
                 pv = expf(z[v] - m) / s;
-                if (GREEDY && v >= 1 && pv > best) { best = pv; best_v = v; }   // first maximum among v>=1
+                if (GREEDY && v >= 1) {
+                    if (pv > best) { second = best; best = pv; best_v = v; }   // first maximum among v>=1
+                    else second = fmaxf(second, pv);
+                }
             }
             store_split(g.p, g.p_lo, (size_t)row * ld + v, pv);
         }
     }
     if (!GREEDY) return;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-        const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
-        if (ob > best || (ob == best && ov < best_v)) { best = ob; best_v = ov; }
-    }
+    top2_merge(best, best_v, second);
     if (lane == 0) {
         const bool alive = !g.done[row] && g.live[row] && g.step < 2 * g.row_T[row];
         if (alive) {
@@ -223,6 +238,7 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
             g.score_sum[row] += (double)(-logf(best));
             g.out_len[row] = n + 1;
             if (best_v == g.eos) g.done[row] = 1;
+            if (g.out_ties && best - second <= kTieMargin * best) g.out_ties[row] += 1;
         }
     }
 }
@@ -261,14 +277,14 @@ int launch_embed(cudaStream_t st, const int32_t* idx, const float* val, const in
     (void)V;
     dim3 grid(t_max, n_rows);
     embed_kernel<<<grid, 128, 0, st>>>(idx, val, row_T, n_rows, t_max, k_alt, E, W, X, X_lo, Xr, Xr_lo);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
 
 int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int n_rows, int t_max, int k_alt, uint8_t* live) {
     live_rows_kernel<<<n_rows, 128, 0, st>>>(idx, val, n_rows, t_max, k_alt, live);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -278,7 +294,7 @@ int launch_attention_reg(cudaStream_t st, const AttnArgs& a) {
     COR_CHECK(a.W % 4 == 0 && a.D % 4 == 0, "W and D must be multiples of 4");
     if (a.R <= 0) return 0;
     attention_kernel<<<(a.R + 3) / 4, 128, 0, st>>>(a);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -289,7 +305,7 @@ int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a) {
     if (ld == 512) softmax_kernel<true, 16><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
     else if (ld == 128) softmax_kernel<true, 4><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
     else softmax_kernel<true, 0><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -302,7 +318,7 @@ int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, 
     if (ld == 512) softmax_kernel<false, 16><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
     else if (ld == 128) softmax_kernel<false, 4><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
     else softmax_kernel<false, 0><<<(R + 3) / 4, 128, 0, st>>>(g, r_dev);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -312,7 +328,7 @@ int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n
     int blocks = (int)((n + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     split_kernel<<<blocks, 256, 0, st>>>(x, hi, lo, n);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -322,7 +338,7 @@ int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, s
     int blocks = (int)((n + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     join_kernel<<<blocks, 256, 0, st>>>(hi, lo, out, n);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
@@ -332,14 +348,14 @@ int launch_join_lt(cudaStream_t st, const float* hi, const float* lo, float* out
     if (!n) return 0;
     int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
     join_lt_kernel<<<blocks, 256, 0, st>>>(hi, lo, out, L, T, D);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }
 
 int launch_finish_scores(cudaStream_t st, double* score_sum, const int32_t* len, int R) {
     finish_scores_kernel<<<(R + 255) / 256, 256, 0, st>>>(score_sum, len, R);
-    ++g_launches;
+    ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;
 }

@@ -23,9 +23,25 @@ struct LstmW {
 
 struct HostWeight { std::vector<int64_t> shape; std::vector<float> data; };
 
+// Per-launch timing of the LSTM-GEMM launches of one handle (bench.py's roofline pass): when enabled, every such
+// launch is bracketed by two events on the launching stream; cor_prof_read sums the elapsed times after a synchronize.
+struct Prof {
+    bool on = false;
+    std::vector<cudaEvent_t> ev;     // pairs
+    size_t used = 0;
+    double flops = 0;                // launches whose row count is known on the host
+    int64_t launches = 0;
+    // launches whose row count lives on the device (beam): the count is copied into pinned memory
+    // right behind the kernel, and the flops are added up in cor_prof_read
+    int32_t* rows = nullptr;         // pinned [kMaxDeferred]
+    std::vector<double> per_row;     // 2*N*K of the deferred launch
+};
+
 }  // namespace cor
 
 struct cor_model {
+    cor::Ctx ctx;             // counters, tensor-map cache, test switches of THIS handle
+    cor::Prof prof;
     cor_config cfg{};
     int device = 0;
     int W = 0, d = 0, V = 0, Vp = 0, D = 0;
@@ -84,6 +100,7 @@ struct Ws {
     float *logits = nullptr, *p = nullptr, *p_lo = nullptr;
     float *h_lm = nullptr, *h_lm_lo = nullptr, *c_lm = nullptr, *logits_lm = nullptr, *p_lm = nullptr;
     int32_t* o_chars = nullptr; float* o_probs = nullptr; double* o_score = nullptr; int32_t* o_len = nullptr;
+    int32_t* o_ties = nullptr;
     float* o_align = nullptr;
     float* enc_out() const { return seq.back(); }
     float* enc_out_lo() const { return seq_lo.back(); }

@@ -203,7 +203,7 @@ int launch_lstm_recur(cudaStream_t st, const RecurArgs& a) {
     at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;      // co-residency of the whole grid
     cfg.attrs = at; cfg.numAttrs = 1;
     COR_CUDA(cudaLaunchKernelEx(&cfg, lstm_recur_kernel, a));
-    ++g_launches;
+    ++ctx().launches;
     return 0;
 }
 

@@ -11,6 +11,10 @@ from . import _lib
 from ._lib import CorConfig, CorLines, CorBeamParams, check
 
 
+BEAM_STATS = 8     # int64 statistics per line (COR_BEAM_STATS in include/cor_b200.h)
+STAT_NAMES = ("iterations", "hypothesis_steps", "finals", "open_left", "score_ties", "near_ties", "pop_checksum", "fringe_peak")
+
+
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
 
@@ -53,6 +57,7 @@ class Engine:
             check(self.lib.cor_model_finalize(self.handle))
         self._ws = None
         self._geom = None
+        self.last_ties = None      # int32 [B]: near-tie argmaxes per line of the last greedy call (device or pinned host tensor)
 
     def close(self):
         if getattr(self, "handle", None):
@@ -93,7 +98,7 @@ class Engine:
         enc_out = torch.empty((T, B, self.D), dtype=torch.float32, device=self.device) if want_outputs else None
         states = torch.empty((2 * self.d, B, self.W), dtype=torch.float32, device=self.device) if want_outputs else None
         with torch.cuda.device(self.device):
-            check(self.lib.cor_encode(self.handle, C.byref(lines), _ptr(ws), ws.numel(),
+            check(self.lib.cor_encode(self.handle, C.byref(lines), int(want_align), _ptr(ws), ws.numel(),
                                       _ptr(enc_out), _ptr(states), self._stream()))
         self._geom = (B, T, k, bool(want_align))
         return enc_out, states
@@ -126,9 +131,11 @@ class Engine:
         scores = torch.empty((B,), dtype=torch.float64, device=dev)
         lens = torch.empty((B,), dtype=torch.int32, device=dev)
         align = torch.empty((2 * T, B, T), dtype=torch.float32, device=dev) if want_align else None
+        ties = torch.empty((B,), dtype=torch.int32, device=dev)
         with torch.cuda.device(dev):
             check(self.lib.cor_decode_greedy_batch(self.handle, _ptr(self._ws), self._ws.numel(), _ptr(chars),
-                                                   _ptr(probs), _ptr(scores), _ptr(lens), _ptr(align), self._stream()))
+                                                   _ptr(probs), _ptr(scores), _ptr(lens), _ptr(ties), _ptr(align), self._stream()))
+        self.last_ties = ties
         return chars, probs, scores, lens, align
 
     def correct_greedy_host(self, idx, val, row_T, want_align=False, out=None):
@@ -140,10 +147,14 @@ class Engine:
         if out is None:
             out = self.host_outputs(B, T, want_align)
         chars, probs, scores, lens, align = out
+        ties = self.last_ties
+        if ties is None or ties.is_cuda or ties.numel() != B:
+            ties = torch.empty((B,), dtype=torch.int32, pin_memory=True)
         lines = CorLines(B, T, k, _ptr(row_T), _ptr(idx), _ptr(val))
         with torch.cuda.device(self.device):
             check(self.lib.cor_correct_greedy_host(self.handle, C.byref(lines), _ptr(ws), ws.numel(), _ptr(chars),
-                                                   _ptr(probs), _ptr(scores), _ptr(lens), _ptr(align), self._stream()))
+                                                   _ptr(probs), _ptr(scores), _ptr(lens), _ptr(ties), _ptr(align), self._stream()))
+        self.last_ties = ties
         return out
 
     @staticmethod
@@ -174,7 +185,7 @@ class Engine:
                    torch.empty((B,), dtype=torch.float64, pin_memory=pin),
                    torch.empty((B,), dtype=torch.int32, pin_memory=pin),
                    torch.empty((B, 2 * T, T), dtype=torch.float32, pin_memory=pin) if want_align else None,
-                   torch.empty((B, 4), dtype=torch.int64, pin_memory=pin))
+                   torch.empty((B, BEAM_STATS), dtype=torch.int64, pin_memory=pin))
         chars, probs, scores, lens, align, stats = out
         lines = CorLines(B, T, k, _ptr(row_T), _ptr(idx), _ptr(val))
         with torch.cuda.device(self.device):
@@ -190,14 +201,14 @@ class Engine:
 
     def beam_device(self, idx, val, row_T, bp, budget_bytes=32 << 30, out=None):
         """Beam search with the lines already on the device; results stay on the device.
-        Returns (chars [B,2T], probs, scores, lens, None, stats [B,4]) as device tensors."""
+        Returns (chars [B,2T], probs, scores, lens, None, stats [B,8]) as device tensors."""
         B, T, k = idx.shape
         ws = self.beam_workspace(B, T, k, bp, budget_bytes)
         dev = self.device
         if out is None:
             out = (torch.empty((B, 2 * T), dtype=torch.int32, device=dev), torch.empty((B, 2 * T), dtype=torch.float32, device=dev),
                    torch.empty((B,), dtype=torch.float64, device=dev), torch.empty((B,), dtype=torch.int32, device=dev), None,
-                   torch.empty((B, 4), dtype=torch.int64, device=dev))
+                   torch.empty((B, BEAM_STATS), dtype=torch.int64, device=dev))
         chars, probs, scores, lens, align, stats = out
         lines = CorLines(B, T, k, _ptr(row_T), _ptr(idx), _ptr(val))
         with torch.cuda.device(dev):
@@ -231,16 +242,25 @@ class Engine:
         return path, dist
 
     def prof_enable(self, on=True):
-        check(self.lib.cor_prof_enable(int(on)))
+        check(self.lib.cor_prof_enable(self.handle, int(on)))
 
     def prof_read(self):
         """(total ms, launches, algorithmic flops) of the LSTM-GEMM launches since prof_enable(True)."""
         ms, n, fl = C.c_double(), C.c_int64(), C.c_double()
-        check(self.lib.cor_prof_read(C.byref(ms), C.byref(n), C.byref(fl)))
+        check(self.lib.cor_prof_read(self.handle, C.byref(ms), C.byref(n), C.byref(fl)))
         return ms.value, n.value, fl.value
 
     def launch_count(self, reset=False):
-        return int(self.lib.cor_launch_count(int(reset)))
+        return int(self.lib.cor_launch_count(self.handle, int(reset)))
+
+    KERNEL_KINDS = ("tc_store_narrow", "tc_store_single", "tc_store_pair", "tc_lstm_narrow", "tc_lstm_single", "tc_lstm_pair",
+                    "ffma_store", "ffma_lstm")
+
+    def kernel_counters(self, reset=False):
+        """GEMM launches of this handle by kernel variant (cor_debug_counters): which kernel a test really ran."""
+        out = (C.c_int64 * 8)()
+        check(self.lib.cor_debug_counters(self.handle, out, int(reset)))
+        return dict(zip(self.KERNEL_KINDS, (int(v) for v in out)))
 
 
 def _as_cpu(x, dtype):

@@ -612,7 +612,7 @@ class Sequence2Sequence(object):
                                  rejection_threshold=self.rejection_threshold)
             out = (torch.empty((B, 2 * T), dtype=torch.int32, device=dev), torch.empty((B, 2 * T), dtype=torch.float32, device=dev),
                    torch.empty((B,), dtype=torch.float64, device=dev), torch.empty((B,), dtype=torch.int32, device=dev),
-                   torch.empty((B, 2 * T, T), dtype=torch.float32, device=dev), torch.empty((B, 4), dtype=torch.int64, device=dev))
+                   torch.empty((B, 2 * T, T), dtype=torch.float32, device=dev), torch.empty((B, 8), dtype=torch.int64, device=dev))
             chars, probs, scores, lens, align, stats = eng.beam_device(d_idx, d_val, d_T, bp,
                                                                        budget_bytes=self.beam_budget_bytes, out=out)
             self.last_beam_stats = stats.cpu().numpy()

@@ -88,8 +88,11 @@ int cor_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
 
 /* ---- encoder: replaces encoder_model.predict_on_batch (seq2seq.py:811,1231,1306,1383).
  * `lines` holds DEVICE pointers.  Results stay inside `workspace`; the optional outputs
- * receive copies: enc_out [t_max][n_rows][D], states [2*depth][n_rows][W] (h1,c1,...,hd,cd). */
-int cor_encode(cor_model* m, const cor_lines* lines, void* workspace, size_t workspace_bytes,
+ * receive copies: enc_out [t_max][n_rows][D], states [2*depth][n_rows][W] (h1,c1,...,hd,cd).
+ * want_alignments != 0 reserves the alignment history of a following cor_decode_greedy_batch
+ * (workspace size from cor_workspace_bytes with the same flag); it is the caller's explicit choice,
+ * never inferred from the size of the buffer. */
+int cor_encode(cor_model* m, const cor_lines* lines, int want_alignments, void* workspace, size_t workspace_bytes,
                float* enc_out, float* states, void* stream);
 
 /* ---- one decoder timestep: replaces decoder_model.predict_on_batch (seq2seq.py:1245,1321,1428).
@@ -107,10 +110,13 @@ int cor_decode_step(cor_model* m, void* workspace, size_t workspace_bytes,
 /* ---- fast mode: replaces decode_batch_greedy (seq2seq.py:1215-1286) for rows already
  * encoded into `workspace` by cor_encode.  Runs 2*row_T[row] steps per row.
  * out_chars int32 [n_rows][2*t_max], out_probs [n_rows][2*t_max], out_scores double [n_rows]
- * (mean -log p), out_len int32 [n_rows], out_align [2*t_max][n_rows][t_max] or NULL. All DEVICE. */
+ * (mean -log p), out_len int32 [n_rows], out_align [2*t_max][n_rows][t_max] or NULL. All DEVICE.
+ * out_ties int32 [n_rows] or NULL: per line, the number of emitted characters whose runner-up probability
+ * lies within 1e-6 relative of the winner's -- the near-tie argmaxes the north star wants logged (an
+ * fp32-grade implementation may legitimately pick either; parity reports such lines separately). */
 int cor_decode_greedy_batch(cor_model* m, void* workspace, size_t workspace_bytes,
                             int32_t* out_chars, float* out_probs, double* out_scores,
-                            int32_t* out_len, float* out_align, void* stream);
+                            int32_t* out_len, int32_t* out_ties, float* out_align, void* stream);
 
 /* ---- the call a host program makes: HOST lines in, HOST results out; host<->device copies
  * happen inside, on `stream`, and the call returns after the results have landed.
@@ -118,14 +124,21 @@ int cor_decode_greedy_batch(cor_model* m, void* workspace, size_t workspace_byte
 int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines,
                             void* workspace, size_t workspace_bytes,
                             int32_t* out_chars, float* out_probs, double* out_scores,
-                            int32_t* out_len, float* out_align, void* stream);
+                            int32_t* out_len, int32_t* out_ties, float* out_align, void* stream);
 
 /* ---- beam mode: replaces the per-line loop of correct_lines(fast=False, greedy=False)
  * over decode_sequence_beam (seq2seq.py:823-836, 1356-1544) for all rows at once.
  * Workspace size comes from cor_beam_workspace_bytes.  Per row: the best final hypothesis
  * (out_len = 0 when the search yields none, i.e. the reference's StopIteration fallback),
  * out_scores = cum_cost/(len-1), out_align compact [n_rows][2*t_max][t_max] or NULL;
- * stats int64 [n_rows][4] = iterations, hypothesis-steps, finals, open nodes left. All HOST. */
+ * stats int64 [n_rows][8] (COR_BEAM_STATS) = [0] iterations, [1] hypothesis-steps, [2] finals, [3] open nodes left,
+ * [4] expanded hypotheses whose two best scores are EXACTLY equal (the argsort tie the reference leaves to numpy),
+ * [5] near-tie ordering decisions (candidate order, beam-threshold cut or pop boundary within 1e-6 relative): where
+ *     an fp32-grade implementation may legitimately search differently -- the ties the north star wants logged,
+ * [6] order-sensitive checksum of the popped hypotheses (length, character, pop index; uint64 bit pattern),
+ * [7] peak fringe length.  [0] is -1 for a line whose arena overflowed (internal, retried) and -2 for an empty line.
+ * All HOST. */
+#define COR_BEAM_STATS 8
 int cor_beam_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
                              const cor_beam_params* bp, size_t budget_bytes, size_t* bytes);
 int cor_correct_beam_host(cor_model* m, const cor_lines* host_lines, const cor_beam_params* bp,
@@ -157,13 +170,17 @@ int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_
                         int n_rows, int t_max, int s_max, const int32_t* in_len, const int32_t* out_len,
                         double min_score, int32_t* out_path, int path_ld, double* out_dist, void* stream);
 
-/* ---- instrumentation for bench.py: kernels launched since the last reset, and device
- * time accumulated by the GEMM kernels between cor_prof_enable(1) and cor_prof_enable(0). */
-int64_t cor_launch_count(int reset);
+/* ---- instrumentation for bench.py and the tests, all PER HANDLE: kernels launched since the last
+ * reset; launches by GEMM kernel variant; device time accumulated by the LSTM-GEMM launches between
+ * cor_prof_enable(m, 1) and cor_prof_enable(m, 0). */
+int64_t cor_launch_count(cor_model* m, int reset);
+/* out[8]: tcgen05 launches with the plain epilogue on 128x32 / 128x256 / CTA-pair 256x256 tiles, the same three
+ * with the fused LSTM epilogue, then FFMA launches plain / LSTM.  Lets a parity test assert WHICH kernel it checked. */
+int cor_debug_counters(cor_model* m, int64_t* out, int reset);
 /* test hook: C[M,N] = A[M,K] . B[N,K]^T (device fp32) through one GEMM kernel: 1 = FFMA, 2 = tcgen05 3-pass fp16 hi/lo, 3 = the same with the page-sized 128x32 tiles forced */
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream);
-int cor_prof_enable(int on);   /* on: reset and start bracketing every LSTM-GEMM launch with events */
-int cor_prof_read(double* total_ms, int64_t* launches, double* flops);   /* synchronizes the device */
+int cor_prof_enable(cor_model* m, int on);   /* on: reset and start bracketing every LSTM-GEMM launch with events */
+int cor_prof_read(cor_model* m, double* total_ms, int64_t* launches, double* flops);   /* synchronizes the device */
 
 #ifdef __cplusplus
 }

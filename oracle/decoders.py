@@ -238,7 +238,9 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
     fringe.push(Node(state=states0, value='', scores=np.zeros(V), prob=[], cost=0.0,
                      alignment=[], length0=T, cost0=3.0))
     max_batches = 2 * T
-    n_iter = n_hyp = n_score_ties = 0
+    n_iter = n_hyp = n_score_ties = n_near = 0
+    pop_sum, fringe_peak = 0, 1
+    c2i = mapping[0]
     for _ in range(max_batches):
         beam = []
         while len(fringe):
@@ -255,6 +257,16 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
             break
         if len(finals) > beam_width_out and finals.nodes[-1].pro_cost() > beam[0].pro_cost():
             break
+        if stats is not None:
+            # diagnostics the CUDA search reports as stats[5..7] (include/cor_b200.h): pop-boundary near-ties, an
+            # order-sensitive checksum of the popped hypotheses, the peak fringe length
+            for t, nd in enumerate(beam):
+                xx = (int(nd.length) << 16) + (c2i[nd.value] if nd.length > 1 else 0) + 1
+                pop_sum = (pop_sum + xx * (2 * (n_hyp + t) + 1) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+            if len(fringe):
+                ka, kb = -fringe.keys[-1][0], -float(beam[-1].pro_cost())
+                if abs(ka - kb) <= 1e-6 * max(1.0, abs(ka)):
+                    n_near += 1
         n_iter += 1
         n_hyp += len(beam)
         p_in = np.vstack([n.scores for n in beam]).astype(enc_out.dtype)
@@ -294,6 +306,15 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
             beampos = min(beampos, beam_width_in)
             if stats is not None and V > 1 and sc[order[-1]] == sc[order[-2]]:
                 n_score_ties += 1
+            if stats is not None:
+                # near-tie ordering decisions of this expansion (same definition as csrc/beam.cu, margin 1e-6 relative):
+                # two consecutive walked candidates, the last one taken against the first left out, the threshold cut
+                so = sc[order[::-1]].astype(np.float64)
+                bound = np.float64(so[0]) * beam_threshold_in
+                nw = min(beampos + 1, V)
+                tie = bool(np.any(np.abs(so - bound) <= 1e-6 * bound))
+                tie = tie or bool(np.any(so[:nw - 1] - so[1:nw] <= 1e-6 * so[:nw - 1]))
+                n_near += int(tie)
             rank = 0
             for v in order[::-1]:
                 v = int(v)
@@ -317,9 +338,11 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
                 fringe.push(Node(parent=node, state=st, value=ch, scores=feedback,
                                  prob=prob, cost=cost, alignment=al1))
         fringe.keep_best(max_batches * batch_size)
+        fringe_peak = max(fringe_peak, len(fringe))
     if stats is not None:
         stats.update(iterations=n_iter, hypothesis_steps=n_hyp, score_ties=n_score_ties,
-                     finals=len(finals), open_left=len(fringe))
+                     finals=len(finals), open_left=len(fringe), near_ties=n_near,
+                     pop_checksum=pop_sum, fringe_peak=fringe_peak)
     while len(finals):
         node = finals.pop()
         nodes = node.path()[1:]

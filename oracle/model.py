@@ -80,15 +80,21 @@ def init_weights(topo, seed=0, variant="U"):
     variant "U": same, embedding rows rescaled to unit norm (what the regulariser
     at seq2seq.py:549-551 drives trained models to) — gives realistic softmax margins —
     and N(0, 0.1) noise on the LSTM biases (so that padding steps change the state).
+    variant "P" ("peaked"): as "U" with embedding rows of norm 12, i.e. logits of standard deviation ~3 like a
+    trained model's: the softmax becomes selective (a few candidates above ``beam_threshold_in`` times the
+    best instead of none or hundreds), which is what makes the beam search a SEARCH -- tens of live
+    hypotheses per line and iteration, finals found among them, early exit by ``beam_width_out``.
     Returns ``{keras_layer_name: [ndarray, ...]}``.
     """
     rng = np.random.default_rng(seed)
     W, d, V, D = topo.width, topo.depth, topo.voc_size, topo.enc_dim
     w = {}
-    bn = 0.1 if variant == "U" else 0.0
+    bn = 0.1 if variant in ("U", "P") else 0.0
     E = (rng.standard_normal((V, W)) * 0.001).astype(np.float32)
-    if variant == "U":
+    if variant in ("U", "P"):
         E = (E / np.linalg.norm(E, axis=1, keepdims=True)).astype(np.float32)
+    if variant == "P":
+        E = (E * np.float32(12.0)).astype(np.float32)
     w["char_input_projection"] = [E]
     for n in range(d):
         name = "encoder_lstm_%d" % (n + 1)

@@ -81,6 +81,14 @@ def make_kant():
     return alphabet, pages
 
 
+def stat_row(s):
+    """The oracle's search statistics in the order of the C ABI's stats[8] (include/cor_b200.h); the uint64 checksum
+    is stored as its int64 bit pattern."""
+    ck = int(s.get("pop_checksum", 0))
+    return [s.get("iterations", 0), s.get("hypothesis_steps", 0), s.get("finals", 0), s.get("open_left", 0),
+            s.get("score_ties", 0), s.get("near_ties", 0), ck - (1 << 64) if ck >= (1 << 63) else ck, s.get("fringe_peak", 1)]
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     from oracle import model as om, decoders as od
@@ -115,8 +123,7 @@ def main():
         stats = {}
         text, probs, score, _ = od.correct_lines(topo, w, mapping, lines, fast=False, greedy=False,
                                                  beam_params=params, stats=stats)
-        st = np.array([[s.get("iterations", 0), s.get("hypothesis_steps", 0), s.get("finals", 0), s.get("open_left", 0)]
-                       for s in stats["lines"]], np.int64)
+        st = np.array([stat_row(s) for s in stats["lines"]], np.int64)
         np.savez_compressed(os.path.join(GOLDEN, "beam_%s.npz" % case), lines=np.array(lines, dtype=object),
                             text=np.array(text, dtype=object), score=np.array(score, np.float64), stats=st,
                             probs=np.array([np.array(p, np.float32) for p in probs] + [None], dtype=object)[:-1])

@@ -11,6 +11,7 @@ import torch
 
 from oracle import decoders as od
 from tests.common import make_model, synthetic_lines, topo_dict, BEAM_CASES, GOLDEN_DIR
+from tests.make_golden import stat_row
 
 pytestmark = pytest.mark.gpu
 
@@ -44,7 +45,10 @@ def test_beam_golden(case, gemm_mode):
     for j, line in enumerate(lines):
         got = text[j] if lens[j] > 0 else line           # StopIteration fallback (seq2seq.py:826-836)
         assert got == want_text[j], "line %d: %r != %r (stats %s vs %s)" % (j, got, want_text[j], stats[j], want_stats[j])
-        assert (stats[j] == want_stats[j]).all(), "line %d stats %s != %s" % (j, stats[j], want_stats[j])
+        # iterations, hypothesis-steps, finals, open nodes, exact score ties, pop-order checksum, peak fringe length
+        # ([5], the near-tie count, is a diagnostic of each implementation's own arithmetic and is not compared)
+        for c in (0, 1, 2, 3, 4, 6, 7):
+            assert stats[j, c] == want_stats[j, c], "line %d stats %s != %s" % (j, stats[j], want_stats[j])
         if lens[j] > 0:
             assert abs(scores[j] - want_score[j]) < 1e-4
             assert np.abs(probs[j, :lens[j]] - np.asarray(want_probs[j], np.float32)).max() < 1e-4
@@ -68,7 +72,7 @@ def test_beam_alignments_and_overflow_retry():
                 continue
             s = st["lines"][k]
             k += 1
-            assert list(stats[j]) == [s["iterations"], s["hypothesis_steps"], s["finals"], s["open_left"]]
+            assert list(stats[j]) == stat_row(s)[:5] + [stats[j, 5]] + stat_row(s)[6:]
             got = text[j] if lens[j] > 0 else line
             assert got == r_text[j]
             if lens[j] > 0:
@@ -94,7 +98,7 @@ def test_beam_confmat_input_rejection_candidates():
     text, probs, scores, lens, _, stats = _run_beam(eng, mapping, conf, params, conf=conf)
     for j in range(len(page)):
         s = st["lines"][j]
-        assert list(stats[j]) == [s["iterations"], s["hypothesis_steps"], s["finals"], s["open_left"]]
+        assert list(stats[j, :5]) == stat_row(s)[:5] and list(stats[j, 6:]) == stat_row(s)[6:]
         if lens[j] > 0:
             assert text[j].replace('\a', '') == r_text[j]
             assert abs(scores[j] - r_score[j]) < 1e-4

@@ -73,11 +73,15 @@ def test_encoder_confidence_and_confmat_input():
     assert np.abs(enc_out.permute(1, 0, 2).cpu().numpy() - ref[0]).max() < TOL_H
 
 
+@pytest.mark.parametrize("gemm_mode", [1, 2])
 @pytest.mark.parametrize("name", ["c1", "c2s", "c4s"])
-def test_decoder_step_parity(name):
+def test_decoder_step_parity(name, gemm_mode):
+    """cor_decode_step on the exact FFMA path (1) and on the tcgen05 three-pass path (2), incl. the LM second
+    evaluation of the top cell (c4s)."""
     topo, w, mapping = make_model(name)
     lines = synthetic_lines(mapping, 6, 19, seed=5, min_length=8)
-    topo, w, mapping, x, ref, eng, enc_out, states = _encode_both(name, lines, 1)
+    topo, w, mapping, x, ref, eng, enc_out, states = _encode_both(name, lines, gemm_mode)
+    eng.kernel_counters(reset=True)
     B, T = x.shape[0], x.shape[1]
     d = topo.depth
     st = list(ref[1:])
@@ -96,6 +100,11 @@ def test_decoder_step_parity(name):
         if topo.lm_predict:
             assert np.abs(lm_out.cpu().numpy() - lm_ref).max() < TOL_P
         p, st = p_ref, st_ref
+    kinds = eng.kernel_counters()
+    if gemm_mode == 2:
+        assert kinds["ffma_lstm"] == 0 and kinds["tc_lstm_narrow"] + kinds["tc_lstm_single"] > 0, kinds
+    else:
+        assert kinds["ffma_lstm"] > 0 and kinds["tc_lstm_narrow"] + kinds["tc_lstm_single"] + kinds["tc_lstm_pair"] == 0, kinds
 
 
 def test_decoder_step_broadcast_line():

@@ -24,7 +24,7 @@ def test_header_symbols_are_exported():
     for n in names:
         assert hasattr(lib, n), n
         assert n in _lib.PROTOTYPES, "no ctypes prototype for " + n
-    assert lib.cor_abi_version() == 1
+    assert lib.cor_abi_version() == 2
 
 
 def test_product_fails_loudly_without_gpu():
