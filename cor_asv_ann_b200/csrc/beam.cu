@@ -132,9 +132,10 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     const uint32_t* ids = b.fr_id + ((size_t)cur * b.L + line) * b.cap;
     int first_final = 0x7fffffff, first_open = 0x7fffffff;
     int open_total = 0, consumed = 0, nfin = 0;
-    // order-sensitive checksum of the popped open hypotheses: sum over pops of (length << 16 | char + 1) * odd(pop index),
-    // pop index counted per line over the whole search -- what the oracle computes from its own beam lists
-    const unsigned long long pop0 = (unsigned long long)b.hyp_steps[line];
+    // checksum of WHICH hypotheses are expanded in WHICH iteration: sum over pops of (length << 16 | char + 1) * odd(iteration)
+    // -- what the oracle computes from its own beam lists.  The order inside one batch is left out on purpose: two
+    // hypotheses whose keys differ in the last bits may swap places there without any effect on the search.
+    const unsigned long long it_odd = 2ull * (unsigned long long)b.iter[line] + 1ull;
     unsigned long long csum = 0ull;
     for (int base = 0; base < len && open_total < b.batch; base += 32) {
         const int i = base + lane;
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
                 const size_t pg = (size_t)line * b.quota_x + (id - 1u) / KMAX;
                 x = ((unsigned long long)(b.rec_len[pg] + 1) << 16) + (unsigned long long)b.ch_v[pg * KMAX + (id - 1u) % KMAX] + 1ull;
             }
-            csum += x * (2ull * (pop0 + (unsigned long long)excl) + 1ull) * 0x9E3779B97F4A7C15ull;
+            csum += x * it_odd * 0x9E3779B97F4A7C15ull;
         }
         const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
         const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);

@@ -135,7 +135,7 @@ int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines,
  * [4] expanded hypotheses whose two best scores are EXACTLY equal (the argsort tie the reference leaves to numpy),
  * [5] near-tie ordering decisions (candidate order, beam-threshold cut or pop boundary within 1e-6 relative): where
  *     an fp32-grade implementation may legitimately search differently -- the ties the north star wants logged,
- * [6] order-sensitive checksum of the popped hypotheses (length, character, pop index; uint64 bit pattern),
+ * [6] checksum of which hypotheses (length, character) were expanded in which iteration (uint64 bit pattern),
  * [7] peak fringe length.  [0] is -1 for a line whose arena overflowed (internal, retried) and -2 for an empty line.
  * All HOST. */
 #define COR_BEAM_STATS 8

@@ -258,11 +258,11 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
         if len(finals) > beam_width_out and finals.nodes[-1].pro_cost() > beam[0].pro_cost():
             break
         if stats is not None:
-            # diagnostics the CUDA search reports as stats[5..7] (include/cor_b200.h): pop-boundary near-ties, an
-            # order-sensitive checksum of the popped hypotheses, the peak fringe length
+            # diagnostics the CUDA search reports as stats[5..7] (include/cor_b200.h): pop-boundary near-ties, a
+            # checksum of which hypotheses are expanded in which iteration, the peak fringe length
             for t, nd in enumerate(beam):
                 xx = (int(nd.length) << 16) + (c2i[nd.value] if nd.length > 1 else 0) + 1
-                pop_sum = (pop_sum + xx * (2 * (n_hyp + t) + 1) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+                pop_sum = (pop_sum + xx * (2 * n_iter + 1) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
             if len(fringe):
                 ka, kb = -fringe.keys[-1][0], -float(beam[-1].pro_cost())
                 if abs(ka - kb) <= 1e-6 * max(1.0, abs(ka)):

@@ -21,6 +21,18 @@ def _engine(topo, w, gemm_mode=0):
     return Engine(topo_dict(topo), w, device=0, eos_index=1, gemm_mode=gemm_mode)
 
 
+def _same_search(got, want, what):
+    """Iterations, hypothesis-steps, finals, open nodes, exact score ties and the peak fringe length must be identical.
+    The expansion checksum [6] (which hypotheses were expanded in which iteration) must be identical too, unless one of
+    the two searches logged a near-tie ([5]: an ordering decision within 1e-6 relative, which two fp32-grade
+    arithmetics may resolve differently): that is reported, not hidden."""
+    for c in (0, 1, 2, 3, 4, 7):
+        assert got[c] == want[c], "%s stats %s != %s" % (what, list(got), list(want))
+    if got[6] != want[6]:
+        assert got[5] > 0 or want[5] > 0, "%s: expansion checksum differs without a logged near-tie: %s != %s" % (what, list(got), list(want))
+        print("NOTE %s: expansion checksum differs at a logged near-tie (near-ties %d here, %d in the oracle)" % (what, got[5], want[5]))
+
+
 def _run_beam(eng, mapping, lines, params, want_align=False, budget=2 << 30, conf=None):
     from cor_asv_ann_b200.vectorize import lines_to_sparse
     idx, val = lines_to_sparse(mapping[0], lines, conf)
@@ -45,10 +57,7 @@ def test_beam_golden(case, gemm_mode):
     for j, line in enumerate(lines):
         got = text[j] if lens[j] > 0 else line           # StopIteration fallback (seq2seq.py:826-836)
         assert got == want_text[j], "line %d: %r != %r (stats %s vs %s)" % (j, got, want_text[j], stats[j], want_stats[j])
-        # iterations, hypothesis-steps, finals, open nodes, exact score ties, pop-order checksum, peak fringe length
-        # ([5], the near-tie count, is a diagnostic of each implementation's own arithmetic and is not compared)
-        for c in (0, 1, 2, 3, 4, 6, 7):
-            assert stats[j, c] == want_stats[j, c], "line %d stats %s != %s" % (j, stats[j], want_stats[j])
+        _same_search(stats[j], want_stats[j], "line %d" % j)
         if lens[j] > 0:
             assert abs(scores[j] - want_score[j]) < 1e-4
             assert np.abs(probs[j, :lens[j]] - np.asarray(want_probs[j], np.float32)).max() < 1e-4
@@ -72,7 +81,7 @@ def test_beam_alignments_and_overflow_retry():
                 continue
             s = st["lines"][k]
             k += 1
-            assert list(stats[j]) == stat_row(s)[:5] + [stats[j, 5]] + stat_row(s)[6:]
+            _same_search(stats[j], stat_row(s), "line %d" % j)
             got = text[j] if lens[j] > 0 else line
             assert got == r_text[j]
             if lens[j] > 0:
@@ -98,7 +107,7 @@ def test_beam_confmat_input_rejection_candidates():
     text, probs, scores, lens, _, stats = _run_beam(eng, mapping, conf, params, conf=conf)
     for j in range(len(page)):
         s = st["lines"][j]
-        assert list(stats[j, :5]) == stat_row(s)[:5] and list(stats[j, 6:]) == stat_row(s)[6:]
+        _same_search(stats[j], stat_row(s), "line %d" % j)
         if lens[j] > 0:
             assert text[j].replace('\a', '') == r_text[j]
             assert abs(scores[j] - r_score[j]) < 1e-4

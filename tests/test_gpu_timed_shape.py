@@ -185,8 +185,10 @@ def test_beam_competitive_one_call_pair_kernel():
     assert bad == 0
     assert tie_explained <= 2
 
-    # ---- every line against small calls (other tile shapes, other row capacities)
-    diff = 0
+    # ---- every line against 64-line calls: there the encoder is the persistent recurrence (mma.sync, another
+    # summation order), so the two runs are two fp32-grade arithmetics, like the product and the oracle: a search
+    # may differ only where one of them logged a near-tie
+    diff_text = diff_search = unexplained = 0
     for b0 in range(0, B, 64):
         sl = slice(b0, b0 + 64)
         c2, p2, s2, l2, _, st2 = (None if t is None else t.numpy() for t in
@@ -194,7 +196,13 @@ def test_beam_competitive_one_call_pair_kernel():
         for j in range(64):
             g = b0 + j
             n = int(l2[j])
-            if n != lens[g] or not (c2[j, :n] == chars[g, :n]).all() or not (st2[j] == stats[g]).all():
-                diff += 1
-    print("512-line call vs 64-line calls: %d lines differ" % diff)
-    assert diff <= 2
+            same_text = n == lens[g] and (c2[j, :n] == chars[g, :n]).all()
+            same_search = all(st2[j, c] == stats[g, c] for c in (0, 1, 2, 3, 4, 6, 7))
+            diff_text += not same_text
+            diff_search += not same_search
+            if not (same_text and same_search) and st2[j, 5] == 0 and stats[g, 5] == 0:
+                unexplained += 1
+    print("512-line call vs 64-line calls: %d of %d strings differ, %d searches differ, %d of them without a logged near-tie"
+          % (diff_text, B, diff_search, unexplained))
+    assert unexplained == 0
+    assert diff_text <= B // 20
