@@ -23,7 +23,7 @@ class CorLines(C.Structure):
 
 class CorBeamParams(C.Structure):
     _fields_ = [("batch_size", C.c_int32), ("beam_width_in", C.c_int32), ("beam_width_out", C.c_int32),
-                ("beam_threshold_in", C.c_double), ("rejection_threshold", C.c_double)]
+                ("n_best", C.c_int32), ("beam_threshold_in", C.c_double), ("rejection_threshold", C.c_double)]
 
 
 # name -> (restype, argtypes); every symbol include/cor_b200.h declares
@@ -36,6 +36,7 @@ PROTOTYPES = {
     "cor_model_destroy": (None, [C.c_void_p]),
     "cor_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "cor_encode": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cor_set_encoding": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "cor_decode_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p] + [C.c_void_p] * 9 + [C.c_void_p]),
     "cor_decode_greedy_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),
     "cor_correct_greedy_host": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),

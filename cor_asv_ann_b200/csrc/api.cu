@@ -280,10 +280,28 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
 
 // ------------------------------------------------------------------ encoder
 // seq2seq.py:237-314.  Per layer and direction: one GEMM+LSTM launch per timestep over all rows.
+// Encoder results handed in through cor_set_encoding: enc_out [T][B][D] and states [2d][B][W] (the layouts
+// cor_encode returns) become the workspace's line-major (hi, lo) enc_out, the per-layer initial decoder states
+// and u = enc_out . U -- everything the decoders read, without running the encoder graph.
+static int import_encoding(cor_model* m, const Ws& ws, cudaStream_t st) {
+    const int B = ws.B, T = ws.T, W = m->W, D = m->D;
+    COR_CHECK(m->preset.n_rows == B && m->preset.t_max == T, "the preset encoding has another geometry than this call");
+    if (launch_split_tl(st, m->preset.enc_out, ws.enc_out(), ws.enc_out_lo(), B, T, D)) return 1;
+    const size_t BW = (size_t)B * W;
+    for (int n = 0; n < m->d; ++n) {
+        COR_CUDA(cudaMemcpyAsync(ws.st_h[n], m->preset.states + (size_t)(2 * n) * BW, BW * 4, cudaMemcpyDeviceToDevice, st));
+        COR_CUDA(cudaMemcpyAsync(ws.st_c[n], m->preset.states + (size_t)(2 * n + 1) * BW, BW * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    GemmSeg su = {ws.enc_out(), D, ws.enc_out_lo(), m->U.hi, m->U.ld, m->U.lo, D};
+    StoreEpi eu{ws.u, W, nullptr, nullptr, 0};
+    return gemm_store(m, st, T * B, nullptr, W, &su, 1, eu);
+}
+
 int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
     const int W = m->W, d = m->d, B = ws.B, T = ws.T;
     const bool deep = m->cfg.deep_bidirectional_encoder != 0;
     if (launch_live_rows(st, ws.idx, ws.val, B, T, ws.k, ws.live)) return 1;
+    if (m->preset.enc_out) return import_encoding(m, ws, st);
     if (!m->use_xtab && launch_embed(st, ws.idx, ws.val, ws.row_T, B, T, ws.k, m->E_full, W, m->V, ws.X, ws.X_lo, ws.Xr, ws.Xr_lo)) return 1;
     const size_t BW = (size_t)B * W;
     for (int n = 0; n < d; ++n) {
@@ -814,6 +832,14 @@ void cor_model_destroy(cor_model* m) {
     if (m->prof.rows) cudaFreeHost(m->prof.rows);
     tc_ctx_release(&m->ctx);
     delete m;
+}
+
+int cor_set_encoding(cor_model* m, int n_rows, int t_max, const float* enc_out, const float* states) {
+    COR_CHECK(m && m->finalized, "model not finalized");
+    COR_CHECK((enc_out == nullptr) == (states == nullptr), "enc_out and states must both be given or both be NULL");
+    COR_CHECK(!enc_out || (n_rows > 0 && t_max > 0), "empty geometry");
+    m->preset.enc_out = enc_out; m->preset.states = states; m->preset.n_rows = n_rows; m->preset.t_max = t_max;
+    return 0;
 }
 
 int cor_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt, int want_alignments, size_t* bytes) {

@@ -40,6 +40,7 @@ constexpr int MAX_NEW = 4096;        // batch_size (<= 256) * KMAX
 constexpr int ST_ACTIVE = 0, ST_DONE = 1, ST_OVERFLOW = 2, ST_EMPTY = 3;
 constexpr uint32_t FINAL_BIT = 0x80000000u;
 constexpr int kStats = 8;            // int64 statistics per line (include/cor_b200.h)
+constexpr int FMAX = 64;             // final hypotheses kept per line for the n-best read-out (COR_BEAM_NBEST_MAX)
 
 struct BeamDev {
     // geometry and parameters
@@ -57,6 +58,9 @@ struct BeamDev {
     // diagnostics per line (stats[4..7]): exact top-2 score ties, near-tie ordering decisions, order-sensitive checksum of
     // the popped hypotheses, peak fringe length
     long long *score_ties, *near_ties; unsigned long long* pop_sum; int32_t* fr_peak;
+    // final hypotheses in pop order, the first FMAX of them (decode_sequence_beam yields every final, best first)
+    uint32_t* fin_id; double* fin_key; int n_best;
+    int32_t* r_chars; float* r_probs; double* r_score; int32_t* r_len;      // result staging [L][n_best][...]
     double* fr_key; uint32_t* fr_id;       // [2][L][cap]
     uint32_t* beam_nodes;                  // [L][batch]
     int32_t* rej_table;                    // [L][T]
@@ -137,6 +141,7 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     // hypotheses whose keys differ in the last bits may swap places there without any effect on the search.
     const unsigned long long it_odd = 2ull * (unsigned long long)b.iter[line] + 1ull;
     unsigned long long csum = 0ull;
+    const int fc0 = b.finals_count[line];
     for (int base = 0; base < len && open_total < b.batch; base += 32) {
         const int i = base + lane;
         const bool valid = i < len;
@@ -158,6 +163,10 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
         }
         const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
         const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);
+        if (take && fin) {       // n-best read-out: the finals in pop order (finals_count is only written by lane 0 below)
+            const int slot = fc0 + nfin + __popc(t_fin & ((1u << lane) - 1u));
+            if (slot < FMAX) { b.fin_id[(size_t)line * FMAX + slot] = id & ~FINAL_BIT; b.fin_key[(size_t)line * FMAX + slot] = keys[i]; }
+        }
         if (t_open && first_open == 0x7fffffff) first_open = base + __ffs(t_open) - 1;
         if (t_fin && first_final == 0x7fffffff) first_final = base + __ffs(t_fin) - 1;
         consumed += __popc(t_open | t_fin);
@@ -168,7 +177,7 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     for (int o = 16; o > 0; o >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, o);
     if (lane != 0) return;
     const int count = min(open_total, b.batch);
-    int fc = b.finals_count[line] + nfin;
+    int fc = fc0 + nfin;
     double bk = b.best_key[line];
     if (nfin > 0) {
         const double kf = keys[first_final];
@@ -915,37 +924,62 @@ __global__ void __launch_bounds__(256) beam_push_kernel(BeamDev b) {
 // ------------------------------------------------------------------ finish: best final hypothesis per line (:1538-1544)
 __global__ void __launch_bounds__(128) beam_finish_kernel(BeamDev b, int32_t* o_chars, float* o_probs, double* o_score,
                                                           int32_t* o_len, float* o_align, long long* o_stats) {
+    // Slot (line, r) of the outputs holds the r-th best final hypothesis, r < n_best; unused slots have length 0.
     const int line = blockIdx.x, tid = threadIdx.x;
-    const int S = 2 * b.T;
-    __shared__ int s_n;
+    const int S = 2 * b.T, N = b.n_best;
+    __shared__ int s_n[FMAX];
+    __shared__ uint32_t s_fin[FMAX];
     const int st = b.status[line];
-    const int best = b.best_final[line];
     if (tid == 0) {
-        int n = 0;
-        if (st != ST_OVERFLOW && st != ST_EMPTY && best > 0) {
-            // walk to the root, then reverse in place
-            uint32_t node = (uint32_t)best;
-            const size_t g0 = (size_t)line * b.quota_x + (node - 1u) / KMAX;
-            const int length = b.rec_len[g0] + 1;
-            n = length - 1;
-            o_score[line] = b.ch_cum[g0 * KMAX + (node - 1u) % KMAX] / (double)(length - 1);
-            int i = n - 1;
-            while (node != 0u && i >= 0) {
-                const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
-                const int k = (int)((node - 1u) % KMAX);
-                o_chars[(size_t)line * S + i] = b.ch_v[g * KMAX + k];
-                o_probs[(size_t)line * S + i] = b.ch_p[g * KMAX + k];
-                if (o_align) {      // temporarily keep the node id in the first cell of its alignment row
-                    reinterpret_cast<uint32_t*>(o_align)[((size_t)line * S + i) * b.T] = node;
+        int nf = 0;
+        if (st != ST_OVERFLOW && st != ST_EMPTY && b.best_final[line] > 0) {
+            if (N == 1) {
+                s_fin[0] = (uint32_t)b.best_final[line]; nf = 1;
+            } else {
+                // the recorded finals, best first: ascending (key, id) like the reference's final_beam read from its best end
+                const int have = min(b.finals_count[line], FMAX);
+                uint32_t* fid = b.fin_id + (size_t)line * FMAX; double* fk = b.fin_key + (size_t)line * FMAX;
+                for (int i = 1; i < have; ++i) {
+                    const double k = fk[i]; const uint32_t id = fid[i];
+                    int j = i - 1;
+                    while (j >= 0 && key_less(k, id, fk[j], fid[j])) { fk[j + 1] = fk[j]; fid[j + 1] = fid[j]; --j; }
+                    fk[j + 1] = k; fid[j + 1] = id;
                 }
-                node = b.rec_parent[g];
-                --i;
+                nf = min(have, N);
+                for (int r = 0; r < nf; ++r) s_fin[r] = fid[r];
+                // more than FMAX finals: the best one is tracked on its own and always comes first
+                if (nf > 0 && s_fin[0] != (uint32_t)b.best_final[line] && b.finals_count[line] > FMAX) {
+                    for (int r = nf - 1; r > 0; --r) s_fin[r] = s_fin[r - 1];
+                    s_fin[0] = (uint32_t)b.best_final[line];
+                }
             }
-        } else {
-            o_score[line] = 0.0;
         }
-        o_len[line] = n;
-        s_n = n;
+        for (int r = 0; r < N; ++r) {
+            const size_t slot = (size_t)line * N + r;
+            int n = 0;
+            o_score[slot] = 0.0;
+            if (r < nf) {
+                // walk to the root, filling the slot from its end
+                uint32_t node = s_fin[r];
+                const size_t g0 = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+                const int length = b.rec_len[g0] + 1;
+                n = length - 1;
+                o_score[slot] = b.ch_cum[g0 * KMAX + (node - 1u) % KMAX] / (double)(length - 1);
+                int i = n - 1;
+                while (node != 0u && i >= 0) {
+                    const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+                    const int k = (int)((node - 1u) % KMAX);
+                    o_chars[slot * S + i] = b.ch_v[g * KMAX + k];
+                    o_probs[slot * S + i] = b.ch_p[g * KMAX + k];
+                    if (o_align)        // temporarily keep the node id in the first cell of its alignment row
+                        reinterpret_cast<uint32_t*>(o_align)[(slot * S + i) * b.T] = node;
+                    node = b.rec_parent[g];
+                    --i;
+                }
+            }
+            o_len[slot] = n;
+            s_n[r] = n;
+        }
         long long* os = o_stats + (size_t)line * kStats;
         os[0] = st == ST_OVERFLOW ? -1 : (st == ST_EMPTY ? -2 : b.iter[line]);
         os[1] = b.hyp_steps[line];
@@ -958,17 +992,18 @@ __global__ void __launch_bounds__(128) beam_finish_kernel(BeamDev b, int32_t* o_
     }
     __syncthreads();
     if (!o_align) return;
-    for (int i = 0; i < s_n; ++i) {
-        float* row = o_align + ((size_t)line * S + i) * b.T;
-        const uint32_t node = reinterpret_cast<uint32_t*>(row)[0];
-        __syncthreads();
-        const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
-        const bool rej = b.ch_rej[g * KMAX + (node - 1u) % KMAX] != 0;
-        const int pos = b.rec_pos[g];
-        const float* ra = b.rec_a + g * b.T;
-        for (int j = tid; j < b.T; j += 128) row[j] = rej ? (j == pos ? 1.0f : 0.0f) : ra[j];   // np.eye(T)[pos] (:1494-1495)
-        __syncthreads();
-    }
+    for (int r = 0; r < N; ++r)
+        for (int i = 0; i < s_n[r]; ++i) {
+            float* row = o_align + (((size_t)line * N + r) * S + i) * b.T;
+            const uint32_t node = reinterpret_cast<uint32_t*>(row)[0];
+            __syncthreads();
+            const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
+            const bool rej = b.ch_rej[g * KMAX + (node - 1u) % KMAX] != 0;
+            const int pos = b.rec_pos[g];
+            const float* ra = b.rec_a + g * b.T;
+            for (int j = tid; j < b.T; j += 128) row[j] = rej ? (j == pos ? 1.0f : 0.0f) : ra[j];   // np.eye(T)[pos] (:1494-1495)
+            __syncthreads();
+        }
 }
 
 // ------------------------------------------------------------------ workspace layout of one wave
@@ -1024,7 +1059,12 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     b->counters = c.take<int32_t>(4);
     b->heavy = c.take<int32_t>(L);
     b->o_stats = c.take<long long>((size_t)L * kStats);
-    b->o_align = want_align ? c.take<float>((size_t)L * 2 * T * T) : nullptr;
+    const int NB = std::max(1, std::min(bp->n_best, FMAX));
+    b->n_best = NB;
+    b->fin_id = c.take<uint32_t>((size_t)L * FMAX); b->fin_key = c.take<double>((size_t)L * FMAX);
+    b->r_chars = c.take<int32_t>((size_t)L * NB * 2 * T); b->r_probs = c.take<float>((size_t)L * NB * 2 * T);
+    b->r_score = c.take<double>((size_t)L * NB); b->r_len = c.take<int32_t>((size_t)L * NB);
+    b->o_align = want_align ? c.take<float>((size_t)L * NB * 2 * T * T) : nullptr;
     const size_t G = (size_t)L * quota_x;
     b->rec_p = c.take<float>(G * Vp); b->rec_h = c.take<float>(G * d * W); b->rec_c = c.take<float>(G * d * W);
     b->rec_a = c.take<float>(G * T);
@@ -1098,6 +1138,7 @@ int check_params(const cor_model* m, const cor_beam_params* bp) {
     COR_CHECK(bp->batch_size >= 1 && bp->batch_size <= 256, "batch_size must be in 1..256");
     COR_CHECK(bp->beam_width_in >= 1 && bp->beam_width_in <= KMAX - 1, "beam_width_in must be in 1..15");
     COR_CHECK(bp->beam_width_out >= 0, "beam_width_out must be non-negative");
+    COR_CHECK(bp->n_best >= 0 && bp->n_best <= FMAX, "n_best must be in 0..64");
     COR_CHECK(m->d <= 8, "depth above 8 is not supported");
     return 0;
 }
@@ -1155,9 +1196,9 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         ctx().launches += 3;
         COR_CUDA(cudaGetLastError());
     }
-    // results: staged in the encoder workspace's output slots and the wave's own staging buffers
-    const size_t S = 2 * (size_t)T;
-    int32_t* d_chars = ws.o_chars; float* d_probs = ws.o_probs; double* d_score = ws.o_score; int32_t* d_len = ws.o_len;
+    // results: staged in the wave's own buffers, n_best slots per line
+    const size_t S = 2 * (size_t)T * b.n_best;
+    int32_t* d_chars = b.r_chars; float* d_probs = b.r_probs; double* d_score = b.r_score; int32_t* d_len = b.r_len;
     float* d_align = b.o_align;
     COR_CUDA(cudaMemsetAsync(d_chars, 0, (size_t)L * S * 4, st));
     COR_CUDA(cudaMemsetAsync(d_probs, 0, (size_t)L * S * 4, st));
@@ -1166,8 +1207,8 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     COR_CUDA(cudaGetLastError());
     COR_CUDA(cudaMemcpyAsync(o_chars, d_chars, (size_t)L * S * 4, kout, st));
     COR_CUDA(cudaMemcpyAsync(o_probs, d_probs, (size_t)L * S * 4, kout, st));
-    COR_CUDA(cudaMemcpyAsync(o_scores, d_score, (size_t)L * 8, kout, st));
-    COR_CUDA(cudaMemcpyAsync(o_len, d_len, (size_t)L * 4, kout, st));
+    COR_CUDA(cudaMemcpyAsync(o_scores, d_score, (size_t)L * b.n_best * 8, kout, st));
+    COR_CUDA(cudaMemcpyAsync(o_len, d_len, (size_t)L * b.n_best * 4, kout, st));
     COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * kStats * 8, kout, st));
     COR_CUDA(cudaMemcpyAsync(host_stats, b.o_stats, (size_t)L * kStats * 8, cudaMemcpyDeviceToHost, st));
     if (o_align) COR_CUDA(cudaMemcpyAsync(o_align, d_align, (size_t)L * S * T * 4, kout, st));
@@ -1221,7 +1262,8 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
     COR_CUDA(cudaSetDevice(m->device));
     COR_CUDA(cudaFuncSetAttribute(beam_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
     const int B = hl->n_rows, T = hl->t_max, k = hl->k_alt;
-    const size_t S = 2 * (size_t)T, tk = (size_t)T * k;
+    const int NB = std::max(1, bp->n_best);                  // result slots per line
+    const size_t S = 2 * (size_t)T * NB, tk = (size_t)T * k;
     auto xcopy = [&](void* dst, const void* src, size_t bytes) -> int {
         if (!on_device) { memcpy(dst, src, bytes); return 0; }
         COR_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st));
@@ -1248,7 +1290,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                 int32_t* ix = (int32_t*)stage.take((size_t)L * tk * 4);
                 float* vl = hl->val ? (float*)stage.take((size_t)L * tk * 4) : nullptr;
                 w_chars = (int32_t*)stage.take((size_t)L * S * 4); w_probs = (float*)stage.take((size_t)L * S * 4);
-                w_scores = (double*)stage.take((size_t)L * 8); w_len = (int32_t*)stage.take((size_t)L * 4);
+                w_scores = (double*)stage.take((size_t)L * NB * 8); w_len = (int32_t*)stage.take((size_t)L * NB * 4);
                 w_stats = (int64_t*)stage.take((size_t)L * kStats * 8);
                 w_align = out_align ? (float*)stage.take((size_t)L * S * T * 4) : nullptr;
                 COR_CHECK(rT && ix && (vl || !hl->val) && w_chars && w_probs && w_scores && w_len && w_stats && (w_align || !out_align),
@@ -1271,7 +1313,8 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                 if (direct) continue;
                 if (xcopy(out_chars + (size_t)dst * S, w_chars + (size_t)j * S, S * 4) ||
                     xcopy(out_probs + (size_t)dst * S, w_probs + (size_t)j * S, S * 4) ||
-                    xcopy(out_scores + dst, w_scores + j, 8) || xcopy(out_len + dst, w_len + j, 4) ||
+                    xcopy(out_scores + (size_t)dst * NB, w_scores + (size_t)j * NB, (size_t)NB * 8) ||
+                    xcopy(out_len + (size_t)dst * NB, w_len + (size_t)j * NB, (size_t)NB * 4) ||
                     xcopy(stats + (size_t)dst * kStats, w_stats + (size_t)j * kStats, kStats * 8)) return 1;
                 if (out_align && xcopy(out_align + (size_t)dst * S * T, w_align + (size_t)j * S * T, S * T * 4)) return 1;
             }

@@ -199,6 +199,7 @@ int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, 
 int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n);
 int launch_join(cudaStream_t st, const float* hi, const float* lo, float* out, size_t n);
 int launch_join_lt(cudaStream_t st, const float* hi, const float* lo, float* out, int L, int T, int D);   // line-major (hi, lo) -> time-major fp32
+int launch_split_tl(cudaStream_t st, const float* in, float* hi, float* lo, int L, int T, int D);         // time-major fp32 -> line-major (hi, lo)
 int launch_finish_scores(cudaStream_t st, double* score_sum, const int32_t* len, int R);
 int launch_live_rows(cudaStream_t st, const int32_t* idx, const float* val, int n_rows, int t_max, int k_alt, uint8_t* live);
 

@@ -264,6 +264,15 @@ __global__ void join_lt_kernel(const float* __restrict__ hi, const float* __rest
     }
 }
 
+// hi/lo[l][t][:] (line-major, internal) = in[t][l][:] (fp32, time-major: the C-ABI layout of cor_encode)
+__global__ void split_tl_kernel(const float* __restrict__ in, float* hi, float* lo, int L, int T, int D) {
+    const size_t n = (size_t)L * T * D;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int dd = (int)(i % D); const size_t lt = i / D; const int t = (int)(lt % T), l = (int)(lt / T);
+        store_split(hi, lo, i, in[((size_t)t * L + l) * D + dd]);
+    }
+}
+
 __global__ void finish_scores_kernel(double* score_sum, const int32_t* len, int R) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < R && len[r] > 0) score_sum[r] /= (double)len[r];
@@ -348,6 +357,16 @@ int launch_join_lt(cudaStream_t st, const float* hi, const float* lo, float* out
     if (!n) return 0;
     int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
     join_lt_kernel<<<blocks, 256, 0, st>>>(hi, lo, out, L, T, D);
+    ++ctx().launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_split_tl(cudaStream_t st, const float* in, float* hi, float* lo, int L, int T, int D) {
+    const size_t n = (size_t)L * T * D;
+    if (!n) return 0;
+    int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+    split_tl_kernel<<<blocks, 256, 0, st>>>(in, hi, lo, L, T, D);
     ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;

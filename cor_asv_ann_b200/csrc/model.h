@@ -70,6 +70,9 @@ struct cor_model {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cor::Mat LowCat, TopCat;  // page decoder (decpage.cu): [E.Kx | R] and [Kx | Kc | R] concatenated along K (depth 2 only)
     unsigned* grid_bar = nullptr;         // grid barrier counter of the persistent recurrence (recur.cu)
+    // cor_set_encoding: encoder results handed in by the caller (decode_sequence_*(encoder_outputs=...),
+    // decoder_model.predict_on_batch); while set, run_encoder imports them instead of running the encoder graph
+    struct { const float* enc_out = nullptr; const float* states = nullptr; int n_rows = 0, t_max = 0; } preset;
     float* b_UW = nullptr;    // [W]
     float* v_a = nullptr;     // [W]
     float b_v = 0.f;

@@ -103,6 +103,20 @@ class Engine:
         self._geom = (B, T, k, bool(want_align))
         return enc_out, states
 
+    def set_encoding(self, enc_out=None, states=None):
+        """Install (or, without arguments, remove) encoder results to be imported instead of running the encoder:
+        enc_out [T,B,D], states [2d,B,W] float32 device tensors (cor_set_encoding); kept alive by this object."""
+        if enc_out is None:
+            check(self.lib.cor_set_encoding(self.handle, 0, 0, None, None))
+            self._preset = None
+            return
+        enc_out = enc_out.to(self.device, torch.float32).contiguous()
+        states = states.to(self.device, torch.float32).contiguous()
+        T, B, D = enc_out.shape
+        assert D == self.D and tuple(states.shape) == (2 * self.d, B, self.W), (enc_out.shape, states.shape)
+        self._preset = (enc_out, states)
+        check(self.lib.cor_set_encoding(self.handle, B, T, _ptr(enc_out), _ptr(states)))
+
     # ------------------------------------------------------------------ one decoder step
     def decode_step(self, p_in, h_in, c_in, a_in, row_line=None):
         """p_in [R,V], h_in/c_in [d,R,W], a_in [R,T] -> (p, lm or None, h, c, a)."""
@@ -168,8 +182,8 @@ class Engine:
 
     # ------------------------------------------------------------------ beam
     def beam_params(self, batch_size=256, beam_width_in=15, beam_threshold_in=0.2, beam_width_out=16,
-                    rejection_threshold=0.3):
-        return CorBeamParams(int(batch_size), int(beam_width_in), int(beam_width_out),
+                    rejection_threshold=0.3, n_best=1):
+        return CorBeamParams(int(batch_size), int(beam_width_in), int(beam_width_out), int(n_best),
                              float(beam_threshold_in), float(rejection_threshold or 0.0))
 
     def correct_beam_host(self, idx, val, row_T, bp, want_align=False, budget_bytes=32 << 30, out=None):
@@ -180,11 +194,13 @@ class Engine:
         ws = self._workspace(n.value)
         if out is None:
             pin = True
-            out = (torch.empty((B, 2 * T), dtype=torch.int32, pin_memory=pin),
-                   torch.empty((B, 2 * T), dtype=torch.float32, pin_memory=pin),
-                   torch.empty((B,), dtype=torch.float64, pin_memory=pin),
-                   torch.empty((B,), dtype=torch.int32, pin_memory=pin),
-                   torch.empty((B, 2 * T, T), dtype=torch.float32, pin_memory=pin) if want_align else None,
+            N = max(1, int(bp.n_best))
+            slots = (B,) if N == 1 else (B, N)       # n_best > 1: N result slots per line, best first (length 0 = unused)
+            out = (torch.empty(slots + (2 * T,), dtype=torch.int32, pin_memory=pin),
+                   torch.empty(slots + (2 * T,), dtype=torch.float32, pin_memory=pin),
+                   torch.empty(slots, dtype=torch.float64, pin_memory=pin),
+                   torch.empty(slots, dtype=torch.int32, pin_memory=pin),
+                   torch.empty(slots + (2 * T, T), dtype=torch.float32, pin_memory=pin) if want_align else None,
                    torch.empty((B, BEAM_STATS), dtype=torch.int64, pin_memory=pin))
         chars, probs, scores, lens, align, stats = out
         lines = CorLines(B, T, k, _ptr(row_T), _ptr(idx), _ptr(val))

@@ -12,8 +12,10 @@ Python loops around it cost more than the GPU work.  Here
   one (the ctypes call releases the GIL);
 * result strings are built by one table lookup over the whole (B,S) index array.
 """
+import pickle
 import queue
 import threading
+import unicodedata
 
 import numpy as np
 
@@ -68,14 +70,16 @@ class StringTable:
         return [text[e - c:e] for c, e in zip(counts.tolist(), ends.tolist())]
 
 
-def float32_mean_neglog(probs_row):
-    """decode_sequence_greedy's score (seq2seq.py:1312, 1343, 1352): the float32 running sum of
-    -log p in output order, divided by the number of characters.  cumsum adds strictly left to right
-    in float32, i.e. exactly the reference's ``score += -np.log(p)`` chain."""
+def greedy_line_score(probs_row):
+    """decode_sequence_greedy's score (seq2seq.py:1318, 1330, 1341, 1353): ``decoded_score = 0`` then
+    ``decoded_score += -np.log(prob)`` with float32 terms.  Under the reference's pinned numpy (< 1.24, legacy
+    promotion) ``int + np.float32`` is a float64, so the running sum is float64 from the first character on:
+    float32 logarithms, added left to right in float64 (cumsum is strictly sequential), divided by the number
+    of characters."""
     p = np.asarray(probs_row, dtype=np.float32)
     if not len(p):
         return 0
-    return np.cumsum(-np.log(p), dtype=np.float32)[-1] / len(p)
+    return np.cumsum(-np.log(p), dtype=np.float64)[-1] / len(p)
 
 
 class Prefetcher:
@@ -131,3 +135,85 @@ def chunked(iterable, n):
             chunk = []
     if chunk:
         yield chunk
+
+
+# ----------------------------------------------------------------------------- line files -> reference batches
+
+class LineFiles:
+    """The line stream of ``Sequence2Sequence.gen_lines`` (ocrd_cor_asv_ann/lib/seq2seq.py:919-1018) as a reader
+    object: records come out of ``records()`` one at a time (text files are streamed, pickles are loaded once),
+    ``batches()`` groups them the way the reference's consumers expect.
+
+    File formats: text files hold ``source<TAB>target`` lines (or plain lines when ``unsupervised``); ``*.pkl``
+    files hold (source, target) pairs whose source is a string, a list of (char, prob) tuples or a confusion
+    network (list of chunks of (string, prob) alternatives) and already ends in a newline.
+    """
+
+    SPLIT_RATIO = 0.2       # share of the lines that belongs to the validation generator (seq2seq.py:927)
+
+    def __init__(self, filenames, split=None, train=False, unsupervised=False, charmap=None, reject=None):
+        self.filenames = list(filenames)
+        self.split = split if isinstance(split, np.ndarray) else None
+        self.train, self.unsupervised = train, unsupervised
+        self.table = str.maketrans(charmap) if charmap else None
+        self.reject = reject            # callable(source, target) -> True to drop a training pair (bad OCR)
+        self.soft = False               # the file being read carries confidences
+
+    @staticmethod
+    def _from_pickle(item):
+        source, target = item
+        if not source:
+            text, conf = '', []
+        elif type(source[0]) is tuple:                  # one (char, prob) per position
+            conf = [p for _, p in source]
+            text = ''.join(c for c, _ in source)
+        else:                                           # confusion network: first alternative of every chunk
+            conf = source
+            text = ''.join(chunk[0][0] if chunk else '' for chunk in source)
+        if not text.endswith('\n'):                     # degenerate entry: becomes an empty line
+            text, conf = '\n', [[('\n', 1.0)]]
+        return text, conf, target
+
+    def _from_text(self, line):
+        if self.unsupervised and '\t' not in line:
+            return line, None, line
+        source, target = line.split('\t')
+        return source + '\n', None, target             # the file iterator left the newline on the target
+
+    def records(self):
+        """(source text, source confidences or None, target text, filename) per usable line, in file order."""
+        for filename in self.filenames:
+            self.soft = filename.endswith('.pkl')
+            with open(filename, 'rb' if self.soft else 'r') as handle:
+                items = pickle.load(handle) if self.soft else handle
+                for line_no, item in enumerate(items):
+                    if self.split is not None and (self.split[line_no] < self.SPLIT_RATIO) == self.train:
+                        continue                        # this line belongs to the other generator
+                    source, conf, target = self._from_pickle(item) if self.soft else self._from_text(item)
+                    if self.unsupervised:
+                        target = source
+                    if self.table:
+                        source, target = source.translate(self.table), target.translate(self.table)
+                    source = unicodedata.normalize('NFC', source)
+                    target = unicodedata.normalize('NFC', target)
+                    if self.train and self.reject is not None and self.reject(source, target):
+                        continue
+                    yield source, conf, target, filename
+
+    def batches(self, batch_size, pad_last):
+        """4-tuples (sources, confidences or None, targets, filenames) of ``batch_size`` lines; the remainder is
+        padded with empty lines when ``pad_last``, dropped otherwise (seq2seq.py:997-1017)."""
+        src, cnf, tgt, names = [], [], [], []
+        for source, conf, target, filename in self.records():
+            src.append(source)
+            tgt.append(target)
+            names.append(filename)
+            if self.soft:
+                cnf.append(conf)
+            if len(src) == batch_size:
+                yield src, (cnf if self.soft else None), tgt, names
+                src, cnf, tgt, names = [], [], [], []
+        if src and pad_last:
+            pad = batch_size - len(src)
+            yield (src + [''] * pad, (cnf + [[] for _ in range(batch_size - len(cnf))]) if self.soft else None,
+                   tgt + [''] * pad, names + [None] * pad)

@@ -6,18 +6,18 @@ Mirrors the reference class (/root/reference/ocrd_cor_asv_ann/lib/seq2seq.py:108
 inference path: same attribute names, method signatures, return types and error behaviour, so that
 ``cor-asv-ann-proc`` / ``-eval`` and ``ocrd-cor-asv-ann-process`` can import this class instead.
 All arithmetic runs in libcor_b200.so (CUDA, sm_100a) through ``engine.Engine``; there is no CPU
-fallback — decoding without a CUDA device raises.  Training (``train``) is out of scope
-(DESIGN.md), ``evaluate`` needs the reference's own ``alignment`` module.
+fallback — decoding without a CUDA device raises.  ``evaluate`` runs its string metrics
+(``metrics.py``) on host processes beside the GPU.
 """
 import logging
-import pickle
-import unicodedata
+import math
+import os
 
 import numpy as np
 
 from . import h5lite
 from .vectorize import lines_to_sparse, dense_to_sparse
-from .pipeline import StringTable, Prefetcher, chunked, float32_mean_neglog, merge_batches
+from .pipeline import StringTable, Prefetcher, chunked, greedy_line_score, merge_batches, LineFiles
 
 GAP = '\a'  # reserved for gap in input (seq2seq.py:29)
 
@@ -94,7 +94,8 @@ class Sequence2Sequence(object):
         self.encoder_decoder_model = None
         self.encoder_model = None
         self.decoder_model = None
-        self.aligner = None
+        from .metrics import Alignment
+        self.aligner = Alignment(0, logger=self.logger)  # aligner (for training) with internal state (:177)
         self.progbars = progbars
         self.status = 0  # empty / configured / trained?
         ### engine
@@ -103,6 +104,7 @@ class Sequence2Sequence(object):
         self.beam_budget_bytes = 8 << 30
         self.superbatch = 64     # reference batches per engine call in predict() (16 384 lines at batch_size 256)
         self.prefetch = True     # read + encode the next super-batch in a worker thread
+        self.metric_workers = min(8, os.cpu_count() or 1)   # host processes for evaluate()'s string alignments
         self._weights = {}
         self._engine = None
 
@@ -183,7 +185,8 @@ class Sequence2Sequence(object):
         enc = [n for n in names if n.startswith(('char_input', 'encoder_lstm', 'bridge'))]
         self.encoder_decoder_model = _Model(self, 'encoder_decoder_model', names)
         self.encoder_model = _Model(self, 'encoder_model', enc, predict=self._predict_encoder)
-        self.decoder_model = _Model(self, 'decoder_model', [n for n in names if n not in enc or n.startswith('char_input')])
+        self.decoder_model = _Model(self, 'decoder_model', [n for n in names if n not in enc or n.startswith('char_input')],
+                                    predict=self._predict_decoder)
         self.graph = object()
         self.status = 1
 
@@ -368,75 +371,103 @@ class Sequence2Sequence(object):
 
     def evaluate(self, filenames, fast=False, normalization='historic_latin', charmap=None, gt_level=1,
                  confusion=10, histogram=True):
-        raise NotImplementedError('evaluate() needs the reference\'s alignment module (uniseg/rapidfuzz), which is '
-                                  'outside the neural hot path; use predict()/correct_lines() and score externally')
+        '''evaluate model on text files (seq2seq.py:651-754): character and word error rates of the OCR input
+        and of the greedy and beamed predictions against the ground truth, confusion tables, histograms and
+        perplexities, logged like the reference does.
+
+        Same batches, lines and numbers as the reference's loop.  `superbatch` reference batches share one
+        engine call, and the string metrics of a group (difflib alignments, pure Python) run on
+        `metric_workers` host processes while the GPU decodes the next group; they are folded into the running
+        statistics in line order, so the order-dependent recurrences give the reference's values.  The final
+        figures are also kept in ``self.last_evaluation``.'''
+        assert self.status == 2
+        from .metrics import Alignment, Edits, LineScorer
+        kinds = ('origin', 'greedy', 'beamed')
+        counts = {lv + '_' + k: Edits(self.logger, histogram=histogram and lv == 'c') for lv in 'cw' for k in kinds}
+        aligners = {lv + '_' + k: Alignment(0, logger=self.logger, confusion=confusion > 0 and lv == 'c')
+                    for lv in 'cw' for k in kinds}
+        scorer = LineScorer(self.metric_workers)
+
+        def fold(group, greedy, beamed, results):
+            rows = iter(results())
+            for batch, res_g, res_b in zip(group, greedy, beamed):
+                lines_source, _, lines_target, _ = batch
+                for j in range(len(lines_source)):
+                    if not lines_source[j] or not lines_target[j]:
+                        continue  # from partially filled batch
+                    self.logger.info('Source input              : %s', lines_source[j].rstrip(u'\n'))
+                    self.logger.info('Target output             : %s', lines_target[j].rstrip(u'\n'))
+                    self.logger.info('Target prediction (greedy): %s [%.2f]', res_g[0][j].rstrip(u'\n'), res_g[2][j])
+                    self.logger.info('Target prediction (beamed): %s [%.2f]', res_b[0][j].rstrip(u'\n'), res_b[2][j])
+                    row = next(rows)
+                    for name in ('c_origin', 'c_greedy', 'c_beamed', 'w_origin', 'w_greedy', 'w_beamed'):
+                        dist, length, seq1, seq2, conf = row[name]
+                        if conf:
+                            aligners[name].count_confusion(conf)
+                        counts[name].add(dist, length, seq1, seq2)
+                counts['c_greedy'].score += sum(res_g[2])
+                counts['c_beamed'].score += sum(res_b[2])
+
+        batches = self.gen_lines(filenames, False, charmap=charmap)
+        groups = chunked(batches, max(int(self.superbatch), 1))
+        if self.prefetch:
+            groups = Prefetcher(groups, depth=2)
+        waiting = None
+        try:
+            for group in groups:
+                pairs = [(b[0], b[1]) for b in group]
+                greedy = self.correct_batches(pairs, fast=fast, greedy=True, want_probs=False)
+                beamed = greedy if fast else self.correct_batches(pairs, fast=False, greedy=False, want_probs=False)
+                if waiting is not None:
+                    fold(*waiting)          # the previous group's alignments ran while this one was decoded
+                jobs = [(b[0][j], b[2][j], g[0][j], m[0][j], normalization, gt_level, confusion > 0)
+                        for b, g, m in zip(group, greedy, beamed) for j in range(len(b[0])) if b[0][j] and b[2][j]]
+                waiting = (group, greedy, beamed, scorer.submit(jobs))
+            if waiting is not None:
+                fold(*waiting)
+        finally:
+            scorer.close()
+
+        c_o, c_g, c_b = counts['c_origin'], counts['c_greedy'], counts['c_beamed']
+        w_o, w_g, w_b = counts['w_origin'], counts['w_greedy'], counts['w_beamed']
+        self.logger.info('finished %d lines', c_o.length)
+        if confusion > 0:
+            self.logger.info('OCR    confusion: %s', aligners['c_origin'].get_confusion(confusion))
+            self.logger.info('greedy confusion: %s', aligners['c_greedy'].get_confusion(confusion))
+            self.logger.info('beamed confusion: %s', aligners['c_beamed'].get_confusion(confusion))
+        if histogram:
+            self.logger.info('OCR    histogram: %s', repr(c_o.hist()))
+            self.logger.info('greedy histogram: %s', repr(c_g.hist()))
+            self.logger.info('beamed histogram: %s', repr(c_b.hist()))
+        self.logger.info('ppl greedy: %.3f', math.exp(c_g.score / c_g.length))
+        self.logger.info('ppl beamed: %.3f', math.exp(c_b.score / c_b.length))
+        self.logger.info("CER OCR:    %.3f±%.3f", c_o.mean, math.sqrt(c_o.varia))
+        self.logger.info("CER greedy: %.3f±%.3f", c_g.mean, math.sqrt(c_g.varia))
+        self.logger.info("CER beamed: %.3f±%.3f", c_b.mean, math.sqrt(c_b.varia))
+        self.logger.info("WER OCR:    %.3f±%.3f", w_o.mean, math.sqrt(w_o.varia))
+        self.logger.info("WER greedy: %.3f±%.3f", w_g.mean, math.sqrt(w_g.varia))
+        self.logger.info("WER beamed: %.3f±%.3f", w_b.mean, math.sqrt(w_b.varia))
+        self.last_evaluation = {name: dict(mean=c.mean, varia=c.varia, length=c.length, steps=c.steps, score=c.score)
+                                for name, c in counts.items()}
+        self.last_evaluation['confusion'] = {k: aligners['c_' + k].get_confusion(confusion) for k in kinds} if confusion > 0 else {}
 
     # ------------------------------------------------------------------ data
     def gen_lines(self, filenames, repeat=True, split=None, train=False, unsupervised=False, charmap=None):
-        """Generate batches of lines from the given files (seq2seq.py:919-1018): text files with
-        ``source\\ttarget`` lines (or plain lines if ``unsupervised``), or pickled (source, target) pairs
-        with confidences; ``batch_size`` lines per batch in file order, the last one padded with ''."""
-        split_ratio = 0.2
-        if charmap:
-            charmap = str.maketrans(charmap)
+        """Generate batches of lines from the given files (seq2seq.py:919-1018): 4-tuples (sources, source
+        confidences or None, targets, filenames) of ``batch_size`` lines in file order.  With ``repeat`` the
+        files are read again and again, ``False`` marks the end of every pass and the incomplete last batch of
+        a pass is dropped; without, there is one pass whose last batch is padded with empty lines.
+        Reading, normalisation and batching live in ``pipeline.LineFiles``."""
+        def too_bad(source, target):                    # training skips pairs the OCR got too wrong (:979-987)
+            self.aligner.set_seqs(source, target)
+            return self.aligner.is_bad()
         while True:
-            lines_source, lines_sourceconf, lines_target, lines_filename = [], [], [], []
-            with_confidence = False
-            for filename in filenames:
-                with_confidence = filename.endswith('.pkl')
-                with open(filename, 'rb' if with_confidence else 'r') as file:
-                    if with_confidence:
-                        file = pickle.load(file)
-                    for line_no, line in enumerate(file):
-                        if isinstance(split, np.ndarray) and (split[line_no] < split_ratio) == train:
-                            continue
-                        if with_confidence:
-                            source_text, target_text = line
-                            if not source_text:
-                                source_text, source_conf = '', []
-                            elif type(source_text[0]) is tuple:     # prob line
-                                source_text, source_conf = map(list, zip(*source_text))
-                                source_text = ''.join(source_text)
-                            else:                                   # confmat
-                                source_conf = source_text
-                                source_text = ''.join(chunk[0][0] if chunk else '' for chunk in source_conf)
-                            if not source_text.endswith('\n'):
-                                source_conf = [[('\n', 1.0)]]
-                                source_text = '\n'
-                        elif unsupervised and '\t' not in line:
-                            source_text = target_text = line
-                        else:
-                            source_text, target_text = line.split('\t')
-                            source_text = source_text + '\n'
-                        if unsupervised:
-                            target_text = source_text
-                        if charmap:
-                            source_text = source_text.translate(charmap)
-                            target_text = target_text.translate(charmap)
-                        source_text = unicodedata.normalize('NFC', source_text)
-                        target_text = unicodedata.normalize('NFC', target_text)
-                        lines_source.append(source_text)
-                        lines_target.append(target_text)
-                        if with_confidence:
-                            lines_sourceconf.append(source_conf)
-                        lines_filename.append(filename)
-                        if len(lines_source) == self.batch_size:
-                            yield (lines_source, lines_sourceconf if with_confidence else None,
-                                   lines_target, lines_filename)
-                            lines_source, lines_sourceconf, lines_target, lines_filename = [], [], [], []
-            if repeat:
-                yield False
-            else:
-                if lines_source:
-                    pad = self.batch_size - len(lines_source)
-                    lines_source.extend(pad * [''])
-                    lines_target.extend(pad * [''])
-                    if with_confidence:
-                        lines_sourceconf.extend(pad * [[]])
-                    lines_filename.extend(pad * [None])
-                    yield (lines_source, lines_sourceconf if with_confidence else None,
-                           lines_target, lines_filename)
-                break
+            reader = LineFiles(filenames, split=split, train=train, unsupervised=unsupervised, charmap=charmap,
+                               reject=too_bad if train and self.aligner is not None else None)
+            yield from reader.batches(self.batch_size, pad_last=not repeat)
+            if not repeat:
+                return
+            yield False
 
     def predict(self, filenames, fast=False, greedy=False, charmap=None):
         '''apply model on text files (seq2seq.py:756-780): yields (filenames, lines, scores) per batch.
@@ -501,6 +532,47 @@ class Sequence2Sequence(object):
         out.append(np.zeros(idx.shape[:2], np.float32))
         return out
 
+    def _preset_from(self, encoder_outputs):
+        """[enc_out (B,T,D)] + [h_n, c_n]*depth + [a0] (the encoder model's output list, or [j:j+1] slices of it)
+        -> the engine's preset layouts: enc_out [T,B,D], states [2d,B,W]."""
+        import torch
+        enc_out = np.ascontiguousarray(np.asarray(encoder_outputs[0], np.float32).transpose(1, 0, 2))
+        states = np.stack([np.asarray(s, np.float32) for s in encoder_outputs[1:1 + 2 * int(self.depth)]])
+        return torch.from_numpy(enc_out), torch.from_numpy(states)
+
+    def _predict_decoder(self, inputs):
+        """decoder_model.predict_on_batch (seq2seq.py:477-480): [p (B,1,V), enc_out (B or 1,T,D)] + [h_1, c_1, ..., h_d,
+        c_d, a] -> [scores (B,1,V)] (+ [lm scores]) + the new states, one cor_decode_step on the engine."""
+        import torch
+        eng = self._get_engine()
+        dev = eng.device
+        p = np.asarray(inputs[0], np.float32)
+        attended = np.asarray(inputs[1], np.float32)
+        states = [np.asarray(s, np.float32) for s in inputs[2:]]
+        R, d = p.shape[0], int(self.depth)
+        L, T = attended.shape[0], attended.shape[1]
+        assert L in (1, R), "attended sequence must have batch 1 or the batch of the states"
+        # the attended lines enter as a preset encoding (their encoder states are irrelevant for a single step)
+        eng.set_encoding(torch.from_numpy(np.ascontiguousarray(attended.transpose(1, 0, 2))),
+                         torch.zeros((2 * d, L, int(self.width))))
+        try:
+            idx = torch.ones((L, T, 1), dtype=torch.int32, device=dev)
+            eng.encode(idx, None, torch.full((L,), T, dtype=torch.int32, device=dev), want_outputs=False)
+        finally:
+            eng.set_encoding()
+        row_line = torch.zeros((R,), dtype=torch.int32, device=dev) if L == 1 and R > 1 else None
+        h_in = torch.as_tensor(np.stack(states[0:2 * d:2]), device=dev)
+        c_in = torch.as_tensor(np.stack(states[1:2 * d:2]), device=dev)
+        p_out, lm_out, h_out, c_out, a_out = eng.decode_step(torch.as_tensor(p[:, -1, :], device=dev), h_in, c_in,
+                                                             torch.as_tensor(states[2 * d], device=dev), row_line)
+        out = [p_out.cpu().numpy()[:, None, :]]
+        if self.lm_predict:
+            out.append(lm_out.cpu().numpy()[:, None, :])
+        for n in range(d):
+            out += [h_out[n].cpu().numpy(), c_out[n].cpu().numpy()]
+        out.append(a_out.cpu().numpy())
+        return out
+
     def _strings(self, chars, lens):
         table = getattr(self, '_string_table', None)
         if table is None or table.i2c is not self.mapping[1]:
@@ -543,7 +615,7 @@ class Sequence2Sequence(object):
         if greedy:
             # decode_sequence_greedy per line (:817-819) picks the same characters as the batch decoder —
             # "argmax, and if '' wins the argmax of the rest" == argmax over indices >= 1 — from the same
-            # batch encoding; only the score is accumulated in float32 there (:1312, :1343)
+            # batch encoding; only the score has its own accumulation there (float32 logarithms, :1330, :1341)
             out_lines, out_probs, _, alignments = self._greedy_sparse(idx, val, want_align, row_T, want_probs)
             out_scores = []
             for j, line in enumerate(lines):
@@ -551,7 +623,7 @@ class Sequence2Sequence(object):
                     out_lines[j], out_probs[j], alignments[j] = '', [], []
                     out_scores.append(0)
                     continue
-                out_scores.append(float32_mean_neglog(out_probs[j]) if out_lines[j] else 0)
+                out_scores.append(greedy_line_score(out_probs[j]) if out_lines[j] else 0)
                 out_lines[j] = out_lines[j].replace(GAP, '')
             return out_lines, out_probs, out_scores, alignments
         return self._beam_sparse(lines, idx, val, want_align, row_T)
@@ -628,11 +700,8 @@ class Sequence2Sequence(object):
                 prob = list(probs[j, :n])
                 if fast or not greedy:
                     score = float(scores[j])
-                else:                       # decode_sequence_greedy accumulates in float32 (:1312, :1343)
-                    total = np.float32(0)
-                    for p in prob:
-                        total = np.float32(total + -np.log(p))
-                    score = total / len(line)
+                else:                       # decode_sequence_greedy's own accumulation (:1318, :1341)
+                    score = greedy_line_score(prob)
                 if not fast:
                     line = line.replace(GAP, '')
                 jl = len(line)
@@ -726,33 +795,54 @@ class Sequence2Sequence(object):
     def decode_sequence_greedy(self, source_seq=None, encoder_outputs=None):
         '''Predict from one line vector without alternatives (seq2seq.py:1288-1354).
 
-        ``encoder_outputs`` (slices of an earlier batch encoding) cannot be re-imported into the engine;
-        pass ``source_seq`` padded to the batch length instead.'''
-        if source_seq is None:
-            raise NotImplementedError('decode_sequence_greedy needs source_seq (T,V) on the B200 engine')
-        idx, val = dense_to_sparse(np.asarray(source_seq)[None])
-        lines, probs, _, alignments = self._greedy_sparse(idx, val)
-        total = np.float32(0)
-        for p in probs[0]:
-            total = np.float32(total + -np.log(p))
-        return lines[0], probs[0], total / len(lines[0]), alignments[0]
+        ``encoder_outputs`` (the encoder model's output list for this line, e.g. ``[e[j:j+1] for e in
+        encoder_model.predict_on_batch(batch)]`` as correct_lines does, :817-819) are imported into the engine
+        instead of encoding ``source_seq`` again.'''
+        if encoder_outputs is None:
+            idx, val = dense_to_sparse(np.asarray(source_seq)[None])
+            lines, probs, _, alignments = self._greedy_sparse(idx, val)
+        else:
+            eng = self._get_engine()
+            T = np.asarray(encoder_outputs[0]).shape[1]
+            if source_seq is not None:
+                idx, val = dense_to_sparse(np.asarray(source_seq)[None])
+            else:
+                idx, val = np.ones((1, T, 1), np.int32), None       # any non-empty line: only the empty-line flag reads it
+            eng.set_encoding(*self._preset_from(encoder_outputs))
+            try:
+                lines, probs, _, alignments = self._greedy_sparse(idx, val)
+            finally:
+                eng.set_encoding()
+        return lines[0], probs[0], greedy_line_score(probs[0]), alignments[0]
 
     def decode_sequence_beam(self, source_seq=None, encoder_outputs=None):
         '''Predict from one line vector with alternatives (seq2seq.py:1356-1544).
 
-        Generator of (string, probabilities, entropy, alignments); the engine materialises the best
-        final hypothesis only, which is what every caller draws (``next()``, :823, repl.py:80).'''
-        if source_seq is None:
-            raise NotImplementedError('decode_sequence_beam needs source_seq (T,V) on the B200 engine')
+        Generator of (string, probabilities, entropy, alignments) over the final hypotheses of the search, best
+        first like the reference's (:1538-1544); the engine hands back the best ``N_BEST`` (64) of them, far more
+        than ``beam_width_out`` + 1, after which the search normally stops.  ``encoder_outputs`` (this line's
+        slices of an earlier batch encoding, :823-825) are imported instead of encoding ``source_seq`` again.'''
+        assert source_seq is not None, "the beam reads its rejection candidates from source_seq (seq2seq.py:1455)"
         idx, val = dense_to_sparse(np.asarray(source_seq)[None])
         eng = self._get_engine()
         bp = eng.beam_params(batch_size=min(int(self.batch_size), 256), beam_width_in=self.beam_width_in,
                              beam_threshold_in=self.beam_threshold_in, beam_width_out=self.beam_width_out,
-                             rejection_threshold=self.rejection_threshold)
-        chars, probs, scores, lens, align, stats = eng.correct_beam_host(
-            idx, val, self._row_T(idx), bp, want_align=True, budget_bytes=self.beam_budget_bytes)
-        n = int(lens[0])
-        if n > 0:
-            i2c = self.mapping[1]
-            yield (''.join(i2c[int(v)] for v in chars[0, :n]), list(probs[0, :n].numpy()), float(scores[0]),
-                   [align[0, s].numpy().copy() for s in range(n)])
+                             rejection_threshold=self.rejection_threshold, n_best=self.N_BEST)
+        if encoder_outputs is not None:
+            eng.set_encoding(*self._preset_from(encoder_outputs))
+        try:
+            chars, probs, scores, lens, align, stats = eng.correct_beam_host(
+                idx, val, self._row_T(idx), bp, want_align=True, budget_bytes=self.beam_budget_bytes)
+        finally:
+            if encoder_outputs is not None:
+                eng.set_encoding()
+        self.last_beam_stats = stats.numpy()
+        i2c = self.mapping[1]
+        for r in range(chars.shape[1]):
+            n = int(lens[0, r])
+            if n <= 0:
+                break
+            yield (''.join(i2c[int(v)] for v in chars[0, r, :n]), list(probs[0, r, :n].numpy()), float(scores[0, r]),
+                   [align[0, r, s].numpy().copy() for s in range(n)])
+
+    N_BEST = 64     # final hypotheses decode_sequence_beam can yield (COR_BEAM_NBEST_MAX)

@@ -63,6 +63,12 @@ typedef struct cor_beam_params {
     int32_t batch_size;          /* 256 */
     int32_t beam_width_in;       /* 15  */
     int32_t beam_width_out;      /* 16  */
+    int32_t n_best;              /* final hypotheses returned per line, best first, 0 or 1 = the best one only, at most
+                                  * COR_BEAM_NBEST_MAX.  decode_sequence_beam is a generator over ALL finals
+                                  * (seq2seq.py:1538-1544); its callers draw one.  With n_best = N > 1 every per-line output
+                                  * of the beam entry points has N slots: out_chars/out_probs [n_rows][N][2*t_max],
+                                  * out_scores/out_len [n_rows][N], out_align [n_rows][N][2*t_max][t_max]; out_len = 0
+                                  * marks a slot beyond the number of finals found. */
     double  beam_threshold_in;   /* 0.2 */
     double  rejection_threshold; /* 0.3 class default / 0.5 CLI default; 0 disables */
 } cor_beam_params;
@@ -94,6 +100,16 @@ int cor_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
  * never inferred from the size of the buffer. */
 int cor_encode(cor_model* m, const cor_lines* lines, int want_alignments, void* workspace, size_t workspace_bytes,
                float* enc_out, float* states, void* stream);
+
+/* ---- encoder results from the caller: the reference lets every decoder take `encoder_outputs` instead of the
+ * input (decode_sequence_greedy/beam(encoder_outputs=...), seq2seq.py:1288, 1356; correct_lines itself encodes a
+ * batch once and hands slices to the per-line decoders, :811-825) and its decoder model takes the attended
+ * sequence as an input (:477-480).  While a preset is installed, every entry point that would run the encoder
+ * (cor_encode, cor_correct_greedy_host, cor_correct_beam_host, cor_decode_beam_batch) imports these DEVICE arrays
+ * instead: enc_out [t_max][n_rows][D], states [2*depth][n_rows][W], the layouts cor_encode returns; the call's
+ * geometry must match, its lines still provide the rejection candidates of the beam and the empty-line flags.
+ * NULL, NULL removes the preset.  The arrays must stay valid until then. */
+int cor_set_encoding(cor_model* m, int n_rows, int t_max, const float* enc_out, const float* states);
 
 /* ---- one decoder timestep: replaces decoder_model.predict_on_batch (seq2seq.py:1245,1321,1428).
  * Rows are hypotheses; row_line[r] (NULL = identity) names the encoded line in `workspace`
@@ -139,6 +155,7 @@ int cor_correct_greedy_host(cor_model* m, const cor_lines* host_lines,
  * [7] peak fringe length.  [0] is -1 for a line whose arena overflowed (internal, retried) and -2 for an empty line.
  * All HOST. */
 #define COR_BEAM_STATS 8
+#define COR_BEAM_NBEST_MAX 64
 int cor_beam_workspace_bytes(const cor_model* m, int n_rows, int t_max, int k_alt,
                              const cor_beam_params* bp, size_t budget_bytes, size_t* bytes);
 int cor_correct_beam_host(cor_model* m, const cor_lines* host_lines, const cor_beam_params* bp,

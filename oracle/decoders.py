@@ -135,7 +135,10 @@ def decode_sequence_greedy(topo, w, mapping, enc_slices, events=None):
     T = enc_out.shape[1]
     u = enc_out @ w["attention_dense"][0]
     p = np.zeros((1, topo.voc_size), enc_out.dtype)
-    text, probs, total, aligns = '', [], np.float32(0), []   # int 0 + np.float32 stays float32 (legacy rules)
+    # ``decoded_score = 0; decoded_score += -np.log(prob)``: int + np.float32 is float64 under the reference's numpy
+    # (< 1.24, legacy promotion), float32 under numpy >= 2 (PROMOTION "nep50", used by tests/ref_harness.py)
+    acc = np.float32 if _nep50() else np.float64
+    text, probs, total, aligns = '', [], acc(0), []
     for step in range(2 * T):
         p, _, states = decode_step(topo, w, p, enc_out, states, u=u)
         row = p[0]
@@ -148,7 +151,7 @@ def decode_sequence_greedy(topo, w, mapping, enc_slices, events=None):
             v = int(np.nanargmax(patched))
         text += i2c[v]
         probs.append(row[v])
-        total = np.float32(total + -np.log(row[v]))
+        total = acc(total + acc(-np.log(row[v])))
         aligns.append(states[-1][0])
         if i2c[v] == '\n':
             break
