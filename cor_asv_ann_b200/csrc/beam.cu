@@ -163,10 +163,6 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
         }
         const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
         const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);
-        if (take && fin) {       // n-best read-out: the finals in pop order (finals_count is only written by lane 0 below)
-            const int slot = fc0 + nfin + __popc(t_fin & ((1u << lane) - 1u));
-            if (slot < FMAX) { b.fin_id[(size_t)line * FMAX + slot] = id & ~FINAL_BIT; b.fin_key[(size_t)line * FMAX + slot] = keys[i]; }
-        }
         if (t_open && first_open == 0x7fffffff) first_open = base + __ffs(t_open) - 1;
         if (t_fin && first_final == 0x7fffffff) first_final = base + __ffs(t_fin) - 1;
         consumed += __popc(t_open | t_fin);
@@ -182,6 +178,21 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     if (nfin > 0) {
         const double kf = keys[first_final];
         if (kf < bk) { bk = kf; b.best_key[line] = kf; b.best_final[line] = (int32_t)(ids[first_final] & ~FINAL_BIT); }
+    }
+    if (b.n_best > 1 && nfin > 0) {
+        // n-best read-out: keep the FMAX best finals seen so far (unsorted; beam_finish_kernel sorts them).  Finals are
+        // rare events, so one lane walks the consumed prefix.
+        uint32_t* fid = b.fin_id + (size_t)line * FMAX; double* fk = b.fin_key + (size_t)line * FMAX;
+        int have = min(fc0, FMAX);
+        for (int i = 0; i < consumed; ++i) {
+            const uint32_t id = ids[i];
+            if (!(id & FINAL_BIT)) continue;
+            const uint32_t nid_ = id & ~FINAL_BIT; const double k = keys[i];
+            if (have < FMAX) { fid[have] = nid_; fk[have] = k; ++have; continue; }
+            int worst = 0;
+            for (int q = 1; q < FMAX; ++q) if (key_less(fk[worst], fid[worst], fk[q], fid[q])) worst = q;
+            if (key_less(k, nid_, fk[worst], fid[worst])) { fid[worst] = nid_; fk[worst] = k; }
+        }
     }
     b.finals_count[line] = fc;
     b.fr_off[line] = consumed;
@@ -418,6 +429,9 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
             const int r = b.rej_table[(size_t)line * b.T + pos];
             if (r >= 0) rej = r;
         }
+        bool near_pos = len_node > 1 && ((!onehot && fabs(fabs(cur - floor(cur)) - 0.5) <= 1e-5) || fabs(mis - 0.1) <= 1e-6);
+        if (rej >= 0 && fabs((double)sp[rej] - b.rej_thr) <= (double)kTieMargin * b.rej_thr) near_pos = true;
+        __syncthreads();
         if (rej >= 0 && tid == 0 && (double)sp[rej] < b.rej_thr) sp[rej] = (float)b.rej_thr;
         __syncthreads();
         // ---- record: scores after the overwrite, states, alignment
@@ -460,7 +474,7 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
         const int cnt_all = s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3];
         const int beampos = min(cnt_all & 1023, b.width_in);
         const bool score_tie = ((cnt_all >> 10) & 1023) >= 2;
-        bool near_tie = ((cnt_all >> 20) & 1023) > 0;
+        bool near_tie = ((cnt_all >> 20) & 1023) > 0 || near_pos;
         float walked_prev = -1.f;
         // ---- walk the candidates best first (:1480-1529)
         int nacc = 0, pending = rej;
@@ -599,9 +613,12 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
             const int r = b.rej_table[(size_t)line * b.T + pos];
             if (r >= 0) rej = r;
         }
+        // discrete decisions that hang on the last bits of the alignment / the candidate's score are near-ties too
+        bool near_pos = len_node > 1 && ((!onehot && fabs(fabs(cur - floor(cur)) - 0.5) <= 1e-5) || fabs(mis - 0.1) <= 1e-6);
         float rej_p = 0.f;
         if (rej >= 0) {
             rej_p = fetch(p, rej);
+            if (fabs((double)rej_p - b.rej_thr) <= (double)kTieMargin * b.rej_thr) near_pos = true;
             if ((double)rej_p < b.rej_thr) {
                 rej_p = (float)b.rej_thr;
 #pragma unroll
@@ -696,7 +713,7 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
         for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULL, cnt, o);
         const int beampos = min(cnt & 1023, b.width_in);
         const bool score_tie = ((cnt >> 10) & 1023) >= 2;
-        bool near_tie = ((cnt >> 20) & 1023) > 0;
+        bool near_tie = ((cnt >> 20) & 1023) > 0 || near_pos;
         float walked_prev = -1.f;
         // ---- walk the candidates best first (:1480-1529)
         int nacc = 0, pending = rej;

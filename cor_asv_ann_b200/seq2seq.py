@@ -553,6 +553,8 @@ class Sequence2Sequence(object):
         L, T = attended.shape[0], attended.shape[1]
         assert L in (1, R), "attended sequence must have batch 1 or the batch of the states"
         # the attended lines enter as a preset encoding (their encoder states are irrelevant for a single step)
+        if L == 1 and R > 1:        # the beam's broadcast form (:1428-1429): every hypothesis row gets the one line
+            attended, L = np.repeat(attended, R, axis=0), R
         eng.set_encoding(torch.from_numpy(np.ascontiguousarray(attended.transpose(1, 0, 2))),
                          torch.zeros((2 * d, L, int(self.width))))
         try:
@@ -560,7 +562,7 @@ class Sequence2Sequence(object):
             eng.encode(idx, None, torch.full((L,), T, dtype=torch.int32, device=dev), want_outputs=False)
         finally:
             eng.set_encoding()
-        row_line = torch.zeros((R,), dtype=torch.int32, device=dev) if L == 1 and R > 1 else None
+        row_line = None
         h_in = torch.as_tensor(np.stack(states[0:2 * d:2]), device=dev)
         c_in = torch.as_tensor(np.stack(states[1:2 * d:2]), device=dev)
         p_out, lm_out, h_out, c_out, a_out = eng.decode_step(torch.as_tensor(p[:, -1, :], device=dev), h_in, c_in,

@@ -317,6 +317,9 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
                 nw = min(beampos + 1, V)
                 tie = bool(np.any(np.abs(so - bound) <= 1e-6 * bound))
                 tie = tie or bool(np.any(so[:nw - 1] - so[1:nw] <= 1e-6 * so[:nw - 1]))
+                if node.length > 1:      # position rounding, misalignment threshold
+                    onehot = np.max(node.alignment) == 1.0
+                    tie = tie or (not onehot and abs(abs(cur - np.floor(cur)) - 0.5) <= 1e-5) or abs(mis - 0.1) <= 1e-6
                 n_near += int(tie)
             rank = 0
             for v in order[::-1]:
