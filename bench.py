@@ -1,15 +1,25 @@
 #!/usr/bin/env python
-"""bench.py — corrected chars/sec of the cor-asv-ann neural hot path on N B200s.
+"""bench.py -- corrected chars/sec of the cor-asv-ann neural hot path on N B200s.
 
-Workloads (BASELINE.json configs):
-  greedy  C3: depth 2 / width 512 / V 512, fast batch-greedy decode of synthetic 80-char lines
-  beam    C2: same model, beamed decode (beam_width_in 4, rejection 0.5), per-line A* semantics
-A "step" is one pass of the hot path (encode + decode) over one super-batch of
-`--lines` synthetic lines per GPU (whole 256-line reference batches, T = 81).  chars = input
-characters excluding the newline (80 per line).  Lines shard across ranks with no data-path
-collective (weak scaling); the only collective is the MAX of the elapsed time.
+Workloads (BASELINE.json configs); every model is random-init of the named topology,
+lines are synthetic (80 characters + newline, T = 81, seeded) unless stated:
+  beam              C2 as configured: depth 2 / width 512 / V 512, beamed decode, beam_width_in 4, rejection 0.5
+                    (weights variant U).  With random weights this is the DEGENERATE bracket: one hypothesis per
+                    iteration, output == input.  It is the literal config and stays the headline `value`.
+  greedy            C3: same model, fast batch-greedy decode (2T steps for every line).
+  beam_competitive  C2 topology with PEAKED weights (variant P: a selective softmax, like a trained model's) and
+                    the class-default beam parameters (beam_width_in 15, rejection 0.3): the search competes --
+                    ~100 live hypotheses per line and iteration, finals found, early exit by beam_width_out.
+  beam_stress       C2 bracket (ii): rejection_threshold 0 -- 256 hypotheses x 2T iterations per line, fringe at
+                    its 2T*256 truncation, no final found (falls back to the input).
+  c4                depth 3 / width 768 deep bidirectional encoder + residual + LM-rated beam (beam_width_in 15).
+  c1                depth 1 / width 128 on the 55 lines of the reference's test pages, one call per page.
+A "step" is one pass of the hot path (encode + decode) over one super-batch of lines per GPU (whole 256-line
+reference batches); chars = input characters excluding the newline.  Lines shard across ranks with no data-path
+collective (weak scaling: the `value`); `strong` is the literal fixed job of the config (C3: 1 000 000 lines,
+C2: 100 000 lines) partitioned over the ranks by cor_asv_ann_b200.shard and gathered on rank 0 in input order.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload greedy|beam] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload beam|greedy|...] [--impl reference]
 """
 import argparse
 import json
@@ -24,33 +34,52 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WIDTH, DEPTH, VOC, LINE_LEN, REF_BATCH = 512, 2, 512, 80, 256
-BEAM = dict(batch_size=256, beam_width_in=4, beam_threshold_in=0.2, beam_width_out=16, rejection_threshold=0.5)
+LINE_LEN, REF_BATCH = 80, 256
+C2 = dict(width=512, depth=2, voc_size=512)
+C4 = dict(width=768, depth=3, voc_size=512, deep_bidirectional_encoder=True, residual_connections=True, lm_predict=True)
+BEAM_C2 = dict(batch_size=256, beam_width_in=4, beam_threshold_in=0.2, beam_width_out=16, rejection_threshold=0.5)
+BEAM_DEFAULT = dict(batch_size=256, beam_width_in=15, beam_threshold_in=0.2, beam_width_out=16, rejection_threshold=0.3)
+WORKLOADS = {
+    "beam": dict(topo=C2, variant="U", seed=1002, beam=BEAM_C2, lines=9472,
+                 name="C2 beamed decode as configured (beam_width_in 4, rejection 0.5): the degenerate bracket, 1 hypothesis per iteration"),
+    "greedy": dict(topo=C2, variant="U", seed=1003, beam=None, lines=16384, name="C3 fast batch-greedy decode"),
+    "beam_competitive": dict(topo=C2, variant="P", seed=1012, beam=BEAM_DEFAULT, lines=2048,
+                             name="C2 topology, peaked weights (variant P), class-default beam (beam_width_in 15, rejection 0.3): competing hypotheses"),
+    "beam_stress": dict(topo=C2, variant="U", seed=1022, beam=dict(BEAM_C2, rejection_threshold=0.0), lines=256,
+                        name="C2 stress bracket: rejection_threshold 0 (256 hypotheses x 2T iterations per line)"),
+    "c4": dict(topo=C4, variant="U", seed=1004, beam=dict(BEAM_C2, beam_width_in=15), lines=1024,
+               name="C4 depth 3 / width 768 deep-bidirectional + residual + LM-rated beam (beam_width_in 15, rejection 0.5)"),
+}
 
 
-def flops_enc(T, W=WIDTH, d=DEPTH):
+def flops_enc(T, topo):
+    W, d = topo["width"], topo["depth"]
+    if topo.get("deep_bidirectional_encoder"):
+        return T * W * W * (32 + 48 * (d - 1)) + 2 * T * (2 * W) * W
     D = 2 * W if d == 1 else W
     return T * W * W * (32 + 24 * (d >= 2) + 16 * max(d - 2, 0)) + 2 * T * D * W
 
 
-def flops_step(W=WIDTH, d=DEPTH, V=VOC):
-    D = 2 * W if d == 1 else W
-    return 4 * V * W + 16 * W * W * (d - 1) + 2 * W * W + 8 * W * (W + D) + 8 * W * W
+def flops_step(topo):
+    W, d, V = topo["width"], topo["depth"], topo["voc_size"]
+    D = 2 * W if (d == 1 or topo.get("deep_bidirectional_encoder")) else W
+    f = 4 * V * W + 16 * W * W * (d - 1) + 2 * W * W + 8 * W * (W + D) + 8 * W * W
+    if topo.get("lm_predict"):
+        f += 8 * W * (W + D) + 8 * W * W + 2 * V * W
+    return f
 
 
-def build_model(seed=20251):
-    from oracle.model import Topology, init_weights
-    from tests.common import synthetic_alphabet
-    topo = Topology(width=WIDTH, depth=DEPTH, voc_size=VOC)
-    return topo, init_weights(topo, seed, "U"), synthetic_alphabet(VOC)
+def build_weights(topo, variant, seed=20251):
+    """Seeded random-init weights of `topo` from the product's own generator (no oracle involved)."""
+    from cor_asv_ann_b200 import synthetic
+    shapes = synthetic.layer_shapes(topo["width"], topo["depth"], topo["voc_size"],
+                                    topo.get("deep_bidirectional_encoder", False), topo.get("bridge_dense", False))
+    return synthetic.random_weights(shapes, topo["width"], topo["depth"], np.random.default_rng(seed), variant)
 
 
-def make_indices(n_lines, seed):
-    """Synthetic lines directly as index arrays [n, 81, 1]: 80 chars uniform over 2..V-1, then '\\n' (=1)."""
-    rng = np.random.default_rng(seed)
-    idx = rng.integers(2, VOC, size=(n_lines, LINE_LEN + 1, 1), dtype=np.int32)
-    idx[:, LINE_LEN, 0] = 1
-    return idx
+def make_indices(n_lines, seed, voc=512):
+    from cor_asv_ann_b200.synthetic import line_indices
+    return line_indices(n_lines, LINE_LEN, voc, seed)
 
 
 class ClockSampler:
@@ -96,30 +125,90 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_oracle_rate(workload, n_lines, seed=77):
-    """The oracle (numpy restatement of the reference schedule) on the host cores: chars/s on n_lines."""
-    from oracle import decoders as od
-    topo, w, mapping = build_model()
-    idx = make_indices(n_lines, seed)[:, :, 0]
-    x = np.zeros((n_lines, LINE_LEN + 1, VOC), np.uint32)
-    x[np.arange(n_lines)[:, None], np.arange(LINE_LEN + 1)[None, :], idx] = 1
-    t0 = time.perf_counter()
-    if workload == "greedy":
-        od.decode_batch_greedy(topo, w, mapping, x, hoist_u=False)   # u recomputed per step like the reference
-    else:
-        from oracle.model import encode
-        enc = encode(topo, w, x)
-        for j in range(n_lines):
-            next(od.decode_sequence_beam(topo, w, mapping, x[j], [e[j:j + 1] for e in enc], **BEAM))
-    dt = time.perf_counter() - t0
-    return LINE_LEN * n_lines / dt, dt
-
-
 def host_threads():
     try:
         return len(os.sched_getaffinity(0))
     except AttributeError:
         return os.cpu_count() or 1
+
+
+# ----------------------------------------------------------------------------- the oracle legs (CPU baseline, parity)
+
+def oracle_topology(topo):
+    from oracle.model import Topology
+    return Topology(**topo)
+
+
+def cpu_oracle_rate(workload, n_lines, seed=77):
+    """The oracle (numpy restatement of the reference schedule) on the host cores: chars/s on n_lines."""
+    from oracle import decoders as od
+    from cor_asv_ann_b200.synthetic import synthetic_alphabet
+    spec = WORKLOADS[workload]
+    topo, w = oracle_topology(spec["topo"]), build_weights(spec["topo"], spec["variant"])
+    mapping = synthetic_alphabet(spec["topo"]["voc_size"])
+    V = spec["topo"]["voc_size"]
+    idx = make_indices(n_lines, seed, V)[:, :, 0]
+    x = np.zeros((n_lines, LINE_LEN + 1, V), np.uint32)
+    x[np.arange(n_lines)[:, None], np.arange(LINE_LEN + 1)[None, :], idx] = 1
+    t0 = time.perf_counter()
+    if spec["beam"] is None:
+        od.decode_batch_greedy(topo, w, mapping, x, hoist_u=False)   # u recomputed per step like the reference
+    else:
+        from oracle.model import encode
+        enc = encode(topo, w, x)
+        for j in range(n_lines):
+            next(od.decode_sequence_beam(topo, w, mapping, x[j], [e[j:j + 1] for e in enc], **spec["beam"]), None)
+    dt = time.perf_counter() - t0
+    return LINE_LEN * n_lines / dt, dt
+
+
+def parity_check(workload, idx_rows, got, n_check):
+    """Oracle on `n_check` lines of the LAST TIMED step's first reference batch against what the GPU returned for
+    them: strings (and search statistics for the beam), per-character probabilities."""
+    from oracle import decoders as od
+    from oracle.model import encode
+    from cor_asv_ann_b200.synthetic import synthetic_alphabet
+    spec = WORKLOADS[workload]
+    topo, w = oracle_topology(spec["topo"]), build_weights(spec["topo"], spec["variant"])
+    V = spec["topo"]["voc_size"]
+    mapping = synthetic_alphabet(V)
+    batch = idx_rows[:REF_BATCH, :, 0]                 # the whole reference batch: its padded T is part of the input
+    T = batch.shape[1]
+    x = np.zeros((batch.shape[0], T, V), np.uint32)
+    x[np.arange(batch.shape[0])[:, None], np.arange(T)[None, :], batch] = 1
+    chars, probs, lens, stats = got
+    t0 = time.perf_counter()
+    same = ties = 0
+    worst = 0.0
+    if spec["beam"] is None:
+        n_check = batch.shape[0]
+        text, r_probs, _, _ = od.decode_batch_greedy(topo, w, mapping, x)
+        for j in range(n_check):
+            g = ''.join(mapping[1][int(v)] for v in chars[j, :lens[j]])
+            if g == text[j]:
+                same += 1
+                if lens[j]:
+                    worst = max(worst, float(np.abs(probs[j, :lens[j]] - np.asarray(r_probs[j], np.float32)).max()))
+    else:
+        from tests.make_golden import stat_row
+        enc = encode(topo, w, x)
+        for j in range(n_check):
+            st = {}
+            r = next(od.decode_sequence_beam(topo, w, mapping, x[j], [e[j:j + 1] for e in enc], stats=st, **spec["beam"]), None)
+            want = stat_row(st)
+            ok = (r is None) == (lens[j] == 0) and list(stats[j, :5]) == want[:5] and stats[j, 6] == want[6]
+            if ok and r is not None:
+                ok = ''.join(mapping[1][int(v)] for v in chars[j, :lens[j]]) == r[0]
+            if ok:
+                same += 1
+                if r is not None:
+                    worst = max(worst, float(np.abs(probs[j, :lens[j]] - np.asarray(r[1], np.float32)).max()))
+            elif stats[j, 5] > 0 or want[5] > 0:
+                ties += 1
+    return {"parity_rows_checked": n_check, "rows_identical": same, "rows_differing_at_logged_near_tie": ties,
+            "rows_differing_otherwise": n_check - same - ties, "max_abs_dp": worst,
+            "compared": "strings + per-character probabilities" + ("" if spec["beam"] is None else " + search statistics and expansion checksum"),
+            "oracle_s": time.perf_counter() - t0}
 
 
 def run_reference(args):
@@ -150,42 +239,47 @@ def run_reference(args):
         "impl": "reference", "metric": "corrected chars/sec (%s)" % args.workload, "value": value, "unit": "chars/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, n),
+        "config": workload_config(args.workload, n),
         "cpu_baseline": {"value": value, "unit": "chars/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "chars/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
-def workload_config(args, lines_per_step, workload=None):
-    workload = workload or args.workload
-    return {"workload": ("C3 fast batch-greedy decode" if workload == "greedy" else
-                         "C2 beamed decode (beam_width_in 4, rejection 0.5)") +
-                        ", depth 2 width 512 V 512, synthetic 80-char lines, T=81, random-init weights (variant U)",
+def workload_config(workload, lines_per_step):
+    spec = WORKLOADS[workload]
+    t = spec["topo"]
+    return {"workload": "%s; depth %d width %d V %d, synthetic %d-char lines, T=%d, random-init weights (variant %s)"
+                        % (spec["name"], t["depth"], t["width"], t["voc_size"], LINE_LEN, LINE_LEN + 1, spec["variant"]),
             "lines_per_step_per_gpu": lines_per_step, "reference_batch": REF_BATCH,
+            "beam_params": spec["beam"],
             "l2": "inputs differ every step; per-step activations (GBs) exceed the 126 MB L2",
             "parallelism": "lines sharded by 256-line reference batch, no data-path collective"}
 
 
-def measure(args, eng, workload, rank, world, local, sample_clocks):
-    """Time `workload` on this rank: device-resident pass (CUDA events) and end-to-end host call."""
+# ----------------------------------------------------------------------------- measurement
+
+def measure(args, eng, workload, lines, rank, world, local, sample_clocks, roofline_pass=True, parity_lines=0):
+    """Time `workload` on this rank: device-resident pass (CUDA events, nothing else inside the timed region), a
+    separate pass with per-launch event bracketing for the roofline, and the end-to-end host call."""
     import torch
     import torch.distributed as dist
-    L = (args.lines // REF_BATCH) * REF_BATCH
-    if workload == "beam":
-        L = (min(args.lines, args.beam_lines) // REF_BATCH) * REF_BATCH
+    spec = WORKLOADS[workload]
+    L = max(REF_BATCH, (lines // REF_BATCH) * REF_BATCH)
     T = LINE_LEN + 1
+    V = spec["topo"]["voc_size"]
     total_steps = args.steps + args.warmup
-    seed0 = 1003 if workload == "greedy" else 1002          # SURVEY.md 8d: config 3 / config 2
+    seed0 = spec["seed"]                                    # SURVEY.md 8d: config 3 seed 1003, config 2 seed 1002, ...
     # distinct lines for every step and rank, resident in HBM before the timed region
-    dev_idx = [torch.as_tensor(make_indices(L, seed0 + 7919 * rank + 101 * s), device="cuda") for s in range(total_steps)]
+    host_steps = [make_indices(L, seed0 + 7919 * rank + 101 * s, V) for s in range(total_steps)]
+    dev_idx = [torch.as_tensor(a, device="cuda") for a in host_steps]
     row_T = torch.full((L,), T, dtype=torch.int32, device="cuda")
-    bp = eng.beam_params(**BEAM)
+    bp = eng.beam_params(**spec["beam"]) if spec["beam"] else None
     budget = int(args.beam_budget_gb * (1 << 30))
     beam_out = None
 
     def device_step(s):
         nonlocal beam_out
-        if workload == "greedy":
+        if bp is None:
             eng.encode(dev_idx[s], None, row_T, want_outputs=False)     # the decoder reads the workspace; no 2.7 GB copy of enc_out
             return eng.greedy()
         beam_out = eng.beam_device(dev_idx[s], None, row_T, bp, budget_bytes=budget, out=beam_out)
@@ -204,7 +298,6 @@ def measure(args, eng, workload, rank, world, local, sample_clocks):
     if sample_clocks:
         sampler.start()
     eng.launch_count(reset=True)
-    eng.prof_enable(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for s in range(args.warmup, total_steps):
@@ -213,24 +306,52 @@ def measure(args, eng, workload, rank, world, local, sample_clocks):
     barrier()
     ms = ev0.elapsed_time(ev1)
     launches = eng.launch_count()
-    k_ms, k_n, k_flops = eng.prof_read()
-    eng.prof_enable(False)
     clocks = sampler.stop() if sample_clocks else None
-    if workload == "greedy":
+    if bp is None:
         dec_steps = 2 * T * L                            # the fast decoder always runs 2T steps for every line
-        extra = {"decoded_chars_last_step": int(out[3].sum().item())}
+        extra = {"decoded_chars_last_step": int(out[3].sum().item()),
+                 "near_tie_argmaxes_last_step": int(eng.last_ties.sum().item())}
+        stats = None
     else:
         stats = out[5].cpu().numpy()
         dec_steps = int(stats[:, 1].sum())               # hypothesis-steps actually run (last step)
         lens = out[3].cpu().numpy()
         same = int((out[0][:, :LINE_LEN + 1].cpu().numpy() == dev_idx[total_steps - 1][:, :, 0].cpu().numpy()).all(axis=1).sum())
         extra = {"beam_iterations_per_line": float(stats[:, 0].mean()), "hypothesis_steps_per_line": dec_steps / L,
+                 "hypotheses_per_line_and_iteration": dec_steps / max(int(stats[:, 0].sum()), 1),
+                 "hypothesis_steps_per_s": dec_steps * args.steps * world / (ms * 1e-3) if ms else None,
+                 "finals_per_line": float(stats[:, 2].mean()), "fringe_peak_mean": float(stats[:, 7].mean()),
+                 "fringe_peak_max": int(stats[:, 7].max()), "near_tie_decisions_per_line": float(stats[:, 5].mean()),
                  "lines_without_final": int((lens == 0).sum()), "lines_equal_to_input": same}
+    parity = None
+    if parity_lines and rank == 0:
+        got = (out[0].cpu().numpy(), out[1].cpu().numpy(), out[3].cpu().numpy(), stats)
+        parity = parity_check(workload, host_steps[total_steps - 1], got, parity_lines)
+
+    # ---- separate pass for the roofline: every LSTM-GEMM launch bracketed by two events (perturbs the step: not in `value`)
+    k_ms = k_n = k_flops = 0
+    prof_ms = None
+    if roofline_pass:
+        barrier()
+        eng.prof_enable(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        n_prof = min(args.steps, 2)
+        for s in range(args.warmup, args.warmup + n_prof):
+            device_step(s)
+        e1.record()
+        torch.cuda.synchronize()
+        k_ms, k_n, k_flops = eng.prof_read()
+        eng.prof_enable(False)
+        prof_ms = e0.elapsed_time(e1)
+        k_ms, k_n = k_ms / n_prof, k_n / n_prof
+        k_flops /= n_prof
+        prof_ms /= n_prof
 
     # ---- end to end through the C-ABI host call: pinned host buffers, H2D and D2H inside
-    host_idx = [torch.as_tensor(make_indices(L, seed0 + 4001 + 7919 * rank + 101 * s)).pin_memory() for s in range(args.steps)]
+    host_idx = [torch.as_tensor(make_indices(L, seed0 + 4001 + 7919 * rank + 101 * s, V)).pin_memory() for s in range(args.steps)]
     host_T = torch.full((L,), T, dtype=torch.int32).pin_memory()
-    if workload == "greedy":
+    if bp is None:
         host_out = eng.host_outputs(L, T)
         call = lambda s: eng.correct_greedy_host(host_idx[s], None, host_T, out=host_out)
         api = "cor_correct_greedy_host (pinned host buffers)"
@@ -255,12 +376,12 @@ def measure(args, eng, workload, rank, world, local, sample_clocks):
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(t_ms[0]), float(t_ms[1])
     chars = LINE_LEN * L * args.steps * world
-    algo_flops_line = flops_enc(T) + dec_steps / L * flops_step()
+    algo_flops_line = flops_enc(T, spec["topo"]) + dec_steps / L * flops_step(spec["topo"])
     del dev_idx, host_idx
     torch.cuda.empty_cache()
     return {"L": L, "ms": ms, "value": chars / (ms * 1e-3), "e2e_value": chars / (e2e_ms * 1e-3), "e2e_ms": e2e_ms,
             "h2d": h2d, "d2h": d2h, "api": api, "launches": launches, "k_ms": k_ms, "k_n": k_n, "k_flops": k_flops,
-            "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra}
+            "prof_ms": prof_ms, "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra, "parity": parity}
 
 
 def measured_traffic(workload, rows):
@@ -299,7 +420,7 @@ def measure_page(args, eng, n_lines):
             "api": "cor_correct_greedy_host (pinned host buffers), T encoder + 2T decoder timesteps"}
     # the OCR-D processor's default mode (fast_mode false, ocrd-tool.json:55-58) is the beamed decoder: same page,
     # config-2 beam parameters (random-init weights: T iterations of one hypothesis per line)
-    bp = eng.beam_params(**BEAM)
+    bp = eng.beam_params(**BEAM_C2)
     b_out = None
     for s in range(2):
         b_out = eng.correct_beam_host(idx[s % 4], None, host_T, bp, budget_bytes=2 << 30, out=b_out)
@@ -311,8 +432,43 @@ def measure_page(args, eng, n_lines):
     torch.cuda.synchronize()
     db = (time.perf_counter() - t0) / reps
     page["beam"] = {"ms_per_call": db * 1e3, "chars_per_s": LINE_LEN * n_lines / db, "gpu_launches_per_call": eng.launch_count() / reps,
-                    "api": "cor_correct_beam_host (pinned host buffers), persistent encoder recurrence + per-iteration beam kernels"}
+                    "api": "cor_correct_beam_host (pinned host buffers)"}
     return page
+
+
+def make_s2s(topo, w, mapping, device):
+    from cor_asv_ann_b200.seq2seq import Sequence2Sequence
+    s = Sequence2Sequence()
+    s.width, s.depth, s.voc_size, s.mapping = topo["width"], topo["depth"], topo["voc_size"], mapping
+    s.device = device
+    s.configure()
+    for layer, arrs in w.items():
+        s.encoder_decoder_model.get_layer(layer).set_weights(arrs)
+    s.status = 2
+    return s
+
+
+def measure_c1(device):
+    """Config 1: depth 1 / width 128 over the alphabet of the 55 lines of the reference's test pages
+    (testdata/.../kant_aufklaerung_1784-complex, frozen in tests/golden/kant_lines.json), one call per page like the
+    OCR-D wrapper: plain strings, fast greedy and per-line-greedy semantics."""
+    d = json.load(open(os.path.join(ROOT, "tests", "golden", "kant_lines.json"), encoding="utf-8"))
+    alphabet, pages = d["alphabet"], d["pages"]
+    topo = dict(width=128, depth=1, voc_size=len(alphabet))
+    mapping = ({c: i for i, c in enumerate(alphabet)}, {i: c for i, c in enumerate(alphabet)})
+    s = make_s2s(topo, build_weights(topo, "U", seed=11), mapping, device)
+    plain = [[''.join(chunk[0][0] for chunk in line).replace('\a', '') for line in page] for page in pages]
+    n_chars = sum(len(l) - 1 for page in plain for l in page)
+    for page in plain:
+        s.correct_lines(page, None, fast=True, greedy=True)
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        for page in plain:
+            s.correct_lines(page, None, fast=True, greedy=True)
+    dt = (time.perf_counter() - t0) / reps
+    return {"workload": "C1 depth 1 width 128, the 55 kant test lines, one fast-greedy correct_lines call per page (strings in, strings + probabilities + alignments out)",
+            "lines": sum(len(p) for p in plain), "pages": len(plain), "chars": n_chars, "ms_all_pages": dt * 1e3, "chars_per_s": n_chars / dt}
 
 
 def measure_predict(args, topo, w, mapping, device, n_lines):
@@ -320,14 +476,8 @@ def measure_predict(args, topo, w, mapping, device, n_lines):
     text file, fast mode, strings in -> strings + scores out; 64 reference batches per engine call with
     the next super-batch read and encoded in a worker thread, against the reference's one-batch loop."""
     import tempfile
-    from cor_asv_ann_b200.seq2seq import Sequence2Sequence
-    s = Sequence2Sequence()
-    s.width, s.depth, s.voc_size, s.mapping = topo.width, topo.depth, topo.voc_size, mapping
-    s.device = device
-    s.configure()
-    for layer, arrs in w.items():
-        s.encoder_decoder_model.get_layer(layer).set_weights(arrs)
-    s.status = 2
+    s = make_s2s(topo, w, mapping, device)
+    VOC = topo["voc_size"]
     i2c = np.array([ord(mapping[1][i]) if mapping[1][i] else 0 for i in range(VOC)], dtype=np.uint32)
     out = {}
     with tempfile.TemporaryDirectory() as tmp:
@@ -349,7 +499,7 @@ def measure_predict(args, topo, w, mapping, device, n_lines):
     # one OCR-D page through the class the wrapper calls (wrapper/transcode.py:111-115): strings in -> strings,
     # probabilities, scores, alignments out, fast greedy mode and the default beamed mode
     page = [i2c[make_indices(1, 5000 + j)[0, :, 0]].tobytes().decode("utf-32-le") for j in range(32)]
-    s.rejection_threshold, s.beam_width_in = BEAM["rejection_threshold"], BEAM["beam_width_in"]
+    s.rejection_threshold, s.beam_width_in = BEAM_C2["rejection_threshold"], BEAM_C2["beam_width_in"]
     for fast in (True, False):
         for _ in range(2):
             s.correct_lines(page, None, fast=fast, greedy=fast)
@@ -361,29 +511,74 @@ def measure_predict(args, topo, w, mapping, device, n_lines):
     return out
 
 
+def measure_strong(args, topo, w, mapping, local, rank, world):
+    """Strong scaling of the LITERAL configs: C3 = 1 000 000 lines fast greedy, C2 = 100 000 lines beamed, a fixed job
+    partitioned over the ranks by whole reference batches (shard.partition_batches), decoded through the product's
+    own sharding (shard.decode_job: host strings -> index encoding -> engine -> result arrays), all results on rank 0
+    in input order INSIDE the timed region."""
+    import torch
+    import torch.distributed as dist
+    from cor_asv_ann_b200 import shard
+    from cor_asv_ann_b200.synthetic import indices_to_lines
+    s = make_s2s(topo, w, mapping, local)
+    s.beam_budget_bytes = int(args.beam_budget_gb * (1 << 30))
+    s.rejection_threshold, s.beam_width_in = BEAM_C2["rejection_threshold"], BEAM_C2["beam_width_in"]
+    out = {}
+    for name, n_lines, fast, seed in (("C3_greedy_1M_lines", args.strong_greedy_lines, True, 1003), ("C2_beam_100k_lines", args.strong_beam_lines, False, 1002)):
+        if n_lines <= 0:
+            continue
+        # every rank materialises only its own part of the job (as it would read its part of a file)
+        parts = shard.partition_batches(n_lines, REF_BATCH, world)
+        lo, hi = (parts[rank][0][0], parts[rank][-1][1]) if parts[rank] else (0, 0)
+
+        mine = indices_to_lines(make_indices(hi - lo, seed + 31 * rank), mapping[1]) if hi > lo else []
+        job = shard.LocalPart(n_lines, lo, mine)
+        runner = shard.engine_runner(s, fast=fast, greedy=fast)
+        shard.decode_job(runner, indices_to_lines(make_indices(2 * REF_BATCH, 9), mapping[1]), batch_size=REF_BATCH)    # warm-up
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        res = shard.decode_job(runner, job, batch_size=REF_BATCH, superbatch=64, rank=rank, world_size=world)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            assert len(res) == n_lines
+            out[name] = {"lines": n_lines, "seconds": float(dt[0]), "chars_per_s": LINE_LEN * n_lines / float(dt[0]),
+                         "result": "chars/lens/scores arrays of all lines on rank 0 in input order (strings on demand)",
+                         "api": "cor_asv_ann_b200.shard.decode_job(engine_runner(Sequence2Sequence)): strings -> arrays, 64 reference batches per engine call"}
+    return out
+
+
 def bench_line(args, r, workload, world, peaks):
     peak = peaks.get("bf16_tflops_sustained", 1400.0)
     traffic, traffic_src = measured_traffic(workload, r["L"])
     peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1400 (of fallback)"
-    achieved = r["k_flops"] / (r["k_ms"] * 1e-3) / 1e12 if r["k_ms"] > 0 else 0.0
+    achieved = r["k_flops"] / (r["k_ms"] * 1e-3) / 1e12 if r["k_ms"] else None
+    whole = r["algo_flops_line"] * r["L"] * args.steps * world / (r["ms"] * 1e-3) / 1e12
     line = {
         "metric": "corrected chars/sec (%s)" % workload, "value": r["value"], "unit": "chars/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f16" if args.gemm_mode == 3 else "f32", "data": "synthetic", "config": workload_config(args, r["L"], workload),
+        "dtype": "f16" if args.gemm_mode == 3 else "f32", "data": "synthetic", "config": workload_config(workload, r["L"]),
         "e2e": {"value": r["e2e_value"], "unit": "chars/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                 "ms_per_step": r["e2e_ms"] / args.steps, "api": r["api"]},
         "gpu_launches": r["launches"],
         "clocks": r["clocks"],
-        "roofline": {"bound": "tensor", "kernel": "GEMM + fused LSTM-cell epilogue", "achieved": achieved,
-                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
-                     "peak_source": peak_src, "launches": r["k_n"], "kernel_ms_per_step": r["k_ms"] / args.steps,
-                     "kernel_share_of_step": r["k_ms"] / r["ms"] if r["ms"] else None,
-                     "precision": {1: "fp32 via FFMA", 3: "fp16 single pass: the reduced-precision VARIANT with the looser tolerance stated in DESIGN.md section 3, not the product default"}.get(args.gemm_mode, "fp32-grade (see DESIGN.md)")},
+        "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel<1,2,256,LstmEpi>: GEMM + fused LSTM-cell epilogue (CTA pairs)", "achieved": achieved,
+                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if (peak and achieved) else None, "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": peak_src, "launches_per_step": r["k_n"], "kernel_ms_per_step": r["k_ms"],
+                     "kernel_share_of_step": r["k_ms"] / r["prof_ms"] if r["prof_ms"] else None,
+                     "measured_in": "a separate pass with every launch of that kernel bracketed by CUDA events (not part of `value`)",
+                     "whole_step_tflops": whole, "whole_step_frac": whole / peak if peak else None,
+                     "precision": {1: "fp32 via FFMA", 3: "fp16 single pass: the reduced-precision VARIANT with the looser tolerance stated in DESIGN.md section 3, not the product default"}.get(args.gemm_mode, "fp32-grade three-pass fp16 hi/lo (ceiling 1/3 of the bf16 peak; see DESIGN.md)")},
         "algorithmic_gflop_per_line": r["algo_flops_line"] / 1e9,
-        "whole_step_tflops": r["algo_flops_line"] * r["L"] * args.steps * world / (r["ms"] * 1e-3) / 1e12,
     }
     line.update(r["extra"])
+    if r["parity"] is not None:
+        line["parity"] = r["parity"]
     return line
 
 
@@ -393,18 +588,20 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "beam"), choices=["greedy", "beam"])
-    ap.add_argument("--lines", type=int, default=int(os.environ.get("COR_BENCH_LINES", "16384")))
-    ap.add_argument("--beam-lines", type=int, default=9472)  # 37 x 256 lines: the GEMM tile count is a whole number of waves on 74 CTA pairs
+    ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "beam"), choices=sorted(WORKLOADS))
+    ap.add_argument("--lines", type=int, default=int(os.environ.get("COR_BENCH_LINES", "0")), help="lines per step per GPU (0 = the workload's default)")
     ap.add_argument("--beam-budget-gb", type=float, default=72.0)
     ap.add_argument("--gemm-mode", type=int, default=0)
     ap.add_argument("--cpu-lines", type=int, default=None)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the last timed step")
     ap.add_argument("--page-lines", type=int, default=32, help="lines of the small-batch (one page) latency leg; 0 = skip")
     ap.add_argument("--page-only", action="store_true", help="run just the small-batch latency leg")
     ap.add_argument("--predict-lines", type=int, default=65536, help="lines of the Sequence2Sequence.predict leg; 0 = skip")
     ap.add_argument("--predict-only", action="store_true", help="run just the predict leg")
-    ap.add_argument("--only", action="store_true", help="measure only --workload (skip the other decoder)")
+    ap.add_argument("--only", action="store_true", help="measure only --workload (skip every other leg)")
+    ap.add_argument("--strong-greedy-lines", type=int, default=1000000, help="fixed job of the strong-scaling leg, C3 (0 = skip)")
+    ap.add_argument("--strong-beam-lines", type=int, default=100000, help="fixed job of the strong-scaling leg, C2 (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -414,7 +611,7 @@ def main():
     import torch
     import torch.distributed as dist
     from cor_asv_ann_b200.engine import Engine
-    from tests.common import topo_dict
+    from cor_asv_ann_b200.synthetic import synthetic_alphabet
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -427,23 +624,48 @@ def main():
     os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    topo, w, mapping = build_model()
-    eng = Engine(topo_dict(topo), w, device=local, eos_index=1, gemm_mode=args.gemm_mode)
+    engines = {}
+
+    def engine_for(workload):
+        spec = WORKLOADS[workload]
+        key = (json.dumps(spec["topo"], sort_keys=True), spec["variant"])
+        if key not in engines:
+            engines[key] = Engine(dict(spec["topo"], window_width=5), build_weights(spec["topo"], spec["variant"]),
+                                  device=local, eos_index=1, gemm_mode=args.gemm_mode)
+        return engines[key]
+
+    mapping = synthetic_alphabet(C2["voc_size"])
+    w_c2 = build_weights(C2, "U")
     if args.predict_only:
-        r = measure_predict(args, topo, w, mapping, local, args.predict_lines)
+        r = measure_predict(args, C2, w_c2, mapping, local, args.predict_lines)
         sys.stdout.flush(); os.dup2(saved_stdout, 1)
         print(json.dumps({"predict": r}))
         return
     if args.page_only:
-        print_page = measure_page(args, eng, args.page_lines)
+        print_page = measure_page(args, engine_for("beam"), args.page_lines)
         sys.stdout.flush(); os.dup2(saved_stdout, 1)
         print(json.dumps({"page": print_page}))
         return
-    other = "greedy" if args.workload == "beam" else "beam"
-    main_r = measure(args, eng, args.workload, rank, world, local, sample_clocks=(rank == 0))
-    other_r = None if args.only else measure(args, eng, other, rank, world, local, sample_clocks=(rank == 0))
-    page_r = measure_page(args, eng, args.page_lines) if (rank == 0 and args.page_lines > 0 and not args.only) else None
-    predict_r = measure_predict(args, topo, w, mapping, local, args.predict_lines) if (rank == 0 and world == 1 and args.predict_lines > 0 and not args.only) else None
+    single = world == 1 and not args.only
+    par = 0 if (args.no_parity or world > 1) else 1
+    lines_of = lambda wl: args.lines or WORKLOADS[wl]["lines"]
+    main_r = measure(args, engine_for(args.workload), args.workload, lines_of(args.workload), rank, world, local, sample_clocks=(rank == 0),
+                     parity_lines=par * {"beam": 64, "greedy": 256, "beam_competitive": 8, "beam_stress": 1, "c4": 0}[args.workload])
+    others = {}
+    if not args.only:
+        first = "greedy" if args.workload == "beam" else "beam"
+        others[first] = measure(args, engine_for(first), first, lines_of(first), rank, world, local, sample_clocks=(rank == 0),
+                                parity_lines=par * (256 if first == "greedy" else 64))
+    if single:
+        short = argparse.Namespace(**dict(vars(args), steps=2, warmup=3))
+        for wl, n_par in (("beam_competitive", 8), ("beam_stress", 1), ("c4", 0)):
+            if wl != args.workload:
+                others[wl] = (short, measure(short, engine_for(wl), wl, WORKLOADS[wl]["lines"], rank, world, local, sample_clocks=False,
+                                             roofline_pass=False, parity_lines=par * n_par))
+    page_r = measure_page(args, engine_for("beam"), args.page_lines) if (rank == 0 and args.page_lines > 0 and single) else None
+    predict_r = measure_predict(args, C2, w_c2, mapping, local, args.predict_lines) if (rank == 0 and single and args.predict_lines > 0) else None
+    c1_r = measure_c1(local) if (rank == 0 and single) else None
+    strong_r = measure_strong(args, C2, w_c2, mapping, local, rank, world) if not args.only else None
 
     if world > 1:
         dist.barrier()
@@ -457,19 +679,30 @@ def main():
         except OSError:
             pass
         line = bench_line(args, main_r, args.workload, world, peaks)
-        if other_r is not None:
-            o = bench_line(args, other_r, other, world, peaks)
-            line["also"] = {k: o[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "gpu_launches",
-                                               "clocks", "roofline", "algorithmic_gflop_per_line", "whole_step_tflops")}
+        keys = ("metric", "value", "unit", "steps", "ms_per_step", "config", "e2e", "gpu_launches", "clocks", "roofline",
+                "algorithmic_gflop_per_line", "parity", "beam_iterations_per_line", "hypothesis_steps_per_line",
+                "hypotheses_per_line_and_iteration", "hypothesis_steps_per_s", "finals_per_line", "fringe_peak_mean", "fringe_peak_max",
+                "near_tie_decisions_per_line", "lines_without_final", "lines_equal_to_input", "near_tie_argmaxes_last_step")
+        also = {}
+        for wl, r in others.items():
+            a2, r2 = (r if isinstance(r, tuple) else (args, r))
+            o = bench_line(a2, r2, wl, world, peaks)
+            also[wl] = {k: o[k] for k in keys if k in o}
+        if also:
+            line["also"] = also
+        if c1_r is not None:
+            line.setdefault("also", {})["c1"] = c1_r
         if page_r is not None:
             line["page"] = page_r
         if predict_r is not None:
             line["predict"] = predict_r
+        if strong_r:
+            line["strong"] = dict(strong_r, scaling="strong", n_gpus=world)
         if world == 1 and not args.no_cpu:
             cores = host_threads()
             from threadpoolctl import threadpool_limits
             threadpool_limits(limits=cores)
-            n_cpu = args.cpu_lines or (256 if args.workload == "greedy" else 384)   # ~10-20 s of CPU work
+            n_cpu = args.cpu_lines or {"greedy": 256, "beam": 384}.get(args.workload, 4)   # ~10-20 s of CPU work
             v, dt = cpu_oracle_rate(args.workload, n_cpu)
             line["cpu_baseline"] = {"value": v, "unit": "chars/s", "cores": cores, "kind": "port",
                                     "sample": "%d lines of the same workload, numpy oracle (Keras/TF unavailable), %.1f s"

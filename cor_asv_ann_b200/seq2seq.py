@@ -124,51 +124,14 @@ class Sequence2Sequence(object):
 
     def _layer_shapes(self):
         """Keras layer name -> list of weight shapes, in Keras weight order."""
-        W, d, V, D = int(self.width), int(self.depth), int(self.voc_size), int(self._enc_dim)
-        shapes = {'char_input_projection': [(V, W)]}
-        for n in range(d):
-            bidi = n == 0 or self.deep_bidirectional_encoder
-            in_dim = W if n == 0 else (2 * W if (self.deep_bidirectional_encoder or n == 1) else W)
-            one = [(in_dim, 4 * W), (W, 4 * W), (4 * W,)]
-            shapes['encoder_lstm_%d' % (n + 1)] = one + one if bidi else one
-            if self.bridge_dense:
-                shapes['bridge_h_%d' % (n + 1)] = [(W, W), (W,)]
-                shapes['bridge_c_%d' % (n + 1)] = [(W, W), (W,)]
-        shapes['attention_dense'] = [(D, W)]
-        for n in range(d - 1):
-            shapes['decoder_lstm_%d' % (n + 1)] = [(W, 4 * W), (W, 4 * W), (4 * W,)]
-        shapes['decoder_lstm_%d' % d] = [(W, W), (W, 1), (W,), (1,), (W + D, 4 * W), (W, 4 * W), (4 * W,)]
-        return shapes
+        from .synthetic import layer_shapes
+        return layer_shapes(self.width, self.depth, self.voc_size, self.deep_bidirectional_encoder, self.bridge_dense)
 
-    def _init_weights(self, rng):
+    def _init_weights(self, rng, variant="K"):
         """Keras default initialisers (seq2seq.py:240: embedding N(0, 0.001); glorot-uniform kernels;
         orthogonal recurrent kernels; zero biases with unit forget gate)."""
-        W = int(self.width)
-
-        def glorot(shape):
-            lim = np.sqrt(6.0 / (shape[0] + shape[1]))
-            return rng.uniform(-lim, lim, size=shape).astype(np.float32)
-
-        def lstm(in_dim):
-            q, _ = np.linalg.qr(rng.standard_normal((4 * W, W)))
-            bias = np.zeros(4 * W, np.float32)
-            bias[W:2 * W] = 1.0
-            return [glorot((in_dim, 4 * W)), q.T.astype(np.float32), bias]
-
-        out = {}
-        for layer, shapes in self._layer_shapes().items():
-            if layer == 'char_input_projection':
-                out[layer] = [(rng.standard_normal(shapes[0]) * 0.001).astype(np.float32)]
-            elif layer == 'decoder_lstm_%d' % self.depth:
-                out[layer] = [glorot(shapes[0]), glorot(shapes[1]), np.zeros(shapes[2], np.float32),
-                              np.zeros(shapes[3], np.float32)] + lstm(shapes[4][0])
-            elif 'lstm' in layer:
-                out[layer] = sum((lstm(shapes[i][0]) for i in range(0, len(shapes), 3)), [])
-            elif len(shapes) == 2:      # bridge: Dense kernel + bias
-                out[layer] = [glorot(shapes[0]), np.zeros(shapes[1], np.float32)]
-            else:
-                out[layer] = [glorot(shapes[0])]
-        return out
+        from .synthetic import random_weights
+        return random_weights(self._layer_shapes(), self.width, self.depth, rng, variant)
 
     def configure(self, batch_size=None):
         '''Define encoder and decoder models for the configured parameters (seq2seq.py:190-489).
