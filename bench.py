@@ -629,6 +629,9 @@ def main():
     def engine_for(workload):
         spec = WORKLOADS[workload]
         key = (json.dumps(spec["topo"], sort_keys=True), spec["variant"])
+        for k2, e in engines.items():           # one workspace at a time: a beam workspace takes its whole budget
+            if k2 != key:
+                e.release_workspace()
         if key not in engines:
             engines[key] = Engine(dict(spec["topo"], window_width=5), build_weights(spec["topo"], spec["variant"]),
                                   device=local, eos_index=1, gemm_mode=args.gemm_mode)
@@ -663,6 +666,8 @@ def main():
                 others[wl] = (short, measure(short, engine_for(wl), wl, WORKLOADS[wl]["lines"], rank, world, local, sample_clocks=False,
                                              roofline_pass=False, parity_lines=par * n_par))
     page_r = measure_page(args, engine_for("beam"), args.page_lines) if (rank == 0 and args.page_lines > 0 and single) else None
+    for e in engines.values():                  # the legs below build their own Sequence2Sequence objects (own engines, own workspaces)
+        e.release_workspace()
     predict_r = measure_predict(args, C2, w_c2, mapping, local, args.predict_lines) if (rank == 0 and single and args.predict_lines > 0) else None
     c1_r = measure_c1(local) if (rank == 0 and single) else None
     strong_r = measure_strong(args, C2, w_c2, mapping, local, rank, world) if not args.only else None

@@ -82,6 +82,13 @@ class Engine:
             self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
         return self._ws
 
+    def release_workspace(self):
+        """Give the workspace back to the allocator (a process that holds several engines, one per model, calls this
+        before switching: a beam workspace is sized by its budget, tens of GB)."""
+        self._ws = None
+        self._geom = None
+        torch.cuda.empty_cache()
+
     @staticmethod
     def _stream():
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
