@@ -2,6 +2,7 @@
 // encoder scan, one decoder timestep, greedy driver.
 #include "model.h"
 #include "epilogue.cuh"
+#include "graphs.h"
 #include <cuda_fp16.h>
 #include <string.h>
 #include <stdlib.h>
@@ -68,6 +69,74 @@ static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int
     else rc = gemm_lstm_ffma(st, M, m_dev, N, s, n, e);
     prof_end(st, M, m_dev, N, s, n, e.xtab ? e.W : 0);
     return rc;
+}
+
+// ------------------------------------------------------------------ loop graphs (graphs.h)
+struct LoopGraphCache {
+    std::vector<LoopGraph> entries;
+    cudaStream_t capture = nullptr;
+    uint64_t tick = 0;
+};
+constexpr size_t kGraphCacheSize = 8;
+static LoopGraphCache* graph_cache(cor_model* m) {
+    if (!m->loop_graphs) m->loop_graphs = new LoopGraphCache();
+    return static_cast<LoopGraphCache*>(m->loop_graphs);
+}
+static void drop_graph(LoopGraph& g) {
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+    g.exec = nullptr; g.graph = nullptr;
+}
+cudaStream_t loop_capture_stream(cor_model* m) {
+    LoopGraphCache* c = graph_cache(m);
+    if (!c->capture && cudaStreamCreateWithFlags(&c->capture, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    return c->capture;
+}
+bool loop_graphs_enabled() {
+    const char* off = getenv("COR_NO_GRAPH");
+    return !prof().on && !(off && off[0] && off[0] != '0');
+}
+int loop_graph_lookup(cor_model* m, const std::vector<uint64_t>& key, LoopGraph** out) {
+    LoopGraphCache* c = graph_cache(m);
+    ++c->tick;
+    for (auto& e : c->entries)
+        if (e.key == key) { e.used = c->tick; *out = &e; return 0; }
+    if (c->entries.size() < kGraphCacheSize) {
+        c->entries.reserve(kGraphCacheSize);
+        c->entries.emplace_back();
+        *out = &c->entries.back();
+    } else {
+        LoopGraph* lru = &c->entries[0];
+        for (auto& e : c->entries) if (e.used < lru->used) lru = &e;
+        // an executable graph may still be running on a caller's stream: drain the device before destroying one
+        COR_CUDA(cudaDeviceSynchronize());
+        drop_graph(*lru);
+        *out = lru;
+    }
+    (*out)->key = key; (*out)->used = c->tick; (*out)->body_kernels = 0;
+    return 0;
+}
+int loop_graph_begin(LoopGraph* g, const cudaKernelNodeParams& first, cudaGraphConditionalHandle* cond, cudaGraph_t* body) {
+    // the handle is an argument of `first` (through its kernelParams, which point at *cond): create it before the node
+    drop_graph(*g);
+    COR_CUDA(cudaGraphCreate(&g->graph, 0));
+    COR_CUDA(cudaGraphConditionalHandleCreate(cond, g->graph, 0, 0));
+    cudaGraphNode_t n_first, n_while;
+    COR_CUDA(cudaGraphAddKernelNode(&n_first, g->graph, nullptr, 0, &first));
+    cudaGraphNodeParams cp{};
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = *cond; cp.conditional.type = cudaGraphCondTypeWhile; cp.conditional.size = 1;
+    COR_CUDA(cudaGraphAddNode(&n_while, g->graph, &n_first, 1, &cp));
+    *body = cp.conditional.phGraph_out[0];
+    return 0;
+}
+void loop_graphs_release(cor_model* m) {
+    if (!m || !m->loop_graphs) return;
+    LoopGraphCache* c = static_cast<LoopGraphCache*>(m->loop_graphs);
+    for (auto& e : c->entries) drop_graph(e);
+    if (c->capture) cudaStreamDestroy(c->capture);
+    delete c;
+    m->loop_graphs = nullptr;
 }
 
 // ------------------------------------------------------------------ weights
@@ -273,6 +342,7 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
     ws->o_score = c.take<double>(B);
     ws->o_len = c.take<int32_t>(B);
     ws->o_ties = c.take<int32_t>(B);
+    ws->loop_state = c.take<int32_t>(4);
     ws->o_align = want_align ? c.take<float>(S * BT) : nullptr;
     ws->bytes = (c.off + 255) & ~size_t(255);
     return 0;
@@ -442,7 +512,7 @@ int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) 
     a.wq = io.wq; a.u = ws.u; a.enc = ws.enc_out(); a.enc_lo = ws.enc_out_lo();
     a.a_prev = io.a_in; a.row_line = io.row_line; a.line_T = ws.row_T;
     a.v_a = m->v_a; a.b_v = m->b_v; a.a_out = io.a_out; a.ctx = io.ctx; a.ctx_lo = io.ctx_lo;
-    a.align_log = io.align_log;
+    a.align_log = io.align_log; a.step_dev = io.step_dev; a.step_off = io.step_off; a.align_stride = io.align_stride;
     a.R = R; a.r_dev = io.r_dev; a.L = ws.B; a.t_max = ws.T; a.W = W; a.D = D;
     a.window = m->cfg.window_width; a.inclusive = 1;
     // The attention of this step depends on the previous step only (query, alignment); with lower
@@ -527,6 +597,17 @@ static int copy_out(cudaStream_t st, const float* hi, const float* lo, float* ds
     return 0;
 }
 
+// Loop condition of the fast-greedy graph.  state[0] = timestep of the body's first step, state[1] = lines finished
+// so far (counted by the softmax launches); total accumulates the steps run (launch count).
+__global__ void greedy_cond_kernel(int32_t* state, int64_t* total, int s_max, int n_rows, cudaGraphConditionalHandle cond, int init) {
+    if (init) { cudaGraphSetConditional(cond, s_max > 0 ? 1u : 0u); return; }
+    const int step = state[0] + 2;
+    const bool more = step < s_max && state[1] < n_rows;
+    state[0] = step;
+    if (total) total[0] += 2;
+    cudaGraphSetConditional(cond, more ? 1u : 0u);
+}
+
 static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
     const int B = ws.B, T = ws.T, W = m->W, d = m->d;
     const size_t BW = (size_t)B * W;
@@ -575,26 +656,80 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         if (rc == 0) return launch_finish_scores(st, ws.o_score, ws.o_len, B);
         // rc == 2: the cooperative launch was refused and nothing ran -- per-timestep launches below
     }
-    for (int s = 0; s < S; ++s) {
+    // one timestep: decoder cells, attention, logits, softmax + greedy bookkeeping.  `s` < 0: the timestep is read on the
+    // device (loop graph; `off` = position of the step inside the graph body)
+    auto timestep = [&](cudaStream_t s_, int s, int off, int cur_) -> int {
         StepIO io{};
         io.R = B; io.first = (s == 0);
         io.p = ws.p; io.p_lo = ws.p_lo; io.x = ws.x; io.x_lo = ws.x_lo;
         for (int n = 0; n < d; ++n) {
-            io.h_in[n] = ws.dh[cur][n]; io.h_in_lo[n] = ws.dh_lo[cur][n];
-            io.h_out[n] = ws.dh[cur ^ 1][n]; io.h_out_lo[n] = ws.dh_lo[cur ^ 1][n];
+            io.h_in[n] = ws.dh[cur_][n]; io.h_in_lo[n] = ws.dh_lo[cur_][n];
+            io.h_out[n] = ws.dh[cur_ ^ 1][n]; io.h_out_lo[n] = ws.dh_lo[cur_ ^ 1][n];
             io.c_in[n] = ws.dc[n]; io.c_out[n] = ws.dc[n];
         }
-        io.a_in = ws.a[cur]; io.a_out = ws.a[cur ^ 1];
-        io.align_log = ws.o_align ? ws.o_align + (size_t)s * B * T : nullptr;
+        io.a_in = ws.a[cur_]; io.a_out = ws.a[cur_ ^ 1];
+        if (s >= 0) io.align_log = ws.o_align ? ws.o_align + (size_t)s * B * T : nullptr;
+        else { io.align_log = ws.o_align; io.step_dev = ws.loop_state; io.step_off = off; io.align_stride = (long long)B * T; }
         io.wq = ws.wq; io.ctx = ws.ctx; io.ctx_lo = ws.ctx_lo; io.logits = ws.logits;
-        io.wq_ready = (s > 0); io.wq_next = ws.wq;
-        if (decoder_core(m, ws, io, st)) return 1;
+        io.wq_ready = (s != 0); io.wq_next = ws.wq;
+        if (decoder_core(m, ws, io, s_)) return 1;
         GreedyArgs g{};
         g.logits = ws.logits; g.p = ws.p; g.p_lo = ws.p_lo; g.row_T = ws.row_T; g.live = ws.live;
         g.out_chars = ws.o_chars; g.out_probs = ws.o_probs; g.score_sum = ws.o_score; g.out_len = ws.o_len; g.done = ws.done;
         g.out_ties = ws.o_ties;
-        g.R = B; g.V = m->V; g.step = s; g.s_max = S; g.eos = m->cfg.eos_index;
-        if (launch_softmax_greedy(st, g)) return 1;
+        g.R = B; g.V = m->V; g.step = s >= 0 ? s : off; g.s_max = S; g.eos = m->cfg.eos_index;
+        if (s < 0) { g.step_dev = ws.loop_state; g.done_count = ws.loop_state + 1; }
+        return launch_softmax_greedy(s_, g);
+    };
+    if (loop_graphs_enabled()) {
+        // ---- all timesteps as ONE graph launch: WHILE { timestep, timestep, condition } with the step counter and the
+        // "some line still wants a step" flag on the device -- the loop ends when every line has emitted its newline
+        // (the reference steps on to 2T and ignores finished lines, seq2seq.py:1255-1256: same results).
+        // Step 0 is made uniform with the rest: zero feedback row instead of a skipped K-segment (adds exact zeros
+        // to the accumulator), its query from its own small GEMM.
+        const int top = d - 1;
+        COR_CUDA(cudaMemsetAsync(ws.p, 0, (size_t)B * m->Vp * 4, st));
+        if (ws.p_lo) COR_CUDA(cudaMemsetAsync(ws.p_lo, 0, (size_t)B * m->Vp * 4, st));
+        COR_CUDA(cudaMemsetAsync(ws.loop_state, 0, 16, st));
+        {
+            GemmSeg sq = {ws.dh[0][top], W, ws.dh_lo[0][top], m->Wa.hi, m->Wa.ld, m->Wa.lo, W};
+            StoreEpi eq{ws.wq, W, nullptr, m->b_UW, 0};
+            if (gemm_store(m, st, B, nullptr, W, &sq, 1, eq)) return 1;
+        }
+        LoopGraph* g = nullptr;
+        const std::vector<uint64_t> key = {0x63EEDull, (uint64_t)(uintptr_t)ws.row_T, (uint64_t)B, (uint64_t)T, (uint64_t)ws.k,
+                                           (uint64_t)(ws.o_align != nullptr), (uint64_t)(ws.val != nullptr), (uint64_t)m->passes,
+                                           (uint64_t)(m->side != nullptr), (uint64_t)ws.bytes};
+        if (loop_graph_lookup(m, key, &g)) return 1;
+        if (!g->exec) {
+            cudaGraphConditionalHandle cond; cudaGraph_t body;
+            int32_t* state = ws.loop_state; int64_t* total = m->dev_counters; int s_max = S, init = 1, no_init = 0;
+            int n_rows = B;
+            void* kargs[6] = {(void*)&state, (void*)&total, (void*)&s_max, (void*)&n_rows, (void*)&cond, (void*)&init};
+            cudaKernelNodeParams kp{};
+            kp.func = (void*)greedy_cond_kernel; kp.gridDim = dim3(1); kp.blockDim = dim3(1); kp.kernelParams = kargs;
+            if (loop_graph_begin(g, kp, &cond, &body)) return 1;
+            cudaStream_t cs = loop_capture_stream(m);
+            COR_CHECK(cs, "no capture stream");
+            const int64_t before = ctx().launches;
+            COR_CUDA(cudaStreamBeginCaptureToGraph(cs, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+            int rc = timestep(cs, -1, 0, 0) || timestep(cs, -1, 1, 1);
+            if (!rc) { greedy_cond_kernel<<<1, 1, 0, cs>>>(state, total, s_max, n_rows, cond, no_init); rc = cudaGetLastError() != cudaSuccess; }
+            cudaGraph_t captured = nullptr;
+            const cudaError_t ce = cudaStreamEndCapture(cs, &captured);
+            g->body_kernels = (int)(ctx().launches - before);
+            ctx().launches = before;            // captured, not run
+            COR_CHECK(!rc, "capturing the greedy timestep failed");
+            COR_CUDA(ce);
+            COR_CUDA(cudaGraphInstantiate(&g->exec, g->graph, 0));
+        }
+        m->greedy_step_kernels = g->body_kernels / 2;
+        COR_CUDA(cudaGraphLaunch(g->exec, st));
+        ctx().launches += 1;
+        return launch_finish_scores(st, ws.o_score, ws.o_len, B);
+    }
+    for (int s = 0; s < S; ++s) {
+        if (timestep(st, s, 0, cur)) return 1;
         cur ^= 1;
     }
     return launch_finish_scores(st, ws.o_score, ws.o_len, B);
@@ -610,6 +745,14 @@ const char* cor_last_error(void) { return g_error.c_str(); }
 int cor_abi_version(void) { return 2; }
 int64_t cor_launch_count(cor_model* m, int reset) {
     if (!m) return -1;
+    if (m->dev_counters && m->greedy_step_kernels) {    // timesteps the fast-greedy loop graphs ran (counted on the device)
+        int64_t steps = 0;
+        if (cudaSetDevice(m->device) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess &&
+            cudaMemcpy(&steps, m->dev_counters, 8, cudaMemcpyDeviceToHost) == cudaSuccess) {
+            m->ctx.launches += steps * m->greedy_step_kernels + steps / 2;
+            cudaMemset(m->dev_counters, 0, 8);
+        }
+    }
     const int64_t v = m->ctx.launches;
     if (reset) m->ctx.launches = 0;
     return v;
@@ -798,6 +941,7 @@ int cor_model_finalize(cor_model* m) {
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
     }
     { void* gb = nullptr; if (dev_alloc(m, 256, &gb)) return 1; m->grid_bar = (unsigned*)gb; }
+    { void* dc = nullptr; if (dev_alloc(m, 64, &dc)) return 1; m->dev_counters = (int64_t*)dc; COR_CUDA(cudaMemset(dc, 0, 64)); }
     if (m->split && m->passes == 3 && d == 2 && m->fuse_pe && !m->cfg.lm_predict) {
         // page decoder: the two cells' kernels concatenated along K, so that a CTA's K-slice is one contiguous range
         const LstmW& lo_w = m->dec[0]; const LstmW& tw = m->dec[1];
@@ -824,6 +968,7 @@ int cor_model_finalize(cor_model* m) {
 void cor_model_destroy(cor_model* m) {
     if (!m) return;
     cudaSetDevice(m->device);
+    loop_graphs_release(m);
     if (m->side) { cudaStreamSynchronize(m->side); cudaStreamDestroy(m->side); }
     if (m->ev_fork) cudaEventDestroy(m->ev_fork);
     if (m->ev_join) cudaEventDestroy(m->ev_join);

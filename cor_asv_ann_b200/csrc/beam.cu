@@ -24,6 +24,7 @@
 // loop in a smaller wave with a larger arena; results do not depend on the wave a line ran in.
 #include "model.h"
 #include "epilogue.cuh"
+#include "graphs.h"
 #include <math.h>
 #include <float.h>
 #include <string.h>
@@ -216,7 +217,9 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
 // ------------------------------------------------------------------ scan: row offsets, row total, active lines
 // One block; thread t owns the consecutive lines [t*per, (t+1)*per): all loads are issued at once,
 // one block-wide scan of the per-thread sums, then the row bases.  Row order = line order.
-__global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b) {
+// `set_cond`: the launch is part of the iteration graph (run_wave): the kernel counts the body and decides whether the
+// WHILE node runs another one (cudaGraphSetConditional is only valid inside the graph that owns the handle).
+__global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b, cudaGraphConditionalHandle cond, int set_cond) {
     __shared__ int s_wsum[32];
     __shared__ int s_total, s_active;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -245,7 +248,20 @@ __global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b) {
     if (total) atomicMax(&s_total, total);
     if (active) atomicAdd(&s_active, active);
     __syncthreads();
-    if (tid == 0) { b.counters[0] = s_total; b.counters[1] = s_active; }
+    if (tid == 0) {
+        b.counters[0] = s_total; b.counters[1] = s_active;
+        if (set_cond) {
+            // a line runs at most 2T iterations (beam_pop_kernel), so the bound below never cuts a search short; it keeps a
+            // protocol bug from looping on the device forever
+            const int bodies = ++b.counters[3];
+            cudaGraphSetConditional(cond, ((s_total > 0 || s_active > 0) && bodies <= 2 * b.T + 2) ? 1u : 0u);
+        }
+    }
+}
+
+// First node of the iteration graph: the WHILE condition from the counters the last directly launched scan left.
+__global__ void beam_cond_kernel(BeamDev b, cudaGraphConditionalHandle cond) {
+    cudaGraphSetConditional(cond, (b.counters[0] > 0 || b.counters[1] > 0) ? 1u : 0u);
 }
 
 // One warp per line: the rows of a line are its popped nodes in fringe order.
@@ -1160,6 +1176,16 @@ int check_params(const cor_model* m, const cor_beam_params* bp) {
     return 0;
 }
 
+
+std::vector<uint64_t> graph_key(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, const Plan& plan, bool want_align,
+                                const void* workspace, bool has_val) {
+    uint64_t thr = 0, rej = 0;
+    memcpy(&thr, &bp->beam_threshold_in, 8); memcpy(&rej, &bp->rejection_threshold, 8);
+    return {0xBEA3ull, (uint64_t)(uintptr_t)workspace, (uint64_t)L, (uint64_t)T, (uint64_t)k, (uint64_t)plan.quota_x, (uint64_t)plan.Rcap,
+            (uint64_t)bp->batch_size, (uint64_t)bp->beam_width_in, (uint64_t)bp->beam_width_out, (uint64_t)bp->n_best, thr, rej,
+            (uint64_t)want_align, (uint64_t)has_val, (uint64_t)m->passes, (uint64_t)(m->side != nullptr)};
+}
+
 // One wave over `L` lines given as HOST arrays; results to HOST arrays (same row order).
 int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const int32_t* h_idx, const float* h_val,
              const cor_beam_params* bp, const Plan& plan, void* workspace,
@@ -1177,6 +1203,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     if (h_val) COR_CUDA(cudaMemcpyAsync(ws.val, h_val, n * 4, kin, st));
     else { ws.val = nullptr; b.val = nullptr; }
     if (run_encoder(m, ws, st)) return 1;
+    COR_CUDA(cudaMemsetAsync(b.counters, 0, 16, st));
     beam_init_kernel<<<L, 128, 0, st>>>(b); ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     const int split = m->split ? 1 : 0;
@@ -1184,34 +1211,78 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const size_t expand_smem = (size_t)(m->cfg.lm_predict ? 2 : 1) * m->Vp * 4;
     const size_t push_smem = (size_t)MAX_NEW * 12;
     const int t_hi = T;      // every row_T is <= t_max
-    for (int it = 0; it <= 2 * t_hi; ++it) {
-        beam_pop_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
-        beam_scan_kernel<<<1, 1024, 0, st>>>(b);
+    // pop + scan: which hypotheses of every line are expanded next, their rows, and whether anything is left to do
+    auto select = [&](cudaStream_t s_, cudaGraphConditionalHandle cond, int set_cond) -> int {
+        beam_pop_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
+        beam_scan_kernel<<<1, 1024, 0, s_>>>(b, cond, set_cond);
         ctx().launches += 2;
-        if (it % 8 == 7 || it == 2 * t_hi) {          // host check: has every line finished?
+        COR_CUDA(cudaGetLastError());
+        return 0;
+    };
+    // one decoder step over the selected rows and the insertion of their children
+    auto iteration = [&](cudaStream_t s_, bool roots) -> int {
+        beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
+        beam_gather_kernel<<<row_grid, 128, 0, s_>>>(b, split);
+        ctx().launches += 2;
+        COR_CUDA(cudaGetLastError());
+        io.wq_ready = !roots;     // iteration 0 expands the roots: their query comes from the encoder state
+        if (decoder_core(m, ws, io, s_)) return 1;
+        const int warp_grid = std::min((plan.Rcap + 3) / 4, 148 * 8);
+        switch (m->Vp) {        // score row in registers when it fits (32 values per lane at most)
+            case 128:  beam_expand_warp_kernel<4><<<warp_grid, 128, 0, s_>>>(b, split); break;
+            case 256:  beam_expand_warp_kernel<8><<<warp_grid, 128, 0, s_>>>(b, split); break;
+            case 512:  beam_expand_warp_kernel<16><<<warp_grid, 128, 0, s_>>>(b, split); break;
+            case 1024: beam_expand_warp_kernel<32><<<warp_grid, 128, 0, s_>>>(b, split); break;
+            default:   beam_expand_kernel<<<row_grid, 128, expand_smem, s_>>>(b, split);
+        }
+        beam_push_small_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
+        beam_push_kernel<<<std::min(L, 148 * 4), 256, push_smem, s_>>>(b);
+        ctx().launches += 3;
+        COR_CUDA(cudaGetLastError());
+        return 0;
+    };
+    // Iterations 1.. are ONE graph launch: a WHILE node whose body is {iteration, select} and whose condition the
+    // scan kernel sets on the device -- no launch latency between the ~10 kernels of an iteration and no host
+    // round trip to find out that every line has finished.  (Per-launch profiling brackets launches with events on
+    // the host: it keeps the host loop, as does COR_NO_GRAPH=1.)
+    const bool use_graph = loop_graphs_enabled();
+    int graph_body_kernels = 0;
+    if (select(st, 0, 0)) return 1;
+    for (int it = 0; it <= 2 * t_hi; ++it) {
+        if (use_graph && it == 1) {
+            LoopGraph* g = nullptr;
+            if (loop_graph_lookup(m, graph_key(m, L, T, k, bp, plan, o_align != nullptr, workspace, ws.val != nullptr), &g)) return 1;
+            if (!g->exec) {
+                cudaGraphConditionalHandle cond; cudaGraph_t body;
+                void* kargs[2] = {(void*)&b, (void*)&cond};
+                cudaKernelNodeParams kp{};
+                kp.func = (void*)beam_cond_kernel; kp.gridDim = dim3(1); kp.blockDim = dim3(1); kp.kernelParams = kargs;
+                if (loop_graph_begin(g, kp, &cond, &body)) return 1;
+                cudaStream_t cs = loop_capture_stream(m);
+                COR_CHECK(cs, "no capture stream");
+                const int64_t before = ctx().launches;
+                COR_CUDA(cudaStreamBeginCaptureToGraph(cs, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+                const int rc = iteration(cs, false) || select(cs, cond, 1);
+                cudaGraph_t captured = nullptr;
+                const cudaError_t ce = cudaStreamEndCapture(cs, &captured);
+                g->body_kernels = (int)(ctx().launches - before);
+                ctx().launches = before;            // captured, not run
+                if (rc) return 1;
+                COR_CUDA(ce);
+                COR_CUDA(cudaGraphInstantiate(&g->exec, g->graph, 0));
+            }
+            COR_CUDA(cudaGraphLaunch(g->exec, st));
+            ctx().launches += 1;                    // beam_cond_kernel; the bodies are counted after the wave's final sync
+            graph_body_kernels = g->body_kernels;
+            break;
+        }
+        if (!use_graph && (it % 8 == 7 || it == 2 * t_hi)) {          // host check: has every line finished?
             int32_t cnt[2] = {0, 0};
             COR_CUDA(cudaMemcpyAsync(cnt, b.counters, 8, cudaMemcpyDeviceToHost, st));
             COR_CUDA(cudaStreamSynchronize(st));
             if (cnt[1] == 0 && cnt[0] == 0) break;
         }
-        beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
-        beam_gather_kernel<<<row_grid, 128, 0, st>>>(b, split);
-        ctx().launches += 2;
-        COR_CUDA(cudaGetLastError());
-        io.wq_ready = it > 0;     // iteration 0 expands the roots: their query comes from the encoder state
-        if (decoder_core(m, ws, io, st)) return 1;
-        const int warp_grid = std::min((plan.Rcap + 3) / 4, 148 * 8);
-        switch (m->Vp) {        // score row in registers when it fits (32 values per lane at most)
-            case 128:  beam_expand_warp_kernel<4><<<warp_grid, 128, 0, st>>>(b, split); break;
-            case 256:  beam_expand_warp_kernel<8><<<warp_grid, 128, 0, st>>>(b, split); break;
-            case 512:  beam_expand_warp_kernel<16><<<warp_grid, 128, 0, st>>>(b, split); break;
-            case 1024: beam_expand_warp_kernel<32><<<warp_grid, 128, 0, st>>>(b, split); break;
-            default:   beam_expand_kernel<<<row_grid, 128, expand_smem, st>>>(b, split);
-        }
-        beam_push_small_kernel<<<(L + 7) / 8, 256, 0, st>>>(b);
-        beam_push_kernel<<<std::min(L, 148 * 4), 256, push_smem, st>>>(b);
-        ctx().launches += 3;
-        COR_CUDA(cudaGetLastError());
+        if (iteration(st, it == 0) || select(st, 0, 0)) return 1;
     }
     // results: staged in the wave's own buffers, n_best slots per line
     const size_t S = 2 * (size_t)T * b.n_best;
@@ -1229,7 +1300,10 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     COR_CUDA(cudaMemcpyAsync(o_stats, b.o_stats, (size_t)L * kStats * 8, kout, st));
     COR_CUDA(cudaMemcpyAsync(host_stats, b.o_stats, (size_t)L * kStats * 8, cudaMemcpyDeviceToHost, st));
     if (o_align) COR_CUDA(cudaMemcpyAsync(o_align, d_align, (size_t)L * S * T * 4, kout, st));
+    int32_t h_cnt[4] = {0, 0, 0, 0};
+    if (graph_body_kernels) COR_CUDA(cudaMemcpyAsync(h_cnt, b.counters, 16, cudaMemcpyDeviceToHost, st));
     COR_CUDA(cudaStreamSynchronize(st));
+    ctx().launches += (int64_t)h_cnt[3] * graph_body_kernels;     // kernels the WHILE node ran (bodies counted by the scan kernel)
     return 0;
 }
 

@@ -178,6 +178,8 @@ struct AttnArgs {
     float* a_out;              // [R][t_max]
     float* ctx; float* ctx_lo; // [R][D]
     float* align_log;          // optional [R][t_max] extra copy (alignment history)
+    // timestep on the device (loop graphs): the history row block of this step is align_log + (*step_dev + step_off) * align_stride
+    const int* step_dev; int step_off; long long align_stride;
     int R; const int* r_dev; int L; int t_max; int W; int D; int window; int inclusive;
 };
 int launch_attention(cudaStream_t st, const AttnArgs& a);
@@ -190,6 +192,8 @@ struct GreedyArgs {
     int32_t* out_chars; float* out_probs; double* score_sum; int32_t* out_len; uint8_t* done;
     int32_t* out_ties;         // [R] or nullptr: emitted characters whose runner-up is within kTieMargin (relative)
     int R; int V; int step; int s_max; int eos;
+    // loop graphs: the timestep is *step_dev + step; *done_count counts the lines that have finished
+    const int* step_dev; int32_t* done_count;
 };
 // An argmax whose runner-up lies within this relative margin is logged as a near-tie: fp32-grade implementations
 // (this one, Keras/TF, the numpy oracle) may legitimately pick either, so parity tests report such lines separately.

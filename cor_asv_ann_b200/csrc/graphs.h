@@ -1,0 +1,34 @@
+// graphs.h — executable CUDA graphs of the two decoder loops (beam search iterations, fast-greedy timesteps).
+//
+// Both loops are a WHILE conditional node whose body is one iteration (a handful of kernel launches) and whose
+// condition a kernel of the body sets on the device: no launch latency between the kernels of an iteration, no
+// host round trip to learn that every line has finished, and the loop ends as soon as it has (the reference
+// keeps stepping finished lines and ignores them, seq2seq.py:1255-1256, so stopping early changes nothing).
+// Kernel arguments are frozen into a graph, so one is valid for exactly one (workspace, geometry, parameters)
+// combination; a handle keeps the last few (a page-by-page caller repeats few geometries, the bench one).
+#pragma once
+#include "model.h"
+#include <vector>
+
+namespace cor {
+
+struct LoopGraph {
+    std::vector<uint64_t> key;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int body_kernels = 0;          // kernel nodes of one body
+    uint64_t used = 0;
+};
+
+// Entry for `key` (created empty -- exec == nullptr -- if absent, evicting the least recently used one).
+int loop_graph_lookup(cor_model* m, const std::vector<uint64_t>& key, LoopGraph** out);
+// Stream to capture bodies on (the caller's stream may be the legacy default stream, which cannot capture).
+cudaStream_t loop_capture_stream(cor_model* m);
+void loop_graphs_release(cor_model* m);
+// False while per-launch profiling is on (it brackets launches with events from the host) or COR_NO_GRAPH is set.
+bool loop_graphs_enabled();
+
+// WHILE node behind `first` (a kernel node that sets the initial condition): returns the body graph to capture into.
+int loop_graph_begin(LoopGraph* g, const cudaKernelNodeParams& first, cudaGraphConditionalHandle* cond, cudaGraph_t* body);
+
+}  // namespace cor

@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
     __syncwarp();
     // alignment row: zero everywhere, a_j = e_j / sum in the window
     float* ao = a.a_out + (size_t)row * a.t_max;
-    float* al = a.align_log ? a.align_log + (size_t)row * a.t_max : nullptr;
+    float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)row * a.t_max : nullptr;
     for (int j = lane; j < a.t_max; j += 32) {
         const int q = j - j0;
         const float v = (q >= 0 && q < nj) ? s_w[wid][q] : 0.f;
@@ -230,7 +230,12 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
     if (!GREEDY) return;
     top2_merge(best, best_v, second);
     if (lane == 0) {
-        const bool alive = !g.done[row] && g.live[row] && g.step < 2 * g.row_T[row];
+        const int step = g.step_dev ? *g.step_dev + g.step : g.step;
+        const int s_row = 2 * g.row_T[row];
+        const bool alive = !g.done[row] && g.live[row] && step < s_row;
+        // loop graphs: a line is counted ONCE, at the step it finishes (newline, last step, or never started) -- the
+        // loop ends when the count reaches the number of rows; one atomic per line and call, not per step
+        if (g.done_count && (alive ? (best_v == g.eos || step + 1 >= s_row) : step == 0)) atomicAdd(g.done_count, 1);
         if (alive) {
             const int n = g.out_len[row];
             g.out_chars[(size_t)row * g.s_max + n] = best_v;

@@ -70,6 +70,9 @@ struct cor_model {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cor::Mat LowCat, TopCat;  // page decoder (decpage.cu): [E.Kx | R] and [Kx | Kc | R] concatenated along K (depth 2 only)
     unsigned* grid_bar = nullptr;         // grid barrier counter of the persistent recurrence (recur.cu)
+    void* loop_graphs = nullptr;          // executable graphs of the decoder loops (graphs.h)
+    int64_t* dev_counters = nullptr;      // device: [0] fast-greedy timesteps run by loop graphs since the last cor_launch_count
+    int greedy_step_kernels = 0;          // kernels of one fast-greedy timestep (for that count)
     // cor_set_encoding: encoder results handed in by the caller (decode_sequence_*(encoder_outputs=...),
     // decoder_model.predict_on_batch); while set, run_encoder imports them instead of running the encoder graph
     struct { const float* enc_out = nullptr; const float* states = nullptr; int n_rows = 0, t_max = 0; } preset;
@@ -105,6 +108,7 @@ struct Ws {
     int32_t* o_chars = nullptr; float* o_probs = nullptr; double* o_score = nullptr; int32_t* o_len = nullptr;
     int32_t* o_ties = nullptr;
     float* o_align = nullptr;
+    int32_t* loop_state = nullptr;                       // [4] fast-greedy loop graph: timestep, lines finished
     float* enc_out() const { return seq.back(); }
     float* enc_out_lo() const { return seq_lo.back(); }
 };
@@ -120,6 +124,7 @@ struct StepIO {
     float* h_out[8] = {}; float* h_out_lo[8] = {};
     const float* c_in[8] = {}; float* c_out[8] = {};
     const float* a_in = nullptr; float* a_out = nullptr; float* align_log = nullptr;
+    const int* step_dev = nullptr; int step_off = 0; long long align_stride = 0;   // loop graphs: see AttnArgs
     float *wq = nullptr, *ctx = nullptr, *ctx_lo = nullptr, *logits = nullptr;
     bool wq_ready = false;                   // wq already holds h_in[top].W_a + b (written by the previous step)
     float* wq_next = nullptr;                // if set: the logits launch also writes h_out[top].W_a + b here

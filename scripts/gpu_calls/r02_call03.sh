@@ -1,0 +1,10 @@
+# round 2, call 3: loop graphs (beam iterations, greedy timesteps with early exit): tests, then A/B against the host loops
+mkdir -p gpurun_out
+( timeout 900 python -m pytest tests/test_gpu_loop_graph.py -m gpu -x -q -s 2>&1 | tail -15 ) | tee gpurun_out/r02_c03_tests.log
+( timeout 900 python -m pytest tests/test_gpu_beam.py tests/test_gpu_core.py tests/test_gpu_reference_pin.py tests/test_gpu_timed_shape.py tests/test_gpu_seq2seq.py -m gpu -x -q 2>&1 | tail -5 ) | tee -a gpurun_out/r02_c03_tests.log
+for g in 0 1; do
+  COR_NO_GRAPH=$g timeout 300 python bench.py --page-only --page-lines 32 > gpurun_out/r02_c03_page32_nograph$g.json 2>> gpurun_out/r02_c03.err; cut -c1-700 gpurun_out/r02_c03_page32_nograph$g.json; echo
+  COR_NO_GRAPH=$g timeout 600 python bench.py --only --workload beam --no-cpu --no-parity --strong-greedy-lines 0 --strong-beam-lines 0 > gpurun_out/r02_c03_beam_nograph$g.json 2>> gpurun_out/r02_c03.err; cut -c1-300 gpurun_out/r02_c03_beam_nograph$g.json; echo
+  COR_NO_GRAPH=$g timeout 600 python bench.py --only --workload greedy --no-cpu --no-parity --strong-greedy-lines 0 --strong-beam-lines 0 > gpurun_out/r02_c03_greedy_nograph$g.json 2>> gpurun_out/r02_c03.err; cut -c1-300 gpurun_out/r02_c03_greedy_nograph$g.json; echo
+done
+tail -5 gpurun_out/r02_c03.err

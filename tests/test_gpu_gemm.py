@@ -67,6 +67,28 @@ def test_tcgen05_small_magnitudes():
     assert err < 2e-7
 
 
+def test_tcgen05_small_magnitude_weights():
+    """Small WEIGHTS (the B operand: Keras-init embedding sigma 0.001, and the tables derived from it): the residual of
+    every element is subnormal, the representation keeps ~2^-15 relative, and the product error is bounded in
+    absolute terms -- |err| <= K * max|a| * 2^-25-ish, far below the 1e-4 parity budget -- NOT in fp32-relative ones."""
+    from cor_asv_ann_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator(device="cuda").manual_seed(6)
+    M, N, K = 256, 512, 512
+    A = torch.tanh(torch.randn(M, K, device="cuda", generator=g))     # LSTM outputs in (-1, 1)
+    B = torch.randn(N, K, device="cuda", generator=g) * 1e-3          # embedding rows, sigma 0.001
+    Cm = torch.empty(M, N, device="cuda")
+    _lib.check(lib.cor_debug_gemm(2, M, N, K, C.c_void_p(A.data_ptr()), C.c_void_p(B.data_ptr()),
+                                  C.c_void_p(Cm.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    ref = A.double() @ B.double().T
+    err = (Cm.double() - ref).abs().max().item()
+    rel = err / ref.abs().max().item()
+    print("abs err %.3g (relative to the largest product %.3g)" % (err, rel))
+    assert err < 5e-7
+    assert rel < 1e-4          # the stated grade for small operands: absolute, i.e. a relative 2^-15..2^-13 here
+
+
 @pytest.mark.parametrize("shape", [(256, 512, 512), (77, 128, 64), (18999, 2048, 1024), (32, 2048, 1536)])
 def test_tcgen05_single_pass_gemm(shape):
     """gemm_mode 3 (fp16 heads only, one tensor pass): the error of ONE rounding of each operand to 11
