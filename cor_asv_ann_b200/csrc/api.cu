@@ -74,7 +74,7 @@ static int gemm_lstm(cor_model* m, cudaStream_t st, int M, const int* m_dev, int
 // ------------------------------------------------------------------ loop graphs (graphs.h)
 struct LoopGraphCache {
     std::vector<LoopGraph> entries;
-    cudaStream_t capture = nullptr;
+    cudaStream_t capture[2] = {nullptr, nullptr};
     uint64_t tick = 0;
 };
 constexpr size_t kGraphCacheSize = 8;
@@ -87,10 +87,24 @@ static void drop_graph(LoopGraph& g) {
     if (g.graph) cudaGraphDestroy(g.graph);
     g.exec = nullptr; g.graph = nullptr;
 }
-cudaStream_t loop_capture_stream(cor_model* m) {
+cudaStream_t loop_capture_stream(cor_model* m, int which) {
     LoopGraphCache* c = graph_cache(m);
-    if (!c->capture && cudaStreamCreateWithFlags(&c->capture, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
-    return c->capture;
+    if (!c->capture[which] && cudaStreamCreateWithFlags(&c->capture[which], cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    return c->capture[which];
+}
+int loop_graph_switch(cudaStream_t cs, cudaGraph_t root, int n, cudaGraphConditionalHandle* sw, cudaGraph_t* branches) {
+    cudaStreamCaptureStatus status; cudaGraph_t cur = nullptr; const cudaGraphNode_t* deps = nullptr; size_t ndeps = 0;
+    COR_CUDA(cudaStreamGetCaptureInfo(cs, &status, nullptr, &cur, &deps, &ndeps));
+    COR_CHECK(status == cudaStreamCaptureStatusActive && cur, "stream is not capturing");
+    COR_CUDA(cudaGraphConditionalHandleCreate(sw, root, 0, 0));
+    cudaGraphNodeParams cp{};
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = *sw; cp.conditional.type = cudaGraphCondTypeSwitch; cp.conditional.size = (unsigned)n;
+    cudaGraphNode_t node;
+    COR_CUDA(cudaGraphAddNode(&node, cur, deps, ndeps, &cp));
+    for (int i = 0; i < n; ++i) branches[i] = cp.conditional.phGraph_out[i];
+    COR_CUDA(cudaStreamUpdateCaptureDependencies(cs, &node, 1, cudaStreamSetCaptureDependencies));
+    return 0;
 }
 bool loop_graphs_enabled() {
     const char* off = getenv("COR_NO_GRAPH");
@@ -134,7 +148,7 @@ void loop_graphs_release(cor_model* m) {
     if (!m || !m->loop_graphs) return;
     LoopGraphCache* c = static_cast<LoopGraphCache*>(m->loop_graphs);
     for (auto& e : c->entries) drop_graph(e);
-    if (c->capture) cudaStreamDestroy(c->capture);
+    for (int i = 0; i < 2; ++i) if (c->capture[i]) cudaStreamDestroy(c->capture[i]);
     delete c;
     m->loop_graphs = nullptr;
 }

@@ -121,10 +121,7 @@ __global__ void beam_init_kernel(BeamDev b) {
 // ------------------------------------------------------------------ pop (seq2seq.py:1398-1420)
 // One warp per line: the fringe is sorted, so the pop is a prefix of it — walked 32 entries at a time
 // until batch_size open nodes have been seen (a few chunks at most, whatever the fringe length).
-__global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
-    const int lane = threadIdx.x & 31;
-    const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (line >= b.L) return;
+__device__ void pop_line(const BeamDev& b, int line, int lane) {
     if (b.status[line] != ST_ACTIVE) { if (lane == 0) b.beam_count[line] = 0; return; }
     const int Tl = b.row_T[line];
     const int len = b.fr_len[line];
@@ -213,13 +210,26 @@ __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     }
     b.beam_count[line] = out;
 }
+__global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
+    const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (line < b.L) pop_line(b, line, threadIdx.x & 31);
+}
 
 // ------------------------------------------------------------------ scan: row offsets, row total, active lines
 // One block; thread t owns the consecutive lines [t*per, (t+1)*per): all loads are issued at once,
 // one block-wide scan of the per-thread sums, then the row bases.  Row order = line order.
 // `set_cond`: the launch is part of the iteration graph (run_wave): the kernel counts the body and decides whether the
 // WHILE node runs another one (cudaGraphSetConditional is only valid inside the graph that owns the handle).
-__global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b, cudaGraphConditionalHandle cond, int set_cond) {
+struct LoopCtl {
+    cudaGraphConditionalHandle cond;    // WHILE: another iteration?
+    cudaGraphConditionalHandle shape;   // SWITCH: tile shape class of the next iteration's GEMMs, from its row count
+    int has_shape, r_narrow, r_single;
+};
+__device__ __forceinline__ void set_loop(const LoopCtl& lc, int rows, bool more) {
+    if (lc.has_shape) cudaGraphSetConditional(lc.shape, rows <= lc.r_narrow ? 0u : (rows <= lc.r_single ? 1u : 2u));
+    cudaGraphSetConditional(lc.cond, more ? 1u : 0u);
+}
+__global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b, LoopCtl lc, int set_cond) {
     __shared__ int s_wsum[32];
     __shared__ int s_total, s_active;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -254,24 +264,20 @@ __global__ void __launch_bounds__(1024) beam_scan_kernel(BeamDev b, cudaGraphCon
             // a line runs at most 2T iterations (beam_pop_kernel), so the bound below never cuts a search short; it keeps a
             // protocol bug from looping on the device forever
             const int bodies = ++b.counters[3];
-            cudaGraphSetConditional(cond, ((s_total > 0 || s_active > 0) && bodies <= 2 * b.T + 2) ? 1u : 0u);
+            set_loop(lc, s_total, (s_total > 0 || s_active > 0) && bodies <= 2 * b.T + 2);
         }
     }
 }
 
 // First node of the iteration graph: the WHILE condition from the counters the last directly launched scan left.
-__global__ void beam_cond_kernel(BeamDev b, cudaGraphConditionalHandle cond) {
-    cudaGraphSetConditional(cond, (b.counters[0] > 0 || b.counters[1] > 0) ? 1u : 0u);
+__global__ void beam_cond_kernel(BeamDev b, const LoopCtl* lc) {
+    set_loop(*lc, b.counters[0], b.counters[0] > 0 || b.counters[1] > 0);
 }
 
 // One warp per line: the rows of a line are its popped nodes in fringe order.
-__global__ void __launch_bounds__(256) beam_rowmap_kernel(BeamDev b) {
-    const int lane = threadIdx.x & 31;
-    const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (line >= b.L) return;
-    const int c = b.beam_count[line];
+__device__ __forceinline__ void rowmap_line(const BeamDev& b, int line, int lane, int c, int rb) {
     if (c <= 0) return;
-    const int rb = b.row_base[line], xb = b.x_count[line];
+    const int xb = b.x_count[line];
     for (int t = lane; t < c; t += 32) {
         b.row_line[rb + t] = line;
         b.row_node[rb + t] = b.beam_nodes[(size_t)line * b.batch + t];
@@ -279,6 +285,53 @@ __global__ void __launch_bounds__(256) beam_rowmap_kernel(BeamDev b) {
     }
     __syncwarp();
     if (lane == 0) { b.x_base[line] = xb; b.x_count[line] = xb + c; }
+}
+__global__ void __launch_bounds__(256) beam_rowmap_kernel(BeamDev b) {
+    const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (line >= b.L) return;
+    rowmap_line(b, line, threadIdx.x & 31, b.beam_count[line], b.row_base[line]);
+}
+
+// pop + scan + rowmap of a page of lines (L <= kSelectSmall) in ONE block: a warp per line (two rounds), the scan by
+// the first warp, no trip through another launch between them.  Same procedure and same results as the three kernels.
+constexpr int kSelectSmall = 64;
+__global__ void __launch_bounds__(1024) beam_select_small_kernel(BeamDev b, LoopCtl lc, int set_cond) {
+    __shared__ int s_cnt[kSelectSmall], s_base[kSelectSmall];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) b.counters[2] = 0;
+    for (int line = warp; line < b.L; line += 32) pop_line(b, line, lane);
+    __syncthreads();
+    if (warp == 0) {
+        int carry = 0, total = 0, active = 0;
+        for (int base = 0; base < b.L; base += 32) {
+            const int line = base + lane;
+            const int c0 = line < b.L ? b.beam_count[line] : 0;
+            int incl = c0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+            const int rb = carry + incl - c0;
+            int c = c0;
+            if (line < b.L) {
+                if (c > 0 && rb + c > b.Rcap) { b.status[line] = ST_OVERFLOW; b.beam_count[line] = 0; c = 0; }
+                b.row_base[line] = rb;
+                s_cnt[line] = c; s_base[line] = rb;
+            }
+            int t = c > 0 ? rb + c : 0, a = (line < b.L && b.status[line] == ST_ACTIVE) ? 1 : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { t = max(t, __shfl_xor_sync(0xffffffffu, t, o)); a += __shfl_xor_sync(0xffffffffu, a, o); }
+            total = max(total, t); active += a;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) {
+            b.counters[0] = total; b.counters[1] = active;
+            if (set_cond) {
+                const int bodies = ++b.counters[3];
+                set_loop(lc, total, (total > 0 || active > 0) && bodies <= 2 * b.T + 2);
+            }
+        }
+    }
+    __syncthreads();
+    for (int line = warp; line < b.L; line += 32) rowmap_line(b, line, lane, s_cnt[line], s_base[line]);
 }
 
 // ------------------------------------------------------------------ gather: decoder-step inputs of every row
@@ -1089,7 +1142,7 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     b->fr_key = c.take<double>((size_t)2 * L * cap); b->fr_id = c.take<uint32_t>((size_t)2 * L * cap);
     b->beam_nodes = c.take<uint32_t>((size_t)L * bp->batch_size);
     b->rej_table = c.take<int32_t>((size_t)L * T);
-    b->counters = c.take<int32_t>(4);
+    b->counters = c.take<int32_t>(4 + 16);      // [4..]: LoopCtl of the iteration graph (run_wave)
     b->heavy = c.take<int32_t>(L);
     b->o_stats = c.take<long long>((size_t)L * kStats);
     const int NB = std::max(1, std::min(bp->n_best, FMAX));
@@ -1212,21 +1265,29 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const size_t push_smem = (size_t)MAX_NEW * 12;
     const int t_hi = T;      // every row_T is <= t_max
     // pop + scan: which hypotheses of every line are expanded next, their rows, and whether anything is left to do
-    auto select = [&](cudaStream_t s_, cudaGraphConditionalHandle cond, int set_cond) -> int {
+    const bool small_sel = L <= kSelectSmall && !getenv("COR_NO_SELECT_SMALL");
+    auto select = [&](cudaStream_t s_, const LoopCtl& lc, int set_cond) -> int {
+        if (small_sel) {        // a page of lines: pop, scan and rowmap in one block
+            beam_select_small_kernel<<<1, 1024, 0, s_>>>(b, lc, set_cond);
+            ctx().launches += 1;
+            COR_CUDA(cudaGetLastError());
+            return 0;
+        }
         beam_pop_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
-        beam_scan_kernel<<<1, 1024, 0, s_>>>(b, cond, set_cond);
+        beam_scan_kernel<<<1, 1024, 0, s_>>>(b, lc, set_cond);
         ctx().launches += 2;
         COR_CUDA(cudaGetLastError());
         return 0;
     };
     // one decoder step over the selected rows and the insertion of their children
-    auto iteration = [&](cudaStream_t s_, bool roots) -> int {
-        beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
+    auto gather = [&](cudaStream_t s_) -> int {
+        if (!small_sel) { beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b); ++ctx().launches; }
         beam_gather_kernel<<<row_grid, 128, 0, s_>>>(b, split);
-        ctx().launches += 2;
+        ctx().launches += 1;
         COR_CUDA(cudaGetLastError());
-        io.wq_ready = !roots;     // iteration 0 expands the roots: their query comes from the encoder state
-        if (decoder_core(m, ws, io, s_)) return 1;
+        return 0;
+    };
+    auto insert = [&](cudaStream_t s_) -> int {
         const int warp_grid = std::min((plan.Rcap + 3) / 4, 148 * 8);
         switch (m->Vp) {        // score row in registers when it fits (32 values per lane at most)
             case 128:  beam_expand_warp_kernel<4><<<warp_grid, 128, 0, s_>>>(b, split); break;
@@ -1241,36 +1302,77 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         COR_CUDA(cudaGetLastError());
         return 0;
     };
+    auto iteration = [&](cudaStream_t s_, bool roots) -> int {
+        io.wq_ready = !roots;     // iteration 0 expands the roots: their query comes from the encoder state
+        return gather(s_) || decoder_core(m, ws, io, s_) || insert(s_);
+    };
     // Iterations 1.. are ONE graph launch: a WHILE node whose body is {iteration, select} and whose condition the
     // scan kernel sets on the device -- no launch latency between the ~10 kernels of an iteration and no host
     // round trip to find out that every line has finished.  (Per-launch profiling brackets launches with events on
     // the host: it keeps the host loop, as does COR_NO_GRAPH=1.)
     const bool use_graph = loop_graphs_enabled();
     int graph_body_kernels = 0;
-    if (select(st, 0, 0)) return 1;
+    const LoopCtl no_ctl{};
+    if (select(st, no_ctl, 0)) return 1;
     for (int it = 0; it <= 2 * t_hi; ++it) {
         if (use_graph && it == 1) {
             LoopGraph* g = nullptr;
             if (loop_graph_lookup(m, graph_key(m, L, T, k, bp, plan, o_align != nullptr, workspace, ws.val != nullptr), &g)) return 1;
             if (!g->exec) {
-                cudaGraphConditionalHandle cond; cudaGraph_t body;
-                void* kargs[2] = {(void*)&b, (void*)&cond};
+                // The GEMMs' tile shape depends on the row count, which only the device knows: where the capacity
+                // (Rcap) would pick another shape than a handful of rows, the decoder step is captured once per
+                // shape class as the branches of a SWITCH node that the scan kernel sets from the next row count
+                // (one page of lines = one hypothesis row per line most of the time: 128x32 tiles over 64 SMs
+                // instead of 8 CTA pairs of a 148-CTA grid).
+                LoopCtl lc{};
+                int r_narrow = 0, r_single = 0;
+                tc_shape_thresholds(4 * m->W, &r_narrow, &r_single);
+                const bool tc = m->split && tc_available();
+                lc.has_shape = (tc && plan.Rcap > r_narrow && !getenv("COR_NO_SHAPE_SWITCH")) ? 1 : 0;
+                lc.r_narrow = r_narrow; lc.r_single = r_single;
+                cudaGraph_t body;
+                LoopCtl* d_lc = reinterpret_cast<LoopCtl*>(b.counters + 4);      // the first node reads the handles from memory: they exist only after it has been added
+                void* kargs[2] = {(void*)&b, (void*)&d_lc};
                 cudaKernelNodeParams kp{};
                 kp.func = (void*)beam_cond_kernel; kp.gridDim = dim3(1); kp.blockDim = dim3(1); kp.kernelParams = kargs;
-                if (loop_graph_begin(g, kp, &cond, &body)) return 1;
-                cudaStream_t cs = loop_capture_stream(m);
-                COR_CHECK(cs, "no capture stream");
+                if (loop_graph_begin(g, kp, &lc.cond, &body)) return 1;
+                cudaStream_t cs = loop_capture_stream(m, 0), cs2 = loop_capture_stream(m, 1);
+                COR_CHECK(cs && cs2, "no capture stream");
                 const int64_t before = ctx().launches;
                 COR_CUDA(cudaStreamBeginCaptureToGraph(cs, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-                const int rc = iteration(cs, false) || select(cs, cond, 1);
+                io.wq_ready = true;
+                int rc = gather(cs);
+                int64_t extra = 0;
+                if (!rc && lc.has_shape) {
+                    cudaGraph_t branch[3];
+                    rc = loop_graph_switch(cs, g->graph, 3, &lc.shape, branch);
+                    for (int c = 0; c < 3 && !rc; ++c) {
+                        const int64_t b0 = ctx().launches;
+                        cudaError_t e = cudaStreamBeginCaptureToGraph(cs2, branch[c], nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed);
+                        if (e != cudaSuccess) { set_error(std::string("capturing a shape branch: ") + cudaGetErrorString(e)); rc = 1; break; }
+                        ctx().force_shape = c + 1;
+                        rc = decoder_core(m, ws, io, cs2);
+                        ctx().force_shape = 0;
+                        cudaGraph_t got = nullptr;
+                        e = cudaStreamEndCapture(cs2, &got);
+                        if (!rc && e != cudaSuccess) { set_error(std::string("capturing a shape branch: ") + cudaGetErrorString(e)); rc = 1; }
+                        if (c > 0) extra += ctx().launches - b0;     // one branch runs per iteration
+                    }
+                } else if (!rc) {
+                    rc = decoder_core(m, ws, io, cs);
+                }
+                rc = rc || insert(cs) || select(cs, lc, 1);
                 cudaGraph_t captured = nullptr;
                 const cudaError_t ce = cudaStreamEndCapture(cs, &captured);
-                g->body_kernels = (int)(ctx().launches - before);
+                g->body_kernels = (int)(ctx().launches - before - extra);
                 ctx().launches = before;            // captured, not run
                 if (rc) return 1;
                 COR_CUDA(ce);
                 COR_CUDA(cudaGraphInstantiate(&g->exec, g->graph, 0));
+                g->ctl.assign(reinterpret_cast<const char*>(&lc), reinterpret_cast<const char*>(&lc) + sizeof(lc));
             }
+            // the loop controls (graph-owned handles) for the first node, in this wave's workspace
+            COR_CUDA(cudaMemcpyAsync(b.counters + 4, g->ctl.data(), g->ctl.size(), cudaMemcpyHostToDevice, st));
             COR_CUDA(cudaGraphLaunch(g->exec, st));
             ctx().launches += 1;                    // beam_cond_kernel; the bodies are counted after the wave's final sync
             graph_body_kernels = g->body_kernels;
@@ -1282,7 +1384,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
             COR_CUDA(cudaStreamSynchronize(st));
             if (cnt[1] == 0 && cnt[0] == 0) break;
         }
-        if (iteration(st, it == 0) || select(st, 0, 0)) return 1;
+        if (iteration(st, it == 0) || select(st, no_ctl, 0)) return 1;
     }
     // results: staged in the wave's own buffers, n_best slots per line
     const size_t S = 2 * (size_t)T * b.n_best;

@@ -38,6 +38,9 @@ struct Ctx {
     int64_t tc_kind[2][3] = {};
     int64_t ffma_kind[2] = {};
     int force_bn = 0;              // test hook (cor_debug_gemm mode 3): force the narrow tile
+    // tile shape of the tcgen05 launches regardless of M: 0 = picked from M and N, 1 = 128x32, 2 = 128x256, 3 = CTA pair 256x256.
+    // Set while the branches of a loop graph's SWITCH node are captured (the row count lives on the device there).
+    int force_shape = 0;
     void* tc_maps = nullptr;       // tensor-map cache (gemm_tc.cu owns the type)
     void* prof = nullptr;          // per-launch event bracketing (api.cu owns the type)
 };
@@ -116,6 +119,8 @@ int gemm_store_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg
 int gemm_lstm_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, const LstmEpi& epi, int passes = 3);
 bool tc_available();
 void tc_force_narrow(bool on);   // test hook: 128x32 tiles regardless of shape (current Ctx)
+// Row counts up to which pick_shape takes the 128x32 tiles / the single-CTA 128x256 tiles for N output columns.
+void tc_shape_thresholds(int N, int* narrow_max_rows, int* single_max_rows);
 
 // ------------------------------------------------------------------ persistent recurrence (recur.cu)
 // One launch = all T timesteps of one LSTM layer (both directions side by side) for a page-sized batch:

@@ -639,6 +639,12 @@ int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg*
 // 32-column tiles still fit in ONE wave (a page of lines: M <= 256 rows at N = 2048 is <= 128 tiles)
 // they spread the weight stream over 8x as many SMs as the wide tiles would.
 void pick_shape(int M, int N, int* ncta, int* bn) {
+    if (ctx().force_shape) {
+        const int f = ctx().force_shape;
+        *bn = f == 1 ? BN_NARROW : BN_WIDE;
+        *ncta = (f == 3 && g_max_pairs > 0) ? 2 : 1;
+        return;
+    }
     const long long tiles_m = (M + BM - 1) / BM, narrow = tiles_m * ((N + BN_NARROW - 1) / BN_NARROW);
     if (ctx().force_bn == BN_NARROW || (narrow <= g_num_sms && !getenv("COR_NO_NARROW"))) { *ncta = 1; *bn = BN_NARROW; return; }
     *bn = BN_WIDE;
@@ -677,6 +683,14 @@ int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* 
 }  // namespace
 
 bool tc_available() { return init_tc(); }
+void tc_shape_thresholds(int N, int* narrow_max_rows, int* single_max_rows) {
+    init_tc();
+    const int tiles_n32 = (N + BN_NARROW - 1) / BN_NARROW, tiles_n256 = (N + BN_WIDE - 1) / BN_WIDE;
+    *narrow_max_rows = getenv("COR_NO_NARROW") ? 0 : (g_num_sms / tiles_n32) * BM;
+    // the pair kernel takes over once ceil(M / 256) * tiles_n256 >= g_max_pairs
+    *single_max_rows = g_max_pairs > 0 ? ((g_max_pairs + tiles_n256 - 1) / tiles_n256 - 1) * 2 * BM : 0x7fffffff;
+    if (*single_max_rows < *narrow_max_rows) *single_max_rows = *narrow_max_rows;
+}
 void tc_force_narrow(bool on) { ctx().force_bn = on ? BN_NARROW : 0; }
 void tc_ctx_release(Ctx* c) {
     if (c && c->tc_maps) { delete static_cast<MapCache*>(c->tc_maps); c->tc_maps = nullptr; }
