@@ -305,7 +305,7 @@ def measure(args, eng, workload, lines, rank, world, local, sample_clocks, roofl
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
-    launches = eng.launch_count()
+    launches, host_launches = eng.launch_count(), eng.host_launch_count()
     clocks = sampler.stop() if sample_clocks else None
     if bp is None:
         dec_steps = 2 * T * L                            # the fast decoder always runs 2T steps for every line
@@ -380,7 +380,7 @@ def measure(args, eng, workload, lines, rank, world, local, sample_clocks, roofl
     del dev_idx, host_idx
     torch.cuda.empty_cache()
     return {"L": L, "ms": ms, "value": chars / (ms * 1e-3), "e2e_value": chars / (e2e_ms * 1e-3), "e2e_ms": e2e_ms,
-            "h2d": h2d, "d2h": d2h, "api": api, "launches": launches, "k_ms": k_ms, "k_n": k_n, "k_flops": k_flops,
+            "h2d": h2d, "d2h": d2h, "api": api, "launches": launches, "host_launches": host_launches, "k_ms": k_ms, "k_n": k_n, "k_flops": k_flops,
             "prof_ms": prof_ms, "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra, "parity": parity}
 
 
@@ -416,7 +416,7 @@ def measure_page(args, eng, n_lines):
     dt = (time.perf_counter() - t0) / reps
     page = {"lines": n_lines, "ms_per_call": dt * 1e3, "us_per_decoder_timestep": dt * 1e6 / (2 * T + T),
             "timesteps_per_call": 3 * T, "chars_per_s": LINE_LEN * n_lines / dt,
-            "gpu_launches_per_call": eng.launch_count() / reps,
+            "gpu_launches_per_call": eng.launch_count() / reps, "host_launch_calls_per_call": eng.host_launch_count() / reps,
             "api": "cor_correct_greedy_host (pinned host buffers), T encoder + 2T decoder timesteps"}
     # the OCR-D processor's default mode (fast_mode false, ocrd-tool.json:55-58) is the beamed decoder: same page,
     # config-2 beam parameters (random-init weights: T iterations of one hypothesis per line)
@@ -432,8 +432,55 @@ def measure_page(args, eng, n_lines):
     torch.cuda.synchronize()
     db = (time.perf_counter() - t0) / reps
     page["beam"] = {"ms_per_call": db * 1e3, "chars_per_s": LINE_LEN * n_lines / db, "gpu_launches_per_call": eng.launch_count() / reps,
+                    "host_launch_calls_per_call": eng.host_launch_count() / reps,
                     "api": "cor_correct_beam_host (pinned host buffers)"}
     return page
+
+
+def measure_early_exit(args, device, n_target=4096):
+    """Fast decoder on lines that END (reference seq2seq.py:1255-1256 steps finished lines to 2T
+    and ignores them).  Random-init decoders never emit a newline, so this leg uses weights of variant E (see
+    cor_asv_ann_b200/synthetic.py) and, from a pool of candidate lines, those that an untimed first pass sees end within
+    T of the 2T steps.  The loop graph stops when the last of them has; the host loop (COR_NO_GRAPH=1) launches all 2T
+    steps.  Results are identical (tests/test_gpu_loop_graph.py); only the time differs."""
+    import torch
+    from cor_asv_ann_b200.engine import Engine
+    eng = Engine(dict(C2, window_width=5), build_weights(C2, "E"), device=device, eos_index=1, gemm_mode=args.gemm_mode)
+    T = LINE_LEN + 1
+    pool = make_indices(4 * n_target, 1031)
+    keep = []
+    for b0 in range(0, len(pool), n_target):
+        idx = torch.as_tensor(pool[b0:b0 + n_target], device="cuda")
+        eng.encode(idx, None, torch.full((len(idx),), T, dtype=torch.int32, device="cuda"), want_outputs=False)
+        lens = eng.greedy()[3].cpu().numpy()
+        keep.append(b0 + np.nonzero(lens < T)[0])
+    keep = np.concatenate(keep)
+    n = (min(len(keep), n_target) // REF_BATCH) * REF_BATCH
+    if n == 0:
+        return None
+    idx = torch.as_tensor(pool[keep[:n]], device="cuda")
+    row_T = torch.full((n,), T, dtype=torch.int32, device="cuda")
+    out = {"workload": "C2 topology, weights of variant E (lines end), %d lines selected by a first pass: those that end within T of the 2T steps" % n, "lines": n}
+    for name, env in (("loop_graph", None), ("host_loop_2T_steps", "1")):
+        if env:
+            os.environ["COR_NO_GRAPH"] = env
+        for _ in range(2):
+            eng.encode(idx, None, row_T, want_outputs=False); res = eng.greedy()
+        torch.cuda.synchronize()
+        eng.launch_count(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            eng.encode(idx, None, row_T, want_outputs=False); res = eng.greedy()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 3
+        lens = res[3].cpu().numpy()
+        out[name] = {"ms_per_call": ms, "chars_per_s": LINE_LEN * n / (ms * 1e-3), "kernels_per_call": eng.launch_count() / 3,
+                     "decoded_length_mean": float(lens.mean()), "decoded_length_max": int(lens.max())}
+        os.environ.pop("COR_NO_GRAPH", None)
+    out["speedup"] = out["host_loop_2T_steps"]["ms_per_call"] / out["loop_graph"]["ms_per_call"]
+    eng.release_workspace()
+    return out
 
 
 def make_s2s(topo, w, mapping, device):
@@ -566,6 +613,7 @@ def bench_line(args, r, workload, world, peaks):
         "e2e": {"value": r["e2e_value"], "unit": "chars/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                 "ms_per_step": r["e2e_ms"] / args.steps, "api": r["api"]},
         "gpu_launches": r["launches"],
+        "host_launch_calls": r["host_launches"],     # the decoder loops are device-side WHILE graphs: one graph launch runs all iterations
         "clocks": r["clocks"],
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel<1,2,256,LstmEpi>: GEMM + fused LSTM-cell epilogue (CTA pairs)", "achieved": achieved,
                      "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if (peak and achieved) else None, "traffic": traffic, "traffic_source": traffic_src,
@@ -670,6 +718,7 @@ def main():
         e.release_workspace()
     predict_r = measure_predict(args, C2, w_c2, mapping, local, args.predict_lines) if (rank == 0 and single and args.predict_lines > 0) else None
     c1_r = measure_c1(local) if (rank == 0 and single) else None
+    early_r = measure_early_exit(args, local) if (rank == 0 and single) else None
     strong_r = measure_strong(args, C2, w_c2, mapping, local, rank, world) if not args.only else None
 
     if world > 1:
@@ -684,7 +733,7 @@ def main():
         except OSError:
             pass
         line = bench_line(args, main_r, args.workload, world, peaks)
-        keys = ("metric", "value", "unit", "steps", "ms_per_step", "config", "e2e", "gpu_launches", "clocks", "roofline",
+        keys = ("metric", "value", "unit", "steps", "ms_per_step", "config", "e2e", "gpu_launches", "host_launch_calls", "clocks", "roofline",
                 "algorithmic_gflop_per_line", "parity", "beam_iterations_per_line", "hypothesis_steps_per_line",
                 "hypotheses_per_line_and_iteration", "hypothesis_steps_per_s", "finals_per_line", "fringe_peak_mean", "fringe_peak_max",
                 "near_tie_decisions_per_line", "lines_without_final", "lines_equal_to_input", "near_tie_argmaxes_last_step")
@@ -697,6 +746,8 @@ def main():
             line["also"] = also
         if c1_r is not None:
             line.setdefault("also", {})["c1"] = c1_r
+        if early_r is not None:
+            line.setdefault("also", {})["greedy_early_exit"] = early_r
         if page_r is not None:
             line["page"] = page_r
         if predict_r is not None:

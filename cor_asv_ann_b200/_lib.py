@@ -46,6 +46,7 @@ PROTOTYPES = {
     "cor_alignment_paths": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                       C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "cor_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
+    "cor_host_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
     "cor_debug_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_int]),
     "cor_debug_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cor_prof_enable": (C.c_int, [C.c_void_p, C.c_int]),

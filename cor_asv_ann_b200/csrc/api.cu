@@ -554,7 +554,7 @@ int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) 
             // submitted behind the persistent GEMM, so that its CTAs take their SMs first and the
             // attention blocks fill the registers and warp slots left beside them
             COR_CUDA(cudaStreamWaitEvent(m->side, m->ev_fork, 0));
-            if (launch_attention(m->side, a)) return 1;
+            if (m->side_attention ? launch_attention_side(m->side, a) : launch_attention(m->side, a)) return 1;
             COR_CUDA(cudaEventRecord(m->ev_join, m->side));
         }
     }
@@ -739,7 +739,7 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         }
         m->greedy_step_kernels = g->body_kernels / 2;
         COR_CUDA(cudaGraphLaunch(g->exec, st));
-        ctx().launches += 1;
+        ctx().launches += 1; ctx().in_graph += 1; ctx().graph_launches += 1;     // the graph's first node
         return launch_finish_scores(st, ws.o_score, ws.o_len, B);
     }
     for (int s = 0; s < S; ++s) {
@@ -764,11 +764,19 @@ int64_t cor_launch_count(cor_model* m, int reset) {
         if (cudaSetDevice(m->device) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess &&
             cudaMemcpy(&steps, m->dev_counters, 8, cudaMemcpyDeviceToHost) == cudaSuccess) {
             m->ctx.launches += steps * m->greedy_step_kernels + steps / 2;
+            m->ctx.in_graph += steps * m->greedy_step_kernels + steps / 2;
             cudaMemset(m->dev_counters, 0, 8);
         }
     }
     const int64_t v = m->ctx.launches;
     if (reset) m->ctx.launches = 0;
+    return v;
+}
+int64_t cor_host_launch_count(cor_model* m, int reset) {
+    if (!m) return -1;
+    const int64_t kernels = cor_launch_count(m, 0);       // folds the device-side counts in
+    const int64_t v = kernels - m->ctx.in_graph + m->ctx.graph_launches;
+    if (reset) { m->ctx.launches = 0; m->ctx.in_graph = 0; m->ctx.graph_launches = 0; }
     return v;
 }
 int cor_debug_counters(cor_model* m, int64_t* out, int reset) {
@@ -949,6 +957,7 @@ int cor_model_finalize(cor_model* m) {
             if (upload_vec(m, tab, &m->xtab[dir])) return 1;
         }
     }
+    m->side_attention = getenv("COR_ATTN_SIDE") != nullptr;
     if (!m->side && getenv("COR_OVERLAP")) {     // experiment switch: attention beside the lower-cell GEMM (no gain measured: DESIGN.md)
         COR_CUDA(cudaStreamCreateWithFlags(&m->side, cudaStreamNonBlocking));
         COR_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));

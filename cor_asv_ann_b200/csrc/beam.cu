@@ -842,7 +842,7 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
 
 // ------------------------------------------------------------------ push: insort of the new children (:1515-1532)
 __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, NW = NT >> 5;
     const int c = b.beam_count[line];
     if (c <= 0) return;
     const int Tl = b.row_T[line];
@@ -855,7 +855,7 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
     if (lane == 31) s_wsum[warp] = incl;
     __syncthreads();
     int off = 0, n_new = 0;
-    for (int w = 0; w < 8; ++w) { if (w < warp) off += s_wsum[w]; n_new += s_wsum[w]; }
+    for (int w = 0; w < NW; ++w) { if (w < warp) off += s_wsum[w]; n_new += s_wsum[w]; }
     off += incl - nj;
     if (tid < c) {
         const size_t g = (size_t)line * b.quota_x + xb + tid;
@@ -869,12 +869,12 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
     int npad = 1;
     while (npad < n_new) npad <<= 1;
     __syncthreads();
-    for (int i = n_new + tid; i < npad; i += 256) { skey[i] = INFINITY; sid[i] = 0x7fffffffu; }
+    for (int i = n_new + tid; i < npad; i += NT) { skey[i] = INFINITY; sid[i] = 0x7fffffffu; }
     __syncthreads();
     // ---- bitonic sort ascending by (key, id)
     for (int k2 = 2; k2 <= npad; k2 <<= 1) {
         for (int j = k2 >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < npad; i += 256) {
+            for (int i = tid; i < npad; i += NT) {
                 const int ixj = i ^ j;
                 if (ixj > i) {
                     const bool up = (i & k2) == 0;
@@ -897,14 +897,14 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
     uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     // truncation to the best max_batches * batch_size = 2T * batch_size of THIS line's reference batch (seq2seq.py:1397, 1531)
     const int keep = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);
-    for (int i = tid; i < n_old; i += 256) {
+    for (int i = tid; i < n_old; i += NT) {
         const double k = okey[i]; const uint32_t id = oid[i];
         int lo = 0, hi = n_new;                   // new entries that precede this old one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = i + lo;
         if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
-    for (int j = tid; j < n_new; j += 256) {
+    for (int j = tid; j < n_new; j += NT) {
         const double k = skey[j]; const uint32_t id = sid[j];
         int lo = 0, hi = n_old;                   // old entries that precede this new one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
@@ -995,11 +995,14 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
 }
 
 // Lines on the heavy list (more than 32 new children), one block per line at a time.
-__global__ void __launch_bounds__(256) beam_push_kernel(BeamDev b) {
+// 1024 threads per line: the bitonic sort of up to 4096 children and the rank-merge with a fringe of up to 2T*256 entries are
+// per-line work that a wave of a few dozen lines cannot spread over more SMs, only over more threads of one.
+constexpr int PUSH_THREADS = 1024;
+__global__ void __launch_bounds__(PUSH_THREADS) beam_push_kernel(BeamDev b) {
     extern __shared__ unsigned char smraw[];
     double* skey = reinterpret_cast<double*>(smraw);                 // [npad]
     uint32_t* sid = reinterpret_cast<uint32_t*>(skey + MAX_NEW);     // [npad]
-    __shared__ int s_wsum[8];
+    __shared__ int s_wsum[PUSH_THREADS / 32];
     const int n = b.counters[2];
     for (int i = blockIdx.x; i < n; i += gridDim.x) {
         push_line(b, b.heavy[i], skey, sid, s_wsum);
@@ -1297,7 +1300,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
             default:   beam_expand_kernel<<<row_grid, 128, expand_smem, s_>>>(b, split);
         }
         beam_push_small_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
-        beam_push_kernel<<<std::min(L, 148 * 4), 256, push_smem, s_>>>(b);
+        beam_push_kernel<<<std::min(L, 148 * 2), PUSH_THREADS, push_smem, s_>>>(b);
         ctx().launches += 3;
         COR_CUDA(cudaGetLastError());
         return 0;
@@ -1374,7 +1377,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
             // the loop controls (graph-owned handles) for the first node, in this wave's workspace
             COR_CUDA(cudaMemcpyAsync(b.counters + 4, g->ctl.data(), g->ctl.size(), cudaMemcpyHostToDevice, st));
             COR_CUDA(cudaGraphLaunch(g->exec, st));
-            ctx().launches += 1;                    // beam_cond_kernel; the bodies are counted after the wave's final sync
+            ctx().launches += 1; ctx().in_graph += 1; ctx().graph_launches += 1;    // beam_cond_kernel; the bodies are counted after the wave's final sync
             graph_body_kernels = g->body_kernels;
             break;
         }
@@ -1406,6 +1409,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     if (graph_body_kernels) COR_CUDA(cudaMemcpyAsync(h_cnt, b.counters, 16, cudaMemcpyDeviceToHost, st));
     COR_CUDA(cudaStreamSynchronize(st));
     ctx().launches += (int64_t)h_cnt[3] * graph_body_kernels;     // kernels the WHILE node ran (bodies counted by the scan kernel)
+    ctx().in_graph += (int64_t)h_cnt[3] * graph_body_kernels;
     return 0;
 }
 

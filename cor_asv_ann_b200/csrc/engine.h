@@ -33,7 +33,9 @@ void set_error(const std::string& msg);
 // models, or one model per GPU) never share them.  A C-ABI entry point installs its handle's Ctx for the duration
 // of the call (CtxScope, thread-local); handle-free test hooks (cor_debug_gemm) run on a default Ctx.
 struct Ctx {
-    int64_t launches = 0;          // kernels launched (bench.py's gpu_launches)
+    int64_t launches = 0;          // kernels launched (bench.py's gpu_launches), graph nodes included
+    int64_t in_graph = 0;          // ... of which ran as nodes of a loop graph
+    int64_t graph_launches = 0;    // cudaGraphLaunch calls
     // tcgen05 launches by [epilogue: 0 store, 1 LSTM][tile: 0 = 128x32, 1 = 128x256, 2 = CTA pair 256x256], then FFMA [store, LSTM]
     int64_t tc_kind[2][3] = {};
     int64_t ffma_kind[2] = {};
@@ -188,6 +190,7 @@ struct AttnArgs {
     int R; const int* r_dev; int L; int t_max; int W; int D; int window; int inclusive;
 };
 int launch_attention(cudaStream_t st, const AttnArgs& a);
+int launch_attention_side(cudaStream_t st, const AttnArgs& a);   // register-only variant that co-resides with the persistent GEMM (overlap mode)
 
 struct GreedyArgs {
     const float* logits;       // [R][V]

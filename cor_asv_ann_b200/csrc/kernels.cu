@@ -4,6 +4,7 @@
 #include "engine.h"
 #include "epilogue.cuh"
 #include <math.h>
+#include <algorithm>
 
 namespace cor {
 
@@ -153,6 +154,119 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
                 }
         }
         store_split4(a.ctx, a.ctx_lo, (size_t)row * a.D + k, c);
+    }
+}
+
+// Variant that shares an SM with the persistent lower-cell GEMM (decoder_core, overlap mode): no shared-memory slab
+// (the GEMM holds ~197 KB), at most 128 registers for 128 threads (the GEMM leaves 16 K), and therefore ALL window
+// positions of a 128-column chunk in flight per lane (13 x 16 B) -- with one resident block per SM that is what keeps
+// enough bytes in flight (4 warps x 6.5 KB) to stream the windows while the tensor pipe works.
+__global__ void __launch_bounds__(128, 4) attention_side_kernel(AttnArgs a) {
+    __shared__ float s_w[4][16];
+    const int R = a.r_dev ? min(*a.r_dev, a.R) : a.R;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int row = blockIdx.x * 4 + wid; row < R; row += gridDim.x * 4) {
+        const int line = a.row_line ? a.row_line[row] : row;
+        const int T = a.line_T[line];
+        const float* ap = a.a_prev + (size_t)row * a.t_max;
+        float part = 0.f;
+        for (int j = lane; j < T; j += 32) part = fmaf(ap[j], (float)j, part);
+        const float centre = warp_sum(part) + 1.0f;
+        const int j_lo = max(0, (int)ceilf(centre - (float)a.window) - 1);
+        const int j_hi = min(T - 1, (int)floorf(centre + (float)a.window) + 1);
+        int j0 = 0, nj = 0;
+        for (int j = j_lo; j <= j_hi && nj < MAXWIN; ++j) {
+            const float dist = fabsf(centre - (float)j);
+            const bool keep = a.inclusive ? (dist <= (float)a.window) : (dist < (float)a.window);
+            if (keep) { if (nj == 0) j0 = j; ++nj; }
+        }
+        const float* wq = a.wq + (size_t)row * a.W;
+        const float* ub = a.u + ((size_t)line * a.t_max + j0) * a.W;
+        float s[MAXWIN];
+#pragma unroll
+        for (int q = 0; q < MAXWIN; ++q) s[q] = 0.f;
+        for (int k = lane * 4; k < a.W; k += 128) {
+            const float4 w4 = *reinterpret_cast<const float4*>(wq + k);
+            const float4 v4 = __ldg(reinterpret_cast<const float4*>(a.v_a + k));
+            constexpr int HALF = 7;
+#pragma unroll
+            for (int q0 = 0; q0 < MAXWIN; q0 += HALF) {
+                float4 u4[HALF];
+#pragma unroll
+                for (int q = 0; q < HALF; ++q)
+                    if (q0 + q < MAXWIN && q0 + q < nj) u4[q] = __ldcs(reinterpret_cast<const float4*>(ub + (size_t)(q0 + q) * a.W + k));
+#pragma unroll
+                for (int q = 0; q < HALF; ++q)
+                    if (q0 + q < MAXWIN && q0 + q < nj) {
+                        float t = s[q0 + q];
+                        t = fmaf(tanhf_fast(w4.x + u4[q].x), v4.x, t);
+                        t = fmaf(tanhf_fast(w4.y + u4[q].y), v4.y, t);
+                        t = fmaf(tanhf_fast(w4.z + u4[q].z), v4.z, t);
+                        t = fmaf(tanhf_fast(w4.w + u4[q].w), v4.w, t);
+                        s[q0 + q] = t;
+                    }
+            }
+        }
+        float esum = 0.f;
+#pragma unroll
+        for (int q = 0; q < MAXWIN; ++q)
+            if (q < nj) { s[q] = expf(warp_sum(s[q]) + a.b_v); esum += s[q]; }
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < MAXWIN; ++q)
+            if (q < nj && lane == 0) s_w[wid][q] = s[q] / esum;
+        __syncwarp();
+        float* ao = a.a_out + (size_t)row * a.t_max;
+        float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)row * a.t_max : nullptr;
+        for (int j = lane; j < a.t_max; j += 32) {
+            const int q = j - j0;
+            const float v = (q >= 0 && q < nj) ? s_w[wid][q] : 0.f;
+            ao[j] = v;
+            if (al) al[j] = v;
+        }
+        const size_t eb = ((size_t)line * a.t_max + j0) * a.D;
+        for (int k = lane * 4; k < a.D; k += 128) {
+            float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+            constexpr int HALF = 7;
+            if (a.enc_lo) {
+#pragma unroll
+                for (int q0 = 0; q0 < MAXWIN; q0 += HALF) {
+                    uint2 h[HALF], l[HALF];
+#pragma unroll
+                    for (int q = 0; q < HALF; ++q)
+                        if (q0 + q < MAXWIN && q0 + q < nj) {
+                            h[q] = __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(a.enc) + eb + (size_t)(q0 + q) * a.D + k));
+                            l[q] = __ldcs(reinterpret_cast<const uint2*>(reinterpret_cast<const __half*>(a.enc_lo) + eb + (size_t)(q0 + q) * a.D + k));
+                        }
+#pragma unroll
+                    for (int q = 0; q < HALF; ++q)
+                        if (q0 + q < MAXWIN && q0 + q < nj) {
+                            const float w = s_w[wid][q0 + q];
+                            const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&h[q].x)), h1 = __half22float2(*reinterpret_cast<const __half2*>(&h[q].y));
+                            const float2 l0 = __half22float2(*reinterpret_cast<const __half2*>(&l[q].x)), l1 = __half22float2(*reinterpret_cast<const __half2*>(&l[q].y));
+                            c.x = fmaf(w, h0.x + l0.x, c.x); c.y = fmaf(w, h0.y + l0.y, c.y);
+                            c.z = fmaf(w, h1.x + l1.x, c.z); c.w = fmaf(w, h1.y + l1.y, c.w);
+                        }
+                }
+            } else {
+#pragma unroll
+                for (int q0 = 0; q0 < MAXWIN; q0 += HALF) {
+                    float4 x4[HALF];
+#pragma unroll
+                    for (int q = 0; q < HALF; ++q)
+                        if (q0 + q < MAXWIN && q0 + q < nj) x4[q] = __ldcs(reinterpret_cast<const float4*>(a.enc + eb + (size_t)(q0 + q) * a.D + k));
+#pragma unroll
+                    for (int q = 0; q < HALF; ++q)
+                        if (q0 + q < MAXWIN && q0 + q < nj) {
+                            const float w = s_w[wid][q0 + q];
+                            c.x = fmaf(w, x4[q].x, c.x); c.y = fmaf(w, x4[q].y, c.y);
+                            c.z = fmaf(w, x4[q].z, c.z); c.w = fmaf(w, x4[q].w, c.w);
+                        }
+                }
+            }
+            store_split4(a.ctx, a.ctx_lo, (size_t)row * a.D + k, c);
+        }
+        __syncwarp();
     }
 }
 
@@ -308,6 +422,19 @@ int launch_attention_reg(cudaStream_t st, const AttnArgs& a) {
     COR_CHECK(a.W % 4 == 0 && a.D % 4 == 0, "W and D must be multiples of 4");
     if (a.R <= 0) return 0;
     attention_kernel<<<(a.R + 3) / 4, 128, 0, st>>>(a);
+    ++ctx().launches;
+    COR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_attention_side(cudaStream_t st, const AttnArgs& a) {
+    COR_CHECK(a.window >= 0 && a.window <= 6, "window_width above 6 is not supported");
+    COR_CHECK(a.W % 4 == 0 && a.D % 4 == 0, "W and D must be multiples of 4");
+    if (a.R <= 0) return 0;
+    // one block per SM fits beside the GEMM: a persistent grid of a few blocks per SM lets the block scheduler refill
+    // the slot the moment a block ends, whatever the row count
+    const int blocks = std::min((a.R + 3) / 4, 148 * 4);
+    attention_side_kernel<<<blocks, 128, 0, st>>>(a);
     ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;

@@ -274,7 +274,16 @@ class Engine:
         return ms.value, n.value, fl.value
 
     def launch_count(self, reset=False):
-        return int(self.lib.cor_launch_count(self.handle, int(reset)))
+        """Kernels run since the last reset (nodes of the loop graphs included)."""
+        if reset:       # both counters share their reset
+            v = int(self.lib.cor_launch_count(self.handle, 0))
+            self.lib.cor_host_launch_count(self.handle, 1)
+            return v
+        return int(self.lib.cor_launch_count(self.handle, 0))
+
+    def host_launch_count(self):
+        """Launch calls the host made since the last reset (kernel launches + graph launches)."""
+        return int(self.lib.cor_host_launch_count(self.handle, 0))
 
     KERNEL_KINDS = ("tc_store_narrow", "tc_store_single", "tc_store_pair", "tc_lstm_narrow", "tc_lstm_single", "tc_lstm_pair",
                     "ffma_store", "ffma_lstm")

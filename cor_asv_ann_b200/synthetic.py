@@ -9,6 +9,10 @@ Weight variants:
        to) and N(0, 0.1) noise on the LSTM biases, so that padding steps change the state;
   "P"  as U with embedding rows of norm 12: logits of standard deviation ~3 like a trained model's, a selective
        softmax -- the variant on which the beam search is a search (tens of live hypotheses per line).
+  "E"  as P with the decoder's recurrent kernels scaled by 12 (the decoder state no longer settles on a fixed point)
+       and the newline row of the embedding scaled by 4: lines END, at different steps, which no random-init model's
+       ever do -- the variant on which the fast decoder's early exit shows (it amplifies rounding differences, so
+       it is compared between drivers of the same kernels, not with the oracle).
 """
 import numpy as np
 
@@ -76,7 +80,7 @@ def layer_shapes(width, depth, voc_size, deep_bidirectional_encoder=False, bridg
 def random_weights(shapes, width, depth, rng, variant="K"):
     """{layer: [arrays]} for `shapes` (layer_shapes) from the initialisers of `variant` (module docstring)."""
     W = int(width)
-    noise = 0.1 if variant in ("U", "P") else 0.0
+    noise = 0.1 if variant in ("U", "P", "E") else 0.0
 
     def glorot(shape):
         lim = np.sqrt(6.0 / (shape[0] + shape[1]))
@@ -94,15 +98,21 @@ def random_weights(shapes, width, depth, rng, variant="K"):
     for layer, sh in shapes.items():
         if layer == 'char_input_projection':
             E = (rng.standard_normal(sh[0]) * 0.001).astype(np.float32)
-            if variant in ("U", "P"):
+            if variant in ("U", "P", "E"):
                 E = (E / np.linalg.norm(E, axis=1, keepdims=True)).astype(np.float32)
-            if variant == "P":
+            if variant in ("P", "E"):
                 E = (E * np.float32(12.0)).astype(np.float32)
+            if variant == "E":
+                E[1] *= np.float32(4.0)
             out[layer] = [E]
         elif layer == 'decoder_lstm_%d' % depth:
             out[layer] = [glorot(sh[0]), glorot(sh[1]), np.zeros(sh[2], np.float32), np.zeros(sh[3], np.float32)] + lstm(sh[4][0])
+            if variant == "E":
+                out[layer][5] = (out[layer][5] * np.float32(12.0)).astype(np.float32)
         elif 'lstm' in layer:
             out[layer] = sum((lstm(sh[i][0]) for i in range(0, len(sh), 3)), [])
+            if variant == "E" and layer.startswith('decoder'):
+                out[layer][1] = (out[layer][1] * np.float32(12.0)).astype(np.float32)
         elif len(sh) == 2:      # bridge: Dense kernel + bias
             out[layer] = [glorot(sh[0]), np.zeros(sh[1], np.float32)]
         else:

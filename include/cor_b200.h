@@ -191,6 +191,10 @@ int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_
  * reset; launches by GEMM kernel variant; device time accumulated by the LSTM-GEMM launches between
  * cor_prof_enable(m, 1) and cor_prof_enable(m, 0). */
 int64_t cor_launch_count(cor_model* m, int reset);
+/* The decoder loops run as device-side WHILE graphs (one graph launch = all iterations): cor_launch_count counts the
+ * KERNELS that ran (graph nodes included, counted on the device), this one the launch calls the host made (kernel
+ * launches + graph launches) -- the number that costs launch latency.  Same reset semantics. */
+int64_t cor_host_launch_count(cor_model* m, int reset);
 /* out[8]: tcgen05 launches with the plain epilogue on 128x32 / 128x256 / CTA-pair 256x256 tiles, the same three
  * with the fused LSTM epilogue, then FFMA launches plain / LSTM.  Lets a parity test assert WHICH kernel it checked. */
 int cor_debug_counters(cor_model* m, int64_t* out, int reset);

@@ -211,22 +211,27 @@ def test_small_magnitude_weights_variant_k():
         res[mode] = [t.numpy().copy() for t in out] + [eng.last_ties.numpy().copy()]
     for mode in (1, 2):
         chars, probs, scores, lens, align, ties = res[mode]
-        same = 0
+        same, dp, rel, da, untied = 0, 0.0, 0.0, 0.0, []
         for j in range(B):
             text = ''.join(mapping[1][int(v)] for v in chars[j, :lens[j]])
-            # common prefix with the oracle: the values there were computed from identical histories
-            n = 0
-            while n < min(len(text), len(r_text[j])) and text[n] == r_text[j][n]:
-                n += 1
+            # the fast decoder feeds the softmax back, not the argmax: every step is comparable whatever the strings say
+            n = min(int(lens[j]), len(r_probs[j]))
+            k = 0
+            while k < min(len(text), len(r_text[j])) and text[k] == r_text[j][k]:
+                k += 1
             same += int(text == r_text[j])
+            if k:       # probabilities belong to the emitted characters: compare where those agree
+                ref_p = np.array(r_probs[j][:k])
+                dp = max(dp, float(np.abs(probs[j, :k] - ref_p).max()))
+                rel = max(rel, float((np.abs(probs[j, :k] - ref_p) / ref_p).max()))
             if n:
-                ref_p = np.array(r_probs[j][:n])
-                assert np.abs(probs[j, :n] - ref_p).max() < TOL_P
-                assert (np.abs(probs[j, :n] - ref_p) / ref_p).max() < 1e-3, "mode %d" % mode
-                assert np.abs(align[:n, j, :] - np.stack(r_align[j][:n])).max() < TOL_P
-            if text != r_text[j]:
-                assert ties[j] > 0, "mode %d line %d differs from the oracle without a logged near-tie" % (mode, j)
-        print("variant K, gemm_mode %d: %d of %d strings identical to the oracle, %d near-ties logged" % (mode, same, B, int(ties.sum())))
+                da = max(da, float(np.abs(align[:n, j, :] - np.stack(r_align[j][:n])).max()))
+            if text != r_text[j] and ties[j] == 0:
+                untied.append(j)
+        print("variant K, gemm_mode %d: %d of %d strings identical to the oracle, %d near-ties logged; max |dp| %.3g (relative %.3g), max |da| %.3g"
+              % (mode, same, B, int(ties.sum()), dp, rel, da))
+        assert dp < TOL_P and rel < 1e-3 and da < TOL_P, "mode %d" % mode
+        assert not untied, "mode %d: lines %s differ from the oracle without a logged near-tie" % (mode, untied)
 
 
 # Stated tolerance of the reduced-precision variant (gemm_mode 3, single-pass fp16 tensor products; the north
