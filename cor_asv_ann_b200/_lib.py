@@ -26,6 +26,12 @@ class CorBeamParams(C.Structure):
                 ("n_best", C.c_int32), ("beam_threshold_in", C.c_double), ("rejection_threshold", C.c_double)]
 
 
+class CorTrainBatch(C.Structure):
+    _fields_ = [("n_rows", C.c_int32), ("t_src", C.c_int32), ("k_alt", C.c_int32), ("t_dec", C.c_int32),
+                ("src_idx", C.c_void_p), ("src_val", C.c_void_p), ("dec_in", C.c_void_p), ("dec_out", C.c_void_p),
+                ("mask_enc", C.c_void_p), ("mask_dec", C.c_void_p), ("mask_cell", C.c_void_p)]
+
+
 # name -> (restype, argtypes); every symbol include/cor_b200.h declares
 PROTOTYPES = {
     "cor_last_error": (C.c_char_p, []),
@@ -45,6 +51,14 @@ PROTOTYPES = {
     "cor_decode_beam_batch": (C.c_int, [C.c_void_p, C.POINTER(CorLines), C.POINTER(CorBeamParams), C.c_void_p, C.c_size_t] + [C.c_void_p] * 6 + [C.c_void_p]),
     "cor_alignment_paths": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                       C.c_double, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "cor_trainer_create": (C.c_int, [C.POINTER(CorConfig), C.c_int, C.POINTER(C.c_void_p)]),
+    "cor_trainer_destroy": (None, [C.c_void_p]),
+    "cor_trainer_param_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "cor_trainer_slot": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "cor_trainer_bind": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cor_trainer_reset_optimizer": (C.c_int, [C.c_void_p]),
+    "cor_train_forward_backward": (C.c_int, [C.c_void_p, C.POINTER(CorTrainBatch), C.POINTER(C.c_double), C.c_void_p]),
+    "cor_train_apply": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_double), C.c_void_p]),
     "cor_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
     "cor_host_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
     "cor_debug_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_int]),

@@ -196,6 +196,11 @@ class Sequence2Sequence(object):
         ``save_weights`` layout plus the ``/config`` group.'''
         assert self.status > 1  # already trained
         self.logger.info('Saving model under "%s"', filename)
+        self._save_weights(filename, with_config=True)
+
+    def _save_weights(self, filename, with_config=False):
+        """Keras ``save_weights`` layout (what ModelCheckpoint(save_weights_only=True) writes per epoch, seq2seq.py:618),
+        plus the reference's ``/config`` group for ``save``."""
         root = h5lite.Group()
         names = list(self._layer_shapes())
         root.attrs['layer_names'] = np.array([n.encode('utf8') for n in names])
@@ -209,6 +214,9 @@ class Sequence2Sequence(object):
                 parts = wname.split('/')
                 sub = group.require_group('/'.join(parts[:-1])) if len(parts) > 1 else group
                 sub[parts[-1]] = np.asarray(arr, np.float32)
+        if not with_config:
+            h5lite.write(filename, root)
+            return
         config = root.require_group('config')
         config['width'] = np.array(int(self.width))
         config['depth'] = np.array(int(self.depth))
@@ -328,9 +336,32 @@ class Sequence2Sequence(object):
         self._engine = None
         self.status = 1
 
+    def map_files(self, filenames):
+        """Character inventory and line count of the files (seq2seq.py:554-590); extends the mapping."""
+        from .training import map_files
+        return map_files(self, filenames)
+
+    def _reconfigure_for_mapping(self):
+        """seq2seq.py:499-525: the embedding grows with the mapping; weights of the characters known before keep their
+        rows, every other layer keeps its weights (incremental training), or everything is initialised afresh."""
+        old, had = self._weights, self.status >= 2
+        old_rows = old['char_input_projection'][0].shape[0] if old else 0
+        if old_rows >= self.voc_size:
+            return
+        self.configure()
+        if had:
+            self.logger.warning('transferring weights from previous model with only %d character types', old_rows)
+            for layer, arrs in old.items():
+                if layer == 'char_input_projection':
+                    self._weights[layer][0][:old_rows] = arrs[0]
+                else:
+                    self._weights[layer] = arrs
+
     def train(self, filenames, val_filenames=None):
-        raise NotImplementedError('training is outside the B200 inference hot path (DESIGN.md: out of scope); '
-                                  'train with the reference and load the .h5 here')
+        '''train model on given text files (seq2seq.py:592-650): epochs of data-parallel steps on the CUDA trainer
+        (csrc/train.cu) with early stopping on the validation loss, see ``training.train``.'''
+        from .training import train
+        return train(self, filenames, val_filenames)
 
     def evaluate(self, filenames, fast=False, normalization='historic_latin', charmap=None, gt_level=1,
                  confusion=10, histogram=True):

@@ -187,6 +187,40 @@ int cor_alignment_paths(const float* align, int64_t stride_step, int64_t stride_
                         int n_rows, int t_max, int s_max, const int32_t* in_len, const int32_t* out_len,
                         double min_score, int32_t* out_path, int path_ld, double* out_dist, void* stream);
 
+/* ---- row T (BASELINE.json config 5): one data-parallel training step.  Replaces encoder_decoder_model.train_on_batch
+ * (lib/keras_train.py:195) on the training graph of seq2seq.py:316-390 compiled by _recompile (:491-497): teacher
+ * forcing, Keras categorical cross-entropy with temporal weights, embedding regulariser (:530-553), Adam(clipnorm=5).
+ * A trainer works on fp32 master weights, gradients and Adam moments as FLAT device vectors; cor_trainer_slot says where a
+ * Keras weight (layer name, index in Keras order, Keras (in, out) layout) lives in them.  Topologies: any depth and
+ * width, residual_connections; not deep_bidirectional_encoder / bridge_dense / LM loss. */
+typedef struct cor_trainer cor_trainer;
+typedef struct cor_train_batch {
+    int32_t n_rows, t_src, k_alt, t_dec;
+    const int32_t* src_idx;    /* DEVICE [n_rows][t_src][k_alt] source non-zeros like cor_lines (idx < 0: none) */
+    const float*   src_val;    /* DEVICE same shape, or NULL = ones */
+    const int32_t* dec_in;     /* DEVICE [n_rows][t_dec] decoder input index per step, -1 = zero vector (start symbol, padding) */
+    const int32_t* dec_out;    /* DEVICE [n_rows][t_dec] target index per step, -1 = padding (temporal weight 0) */
+    const float*   mask_enc;   /* DEVICE [depth-1][2*width] dropout mask (already scaled by 1/keep) on the output of encoder layer n, or NULL */
+    const float*   mask_dec;   /* DEVICE [depth-1][width] the same for the decoder layers below the top, or NULL */
+    const float*   mask_cell;  /* DEVICE [n_rows][width + D] input dropout mask of the attention cell's LSTMCell (seq2seq.py:345), or NULL */
+} cor_train_batch;
+int  cor_trainer_create(const cor_config* cfg, int device, cor_trainer** out);
+void cor_trainer_destroy(cor_trainer* t);
+int  cor_trainer_param_count(const cor_trainer* t, int64_t* n_floats);
+int  cor_trainer_slot(const cor_trainer* t, const char* layer, int index, int64_t* offset, int64_t* count);
+/* the four flat DEVICE vectors (n_floats each, caller-owned: the host side allocates them so that it can all-reduce the
+ * gradient and read / write the weights): parameters, gradient, Adam first and second moments */
+int  cor_trainer_bind(cor_trainer* t, float* params, float* grads, float* adam_m, float* adam_v);
+int  cor_trainer_reset_optimizer(cor_trainer* t);
+/* Forward + backward of this rank's batch.  Leaves in the gradient vector the gradient of the SUM of the weighted
+ * cross-entropies (not divided by the number of target steps) and returns loss_out[0] = that sum, loss_out[1] = the
+ * number of target steps: the caller all-reduces the vector and the pair (NCCL), then every rank applies. */
+int  cor_train_forward_backward(cor_trainer* t, const cor_train_batch* batch, double* loss_out, void* stream);
+/* gradient /= n_target_steps (the GLOBAL count), + regulariser gradient, global-norm clip, Adam (lr <= 0: no update).
+ * stats_out[0] = regulariser value, stats_out[1] = global gradient norm before clipping. */
+int  cor_train_apply(cor_trainer* t, double n_target_steps, int with_regulariser, float lr, float clipnorm,
+                     double* stats_out, void* stream);
+
 /* ---- instrumentation for bench.py and the tests, all PER HANDLE: kernels launched since the last
  * reset; launches by GEMM kernel variant; device time accumulated by the LSTM-GEMM launches between
  * cor_prof_enable(m, 1) and cor_prof_enable(m, 0). */
