@@ -221,6 +221,19 @@ def run_reference(args):
     # torchrun exports OMP_NUM_THREADS=1; the reference arm is meant to use every host thread
     from threadpoolctl import threadpool_limits
     threadpool_limits(limits=cores)
+    if args.workload == "train":
+        n = args.cpu_lines or 64
+        for _ in range(min(args.warmup, 1)):
+            cpu_oracle_train_rate(n)
+        t = [cpu_oracle_train_rate(n)[1] for _ in range(args.steps)]
+        value = LINE_LEN * n * args.steps / sum(t)
+        sample = "%d lines x %d steps of the C5 training step (torch float64 autograd oracle, %d threads)" % (n, args.steps, cores)
+        print(json.dumps({"impl": "reference", "metric": "trained chars/sec (train)", "value": value, "unit": "chars/s", "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(t) / args.steps, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": "C5 training step, %d lines per step" % n},
+                          "cpu_baseline": {"value": value, "unit": "chars/s", "cores": cores, "kind": "port", "sample": sample},
+                          "e2e": {"value": value, "unit": "chars/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
     total = args.steps + args.warmup
     probe_lines = 8 if args.workload == "greedy" else 4
     rate, _ = cpu_oracle_rate(args.workload, probe_lines)
@@ -483,6 +496,101 @@ def measure_early_exit(args, device, n_target=4096):
     return out
 
 
+def cpu_oracle_train_rate(n_lines):
+    """The training oracle (torch float64 autograd, all host threads) on n_lines of the C5 workload: trained chars/s."""
+    import torch
+    from oracle import train as ot
+    from oracle.model import Topology
+    from cor_asv_ann_b200.synthetic import synthetic_alphabet, indices_to_lines
+    torch.set_num_threads(host_threads())
+    topo = Topology(**C2)
+    w = build_weights(C2, "U")
+    mapping = synthetic_alphabet(C2["voc_size"])
+    lines = indices_to_lines(make_indices(n_lines, 1005), mapping[1])
+    x, di, do, _ = ot.teacher_arrays(mapping, C2["voc_size"], lines, lines)
+    t0 = time.perf_counter()
+    _, _, g = ot.loss_and_grads(topo, w, x, di, do)
+    ot.adam_step(w, g, {})
+    dt = time.perf_counter() - t0
+    return LINE_LEN * n_lines / dt, dt
+
+
+def measure_train(args, local, rank, world, lines_per_gpu=64):
+    """Config 5: training forward/backward + Adam(clipnorm 5), depth 2 / width 512 / V 512, 64 lines per GPU per step
+    (source = target, 80 characters + newline: 81 encoder and 82 decoder steps), dropout 0.2 with fresh masks per step,
+    data parallel: NCCL all-reduce of the flat fp32 gradient vector (13.4 M floats) and the loss pair every step."""
+    import torch
+    import torch.distributed as dist
+    from cor_asv_ann_b200.trainer import Trainer, teacher_indices
+    from cor_asv_ann_b200.synthetic import synthetic_alphabet, indices_to_lines
+    mapping = synthetic_alphabet(C2["voc_size"])
+    tr = Trainer(dict(C2, window_width=5), build_weights(C2, "U"), device=local)
+    total = args.steps + args.warmup
+    rng = np.random.default_rng(17 + rank)
+    batches = []
+    for s in range(total):
+        lines = indices_to_lines(make_indices(lines_per_gpu, 1005 + 7919 * rank + 101 * s), mapping[1])
+        batches.append(teacher_indices(mapping[0], lines, lines))
+    dev = [tuple(torch.as_tensor(a, device="cuda") for a in b) for b in batches]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    losses = []
+    for s in range(args.warmup):
+        tr.train_on_batch(dev[s][0], None, dev[s][1], dev[s][2], tr.dropout_masks(rng, 0.2, lines_per_gpu))
+    barrier()
+    tr.launch_count(reset=True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for s in range(args.warmup, total):
+        losses.append(tr.train_on_batch(dev[s][0], None, dev[s][1], dev[s][2], tr.dropout_masks(rng, 0.2, lines_per_gpu)))
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = tr.launch_count()
+    # end to end: host (numpy) batches in, loss out -- the H2D copies of the index arrays inside
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(args.warmup, total):
+        tr.train_on_batch(batches[s][0], None, batches[s][1], batches[s][2], tr.dropout_masks(rng, 0.2, lines_per_gpu))
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    t_ms = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t_ms[0]), float(t_ms[1])
+    chars = LINE_LEN * lines_per_gpu * args.steps * world
+    h2d = sum(a.nbytes for a in batches[0]) + (2 * 512 + 512 + lines_per_gpu * 1024) * 4
+    flops_line = 3.0 * (flops_enc(LINE_LEN + 1, C2) + (LINE_LEN + 2) * flops_step(C2))
+    return {"ms": ms, "value": chars / (ms * 1e-3), "e2e_value": chars / (e2e_ms * 1e-3), "e2e_ms": e2e_ms, "h2d": h2d, "d2h": 16,
+            "launches": launches, "clocks": clocks, "losses": [float(l) for l in losses], "n_params": tr.n_params,
+            "tflops": flops_line * lines_per_gpu * args.steps * world / (ms * 1e-3) / 1e12, "lines_per_gpu": lines_per_gpu}
+
+
+def train_line(args, r, world):
+    return {"metric": "trained chars/sec (train)", "value": r["value"], "unit": "chars/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": r["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C5 training forward/backward + Adam(clipnorm 5): depth 2 width 512 V 512, %d lines per GPU per step, source = target, "
+                                   "80 characters + newline, dropout 0.2, random-init weights (variant U)" % r["lines_per_gpu"],
+                       "lines_per_step_per_gpu": r["lines_per_gpu"], "parallelism": "data parallel: NCCL all-reduce (sum) of the flat fp32 gradient vector (%d floats) per step" % r["n_params"],
+                       "l2": "inputs and dropout masks differ every step; activations + weights + moments (~0.5 GB) exceed the 126 MB L2"},
+            "e2e": {"value": r["e2e_value"], "unit": "chars/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"], "ms_per_step": r["e2e_ms"] / args.steps,
+                    "api": "Trainer.train_on_batch (numpy index arrays in, loss out)"},
+            "gpu_launches": r["launches"], "clocks": r["clocks"],
+            "roofline": {"bound": "latency", "kernel": "the recorded step graph (cuBLAS SGEMM at 64 rows + the hand-written cell / attention / loss kernels)",
+                         "achieved": r["tflops"], "peak": None, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                         "note": "algorithmic 3 x forward FLOPs; at 64 rows per GEMM the step is bound by ~2 500 dependent launches, not by a pipe"},
+            "loss_first_last": [r["losses"][0], r["losses"][-1]]}
+
+
 def make_s2s(topo, w, mapping, device):
     from cor_asv_ann_b200.seq2seq import Sequence2Sequence
     s = Sequence2Sequence()
@@ -636,7 +744,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "beam"), choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("COR_BENCH_WORKLOAD", "beam"), choices=sorted(WORKLOADS) + ["train"])
     ap.add_argument("--lines", type=int, default=int(os.environ.get("COR_BENCH_LINES", "0")), help="lines per step per GPU (0 = the workload's default)")
     ap.add_argument("--beam-budget-gb", type=float, default=72.0)
     ap.add_argument("--gemm-mode", type=int, default=0)
@@ -685,6 +793,21 @@ def main():
                                   device=local, eos_index=1, gemm_mode=args.gemm_mode)
         return engines[key]
 
+    if args.workload == "train":
+        r = measure_train(args, local, rank, world)
+        if world > 1:
+            dist.barrier()
+        sys.stdout.flush(); os.dup2(saved_stdout, 1)
+        if rank == 0:
+            line = train_line(args, r, world)
+            if world == 1 and not args.no_cpu:
+                v, dt = cpu_oracle_train_rate(args.cpu_lines or 64)
+                line["cpu_baseline"] = {"value": v, "unit": "chars/s", "cores": host_threads(), "kind": "port",
+                                        "sample": "%d lines of the same workload, one step of the torch float64 autograd oracle (Keras/TF unavailable), %.1f s" % (args.cpu_lines or 64, dt)}
+            print(json.dumps(line))
+        if world > 1:
+            dist.destroy_process_group()
+        return
     mapping = synthetic_alphabet(C2["voc_size"])
     w_c2 = build_weights(C2, "U")
     if args.predict_only:
@@ -719,6 +842,11 @@ def main():
     predict_r = measure_predict(args, C2, w_c2, mapping, local, args.predict_lines) if (rank == 0 and single and args.predict_lines > 0) else None
     c1_r = measure_c1(local) if (rank == 0 and single) else None
     early_r = measure_early_exit(args, local) if (rank == 0 and single) else None
+    train_r = None
+    if rank == 0 and single:
+        for e in engines.values():
+            e.release_workspace()
+        train_r = train_line(args, measure_train(args, local, 0, 1), 1)
     strong_r = measure_strong(args, C2, w_c2, mapping, local, rank, world) if not args.only else None
 
     if world > 1:
@@ -748,6 +876,8 @@ def main():
             line.setdefault("also", {})["c1"] = c1_r
         if early_r is not None:
             line.setdefault("also", {})["greedy_early_exit"] = early_r
+        if train_r is not None:
+            line.setdefault("also", {})["train_c5"] = {k: train_r[k] for k in ("metric", "value", "unit", "ms_per_step", "config", "e2e", "gpu_launches", "roofline", "loss_first_last")}
         if page_r is not None:
             line["page"] = page_r
         if predict_r is not None:

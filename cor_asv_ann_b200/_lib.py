@@ -57,6 +57,7 @@ PROTOTYPES = {
     "cor_trainer_slot": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "cor_trainer_bind": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cor_trainer_reset_optimizer": (C.c_int, [C.c_void_p]),
+    "cor_trainer_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
     "cor_train_forward_backward": (C.c_int, [C.c_void_p, C.POINTER(CorTrainBatch), C.POINTER(C.c_double), C.c_void_p]),
     "cor_train_apply": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_float, C.c_float, C.POINTER(C.c_double), C.c_void_p]),
     "cor_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),

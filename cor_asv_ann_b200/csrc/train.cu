@@ -62,7 +62,9 @@ struct cor_trainer {
     cor_config cfg{};
     int device = 0;
     int W = 0, d = 0, V = 0, D = 0;
-    cublasHandle_t blas = nullptr;
+    cublasHandle_t blas = nullptr, blas2 = nullptr, cur_blas = nullptr;
+    cudaStream_t side = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    float* d_x2 = nullptr;                                               // input gradient of the backward direction (added after the join)
     std::map<std::string, std::vector<PSlot>> slots;      // Keras layer -> weights
     std::vector<std::string> layer_order;
     size_t n_params = 0;
@@ -88,13 +90,15 @@ struct cor_trainer {
     float *d_top = nullptr, *d_encout = nullptr, *d_u = nullptr, *d_wq = nullptr, *d_ctx = nullptr, *dv_part = nullptr, *dbv_part = nullptr;
     float *d_seq_a = nullptr, *d_seq_b = nullptr;          // [T][B][2W] gradient of a layer's output / input sequence
     float *dh = nullptr, *dc = nullptr, *dh_tmp = nullptr; // [B][W] running recurrent gradients
+    float *dh_r = nullptr, *dc_r = nullptr;                // ... of a backward-direction scan
     std::vector<float*> dh_init, dc_init;                  // gradient wrt the decoder layers' initial states [B][W]
     float* ones = nullptr; size_t ones_n = 0;
     // the batch, staged into buffers of the activation store (a recorded step reads fixed addresses)
     int32_t *s_src = nullptr, *s_din = nullptr, *s_dout = nullptr;
     float *s_val = nullptr, *s_menc = nullptr, *s_mdec = nullptr, *s_mcell = nullptr;
     // one executable graph per batch geometry (a step is ~2 500 launches at T = 81: replayed, not re-issued)
-    struct StepGraph { std::vector<int> key; cudaGraph_t graph; cudaGraphExec_t exec; };
+    struct StepGraph { std::vector<int> key; cudaGraph_t graph; cudaGraphExec_t exec; long long nodes; };
+    long long launches = 0;                               // graph nodes (kernels, copies, memsets) run since the last reset
     std::vector<StepGraph> graphs;
     cudaStream_t cap_stream = nullptr;
 };
@@ -379,7 +383,23 @@ inline int grid_for_n(size_t n) { return (int)std::min<size_t>((n + 255) / 256, 
 int gemm(cor_trainer* t, bool ta, bool tb, int M, int N, int K, float alpha, const float* A, int lda, const float* B, int ldb, float beta, float* C, int ldc) {
     if (M <= 0 || N <= 0) return 0;
     if (K <= 0) return 0;
-    COR_BLAS(cublasSgemm(t->blas, tb ? CUBLAS_OP_T : CUBLAS_OP_N, ta ? CUBLAS_OP_T : CUBLAS_OP_N, N, M, K, &alpha, B, ldb, A, lda, &beta, C, ldc));
+    COR_BLAS(cublasSgemm(t->cur_blas, tb ? CUBLAS_OP_T : CUBLAS_OP_N, ta ? CUBLAS_OP_T : CUBLAS_OP_N, N, M, K, &alpha, B, ldb, A, lda, &beta, C, ldc));
+    return 0;
+}
+// Work issued between fork() and join() on the returned stream runs beside the main stream (the two directions of the
+// bidirectional layer are independent chains of ~T dependent launches each); it has its own cuBLAS handle (workspace).
+int fork_side(cor_trainer* t, cudaStream_t st, cudaStream_t* side) {
+    COR_CUDA(cudaEventRecord(t->ev_fork, st));
+    COR_CUDA(cudaStreamWaitEvent(t->side, t->ev_fork, 0));
+    COR_BLAS(cublasSetStream(t->blas2, t->side));
+    t->cur_blas = t->blas2;
+    *side = t->side;
+    return 0;
+}
+void end_side(cor_trainer* t) { t->cur_blas = t->blas; }      // what follows goes to the main stream again; the side work keeps running
+int join_side(cor_trainer* t, cudaStream_t st) {
+    COR_CUDA(cudaEventRecord(t->ev_join, t->side));
+    COR_CUDA(cudaStreamWaitEvent(st, t->ev_join, 0));
     return 0;
 }
 
@@ -435,7 +455,8 @@ int ensure_store(cor_trainer* t, int B, int Ts, int Td, int k) {
         take(t, (size_t)Td * B, &t->dbv_part)) return 1;
     const size_t Tm = std::max(Ts, Td);
     if (take(t, Tm * B * 2 * W, &t->d_seq_a) || take(t, Tm * B * 2 * W, &t->d_seq_b)) return 1;
-    if (take(t, BW, &t->dh) || take(t, BW, &t->dc) || take(t, BW, &t->dh_tmp)) return 1;
+    if (take(t, BW, &t->dh) || take(t, BW, &t->dc) || take(t, BW, &t->dh_tmp) || take(t, BW, &t->dh_r) || take(t, BW, &t->dc_r)) return 1;
+    if (take(t, (size_t)Ts * BW, &t->d_x2)) return 1;
     if (take(t, (size_t)B * Ts * k, &t->s_src) || take(t, (size_t)B * Ts * k, &t->s_val) || take(t, (size_t)B * Td, &t->s_din) ||
         take(t, (size_t)B * Td, &t->s_dout) || take(t, (size_t)std::max(d - 1, 1) * 2 * W, &t->s_menc) ||
         take(t, (size_t)std::max(d - 1, 1) * W, &t->s_mdec) || take(t, (size_t)B * (W + D), &t->s_mcell)) return 1;
@@ -453,13 +474,18 @@ int lstm_forward(cor_trainer* t, cudaStream_t st, const LstmP& lp, const float* 
     // pre-activations of every step at once: G = x . K + b
     if (gemm(t, false, false, T * B, 4 * W, lp.in, 1.f, x, lp.in, Pm + lp.K, 4 * W, 0.f, a.G, 4 * W)) return 1;
     tr_bias_rows_kernel<<<grid_for_n((size_t)T * B * 4 * W), 256, 0, st>>>(a.G, Pm + lp.b, (size_t)T * B, 4 * W);
-    if (h0) { COR_CUDA(cudaMemcpyAsync(a.H, h0, BW * 4, cudaMemcpyDeviceToDevice, st)); COR_CUDA(cudaMemcpyAsync(a.C, c0, BW * 4, cudaMemcpyDeviceToDevice, st)); }
-    else { COR_CUDA(cudaMemsetAsync(a.H, 0, BW * 4, st)); COR_CUDA(cudaMemsetAsync(a.C, 0, BW * 4, st)); }
+    // state slots: forward scan -- slot s before step s, slot s + 1 after; backward scan -- slot pos + 1 before the step on
+    // position pos, slot pos after (initial state in slot T, final in slot 0): either way "the state before position pos"
+    // of all positions is one contiguous block, which the recurrent-weight gradient wants as one GEMM operand
+    const size_t s0 = reverse ? (size_t)T * BW : 0;
+    if (h0) { COR_CUDA(cudaMemcpyAsync(a.H + s0, h0, BW * 4, cudaMemcpyDeviceToDevice, st)); COR_CUDA(cudaMemcpyAsync(a.C + s0, c0, BW * 4, cudaMemcpyDeviceToDevice, st)); }
+    else { COR_CUDA(cudaMemsetAsync(a.H + s0, 0, BW * 4, st)); COR_CUDA(cudaMemsetAsync(a.C + s0, 0, BW * 4, st)); }
     for (int s = 0; s < T; ++s) {
         const int pos = reverse ? T - 1 - s : s;
+        const size_t before = (size_t)(reverse ? pos + 1 : pos) * BW, after = (size_t)(reverse ? pos : pos + 1) * BW;
         float* Z = a.G + (size_t)pos * B * 4 * W;
-        if (gemm(t, false, false, B, 4 * W, W, 1.f, a.H + (size_t)s * BW, W, Pm + lp.R, 4 * W, 1.f, Z, 4 * W)) return 1;
-        tr_cell_fwd_kernel<<<(int)((BW + 255) / 256), 256, 0, st>>>(Z, a.C + (size_t)s * BW, a.C + (size_t)(s + 1) * BW, a.H + (size_t)(s + 1) * BW, W,
+        if (gemm(t, false, false, B, 4 * W, W, 1.f, a.H + before, W, Pm + lp.R, 4 * W, 1.f, Z, 4 * W)) return 1;
+        tr_cell_fwd_kernel<<<(int)((BW + 255) / 256), 256, 0, st>>>(Z, a.C + before, a.C + after, a.H + after, W,
                                                                   out + (size_t)pos * B * ld_out, ld_out, B, W);
     }
     COR_CUDA(cudaGetLastError());
@@ -475,24 +501,21 @@ int lstm_backward(cor_trainer* t, cudaStream_t st, const LstmP& lp, const float*
     const int W = t->W;
     const size_t BW = (size_t)B * W;
     const float* Pm = t->P; float* Gm = t->Gd;
-    if (dh_last) { COR_CUDA(cudaMemcpyAsync(t->dh, dh_last, BW * 4, cudaMemcpyDeviceToDevice, st)); COR_CUDA(cudaMemcpyAsync(t->dc, dc_last, BW * 4, cudaMemcpyDeviceToDevice, st)); }
-    else { COR_CUDA(cudaMemsetAsync(t->dh, 0, BW * 4, st)); COR_CUDA(cudaMemsetAsync(t->dc, 0, BW * 4, st)); }
+    float* dh = reverse ? t->dh_r : t->dh; float* dc = reverse ? t->dc_r : t->dc;     // the two directions of a layer may run side by side
+    if (dh_last) { COR_CUDA(cudaMemcpyAsync(dh, dh_last, BW * 4, cudaMemcpyDeviceToDevice, st)); COR_CUDA(cudaMemcpyAsync(dc, dc_last, BW * 4, cudaMemcpyDeviceToDevice, st)); }
+    else { COR_CUDA(cudaMemsetAsync(dh, 0, BW * 4, st)); COR_CUDA(cudaMemsetAsync(dc, 0, BW * 4, st)); }
     for (int s = T - 1; s >= 0; --s) {
         const int pos = reverse ? T - 1 - s : s;
+        const size_t before = (size_t)(reverse ? pos + 1 : pos) * BW, after = (size_t)(reverse ? pos : pos + 1) * BW;
         float* G = a.G + (size_t)pos * B * 4 * W;
-        tr_cell_bwd_kernel<<<(int)((BW + 255) / 256), 256, 0, st>>>(G, a.C + (size_t)s * BW, a.C + (size_t)(s + 1) * BW, t->dh,
-                                                                  d_out ? d_out + (size_t)pos * B * ld : nullptr, ld, t->dc, B, W);
+        tr_cell_bwd_kernel<<<(int)((BW + 255) / 256), 256, 0, st>>>(G, a.C + before, a.C + after, dh,
+                                                                  d_out ? d_out + (size_t)pos * B * ld : nullptr, ld, dc, B, W);
         // dh_{s-1} = dZ . R^T
-        if (gemm(t, false, true, B, W, 4 * W, 1.f, G, 4 * W, Pm + lp.R, 4 * W, 0.f, t->dh, W)) return 1;
+        if (gemm(t, false, true, B, W, 4 * W, 1.f, G, 4 * W, Pm + lp.R, 4 * W, 0.f, dh, W)) return 1;
     }
     COR_CUDA(cudaGetLastError());
-    // parameter gradients over all steps at once.  H by scan step: slot s = state BEFORE step s; dZ is stored by position.
-    if (!reverse) {
-        if (gemm(t, true, false, W, 4 * W, T * B, 1.f, a.H, W, a.G, 4 * W, 1.f, Gm + lp.R, 4 * W)) return 1;
-    } else {
-        for (int s = 0; s < T; ++s)     // position T-1-s pairs with scan slot s
-            if (gemm(t, true, false, W, 4 * W, B, 1.f, a.H + (size_t)s * BW, W, a.G + (size_t)(T - 1 - s) * B * 4 * W, 4 * W, 1.f, Gm + lp.R, 4 * W)) return 1;
-    }
+    // parameter gradients over all steps at once: "state before position pos" is slots 0..T-1 (forward) or 1..T (backward)
+    if (gemm(t, true, false, W, 4 * W, T * B, 1.f, a.H + (reverse ? BW : 0), W, a.G, 4 * W, 1.f, Gm + lp.R, 4 * W)) return 1;
     if (gemm(t, true, false, lp.in, 4 * W, T * B, 1.f, x, lp.in, a.G, 4 * W, 1.f, Gm + lp.K, 4 * W)) return 1;
     tr_colsum_kernel<<<(4 * W + 31) / 32, dim3(32, 8), 0, st>>>(a.G, 4 * W, (size_t)T * B, 4 * W, Gm + lp.b, 1);
     if (d_x && gemm(t, false, true, T * B, lp.in, 4 * W, 1.f, a.G, 4 * W, Pm + lp.K, 4 * W, beta_x, d_x, lp.in)) return 1;
@@ -553,8 +576,12 @@ int cor_trainer_create(const cor_config* cfg, int device, cor_trainer** out) {
         }
     }
     if (cudaMalloc((void**)&t->d_scal, 64) != cudaSuccess) { set_error("out of device memory for the trainer"); delete t; return 1; }
-    if (cublasCreate(&t->blas) != CUBLAS_STATUS_SUCCESS) { set_error("cublasCreate failed"); delete t; return 1; }
-    cublasSetMathMode(t->blas, CUBLAS_PEDANTIC_MATH);       // plain fp32: no TF32, no reduced-precision accumulation
+    if (cublasCreate(&t->blas) != CUBLAS_STATUS_SUCCESS || cublasCreate(&t->blas2) != CUBLAS_STATUS_SUCCESS) { set_error("cublasCreate failed"); delete t; return 1; }
+    t->cur_blas = t->blas;
+    cublasSetMathMode(t->blas2, CUBLAS_DEFAULT_MATH);
+    if (cudaStreamCreateWithFlags(&t->side, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&t->ev_join, cudaEventDisableTiming) != cudaSuccess) { set_error("cannot create the side stream"); delete t; return 1; }
+    cublasSetMathMode(t->blas, CUBLAS_DEFAULT_MATH);        // plain fp32 FFMA: TF32 tensor ops stay off unless asked for, which nothing here does
     *out = t;
     return 0;
 }
@@ -565,6 +592,10 @@ void cor_trainer_destroy(cor_trainer* t) {
     free_store(t);
     if (t->cap_stream) cudaStreamDestroy(t->cap_stream);
     if (t->blas) cublasDestroy(t->blas);
+    if (t->blas2) cublasDestroy(t->blas2);
+    if (t->side) cudaStreamDestroy(t->side);
+    if (t->ev_fork) cudaEventDestroy(t->ev_fork);
+    if (t->ev_join) cudaEventDestroy(t->ev_join);
     cudaFree(t->d_scal);
     if (t->ones) cudaFree(t->ones);
     delete t;
@@ -588,6 +619,13 @@ int cor_trainer_bind(cor_trainer* t, float* params, float* grads, float* adam_m,
     COR_CHECK(t && params && grads && adam_m && adam_v, "null argument");
     t->P = params; t->Gd = grads; t->M1 = adam_m; t->M2 = adam_v;
     return 0;
+}
+
+int64_t cor_trainer_launch_count(cor_trainer* t, int reset) {
+    if (!t) return -1;
+    const int64_t v = t->launches;
+    if (reset) t->launches = 0;
+    return v;
 }
 
 int cor_trainer_reset_optimizer(cor_trainer* t) {
@@ -618,8 +656,13 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
         const float* x = t->enc_in[n];
         const int Dn = n == 0 ? 2 * W : W;
         float* raw = t->enc_out_raw[n];
+        if (n == 0) {       // the backward direction beside the forward one
+            cudaStream_t side;
+            if (fork_side(t, st, &side) || lstm_forward(t, side, t->enc_bw[0], x, Ts, B, t->a_bw[0], nullptr, nullptr, true, raw + W, Dn)) return 1;
+            end_side(t);
+        }
         if (lstm_forward(t, st, t->enc_fw[n], x, Ts, B, t->a_fw[n], nullptr, nullptr, false, raw, Dn)) return 1;
-        if (n == 0 && lstm_forward(t, st, t->enc_bw[0], x, Ts, B, t->a_bw[0], nullptr, nullptr, true, raw + W, Dn)) return 1;
+        if (n == 0 && join_side(t, st)) return 1;
         // what the next layer (or the attention) sees: residual from the third forward layer up, then the time-constant dropout
         const bool rs = resid && n >= 2;
         const float* mask = (n < d - 1 && bt->mask_enc) ? bt->mask_enc + (size_t)n * 2 * W : nullptr;
@@ -630,7 +673,8 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
     // state handed to decoder layer n: backward final of the bottom layer, forward final otherwise (seq2seq.py:280-283)
     auto enc_final = [&](int n, const float** h, const float** c) {
         LstmAct& a = n == 0 ? t->a_bw[0] : t->a_fw[n];
-        *h = a.H + (size_t)Ts * BW; *c = a.C + (size_t)Ts * BW;
+        const size_t fin = n == 0 ? 0 : (size_t)Ts * BW;          // final state: slot 0 of a backward scan, slot T of a forward one
+        *h = a.H + fin; *c = a.C + fin;
     };
     // ---- decoder layers below the top
     for (int n = 0; n + 1 < d; ++n) {
@@ -787,8 +831,12 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
         float* d_x = bufs[pp];                       // gradient wrt the layer's input sequence [Ts][B][in]
         // decoder layer n started from this layer's final state: backward final for the bottom layer, forward final otherwise
         if (n == 0) {
-            if (lstm_backward(t, st, t->enc_fw[0], x, Ts, B, t->a_fw[0], false, d_enc, Dn, nullptr, nullptr, d_x, 0.f)) return 1;
-            if (lstm_backward(t, st, t->enc_bw[0], x, Ts, B, t->a_bw[0], true, d_enc + W, Dn, t->dh_init[0], t->dc_init[0], d_x, 1.f)) return 1;
+            cudaStream_t side;
+            if (fork_side(t, st, &side) ||
+                lstm_backward(t, side, t->enc_bw[0], x, Ts, B, t->a_bw[0], true, d_enc + W, Dn, t->dh_init[0], t->dc_init[0], t->d_x2, 0.f)) return 1;
+            end_side(t);
+            if (lstm_backward(t, st, t->enc_fw[0], x, Ts, B, t->a_fw[0], false, d_enc, Dn, nullptr, nullptr, d_x, 0.f) || join_side(t, st)) return 1;
+            tr_accum_kernel<<<grid_for_n((size_t)Ts * B * W), 256, 0, st>>>(d_x, W, t->d_x2, W, nullptr, 1, B, (size_t)Ts * B, W);
         } else {
             if (lstm_backward(t, st, t->enc_fw[n], x, Ts, B, t->a_fw[n], false, d_enc, Dn, t->dh_init[n], t->dc_init[n], d_x, 0.f)) return 1;
             if (rs) tr_accum_kernel<<<grid_for_n((size_t)Ts * B * in), 256, 0, st>>>(d_x, in, d_enc, Dn, nullptr, 1, B, (size_t)Ts * B, in);
@@ -830,7 +878,8 @@ int cor_train_forward_backward(cor_trainer* t, const cor_train_batch* bt, double
     } else {
         const std::vector<int> key = {B, Ts, Td, k, sb.src_val != nullptr, sb.mask_enc != nullptr, sb.mask_dec != nullptr, sb.mask_cell != nullptr};
         cudaGraphExec_t exec = nullptr;
-        for (auto& g : t->graphs) if (g.key == key) exec = g.exec;
+        long long nodes = 0;
+        for (auto& g : t->graphs) if (g.key == key) { exec = g.exec; nodes = g.nodes; }
         if (!exec) {
             if (!t->cap_stream) COR_CUDA(cudaStreamCreateWithFlags(&t->cap_stream, cudaStreamNonBlocking));
             COR_CUDA(cudaStreamSynchronize(st));                 // the staging copies above must not race the warm-up run below
@@ -844,10 +893,14 @@ int cor_train_forward_backward(cor_trainer* t, const cor_train_batch* bt, double
             if (rc) return 1;
             COR_CUDA(ce);
             COR_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+            size_t n_nodes = 0;
+            COR_CUDA(cudaGraphGetNodes(graph, nullptr, &n_nodes));
+            nodes = (long long)n_nodes;
             if (t->graphs.size() >= 16) drop_graphs(t);
-            t->graphs.push_back(cor_trainer::StepGraph{key, graph, exec});
+            t->graphs.push_back(cor_trainer::StepGraph{key, graph, exec, nodes});
         }
         COR_CUDA(cudaGraphLaunch(exec, st));
+        t->launches += nodes;
     }
     double scal[3];
     COR_CUDA(cudaMemcpyAsync(scal, t->d_scal, sizeof(scal), cudaMemcpyDeviceToHost, st));
@@ -867,6 +920,7 @@ int cor_train_apply(cor_trainer* t, double n_target_steps, int with_regulariser,
     tr_scale_kernel<<<grid_for_n(t->n_params), 256, 0, st>>>(t->Gd, t->n_params, inv);
     if (with_regulariser) tr_regulariser_kernel<<<1, 256, (size_t)W * 4, st>>>(t->P + t->E, V, W, t->Gd + t->E, t->d_scal);
     tr_sumsq_kernel<<<grid_for_n(t->n_params), 256, 0, st>>>(t->Gd, t->n_params, t->d_scal + 3);
+    t->launches += 3 + (with_regulariser ? 1 : 0);
     if (lr > 0.f) {
         t->adam_t += 1;
         const double b1 = 0.9, b2 = 0.999;

@@ -118,6 +118,9 @@ class Trainer:
     def get_gradients(self):
         return self._unflatten(self.grads)
 
+    def launch_count(self, reset=False):
+        return int(self.lib.cor_trainer_launch_count(self.handle, int(reset)))
+
     def reset_optimizer(self):
         check(self.lib.cor_trainer_reset_optimizer(self.handle))
 

@@ -212,6 +212,7 @@ int  cor_trainer_slot(const cor_trainer* t, const char* layer, int index, int64_
  * gradient and read / write the weights): parameters, gradient, Adam first and second moments */
 int  cor_trainer_bind(cor_trainer* t, float* params, float* grads, float* adam_m, float* adam_v);
 int  cor_trainer_reset_optimizer(cor_trainer* t);
+int64_t cor_trainer_launch_count(cor_trainer* t, int reset);     /* graph nodes (kernels, copies) the steps ran since the last reset */
 /* Forward + backward of this rank's batch.  Leaves in the gradient vector the gradient of the SUM of the weighted
  * cross-entropies (not divided by the number of target steps) and returns loss_out[0] = that sum, loss_out[1] = the
  * number of target steps: the caller all-reduces the vector and the pair (NCCL), then every rank applies. */
