@@ -92,14 +92,13 @@ cudaStream_t loop_capture_stream(cor_model* m, int which) {
     if (!c->capture[which] && cudaStreamCreateWithFlags(&c->capture[which], cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     return c->capture[which];
 }
-int loop_graph_switch(cudaStream_t cs, cudaGraph_t root, int n, cudaGraphConditionalHandle* sw, cudaGraph_t* branches) {
+int loop_graph_switch(cudaStream_t cs, int n, cudaGraphConditionalHandle sw, cudaGraph_t* branches) {
     cudaStreamCaptureStatus status; cudaGraph_t cur = nullptr; const cudaGraphNode_t* deps = nullptr; size_t ndeps = 0;
     COR_CUDA(cudaStreamGetCaptureInfo(cs, &status, nullptr, &cur, &deps, &ndeps));
     COR_CHECK(status == cudaStreamCaptureStatusActive && cur, "stream is not capturing");
-    COR_CUDA(cudaGraphConditionalHandleCreate(sw, root, 0, 0));
     cudaGraphNodeParams cp{};
     cp.type = cudaGraphNodeTypeConditional;
-    cp.conditional.handle = *sw; cp.conditional.type = cudaGraphCondTypeSwitch; cp.conditional.size = (unsigned)n;
+    cp.conditional.handle = sw; cp.conditional.type = cudaGraphCondTypeSwitch; cp.conditional.size = (unsigned)n;
     cudaGraphNode_t node;
     COR_CUDA(cudaGraphAddNode(&node, cur, deps, ndeps, &cp));
     for (int i = 0; i < n; ++i) branches[i] = cp.conditional.phGraph_out[i];

@@ -121,7 +121,9 @@ __global__ void beam_init_kernel(BeamDev b) {
 // ------------------------------------------------------------------ pop (seq2seq.py:1398-1420)
 // One warp per line: the fringe is sorted, so the pop is a prefix of it — walked 32 entries at a time
 // until batch_size open nodes have been seen (a few chunks at most, whatever the fringe length).
-__device__ void pop_line(const BeamDev& b, int line, int lane) {
+// `bump`: also reserve the expansion records of the popped nodes (x_base / x_count), which beam_rowmap_kernel does on the
+// three-kernel path.
+__device__ void pop_line(const BeamDev& b, int line, int lane, bool bump = false) {
     if (b.status[line] != ST_ACTIVE) { if (lane == 0) b.beam_count[line] = 0; return; }
     const int Tl = b.row_T[line];
     const int len = b.fr_len[line];
@@ -209,6 +211,7 @@ __device__ void pop_line(const BeamDev& b, int line, int lane) {
         if (consumed < len && consumed > 0 && fabs(keys[consumed] - keys[consumed - 1]) <= 1e-6 * fmax(1.0, fabs(keys[consumed]))) b.near_ties[line] += 1;
     }
     b.beam_count[line] = out;
+    if (bump && out > 0) { const int xb = b.x_count[line]; b.x_base[line] = xb; b.x_count[line] = xb + out; }
 }
 __global__ void __launch_bounds__(256) beam_pop_kernel(BeamDev b) {
     const int line = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -336,13 +339,10 @@ __global__ void __launch_bounds__(1024) beam_select_small_kernel(BeamDev b, Loop
 
 // ------------------------------------------------------------------ gather: decoder-step inputs of every row
 // (seq2seq.py:1423-1429: vstack of node.scores / node.state)
-__global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) {
+__device__ __forceinline__ void gather_row(const BeamDev& b, int split, int row, int line, uint32_t node) {
     // 128-bit accesses throughout: a record is ~12 KB (p, h, c, query) and is read exactly once
-    const int R = b.counters[0];
     const int W4 = b.W >> 2, V4 = b.Vp >> 2;
-    for (int row = blockIdx.x; row < R; row += gridDim.x) {
-        const int line = b.row_line[row];
-        const uint32_t node = b.row_node[row];
+    do {
         float* p_lo = split ? b.p_lo : nullptr;       // split operands: base pointers + element offsets only
         const size_t po = (size_t)row * b.Vp;
         float* a_in = b.a_in + (size_t)row * b.T;
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) 
                     ci[u] = sc[u];
                 }
             }
-            continue;
+            break;
         }
         const int k = (int)((node - 1u) % KMAX);
         const size_t g = (size_t)line * b.quota_x + (node - 1u) / KMAX;
@@ -413,6 +413,62 @@ __global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) 
                 ci[u] = rc[u];
             }
         }
+    } while (0);
+}
+__global__ void __launch_bounds__(128) beam_gather_kernel(BeamDev b, int split) {
+    const int R = b.counters[0];
+    for (int row = blockIdx.x; row < R; row += gridDim.x) gather_row(b, split, row, b.row_line[row], b.row_node[row]);
+}
+
+// Page of lines (L <= kSelectSmall), line-kernel path: the scan over the lines' pop counts is so small that EVERY block of
+// the gather redoes it in shared memory instead of waiting for another launch; block 0 publishes the row count for the
+// GEMMs, marks overflowing lines and sets the loop controls.  A row finds its line by bisection over <= 64 bases.
+__global__ void __launch_bounds__(128) beam_gather_scan_kernel(BeamDev b, int split, LoopCtl lc, int set_cond) {
+    __shared__ int s_base[kSelectSmall], s_cnt[kSelectSmall];
+    __shared__ int s_total;
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) {
+        int carry = 0, total = 0, active = 0;
+        for (int base = 0; base < b.L; base += 32) {
+            const int line = base + lane;
+            const bool live = line < b.L && b.status[line] == ST_ACTIVE;
+            const int c0 = live ? b.beam_count[line] : 0;
+            int incl = c0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+            const int rb = carry + incl - c0;
+            const bool over = c0 > 0 && rb + c0 > b.Rcap;
+            const int c = over ? 0 : c0;
+            if (line < b.L) {
+                s_cnt[line] = c; s_base[line] = rb;
+                if (blockIdx.x == 0) { b.row_base[line] = rb; if (over) b.status[line] = ST_OVERFLOW; }
+            }
+            int t = c > 0 ? rb + c : 0, a = (live && !over) ? 1 : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { t = max(t, __shfl_xor_sync(0xffffffffu, t, o)); a += __shfl_xor_sync(0xffffffffu, a, o); }
+            total = max(total, t); active += a;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) {
+            s_total = total;
+            if (blockIdx.x == 0) {
+                b.counters[0] = total; b.counters[1] = active; b.counters[2] = 0;
+                if (set_cond) {
+                    const int bodies = ++b.counters[3];
+                    set_loop(lc, total, (total > 0 || active > 0) && bodies <= 2 * b.T + 2);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int R = s_total;
+    for (int row = blockIdx.x; row < R; row += gridDim.x) {
+        int lo = 0, hi = b.L - 1;                  // last line whose base is <= row
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (s_base[mid] <= row) lo = mid; else hi = mid - 1; }
+        const int line = lo, j = row - s_base[lo];
+        const uint32_t node = b.beam_nodes[(size_t)line * b.batch + j];
+        if (threadIdx.x == 0) { b.row_line[row] = line; b.row_node[row] = node; b.row_xid[row] = b.x_base[line] + j; }
+        gather_row(b, split, row, line, node);
     }
 }
 
@@ -612,11 +668,9 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
 // slot k, the assignment softmax_kernel uses, so both decoders see bit-identical probabilities), every
 // reduction is a shuffle, and no block barrier is needed.  Same procedure as beam_expand_kernel.
 template <int NVL>
-__global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int split) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int R = b.counters[0];
+__device__ __forceinline__ void expand_row(const BeamDev& b, int split, int row, int lane) {
     const unsigned FULL = 0xffffffffu;
-    for (int row = blockIdx.x * 4 + wid; row < R; row += gridDim.x * 4) {
+    {
         const int line = b.row_line[row];
         const uint32_t node = b.row_node[row];
         const int Tl = b.row_T[line];
@@ -839,6 +893,12 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
         }
     }
 }
+template <int NVL>
+__global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int split) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int R = b.counters[0];
+    for (int row = blockIdx.x * 4 + wid; row < R; row += gridDim.x * 4) expand_row<NVL>(b, split, row, lane);
+}
 
 // ------------------------------------------------------------------ push: insort of the new children (:1515-1532)
 __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum) {
@@ -925,14 +985,10 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
 // or a narrow beam prunes the expansion).  Lane t holds child t; its slot in the merged fringe is its rank
 // among the new children plus the number of old entries that precede it.  Lines with more children go on
 // the heavy list for beam_push_kernel.  Same total order as there: (key, id), first inserted first.
-__global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
-    __shared__ double s_key[8][32];
-    __shared__ uint32_t s_id[8][32];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int line = blockIdx.x * 8 + wid;
-    if (line >= b.L) return;
+// returns true when the line has more than 32 new children (left to push_line)
+__device__ bool push_small_line(const BeamDev& b, int line, int lane, double* s_key_w, uint32_t* s_id_w) {
     const int c = b.beam_count[line];
-    if (c <= 0) return;
+    if (c <= 0) return false;
     const unsigned FULL = 0xffffffffu;
     const int xb = b.x_base[line];
     int n_new = 33;
@@ -945,18 +1001,15 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
         n_new = __shfl_sync(FULL, incl, 31);
         off = incl - nj;
     }
-    if (n_new > 32) {
-        if (lane == 0) b.heavy[atomicAdd(&b.counters[2], 1)] = line;
-        return;
-    }
+    if (n_new > 32) return true;
     const int Tl = b.row_T[line];
     if (lane < c) {
         const size_t g = (size_t)line * b.quota_x + xb + lane;
         const int len_child = b.rec_len[g] + 1;
         const double pen = 3.0 * fabs((double)(len_child - Tl));      // cost0 * |length - length0| (:1588-1595)
         for (int q = 0; q < nj; ++q) {
-            s_key[wid][off + q] = b.ch_cum[g * KMAX + q] + pen;
-            s_id[wid][off + q] = (1u + (uint32_t)(xb + lane) * KMAX + q) | (b.ch_v[g * KMAX + q] == b.eos ? FINAL_BIT : 0u);
+            s_key_w[off + q] = b.ch_cum[g * KMAX + q] + pen;
+            s_id_w[off + q] = (1u + (uint32_t)(xb + lane) * KMAX + q) | (b.ch_v[g * KMAX + q] == b.eos ? FINAL_BIT : 0u);
         }
     }
     __syncwarp();
@@ -969,9 +1022,9 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
     uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     const int keep = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);     // see push_line
     if (lane < n_new) {
-        const double k = s_key[wid][lane]; const uint32_t id = s_id[wid][lane];
+        const double k = s_key_w[lane]; const uint32_t id = s_id_w[lane];
         int rank = 0;
-        for (int t = 0; t < n_new; ++t) rank += key_less(s_key[wid][t], s_id[wid][t], k, id);
+        for (int t = 0; t < n_new; ++t) rank += key_less(s_key_w[t], s_id_w[t], k, id);
         int lo = 0, hi = n_old;                   // old entries that precede this new one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = rank + lo;
@@ -980,7 +1033,7 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
     for (int i = lane; i < n_old; i += 32) {
         const double k = okey[i]; const uint32_t id = oid[i];
         int before = 0;                           // new entries that precede this old one
-        for (int t = 0; t < n_new; ++t) before += key_less(s_key[wid][t], s_id[wid][t], k, id);
+        for (int t = 0; t < n_new; ++t) before += key_less(s_key_w[t], s_id_w[t], k, id);
         const int pos = i + before;
         if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
@@ -992,6 +1045,15 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
         b.fr_buf[line] = cur ^ 1;
         if (nl > b.fr_peak[line]) b.fr_peak[line] = nl;
     }
+    return false;
+}
+__global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
+    __shared__ double s_key[8][32];
+    __shared__ uint32_t s_id[8][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int line = blockIdx.x * 8 + wid;
+    if (line >= b.L) return;
+    if (push_small_line(b, line, lane, s_key[wid], s_id[wid]) && lane == 0) b.heavy[atomicAdd(&b.counters[2], 1)] = line;
 }
 
 // Lines on the heavy list (more than 32 new children), one block per line at a time.
@@ -1008,6 +1070,36 @@ __global__ void __launch_bounds__(PUSH_THREADS) beam_push_kernel(BeamDev b) {
         push_line(b, b.heavy[i], skey, sid, s_wsum);
         __syncthreads();
     }
+}
+
+// ------------------------------------------------------------------ page of lines: one block per line does the rest
+// expand the line's rows (a warp per row), insert their children into the line's fringe (warp-level insert, or the
+// block-wide sort + merge when there are more than 32), pop the next batch -- everything of an iteration that touches
+// one line only, without a launch boundary in between.  What crosses lines (row offsets) is the gather's scan.
+template <int NVL>
+__global__ void __launch_bounds__(256) beam_line_kernel(BeamDev b, int split, int do_expand) {
+    extern __shared__ unsigned char smraw[];
+    double* skey = reinterpret_cast<double*>(smraw);
+    uint32_t* sid = reinterpret_cast<uint32_t*>(skey + MAX_NEW);
+    __shared__ double s_key[32];
+    __shared__ uint32_t s_id[32];
+    __shared__ int s_wsum[32];
+    __shared__ int s_heavy;
+    const int line = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = (do_expand && b.status[line] == ST_ACTIVE) ? b.beam_count[line] : 0;     // rows of this line in the step that just ran
+    if (c > 0) {
+        const int rb = b.row_base[line];
+        for (int j = warp; j < c; j += 8) expand_row<NVL>(b, split, rb + j, lane);
+        __syncthreads();            // the records of all rows of the line are complete
+        if (warp == 0) {
+            const bool heavy = push_small_line(b, line, lane, s_key, s_id);
+            if (lane == 0) s_heavy = heavy ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_heavy) push_line(b, line, skey, sid, s_wsum);
+        __syncthreads();
+    }
+    if (warp == 0) pop_line(b, line, lane, true);
 }
 
 // ------------------------------------------------------------------ finish: best final hypothesis per line (:1538-1544)
@@ -1269,7 +1361,25 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const int t_hi = T;      // every row_T is <= t_max
     // pop + scan: which hypotheses of every line are expanded next, their rows, and whether anything is left to do
     const bool small_sel = L <= kSelectSmall && !getenv("COR_NO_SELECT_SMALL");
+    // Page of lines with the score row in registers: gather (with the scan) -> decoder step -> one kernel per line for the
+    // rest (6 kernels per iteration instead of 9).  OPT-IN (COR_LINE_KERNEL=1): measured 8.08 -> 7.67 ms on a 32-line page
+    // of one hypothesis per line, but 96 -> 257 ms on a 64-line page with ~116 hypotheses per line -- one block per line
+    // serialises what the row-parallel expand and the 1024-thread push spread out -- and which of the two a page is
+    // is not known when the graph is recorded.
+    const bool line_path = small_sel && (m->Vp == 128 || m->Vp == 256 || m->Vp == 512 || m->Vp == 1024) && getenv("COR_LINE_KERNEL") != nullptr;
+    auto line_kernel = [&](cudaStream_t s_, int do_expand) -> int {
+        switch (m->Vp) {
+            case 128:  beam_line_kernel<4><<<L, 256, push_smem, s_>>>(b, split, do_expand); break;
+            case 256:  beam_line_kernel<8><<<L, 256, push_smem, s_>>>(b, split, do_expand); break;
+            case 512:  beam_line_kernel<16><<<L, 256, push_smem, s_>>>(b, split, do_expand); break;
+            default:   beam_line_kernel<32><<<L, 256, push_smem, s_>>>(b, split, do_expand); break;
+        }
+        ctx().launches += 1;
+        COR_CUDA(cudaGetLastError());
+        return 0;
+    };
     auto select = [&](cudaStream_t s_, const LoopCtl& lc, int set_cond) -> int {
+        if (line_path) return 0;       // the line kernel pops; the scan lives in the gather
         if (small_sel) {        // a page of lines: pop, scan and rowmap in one block
             beam_select_small_kernel<<<1, 1024, 0, s_>>>(b, lc, set_cond);
             ctx().launches += 1;
@@ -1282,8 +1392,15 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         COR_CUDA(cudaGetLastError());
         return 0;
     };
-    // one decoder step over the selected rows and the insertion of their children
+    LoopCtl body_ctl{};             // loop controls of the body being captured (the line path sets them in its gather)
+    int body_cond = 0;
     auto gather = [&](cudaStream_t s_) -> int {
+        if (line_path) {
+            beam_gather_scan_kernel<<<row_grid, 128, 0, s_>>>(b, split, body_ctl, body_cond);
+            ctx().launches += 1;
+            COR_CUDA(cudaGetLastError());
+            return 0;
+        }
         if (!small_sel) { beam_rowmap_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b); ++ctx().launches; }
         beam_gather_kernel<<<row_grid, 128, 0, s_>>>(b, split);
         ctx().launches += 1;
@@ -1291,6 +1408,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
         return 0;
     };
     auto insert = [&](cudaStream_t s_) -> int {
+        if (line_path) return line_kernel(s_, 1);
         const int warp_grid = std::min((plan.Rcap + 3) / 4, 148 * 8);
         switch (m->Vp) {        // score row in registers when it fits (32 values per lane at most)
             case 128:  beam_expand_warp_kernel<4><<<warp_grid, 128, 0, s_>>>(b, split); break;
@@ -1316,7 +1434,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const bool use_graph = loop_graphs_enabled();
     int graph_body_kernels = 0;
     const LoopCtl no_ctl{};
-    if (select(st, no_ctl, 0)) return 1;
+    if (line_path ? line_kernel(st, 0) : select(st, no_ctl, 0)) return 1;
     for (int it = 0; it <= 2 * t_hi; ++it) {
         if (use_graph && it == 1) {
             LoopGraph* g = nullptr;
@@ -1344,11 +1462,16 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
                 const int64_t before = ctx().launches;
                 COR_CUDA(cudaStreamBeginCaptureToGraph(cs, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
                 io.wq_ready = true;
+                // the SWITCH selector is an argument of the kernel that sets it (the gather's scan on the line path), which is
+                // captured BEFORE the node exists: create the handle first
+                if (lc.has_shape) COR_CUDA(cudaGraphConditionalHandleCreate(&lc.shape, g->graph, 0, 0));
+                body_ctl = lc; body_cond = 1;
                 int rc = gather(cs);
+                body_ctl = LoopCtl{}; body_cond = 0;
                 int64_t extra = 0;
                 if (!rc && lc.has_shape) {
                     cudaGraph_t branch[3];
-                    rc = loop_graph_switch(cs, g->graph, 3, &lc.shape, branch);
+                    rc = loop_graph_switch(cs, 3, lc.shape, branch);
                     for (int c = 0; c < 3 && !rc; ++c) {
                         const int64_t b0 = ctx().launches;
                         cudaError_t e = cudaStreamBeginCaptureToGraph(cs2, branch[c], nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed);
@@ -1458,6 +1581,10 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
     COR_CHECK(hl->n_rows > 0 && hl->t_max > 0 && hl->k_alt > 0, "empty call geometry");
     COR_CUDA(cudaSetDevice(m->device));
     COR_CUDA(cudaFuncSetAttribute(beam_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
+    COR_CUDA(cudaFuncSetAttribute(beam_line_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
+    COR_CUDA(cudaFuncSetAttribute(beam_line_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
+    COR_CUDA(cudaFuncSetAttribute(beam_line_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
+    COR_CUDA(cudaFuncSetAttribute(beam_line_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_NEW * 12));
     const int B = hl->n_rows, T = hl->t_max, k = hl->k_alt;
     const int NB = std::max(1, bp->n_best);                  // result slots per line
     const size_t S = 2 * (size_t)T * NB, tk = (size_t)T * k;

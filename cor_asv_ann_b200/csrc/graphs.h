@@ -33,8 +33,9 @@ bool loop_graphs_enabled();
 // WHILE node behind `first` (a kernel node that sets the initial condition): returns the body graph to capture into.
 int loop_graph_begin(LoopGraph* g, const cudaKernelNodeParams& first, cudaGraphConditionalHandle* cond, cudaGraph_t* body);
 
-// While `cs` is capturing: a SWITCH node with `n` branches behind everything captured so far; what is captured on `cs`
-// afterwards depends on it.  Returns the branch graphs (to capture into with another stream).  `root` = the top-level graph.
-int loop_graph_switch(cudaStream_t cs, cudaGraph_t root, int n, cudaGraphConditionalHandle* sw, cudaGraph_t* branches);
+// While `cs` is capturing: a SWITCH node on the selector `sw` (a handle of the top-level graph) with `n` branches behind
+// everything captured so far; what is captured on `cs` afterwards depends on it.  Returns the branch graphs (to capture
+// into with another stream).
+int loop_graph_switch(cudaStream_t cs, int n, cudaGraphConditionalHandle sw, cudaGraph_t* branches);
 
 }  // namespace cor

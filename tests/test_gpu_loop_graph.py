@@ -141,3 +141,26 @@ def test_beam_graph_page_of_c2_lines():
     for j in range(3):
         got = ''.join(mapping[1][int(v)] for v in chars[j, :lens[j]]) if lens[j] > 0 else lines[j]
         assert got == ref_text[j]
+
+
+@pytest.mark.parametrize("case", ["c2s_mix", "c2s_rej0", "c1_mix_wide"])
+def test_line_kernel_path_identical(case):
+    """The opt-in line-kernel path of a page (COR_LINE_KERNEL=1: gather with the scan, one block per line for expand + push +
+    pop) gives the results of the default path bit for bit."""
+    name, n, length, seed, params = BEAM_CASES[case]
+    topo, w, mapping = make_model(name)
+    lines = synthetic_lines(mapping, n, length, seed=seed, min_length=max(3, length // 2))
+    idx, val = _sparse(mapping, lines)
+    B, T, _ = idx.shape
+    row_T = np.full(B, T, np.int32)
+    eng = _engine(topo, w, 2)
+    bp = eng.beam_params(**params)
+    ref = [None if t is None else t.numpy().copy() for t in eng.correct_beam_host(idx, val, row_T, bp, want_align=True, budget_bytes=2 << 30)]
+    os.environ["COR_LINE_KERNEL"] = "1"
+    try:
+        eng2 = _engine(topo, w, 2)          # own graph cache: the key does not know the switch
+        got = [None if t is None else t.numpy().copy() for t in eng2.correct_beam_host(idx, val, row_T, bp, want_align=True, budget_bytes=2 << 30)]
+    finally:
+        os.environ.pop("COR_LINE_KERNEL", None)
+    for a, b in zip(got, ref):
+        assert np.array_equal(a, b)
