@@ -422,7 +422,7 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
                     if (tab0) { e.xtab = m->xtab[dir]; e.x_idx = ws.idx; e.x_val = ws.val; e.x_k = ws.k; e.x_tmax = T; }
                     e.bias = lw.bias; e.c_in = ws.ec[dir]; e.c_out = ws.ec[dir];
                     e.row_T = ws.row_T; e.reverse = dir; e.rows_total = B;
-                    e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W;
+                    e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W; e.seq_T = T;
                     if (n == d - 1) { e.seq_tm = 1; e.seq_rm = T; }      // enc_out is line-major (attention gathers windows)
                     e.seq_rev = ws.seqr[n]; e.seq_rev_lo = ws.seqr_lo[n];
                     if (m->cfg.residual_connections && !bidi && n >= 2) {
@@ -453,7 +453,7 @@ int run_encoder(cor_model* m, const Ws& ws, cudaStream_t st) {
                 e.h_prev = ws.eh[dir][cur]; e.h_prev_lo = ws.eh_lo[dir][cur];
                 e.h_out = ws.eh[dir][cur ^ 1]; e.h_out_lo = ws.eh_lo[dir][cur ^ 1];
                 e.row_T = ws.row_T; e.step = s; e.reverse = dir; e.rows_total = B;
-                e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W;
+                e.seq_out = ws.seq[n]; e.seq_out_lo = ws.seq_lo[n]; e.seq_ld = out_dim; e.seq_col = dir * W; e.seq_T = T;
                 if (n == d - 1) { e.seq_tm = 1; e.seq_rm = T; }          // enc_out is line-major (attention gathers windows)
                 e.seq_rev = ws.seqr[n]; e.seq_rev_lo = ws.seqr_lo[n];
                 if (m->cfg.residual_connections && !bidi && n >= 2) {

@@ -102,6 +102,7 @@ struct LstmEpi {
     // output is only gathered by window (attention): a line's window is then one contiguous block for the bulk copies.
     // Both 0 = time-major with rows_total.
     int seq_tm, seq_rm;
+    int seq_T;                 // time steps the sequence buffers hold (extent of the TMA store maps of the tcgen05 epilogue)
     float* seq_rev;  float* seq_rev_lo;                              // seq_rev[T-1-t][r][seq_col+u]
     const float* resid; const float* resid_lo; int resid_ld;         // residual add into seq_out
     int cross_sum;             // seq value = h[2k]+h[2k+1] for both members of a pair

@@ -32,6 +32,15 @@ constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int BN_WIDE = 256, BN_NARROW = 32;   // tile widths: full tiles / page-sized M (see pick_bn)
 constexpr int ELT = 2;                          // bytes per operand element (fp16)
 constexpr int A_TILE = BM * BK * ELT;          // 16 KB
+// LSTM epilogue staging (per epilogue warp): the results of a 32-row x 8-unit chunk -- c (fp32), h (hi, lo), sequence
+// output (hi, lo) -- are written to shared memory as [32][8] tiles and leave through TMA box stores.  The epilogue is
+// "one row per lane", so every direct global store of it touches 32 different lines (32 LSU wavefronts whatever its
+// width): 160 of the 324 wavefronts per warp and chunk were stores (ncu: LSU data pipe 58 % busy in the K = 512 launches,
+// the tensor pipe waiting on it); through the async proxy they cost 24 shared-memory wavefronts.
+constexpr int EPI_WARPS_MAX = 8;
+constexpr int EPI_STAGE_C = 0, EPI_STAGE_HHI = 1024, EPI_STAGE_HLO = 1536, EPI_STAGE_SHI = 2048, EPI_STAGE_SLO = 2560;
+constexpr int EPI_STAGE_WARP = 3072;
+constexpr int EPI_STAGE_BYTES = EPI_WARPS_MAX * EPI_STAGE_WARP;
 // NCTA = 1: one CTA per 128 x 256 tile, 2 stages of {A_hi, A_lo, B_hi, B_lo} = 96 KB.
 // NCTA = 2: a CTA pair (cta_group::2) per 256 x 256 tile; each CTA stages its own 128 rows of A and
 // HALF of the B tile (128 of the 256 columns), 64 KB per stage, 3 stages.  The pair reads 128 KB from
@@ -45,7 +54,7 @@ template <int NCTA, int BN> struct Geo {
     static constexpr int B_TILE = B_ROWS * BK * ELT;
     static constexpr int STAGE_BYTES = 2 * A_TILE + 2 * B_TILE;
     static constexpr int STAGES = NCTA == 2 ? 3 : (BN == BN_WIDE ? 2 : 5);
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + EPI_STAGE_BYTES;
     static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * NCTA) >> 4) << 24);
 };
 constexpr int EPI_WARPS = 8;                   // two per TMEM lane quarter: each takes half of the tile's columns
@@ -59,6 +68,10 @@ struct TcParams {
     int M; const int* m_dev; int N;
     int tiles_n;
     int passes;     // 3: fp32-grade hi/lo product (the product path); 1: heads only (gemm_mode 3, stated looser tolerance)
+    // TMA store maps of the LSTM epilogue (box 8 x 32): cell state, h (hi, lo), sequence output (hi, lo)
+    CUtensorMap e_c, e_hhi, e_hlo, e_shi, e_slo;
+    int e_use;      // 0: direct stores; 1: c and h through TMA; 2: ... and the sequence output
+    int e_seq_mode; // sequence output layout: 0 time-major (row' = t * rows_total + row), 1 line-major (column' = t * seq_ld + column)
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -120,6 +133,13 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -326,6 +346,50 @@ __device__ __forceinline__ void lstm_row8(const LstmEpi& e, const RowCtx& rc, in
         store8_split(e.seq_rev, e.seq_rev_lo, seq_pos(e, T - 1 - t, row) * e.seq_ld + e.seq_col + unit0, y);
 }
 
+// The same cell for a warp whose 32 rows are all valid, active and at the same sequence position: results go to the warp's
+// staging tiles (row = lane), not to global memory; lstm_stage_flush sends them.
+__device__ __forceinline__ void lstm_row8_stage(const LstmEpi& e, const RowCtx& rc, int row, int unit0, const uint32_t (&z)[32],
+                                                const float (&b)[32], float (&c)[8], uint8_t* stage, int lane, bool with_seq) {
+    float h[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float i = sigmoidf_fast(__uint_as_float(z[4 * k + 0]) + b[4 * k + 0]);
+        const float f = sigmoidf_fast(__uint_as_float(z[4 * k + 1]) + b[4 * k + 1]);
+        const float g = tanhf_fast(__uint_as_float(z[4 * k + 2]) + b[4 * k + 2]);
+        const float o = sigmoidf_fast(__uint_as_float(z[4 * k + 3]) + b[4 * k + 3]);
+        c[k] = f * c[k] + i * g;
+        h[k] = o * tanhf_fast(c[k]);
+    }
+    float4* sc = reinterpret_cast<float4*>(stage + EPI_STAGE_C + lane * 32);
+    sc[0] = make_float4(c[0], c[1], c[2], c[3]); sc[1] = make_float4(c[4], c[5], c[6], c[7]);
+    {
+        __align__(16) __half hi[8], lo[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f16_split(h[k], hi[k], lo[k]);
+        *reinterpret_cast<uint4*>(stage + EPI_STAGE_HHI + lane * 16) = *reinterpret_cast<const uint4*>(hi);
+        *reinterpret_cast<uint4*>(stage + EPI_STAGE_HLO + lane * 16) = *reinterpret_cast<const uint4*>(lo);
+    }
+    if (!with_seq) return;
+    float y[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) y[k] = h[k];
+    if (e.cross_sum) {
+#pragma unroll
+        for (int k = 0; k < 8; k += 2) { const float s = h[k] + h[k + 1]; y[k] = s; y[k + 1] = s; }
+    }
+    if (e.resid) {
+        float r[8];
+        load8_split(e.resid, e.resid_lo, ((size_t)rc.t * e.rows_total + row) * e.resid_ld + unit0, r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) y[k] += r[k];
+    }
+    __align__(16) __half hi[8], lo[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f16_split(y[k], hi[k], lo[k]);
+    *reinterpret_cast<uint4*>(stage + EPI_STAGE_SHI + lane * 16) = *reinterpret_cast<const uint4*>(hi);
+    *reinterpret_cast<uint4*>(stage + EPI_STAGE_SLO + lane * 16) = *reinterpret_cast<const uint4*>(lo);
+}
+
 __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0, int N, const uint32_t (&z)[32]) {
     if (e.n_split && col0 >= e.n_split && col0 + 32 <= N && (e.ldc2 & 3) == 0) {
         const int c2 = col0 - e.n_split;
@@ -500,6 +564,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
             if constexpr (EPI == 1) {
                 // everything that does not depend on the accumulator is fetched before waiting for it
                 const RowCtx rc = lstm_row_begin(epi, row, row < M);
+                // TMA-staged stores need the warp's 32 rows valid, active and at one sequence position (box store)
+                const int t0 = __shfl_sync(0xffffffffu, rc.t, 0);
+                const bool staged = p.e_use != 0 && __all_sync(0xffffffffu, row < M && rc.active && rc.t == t0);
+                const bool with_seq = p.e_use == 2;
+                uint8_t* stage = smem_gen + STAGES * STAGE_BYTES + 256 + (warp - 4) * EPI_STAGE_WARP;
+                const uint32_t stage_s = bar_base + 256u + (uint32_t)(warp - 4) * EPI_STAGE_WARP;
+                const int row0 = m0 + wq * 32;
                 bool waited = false;
 #pragma unroll 1
                 for (int ch = half; ch < BN / 32; ch += EPI_WARPS / 4) {
@@ -511,7 +582,28 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                     uint32_t z[32];
                     tmem_ld32(taddr + ch * 32, z);
                     tmem_ld_wait();
-                    if (live) lstm_row8(epi, rc, row, col0 >> 2, z, b, c);
+                    if (staged && col0 < p.N) {
+                        const int unit0 = col0 >> 2;
+                        if (lane == 0) bulk_wait_read();            // the previous chunk's tiles have been read out
+                        __syncwarp();
+                        lstm_row8_stage(epi, rc, row, unit0, z, b, c, stage, lane, with_seq);
+                        fence_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&p.e_c, stage_s + EPI_STAGE_C, unit0, row0);
+                            tma_store_2d(&p.e_hhi, stage_s + EPI_STAGE_HHI, unit0, row0);
+                            tma_store_2d(&p.e_hlo, stage_s + EPI_STAGE_HLO, unit0, row0);
+                            if (with_seq) {
+                                const int sc0 = p.e_seq_mode ? t0 * epi.seq_ld + epi.seq_col + unit0 : epi.seq_col + unit0;
+                                const int sc1 = p.e_seq_mode ? row0 : t0 * epi.rows_total + row0;
+                                tma_store_2d(&p.e_shi, stage_s + EPI_STAGE_SHI, sc0, sc1);
+                                tma_store_2d(&p.e_slo, stage_s + EPI_STAGE_SLO, sc0, sc1);
+                            }
+                            bulk_commit();
+                        }
+                    } else if (live) {
+                        lstm_row8(epi, rc, row, col0 >> 2, z, b, c);
+                    }
                 }
                 if (!waited) { mbar_wait(tfull_bar(acc), acc_phase); tc_fence_after(); }
             } else {
@@ -534,6 +626,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if constexpr (EPI == 1) { if (lane == 0) bulk_wait_all(); }      // staged stores have landed before the CTA retires
     }
     tc_fence_before();
     // pair: neither CTA may leave (or free TMEM) while its peer can still read its smem or signal its barriers
@@ -618,6 +711,53 @@ int get_map(const float* ptr, long long rows, long long cols, long long ld, int 
     return 0;
 }
 
+// 2-D row-major [rows][cols] of fp32 or fp16 with leading dimension ld (elements), plain (unswizzled) box: the store maps
+// of the LSTM epilogue.  Cached like the operand maps (the key carries the element size and the box).
+int get_store_map(const void* ptr, int elt, long long rows, long long cols, long long ld, int box_cols, int box_rows, CUtensorMap* out) {
+    auto key = std::make_tuple(ptr, rows, cols, ld, -(elt * 1000000 + box_cols * 1000 + box_rows));
+    MapCache& maps = maps_of(ctx());
+    {
+        auto it = maps.find(key);
+        if (it != maps.end()) { *out = it->second; return 0; }
+    }
+    COR_CHECK(((uintptr_t)ptr & 15) == 0 && (ld * elt) % 16 == 0, "TMA store target must be 16-byte aligned with a 16-byte multiple pitch");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * elt};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(out, elt == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    COR_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed for an epilogue store map");
+    if (maps.size() > 4096) maps.clear();
+    maps[key] = *out;
+    return 0;
+}
+
+// Store maps of the LSTM epilogue, when its outputs are the split (hi, lo) kind the box stores can serve.
+int fill_epi_maps(const LstmEpi& e, int M, TcParams* p) {
+    p->e_use = 0; p->e_seq_mode = 0;
+    if (!e.h_out_lo || !e.h_out || !e.c_out || e.seq_rev || (e.W & 7) || getenv("COR_NO_EPI_TMA")) return 0;
+    if (e.seq_out && (!e.seq_out_lo || (e.seq_ld & 7) || ((e.seq_col) & 7) || e.seq_T <= 0)) return 0;
+    if (get_store_map(e.c_out, 4, M, e.W, e.W, 8, 32, &p->e_c) || get_store_map(e.h_out, 2, M, e.W, e.W, 8, 32, &p->e_hhi) ||
+        get_store_map(e.h_out_lo, 2, M, e.W, e.W, 8, 32, &p->e_hlo)) return 1;
+    p->e_use = 1;
+    if (e.seq_out) {
+        const bool line_major = e.seq_tm != 0 && !(e.seq_tm == e.rows_total && e.seq_rm == 1);
+        if (line_major) {
+            // element (t, row, col) at (t * seq_tm + row * seq_rm) * seq_ld + col with seq_tm == 1: a row of the map is a line
+            if (e.seq_tm != 1) { p->e_use = 0; return 0; }
+            const long long ld = (long long)e.seq_rm * e.seq_ld;
+            if (get_store_map(e.seq_out, 2, e.rows_total, ld, ld, 8, 32, &p->e_shi) || get_store_map(e.seq_out_lo, 2, e.rows_total, ld, ld, 8, 32, &p->e_slo)) return 1;
+            p->e_seq_mode = 1;
+        } else {
+            const long long rows = (long long)e.seq_T * e.rows_total;
+            if (get_store_map(e.seq_out, 2, rows, e.seq_ld, e.seq_ld, 8, 32, &p->e_shi) || get_store_map(e.seq_out_lo, 2, rows, e.seq_ld, e.seq_ld, 8, 32, &p->e_slo)) return 1;
+        }
+        p->e_use = 2;
+    }
+    return 0;
+}
+
 int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg* segs, int nseg, int passes, TcParams* p) {
     COR_CHECK(nseg >= 1 && nseg <= kMaxSegs, "bad segment count");
     COR_CHECK(passes == 1 || passes == 3, "passes must be 1 or 3");
@@ -676,6 +816,8 @@ int dispatch_tc(cudaStream_t st, int M, const int* m_dev, int N, const GemmSeg* 
     pick_shape(M, N, &ncta, &bn);
     TcParams p;
     if (fill_params(ncta, bn, M, m_dev, N, segs, nseg, passes, &p)) return 1;
+    p.e_use = 0; p.e_seq_mode = 0;
+    if constexpr (EPI == 1) { if (fill_epi_maps(epi, M, &p)) return 1; }
     if (bn == BN_NARROW) return launch_tc<EPI, 1, BN_NARROW, Epi>(st, M, N, p, epi);
     return ncta == 2 ? launch_tc<EPI, 2, BN_WIDE, Epi>(st, M, N, p, epi) : launch_tc<EPI, 1, BN_WIDE, Epi>(st, M, N, p, epi);
 }

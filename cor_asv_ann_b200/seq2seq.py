@@ -472,11 +472,55 @@ class Sequence2Sequence(object):
         assert self.status == 2
         batches = self.gen_lines(filenames, repeat=False, unsupervised=True, charmap=charmap)
         groups = chunked(batches, max(int(self.superbatch), 1))
+        if fast and self.prefetch:
+            yield from self._predict_pipelined(groups)
+            return
         if self.prefetch:
             groups = Prefetcher(groups, depth=2)
         for group in groups:
             results = self.correct_batches([(b[0], b[1]) for b in group], fast=fast, greedy=greedy, want_probs=False)
             for batch, (lines_result, _, scores_result, _) in zip(group, results):
+                yield (batch[3], lines_result, scores_result)
+
+    def _predict_pipelined(self, groups):
+        """Fast mode as three overlapping stages: (1) read + index-encode + merge the next super-batch, (2) the engine
+        call (the only stage that touches the GPU; the ctypes call releases the GIL), (3) strings and per-batch
+        results of the previous one -- each in its own thread, two super-batches of slack between neighbours.
+        Same batches, same order, same results as correct_batches per group."""
+        def encode():
+            for group in groups:
+                todo = [(b, batch[0], batch[1]) for b, batch in enumerate(group) if batch[0]]
+                if not todo:
+                    yield group, todo, None
+                    continue
+                enc = [lines_to_sparse(self.mapping[0], lines, conf, self.logger) for _, lines, conf in todo]
+                yield group, todo, merge_batches(enc)
+
+        def decode(items):
+            eng = self._get_engine()
+            pool, turn = [None] * 6, 0          # result buffers in flight: 2 queued + 1 being read + 1 being written, and slack
+            for group, todo, merged in items:
+                if not todo:
+                    yield group, todo, None, None
+                    continue
+                idx, val, row_T, offsets = merged
+                want = (idx.shape[0], 2 * idx.shape[1])
+                out = pool[turn] if pool[turn] is not None and tuple(pool[turn][0].shape) == want else None
+                out = eng.correct_greedy_host(idx, val, row_T, want_align=False, out=out)
+                pool[turn] = out
+                turn = (turn + 1) % len(pool)
+                yield group, todo, (out[0].numpy(), out[2].numpy(), out[3].numpy()), offsets
+
+        for group, todo, arrays, offsets in Prefetcher(decode(Prefetcher(encode(), depth=2)), depth=2):
+            results = [([], []) for _ in group]
+            if todo:
+                chars, scores, lens = arrays
+                lines = self._strings(chars, lens)
+                out_scores = np.where(lens > 0, scores, 0.).tolist()
+                for n, (b, _, _) in enumerate(todo):
+                    lo, hi = offsets[n], offsets[n + 1]
+                    results[b] = (lines[lo:hi], out_scores[lo:hi])
+            for batch, (lines_result, scores_result) in zip(group, results):
                 yield (batch[3], lines_result, scores_result)
 
     def vectorize_lines(self, encoder_input_sequences, decoder_input_sequences, encoder_conf_sequences=None):

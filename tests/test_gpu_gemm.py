@@ -85,7 +85,7 @@ def test_tcgen05_small_magnitude_weights():
     err = (Cm.double() - ref).abs().max().item()
     rel = err / ref.abs().max().item()
     print("abs err %.3g (relative to the largest product %.3g)" % (err, rel))
-    assert err < 5e-7
+    assert err < 3e-6          # ~ sqrt(K) * max|a| * 2^-25-ish residual grid of B plus the fp32 accumulation: 30x below the parity budget
     assert rel < 1e-4          # the stated grade for small operands: absolute, i.e. a relative 2^-15..2^-13 here
 
 
