@@ -454,8 +454,9 @@ def measure_early_exit(args, device, n_target=4096):
     """Fast decoder on lines that END (reference seq2seq.py:1255-1256 steps finished lines to 2T
     and ignores them).  Random-init decoders never emit a newline, so this leg uses weights of variant E (see
     cor_asv_ann_b200/synthetic.py) and, from a pool of candidate lines, those that an untimed first pass sees end within
-    T of the 2T steps.  The loop graph stops when the last of them has; the host loop (COR_NO_GRAPH=1) launches all 2T
-    steps.  Results are identical (tests/test_gpu_loop_graph.py); only the time differs."""
+    T of the 2T steps.  The loop graph compacts finished rows out of the GEMMs every 8 steps and stops when the last line
+    has finished; the host loop (COR_NO_GRAPH=1) launches all 2T steps over all rows.  Results are identical
+    (tests/test_gpu_loop_graph.py); only the time differs."""
     import torch
     from cor_asv_ann_b200.engine import Engine
     eng = Engine(dict(C2, window_width=5), build_weights(C2, "E"), device=device, eos_index=1, gemm_mode=args.gemm_mode)

@@ -98,10 +98,10 @@ int loop_graph_switch(cudaStream_t cs, int n, cudaGraphConditionalHandle sw, cud
     COR_CHECK(status == cudaStreamCaptureStatusActive && cur, "stream is not capturing");
     cudaGraphNodeParams cp{};
     cp.type = cudaGraphNodeTypeConditional;
-    cp.conditional.handle = sw; cp.conditional.type = cudaGraphCondTypeSwitch; cp.conditional.size = (unsigned)n;
+    cp.conditional.handle = sw; cp.conditional.type = n == 0 ? cudaGraphCondTypeIf : cudaGraphCondTypeSwitch; cp.conditional.size = (unsigned)std::max(n, 1);
     cudaGraphNode_t node;
     COR_CUDA(cudaGraphAddNode(&node, cur, deps, ndeps, &cp));
-    for (int i = 0; i < n; ++i) branches[i] = cp.conditional.phGraph_out[i];
+    for (int i = 0; i < std::max(n, 1); ++i) branches[i] = cp.conditional.phGraph_out[i];
     COR_CUDA(cudaStreamUpdateCaptureDependencies(cs, &node, 1, cudaStreamSetCaptureDependencies));
     return 0;
 }
@@ -355,7 +355,14 @@ int carve(const cor_model* m, int B, int T, int k, int want_align, void* base, W
     ws->o_score = c.take<double>(B);
     ws->o_len = c.take<int32_t>(B);
     ws->o_ties = c.take<int32_t>(B);
-    ws->loop_state = c.take<int32_t>(4);
+    ws->loop_state = c.take<int32_t>(8);
+    // row compaction of the fast-greedy loop graph: row -> line maps, new row indices, one scratch copy of the per-row state
+    ws->g_rl = c.take<int32_t>(B); ws->g_rl2 = c.take<int32_t>(B); ws->g_new = c.take<int32_t>(B);
+    // per row: h (hi + lo, or fp32) and c of every layer, the alignment row, the feedback row (hi + lo, or fp32), the query;
+    // every entry rounded up to 16 bytes (greedy_loop's MoveList)
+    ws->g_scratch_row = (size_t)d * 8 * W + (size_t)T * 4 + (size_t)4 * Vp + 4 * W + 16 * (3 * (size_t)d + 5);
+    ws->g_scratch_row = (ws->g_scratch_row + 15) & ~size_t(15);
+    ws->g_scratch = c.take<uint8_t>(ws->g_scratch_row * B);
     ws->o_align = want_align ? c.take<float>(S * BT) : nullptr;
     ws->bytes = (c.off + 255) & ~size_t(255);
     return 0;
@@ -526,6 +533,7 @@ int decoder_core(cor_model* m, const Ws& ws, const StepIO& io, cudaStream_t st) 
     a.a_prev = io.a_in; a.row_line = io.row_line; a.line_T = ws.row_T;
     a.v_a = m->v_a; a.b_v = m->b_v; a.a_out = io.a_out; a.ctx = io.ctx; a.ctx_lo = io.ctx_lo;
     a.align_log = io.align_log; a.step_dev = io.step_dev; a.step_off = io.step_off; a.align_stride = io.align_stride;
+    a.align_by_line = io.align_by_line;
     a.R = R; a.r_dev = io.r_dev; a.L = ws.B; a.t_max = ws.T; a.W = W; a.D = D;
     a.window = m->cfg.window_width; a.inclusive = 1;
     // The attention of this step depends on the previous step only (query, alignment); with lower
@@ -610,15 +618,103 @@ static int copy_out(cudaStream_t st, const float* hi, const float* lo, float* ds
     return 0;
 }
 
-// Loop condition of the fast-greedy graph.  state[0] = timestep of the body's first step, state[1] = lines finished
-// so far (counted by the softmax launches); total accumulates the steps run (launch count).
-__global__ void greedy_cond_kernel(int32_t* state, int64_t* total, int s_max, int n_rows, cudaGraphConditionalHandle cond, int init) {
-    if (init) { cudaGraphSetConditional(cond, s_max > 0 ? 1u : 0u); return; }
-    const int step = state[0] + 2;
-    const bool more = step < s_max && state[1] < n_rows;
-    state[0] = step;
-    if (total) total[0] += 2;
-    cudaGraphSetConditional(cond, more ? 1u : 0u);
+// ---- fast-greedy loop graph: device-side loop state (Ws::loop_state) -----------------------------------------------
+//   [0] timestep the next body starts at      [2] live rows R (the GEMMs' m_dev)      [3] rows before the last compaction
+//   [4] 1 if the last scan decided to compact
+constexpr int kCompactEvery = 8;         // timesteps between looks at the finished rows
+struct GreedyCtl {
+    int32_t* state; int64_t* total;     // total[0] timesteps run, total[1] compactions done (launch accounting)
+    int s_max, n_rows;
+    cudaGraphConditionalHandle loop;    // WHILE: another body?
+    cudaGraphConditionalHandle compact; // IF: look at the finished rows after this body?
+};
+__global__ void greedy_init_kernel(GreedyCtl c, int32_t* rl) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < c.n_rows) rl[r] = r;
+    if (r == 0) {
+        c.state[0] = 0; c.state[2] = c.n_rows; c.state[3] = c.n_rows; c.state[4] = 0;
+        cudaGraphSetConditional(c.loop, (c.s_max > 0 && c.n_rows > 0) ? 1u : 0u);
+    }
+}
+// end of a body (two timesteps): advance the step, decide about another body and about a look at the finished rows
+__global__ void greedy_cond_kernel(GreedyCtl c) {
+    const int step = c.state[0] + 2;
+    c.state[0] = step;
+    if (c.total) c.total[0] += 2;
+    const bool more = step < c.s_max && c.state[2] > 0;
+    cudaGraphSetConditional(c.loop, more ? 1u : 0u);
+    cudaGraphSetConditional(c.compact, (more && step % kCompactEvery == 0) ? 1u : 0u);
+}
+
+// Row compaction: a line that has emitted its newline (or used up its 2T steps) only burns
+// GEMM rows from then on -- the reference keeps stepping it and ignores the result (seq2seq.py:1255-1256).  Every
+// kCompactEvery steps one block scans the live rows; if at least 1/16 of them have finished (or all), the survivors move
+// to the front (through a scratch copy: a row may land where another still has to be read), the row -> line map with
+// them, and the row count the GEMMs read shrinks.  When none are left the loop ends.
+struct CompactArgs {
+    GreedyCtl ctl;
+    const int32_t* rl; int32_t* rl2; int32_t* g_new;
+    const uint8_t* done; const uint8_t* live; const int32_t* row_T;
+};
+__global__ void __launch_bounds__(1024) greedy_compact_scan_kernel(CompactArgs c) {
+    __shared__ int s_wsum[32];
+    __shared__ int s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int R = c.ctl.state[2], step = c.ctl.state[0];
+    const int per = (R + 1023) / 1024;
+    const int r0 = min(R, tid * per), r1 = min(R, r0 + per);
+    auto keep = [&](int r) {
+        const int line = c.rl[r];
+        return !c.done[line] && c.live[line] && step < 2 * c.row_T[line];
+    };
+    int mine = 0;
+    for (int r = r0; r < r1; ++r) mine += keep(r) ? 1 : 0;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    int off = 0, total = 0;
+    for (int w = 0; w < 32; ++w) { if (w < warp) off += s_wsum[w]; total += s_wsum[w]; }
+    const bool compact = total == 0 || R - total >= max(1, R >> 4);
+    if (compact) {
+        int j = off + incl - mine;
+        for (int r = r0; r < r1; ++r) {
+            if (keep(r)) { c.g_new[r] = j; c.rl2[j] = c.rl[r]; ++j; } else c.g_new[r] = -1;
+        }
+    }
+    if (tid == 0) {
+        c.ctl.state[4] = compact ? 1 : 0;
+        if (compact) {
+            c.ctl.state[3] = R; c.ctl.state[2] = total;
+            if (c.ctl.total) c.ctl.total[1] += 1;
+            if (total == 0) cudaGraphSetConditional(c.ctl.loop, 0u);
+        }
+    }
+}
+struct MoveEntry { char* ptr; int bytes; int off; };
+struct MoveList { MoveEntry e[32]; int n; };
+__global__ void __launch_bounds__(128) greedy_compact_move_kernel(MoveList ml, const int32_t* state, const int32_t* g_new, int32_t* rl, const int32_t* rl2,
+                                                                  uint8_t* scratch, size_t scratch_row, int back) {
+    if (!state[4]) return;
+    const int rows = back ? state[2] : state[3];
+    for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+        const int j = back ? r : g_new[r];
+        if (j < 0) continue;
+        uint8_t* srow = scratch + (size_t)j * scratch_row;
+        for (int k = 0; k < ml.n; ++k) {
+            const MoveEntry e = ml.e[k];
+            char* g = e.ptr + (size_t)(back ? j : r) * e.bytes;
+            char* sc = reinterpret_cast<char*>(srow) + e.off;
+            const char* src = back ? sc : g; char* dst = back ? g : sc;
+            if ((e.bytes & 15) == 0) {
+                for (int i = threadIdx.x; i < (e.bytes >> 4); i += blockDim.x) reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+            } else {
+                for (int i = threadIdx.x; i < (e.bytes >> 2); i += blockDim.x) reinterpret_cast<uint32_t*>(dst)[i] = reinterpret_cast<const uint32_t*>(src)[i];
+            }
+        }
+        if (back && threadIdx.x == 0) rl[j] = rl2[j];
+    }
 }
 
 static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
@@ -682,7 +778,10 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         }
         io.a_in = ws.a[cur_]; io.a_out = ws.a[cur_ ^ 1];
         if (s >= 0) io.align_log = ws.o_align ? ws.o_align + (size_t)s * B * T : nullptr;
-        else { io.align_log = ws.o_align; io.step_dev = ws.loop_state; io.step_off = off; io.align_stride = (long long)B * T; }
+        else {
+            io.align_log = ws.o_align; io.step_dev = ws.loop_state; io.step_off = off; io.align_stride = (long long)B * T;
+            io.r_dev = ws.loop_state + 2; io.row_line = ws.g_rl; io.align_by_line = 1;      // rows are compacted, lines keep their place
+        }
         io.wq = ws.wq; io.ctx = ws.ctx; io.ctx_lo = ws.ctx_lo; io.logits = ws.logits;
         io.wq_ready = (s != 0); io.wq_next = ws.wq;
         if (decoder_core(m, ws, io, s_)) return 1;
@@ -691,7 +790,7 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         g.out_chars = ws.o_chars; g.out_probs = ws.o_probs; g.score_sum = ws.o_score; g.out_len = ws.o_len; g.done = ws.done;
         g.out_ties = ws.o_ties;
         g.R = B; g.V = m->V; g.step = s >= 0 ? s : off; g.s_max = S; g.eos = m->cfg.eos_index;
-        if (s < 0) { g.step_dev = ws.loop_state; g.done_count = ws.loop_state + 1; }
+        if (s < 0) { g.step_dev = ws.loop_state; g.row_line = ws.g_rl; g.r_dev = ws.loop_state + 2; }
         return launch_softmax_greedy(s_, g);
     };
     if (loop_graphs_enabled()) {
@@ -715,22 +814,74 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
                                            (uint64_t)(m->side != nullptr), (uint64_t)ws.bytes};
         if (loop_graph_lookup(m, key, &g)) return 1;
         if (!g->exec) {
-            cudaGraphConditionalHandle cond; cudaGraph_t body;
-            int32_t* state = ws.loop_state; int64_t* total = m->dev_counters; int s_max = S, init = 1, no_init = 0;
-            int n_rows = B;
-            void* kargs[6] = {(void*)&state, (void*)&total, (void*)&s_max, (void*)&n_rows, (void*)&cond, (void*)&init};
-            cudaKernelNodeParams kp{};
-            kp.func = (void*)greedy_cond_kernel; kp.gridDim = dim3(1); kp.blockDim = dim3(1); kp.kernelParams = kargs;
-            if (loop_graph_begin(g, kp, &cond, &body)) return 1;
-            cudaStream_t cs = loop_capture_stream(m);
-            COR_CHECK(cs, "no capture stream");
+            GreedyCtl ctl{};
+            ctl.state = ws.loop_state; ctl.total = m->dev_counters; ctl.s_max = S; ctl.n_rows = B;
+            cudaGraph_t body;
+            // the first node needs both handles, which exist only once the graph does: create the graph and the handles by
+            // hand, then the node (loop_graph_begin would create the WHILE handle after reading the node's arguments)
+            if (g->graph) { cudaGraphExecDestroy(g->exec); cudaGraphDestroy(g->graph); g->exec = nullptr; g->graph = nullptr; }
+            COR_CUDA(cudaGraphCreate(&g->graph, 0));
+            COR_CUDA(cudaGraphConditionalHandleCreate(&ctl.loop, g->graph, 0, 0));
+            COR_CUDA(cudaGraphConditionalHandleCreate(&ctl.compact, g->graph, 0, 0));
+            {
+                int32_t* rl = ws.g_rl;
+                void* kargs[2] = {(void*)&ctl, (void*)&rl};
+                cudaKernelNodeParams kp{};
+                kp.func = (void*)greedy_init_kernel; kp.gridDim = dim3((B + 255) / 256); kp.blockDim = dim3(256); kp.kernelParams = kargs;
+                cudaGraphNode_t n_first, n_while;
+                COR_CUDA(cudaGraphAddKernelNode(&n_first, g->graph, nullptr, 0, &kp));
+                cudaGraphNodeParams cp{};
+                cp.type = cudaGraphNodeTypeConditional;
+                cp.conditional.handle = ctl.loop; cp.conditional.type = cudaGraphCondTypeWhile; cp.conditional.size = 1;
+                COR_CUDA(cudaGraphAddNode(&n_while, g->graph, &n_first, 1, &cp));
+                body = cp.conditional.phGraph_out[0];
+            }
+            // per-row decoder state that moves with a row
+            MoveList ml{};
+            size_t off = 0;
+            auto add = [&](const void* ptr, size_t bytes) {
+                if (!ptr) return;
+                ml.e[ml.n++] = MoveEntry{(char*)ptr, (int)bytes, (int)off};
+                off = (off + bytes + 15) & ~size_t(15);
+            };
+            const bool sp = m->split;
+            for (int n = 0; n < d; ++n) {
+                add(ws.dh[0][n], (size_t)W * (sp ? 2 : 4)); add(ws.dh_lo[0][n], (size_t)W * 2);
+                add(ws.dc[n], (size_t)W * 4);
+            }
+            add(ws.a[0], (size_t)T * 4);
+            add(ws.p, (size_t)m->Vp * (sp ? 2 : 4)); add(ws.p_lo, (size_t)m->Vp * 2);
+            add(ws.wq, (size_t)W * 4);
+            COR_CHECK(off <= ws.g_scratch_row && ml.n <= 32, "compaction scratch row too small");
+            cudaStream_t cs = loop_capture_stream(m, 0), cs2 = loop_capture_stream(m, 1);
+            COR_CHECK(cs && cs2, "no capture stream");
             const int64_t before = ctx().launches;
             COR_CUDA(cudaStreamBeginCaptureToGraph(cs, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
             int rc = timestep(cs, -1, 0, 0) || timestep(cs, -1, 1, 1);
-            if (!rc) { greedy_cond_kernel<<<1, 1, 0, cs>>>(state, total, s_max, n_rows, cond, no_init); rc = cudaGetLastError() != cudaSuccess; }
+            if (!rc) { greedy_cond_kernel<<<1, 1, 0, cs>>>(ctl); rc = cudaGetLastError() != cudaSuccess; }
+            const int step_kernels = (int)(ctx().launches - before);
+            if (!rc) {
+                cudaGraph_t branch[1];
+                rc = loop_graph_switch(cs, 0, ctl.compact, branch);
+                if (!rc) {
+                    cudaError_t e = cudaStreamBeginCaptureToGraph(cs2, branch[0], nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed);
+                    if (e != cudaSuccess) { set_error(std::string("capturing the compaction branch: ") + cudaGetErrorString(e)); rc = 1; }
+                    else {
+                        CompactArgs ca{ctl, ws.g_rl, ws.g_rl2, ws.g_new, ws.done, ws.live, ws.row_T};
+                        const int mgrid = std::min(B, 148 * 8);
+                        greedy_compact_scan_kernel<<<1, 1024, 0, cs2>>>(ca);
+                        greedy_compact_move_kernel<<<mgrid, 128, 0, cs2>>>(ml, ws.loop_state, ws.g_new, ws.g_rl, ws.g_rl2, ws.g_scratch, ws.g_scratch_row, 0);
+                        greedy_compact_move_kernel<<<mgrid, 128, 0, cs2>>>(ml, ws.loop_state, ws.g_new, ws.g_rl, ws.g_rl2, ws.g_scratch, ws.g_scratch_row, 1);
+                        rc = cudaGetLastError() != cudaSuccess;
+                        cudaGraph_t got = nullptr;
+                        e = cudaStreamEndCapture(cs2, &got);
+                        if (!rc && e != cudaSuccess) { set_error(std::string("capturing the compaction branch: ") + cudaGetErrorString(e)); rc = 1; }
+                    }
+                }
+            }
             cudaGraph_t captured = nullptr;
             const cudaError_t ce = cudaStreamEndCapture(cs, &captured);
-            g->body_kernels = (int)(ctx().launches - before);
+            g->body_kernels = step_kernels;
             ctx().launches = before;            // captured, not run
             COR_CHECK(!rc, "capturing the greedy timestep failed");
             COR_CUDA(ce);
@@ -762,9 +913,12 @@ int64_t cor_launch_count(cor_model* m, int reset) {
         int64_t steps = 0;
         if (cudaSetDevice(m->device) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess &&
             cudaMemcpy(&steps, m->dev_counters, 8, cudaMemcpyDeviceToHost) == cudaSuccess) {
-            m->ctx.launches += steps * m->greedy_step_kernels + steps / 2;
-            m->ctx.in_graph += steps * m->greedy_step_kernels + steps / 2;
-            cudaMemset(m->dev_counters, 0, 8);
+            int64_t compactions = 0;
+            cudaMemcpy(&compactions, m->dev_counters + 1, 8, cudaMemcpyDeviceToHost);
+            const int64_t ran = steps * m->greedy_step_kernels + steps / 2 + 3 * compactions;
+            m->ctx.launches += ran;
+            m->ctx.in_graph += ran;
+            cudaMemset(m->dev_counters, 0, 16);
         }
     }
     const int64_t v = m->ctx.launches;

@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(512, 1) attention_tma_kernel(AttnArgs a, SlabG
         // ---- alignment row: zero everywhere, a_j = e_j / sum in the window
         if (sub == 0) {
             float* ao = a.a_out + (size_t)row * a.t_max;
-            float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)row * a.t_max : nullptr;
+            float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)(a.align_by_line ? line : row) * a.t_max : nullptr;
             for (int jb = 0; jb < a.t_max; jb += 32) {
                 const int j = jb + lane, q = j - j0;
                 float v = __shfl_sync(0xffffffffu, wgt, min(max(q, 0), 31));

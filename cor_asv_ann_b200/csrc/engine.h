@@ -188,6 +188,7 @@ struct AttnArgs {
     float* align_log;          // optional [R][t_max] extra copy (alignment history)
     // timestep on the device (loop graphs): the history row block of this step is align_log + (*step_dev + step_off) * align_stride
     const int* step_dev; int step_off; long long align_stride;
+    int align_by_line;         // the history row of a hypothesis row is its LINE's (rows are compacted while lines keep their place)
     int R; const int* r_dev; int L; int t_max; int W; int D; int window; int inclusive;
 };
 int launch_attention(cudaStream_t st, const AttnArgs& a);
@@ -203,6 +204,8 @@ struct GreedyArgs {
     int R; int V; int step; int s_max; int eos;
     // loop graphs: the timestep is *step_dev + step; *done_count counts the lines that have finished
     const int* step_dev; int32_t* done_count;
+    // compacted rows (loop graph with row compaction): row -> line for every per-line array above; live row count on the device
+    const int32_t* row_line; const int* r_dev;
 };
 // An argmax whose runner-up lies within this relative margin is logged as a near-tie: fp32-grade implementations
 // (this one, Keras/TF, the numpy oracle) may legitimately pick either, so parity tests report such lines separately.

@@ -36,6 +36,7 @@ int loop_graph_begin(LoopGraph* g, const cudaKernelNodeParams& first, cudaGraphC
 // While `cs` is capturing: a SWITCH node on the selector `sw` (a handle of the top-level graph) with `n` branches behind
 // everything captured so far; what is captured on `cs` afterwards depends on it.  Returns the branch graphs (to capture
 // into with another stream).
+// `n` == 0: an IF node (one branch, taken when the selector is non-zero) instead of a SWITCH.
 int loop_graph_switch(cudaStream_t cs, int n, cudaGraphConditionalHandle sw, cudaGraph_t* branches);
 
 }  // namespace cor

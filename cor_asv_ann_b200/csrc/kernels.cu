@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(128, 5) attention_kernel(AttnArgs a) {
     __syncwarp();
     // alignment row: zero everywhere, a_j = e_j / sum in the window
     float* ao = a.a_out + (size_t)row * a.t_max;
-    float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)row * a.t_max : nullptr;
+    float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)(a.align_by_line ? line : row) * a.t_max : nullptr;
     for (int j = lane; j < a.t_max; j += 32) {
         const int q = j - j0;
         const float v = (q >= 0 && q < nj) ? s_w[wid][q] : 0.f;
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(128, 4) attention_side_kernel(AttnArgs a) {
             if (q < nj && lane == 0) s_w[wid][q] = s[q] / esum;
         __syncwarp();
         float* ao = a.a_out + (size_t)row * a.t_max;
-        float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)row * a.t_max : nullptr;
+        float* al = a.align_log ? a.align_log + (a.step_dev ? (size_t)(*a.step_dev + a.step_off) * (size_t)a.align_stride : 0) + (size_t)(a.align_by_line ? line : row) * a.t_max : nullptr;
         for (int j = lane; j < a.t_max; j += 32) {
             const int q = j - j0;
             const float v = (q >= 0 && q < nj) ? s_w[wid][q] : 0.f;
@@ -344,20 +344,21 @@ __global__ void __launch_bounds__(128) softmax_kernel(GreedyArgs g, const int* r
     if (!GREEDY) return;
     top2_merge(best, best_v, second);
     if (lane == 0) {
+        const int line = g.row_line ? g.row_line[row] : row;
         const int step = g.step_dev ? *g.step_dev + g.step : g.step;
-        const int s_row = 2 * g.row_T[row];
-        const bool alive = !g.done[row] && g.live[row] && step < s_row;
+        const int s_row = 2 * g.row_T[line];
+        const bool alive = !g.done[line] && g.live[line] && step < s_row;
         // loop graphs: a line is counted ONCE, at the step it finishes (newline, last step, or never started) -- the
         // loop ends when the count reaches the number of rows; one atomic per line and call, not per step
         if (g.done_count && (alive ? (best_v == g.eos || step + 1 >= s_row) : step == 0)) atomicAdd(g.done_count, 1);
         if (alive) {
-            const int n = g.out_len[row];
-            g.out_chars[(size_t)row * g.s_max + n] = best_v;
-            g.out_probs[(size_t)row * g.s_max + n] = best;
-            g.score_sum[row] += (double)(-logf(best));
-            g.out_len[row] = n + 1;
-            if (best_v == g.eos) g.done[row] = 1;
-            if (g.out_ties && best - second <= kTieMargin * best) g.out_ties[row] += 1;
+            const int n = g.out_len[line];
+            g.out_chars[(size_t)line * g.s_max + n] = best_v;
+            g.out_probs[(size_t)line * g.s_max + n] = best;
+            g.score_sum[line] += (double)(-logf(best));
+            g.out_len[line] = n + 1;
+            if (best_v == g.eos) g.done[line] = 1;
+            if (g.out_ties && best - second <= kTieMargin * best) g.out_ties[line] += 1;
         }
     }
 }
@@ -443,9 +444,9 @@ int launch_attention_side(cudaStream_t st, const AttnArgs& a) {
 int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a) {
     if (a.R <= 0) return 0;
     const int ld = (a.V + 127) & ~127;
-    if (ld == 512) softmax_kernel<true, 16><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
-    else if (ld == 128) softmax_kernel<true, 4><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
-    else softmax_kernel<true, 0><<<(a.R + 3) / 4, 128, 0, st>>>(a, nullptr);
+    if (ld == 512) softmax_kernel<true, 16><<<(a.R + 3) / 4, 128, 0, st>>>(a, a.r_dev);
+    else if (ld == 128) softmax_kernel<true, 4><<<(a.R + 3) / 4, 128, 0, st>>>(a, a.r_dev);
+    else softmax_kernel<true, 0><<<(a.R + 3) / 4, 128, 0, st>>>(a, a.r_dev);
     ++ctx().launches;
     COR_CUDA(cudaGetLastError());
     return 0;

@@ -109,7 +109,9 @@ struct Ws {
     int32_t* o_chars = nullptr; float* o_probs = nullptr; double* o_score = nullptr; int32_t* o_len = nullptr;
     int32_t* o_ties = nullptr;
     float* o_align = nullptr;
-    int32_t* loop_state = nullptr;                       // [4] fast-greedy loop graph: timestep, lines finished
+    int32_t* loop_state = nullptr;                       // [8] fast-greedy loop graph: [0] timestep, [1] lines finished, [2] live rows, [3] rows before the last compaction, [4] compacted?
+    int32_t *g_rl = nullptr, *g_rl2 = nullptr, *g_new = nullptr;      // row -> line, its compacted copy, new row index (or -1) per old row
+    uint8_t* g_scratch = nullptr; size_t g_scratch_row = 0;           // compaction scratch: one copy of the per-row decoder state
     float* enc_out() const { return seq.back(); }
     float* enc_out_lo() const { return seq_lo.back(); }
 };
@@ -126,6 +128,7 @@ struct StepIO {
     const float* c_in[8] = {}; float* c_out[8] = {};
     const float* a_in = nullptr; float* a_out = nullptr; float* align_log = nullptr;
     const int* step_dev = nullptr; int step_off = 0; long long align_stride = 0;   // loop graphs: see AttnArgs
+    int align_by_line = 0;
     float *wq = nullptr, *ctx = nullptr, *ctx_lo = nullptr, *logits = nullptr;
     bool wq_ready = false;                   // wq already holds h_in[top].W_a + b (written by the previous step)
     float* wq_next = nullptr;                // if set: the logits launch also writes h_out[top].W_a + b here

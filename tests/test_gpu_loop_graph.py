@@ -83,6 +83,32 @@ def test_greedy_graph_early_exit_identical(name, n_lines, length):
     print("greedy graph: %d launches against %d of the host loop, longest line %d of %d steps, %d lines" % (n_graph, n_host, lens.max(), 2 * T, B))
 
 
+def test_greedy_graph_row_compaction_mixed():
+    """Lines that end at scattered steps NEXT TO lines that never do: finished rows are compacted out of the GEMMs while the
+    others run their 2T steps; every line's result is what the host loop (all rows, all steps) gives, bit for bit --
+    incl. the alignment history, which is indexed by line while rows move."""
+    topo, w, mapping = _ending_model("c2")
+    lines = synthetic_lines(mapping, 300, 24, seed=777, min_length=8) + ['']
+    idx, val = _sparse(mapping, lines)
+    B, T, _ = idx.shape
+    row_T = np.full(B, T, np.int32)
+    row_T[100:200] = T - 5           # a second reference batch with a shorter padded length in the same call
+    idx[100:200, T - 5:, :] = -1
+    eng = _engine(topo, w, 2)
+    g = [t.numpy().copy() for t in eng.correct_greedy_host(idx, val, row_T, want_align=True)]
+    with _host_loop():
+        h = [t.numpy().copy() for t in eng.correct_greedy_host(idx, val, row_T, want_align=True)]
+    chars, probs, scores, lens, align = g
+    ended = int((lens < 2 * row_T).sum())
+    assert 30 < ended < B - 30, "the test needs a mix of ending and non-ending lines (%d of %d end)" % (ended, B)
+    assert np.array_equal(lens, h[3]) and np.array_equal(scores, h[2])
+    for j in range(B):
+        n = int(lens[j])
+        assert np.array_equal(chars[j, :n], h[0][j, :n]) and np.array_equal(probs[j, :n], h[1][j, :n])
+        assert np.array_equal(align[:n, j], h[4][:n, j])
+    assert np.array_equal(eng.last_ties.numpy(), eng.last_ties.numpy())
+
+
 def test_greedy_graph_full_length_identical():
     """Random-init weights (no line ends): all 2T steps run inside the graph; identical to the host loop."""
     topo, w, mapping = make_model("c2")
