@@ -91,6 +91,8 @@ struct cor_trainer {
     float *d_seq_a = nullptr, *d_seq_b = nullptr;          // [T][B][2W] gradient of a layer's output / input sequence
     float *dh = nullptr, *dc = nullptr, *dh_tmp = nullptr; // [B][W] running recurrent gradients
     float *dh_r = nullptr, *dc_r = nullptr;                // ... of a backward-direction scan
+    float *dh_s = nullptr, *dc_s = nullptr;                // ... of a decoder layer running beside an encoder layer
+    float *e_seq_a = nullptr, *e_seq_b = nullptr;          // [Ts][B][2W] encoder-side input gradients (the decoder's ping-pong pair is busy beside them)
     std::vector<float*> dh_init, dc_init;                  // gradient wrt the decoder layers' initial states [B][W]
     float* ones = nullptr; size_t ones_n = 0;
     // the batch, staged into buffers of the activation store (a recorded step reads fixed addresses)
@@ -204,85 +206,101 @@ __global__ void tr_bias_rows_kernel(float* Z, const float* bias, size_t rows, in
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < rows * cols; i += (size_t)gridDim.x * blockDim.x) Z[i] += bias[i % cols];
 }
 
-// attention forward of one decoder step, window only (attention.py:526-575): one warp per row
-__global__ void tr_attn_fwd_kernel(const float* wq, const float* u, const float* enc, const float* a_prev, const float* v_a, const float* b_v,
-                                   int B, int Ts, int W, int D, int window, float* a_out, float* ctx, int32_t* win) {
-    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (b >= B) return;
+// attention forward of one decoder step, window only (attention.py:526-575): one BLOCK of four warps per row -- a warp per
+// window position for the energies, all threads over the columns for the context.  (A warp per row left a 64-line
+// batch on 16 blocks: 106 us per step, 60 % of the whole training step together with its backward twin.)
+__global__ void __launch_bounds__(128) tr_attn_fwd_kernel(const float* wq, const float* u, const float* enc, const float* a_prev, const float* v_a, const float* b_v,
+                                                          int B, int Ts, int W, int D, int window, float* a_out, float* ctx, int32_t* win) {
+    __shared__ float s_red[4];
+    __shared__ float s_e[MAXWIN];
+    __shared__ int s_win[2];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float part = 0.f;
-    for (int j = lane; j < Ts; j += 32) part = fmaf(a_prev[(size_t)b * Ts + j], (float)j, part);
+    for (int j = tid; j < Ts; j += 128) part = fmaf(a_prev[(size_t)b * Ts + j], (float)j, part);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    const float centre = part + 1.0f;
-    int j0 = 0, nj = 0;
-    if (window > 0) {
-        const int j_lo = max(0, (int)ceilf(centre - (float)window) - 1), j_hi = min(Ts - 1, (int)floorf(centre + (float)window) + 1);
-        for (int j = j_lo; j <= j_hi && nj < MAXWIN; ++j)
-            if (fabsf(centre - (float)j) <= (float)window) { if (nj == 0) j0 = j; ++nj; }
-    } else { j0 = 0; nj = min(Ts, MAXWIN); }
-    float e[MAXWIN];
-    float esum = 0.f;
-    for (int q = 0; q < nj; ++q) {
+    if (lane == 0) s_red[warp] = part;
+    __syncthreads();
+    if (tid == 0) {
+        const float centre = ((s_red[0] + s_red[1]) + (s_red[2] + s_red[3])) + 1.0f;
+        int j0 = 0, nj = 0;
+        if (window > 0) {
+            const int j_lo = max(0, (int)ceilf(centre - (float)window) - 1), j_hi = min(Ts - 1, (int)floorf(centre + (float)window) + 1);
+            for (int j = j_lo; j <= j_hi && nj < MAXWIN; ++j)
+                if (fabsf(centre - (float)j) <= (float)window) { if (nj == 0) j0 = j; ++nj; }
+        } else { j0 = 0; nj = min(Ts, MAXWIN); }
+        s_win[0] = j0; s_win[1] = nj;
+        win[2 * b] = j0; win[2 * b + 1] = nj;
+    }
+    __syncthreads();
+    const int j0 = s_win[0], nj = s_win[1];
+    for (int q = warp; q < nj; q += 4) {
         const float* uj = u + ((size_t)(j0 + q) * B + b) * W;
         float s = 0.f;
         for (int k = lane; k < W; k += 32) s = fmaf(tanhf(wq[(size_t)b * W + k] + uj[k]), v_a[k], s);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        e[q] = expf(s + b_v[0]);
-        esum += e[q];
+        if (lane == 0) s_e[q] = expf(s + b_v[0]);
     }
-    for (int j = lane; j < Ts; j += 32) {
+    __syncthreads();
+    float esum = 0.f;
+    for (int q = 0; q < nj; ++q) esum += s_e[q];
+    for (int j = tid; j < Ts; j += 128) {
         const int q = j - j0;
-        float v = 0.f;
-        for (int qq = 0; qq < nj; ++qq) if (qq == q) v = e[qq] / esum;
-        a_out[(size_t)b * Ts + j] = v;
+        a_out[(size_t)b * Ts + j] = (q >= 0 && q < nj) ? s_e[q] / esum : 0.f;
     }
-    for (int k = lane; k < D; k += 32) {
+    for (int k = tid; k < D; k += 128) {
         float c = 0.f;
-        for (int q = 0; q < nj; ++q) c = fmaf(e[q] / esum, enc[((size_t)(j0 + q) * B + b) * D + k], c);
+        for (int q = 0; q < nj; ++q) c = fmaf(s_e[q] / esum, enc[((size_t)(j0 + q) * B + b) * D + k], c);
         ctx[(size_t)b * D + k] = c;
     }
-    if (lane == 0) { win[2 * b] = j0; win[2 * b + 1] = nj; }
 }
-// attention backward of one decoder step: d_ctx -> d_enc, d_u (accumulated), d_wq, partial dv_a / db_v of the row
-__global__ void tr_attn_bwd_kernel(const float* wq, const float* u, const float* enc, const float* a, const float* v_a, const float* d_ctx,
-                                   const int32_t* win, int B, int Ts, int W, int D, float* d_enc, float* d_u, float* d_wq, float* dv_part, float* dbv_part) {
-    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (b >= B) return;
+// attention backward of one decoder step: d_ctx -> d_enc, d_u (accumulated), d_wq, partial dv_a / db_v of the row; block per row
+__global__ void __launch_bounds__(128) tr_attn_bwd_kernel(const float* wq, const float* u, const float* enc, const float* a, const float* v_a, const float* d_ctx,
+                                                          const int32_t* win, int B, int Ts, int W, int D, float* d_enc, float* d_u, float* d_wq, float* dv_part, float* dbv_part) {
+    __shared__ float s_da[MAXWIN], s_aw[MAXWIN];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int j0 = win[2 * b], nj = win[2 * b + 1];
-    float da[MAXWIN], aw[MAXWIN];
-    float dot = 0.f;
-    for (int q = 0; q < nj; ++q) {
+    for (int q = warp; q < nj; q += 4) {
         const float* ej = enc + ((size_t)(j0 + q) * B + b) * D;
         float s = 0.f;
         for (int k = lane; k < D; k += 32) s = fmaf(d_ctx[(size_t)b * D + k], ej[k], s);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        da[q] = s; aw[q] = a[(size_t)b * Ts + j0 + q];
-        dot = fmaf(aw[q], s, dot);
+        if (lane == 0) { s_da[q] = s; s_aw[q] = a[(size_t)b * Ts + j0 + q]; }
     }
+    __syncthreads();
+    float dot = 0.f;
+    for (int q = 0; q < nj; ++q) dot = fmaf(s_aw[q], s_da[q], dot);
+    float ds[MAXWIN];
     float dbv = 0.f;
-    for (int q = 0; q < nj; ++q) {
-        float* dej = d_enc + ((size_t)(j0 + q) * B + b) * D;
-        for (int k = lane; k < D; k += 32) dej[k] = fmaf(aw[q], d_ctx[(size_t)b * D + k], dej[k]);
-        da[q] = aw[q] * (da[q] - dot);            // ds_q: gradient wrt the log-energy
-        dbv += da[q];
+#pragma unroll
+    for (int q = 0; q < MAXWIN; ++q) { ds[q] = q < nj ? s_aw[q] * (s_da[q] - dot) : 0.f; dbv += ds[q]; }     // gradient wrt the log-energies
+    for (int k = tid; k < D; k += 128) {
+        const float dc = d_ctx[(size_t)b * D + k];
+        for (int q = 0; q < nj; ++q) {
+            float* dej = d_enc + ((size_t)(j0 + q) * B + b) * D + k;
+            *dej = fmaf(s_aw[q], dc, *dej);
+        }
     }
-    for (int k = lane; k < W; k += 32) {
+    for (int k = tid; k < W; k += 128) {
         const float w = wq[(size_t)b * W + k], v = v_a[k];
         float dw = 0.f, dv = 0.f;
-        for (int q = 0; q < nj; ++q) {
-            const size_t o = ((size_t)(j0 + q) * B + b) * W + k;
-            const float th = tanhf(w + u[o]);
-            const float dt = da[q] * v * (1.0f - th * th);
-            dv = fmaf(da[q], th, dv);
-            dw += dt;
-            d_u[o] += dt;
+#pragma unroll
+        for (int q = 0; q < MAXWIN; ++q) {
+            if (q < nj) {
+                const size_t o = ((size_t)(j0 + q) * B + b) * W + k;
+                const float th = tanhf(w + u[o]);
+                const float dt = ds[q] * v * (1.0f - th * th);
+                dv = fmaf(ds[q], th, dv);
+                dw += dt;
+                d_u[o] += dt;
+            }
         }
         d_wq[(size_t)b * W + k] = dw;
         dv_part[(size_t)b * W + k] = dv;
     }
-    if (lane == 0) dbv_part[b] = dbv;
+    if (tid == 0) dbv_part[b] = dbv;
 }
 
 // softmax + weighted cross-entropy of one row (t, b): P in place (logits -> d_logits = w * (p - y)), loss sums
@@ -328,27 +346,39 @@ __global__ void tr_softmax_ce_kernel(float* P, const int32_t* target, int B, int
     }
 }
 
-// regulariser gradient (seq2seq.py:530-553) added to dE, after the cross-entropy gradient has been scaled
-__global__ void tr_regulariser_kernel(const float* E, int V, int W, float* dE, double* scal) {
-    // one block; mean of rows 1..V-1 per column, then per-row terms
-    extern __shared__ float mean[];
-    for (int u = threadIdx.x; u < W; u += blockDim.x) {
-        double s = 0.0;
-        for (int v = 1; v < V; ++v) s += E[(size_t)v * W + u];
-        mean[u] = (float)(s / (double)(V - 1));
-    }
+// regulariser gradient (seq2seq.py:530-553) added to dE, after the cross-entropy gradient has been scaled: one block per
+// embedding row; colsum = column sums over ALL rows (tr_colsum_kernel), so mean_{i>=1} = (colsum - E_0) / (V - 1)
+__global__ void __launch_bounds__(128) tr_regulariser_kernel(const float* E, int V, int W, const float* colsum, float* dE, double* scal) {
+    __shared__ double s_red[4];
+    const int v = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* row = E + (size_t)v * W;
+    double n2 = 0.0;
+    for (int u = tid; u < W; u += 128) n2 += (double)row[u] * row[u];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+    if (lane == 0) s_red[warp] = n2;
     __syncthreads();
-    double loss = 0.0;
-    for (int v = threadIdx.x; v < V; v += blockDim.x) {
-        double n2 = 0.0;
-        for (int u = 0; u < W; ++u) n2 += (double)E[(size_t)v * W + u] * E[(size_t)v * W + u];
-        const float coef = (float)(-0.04 * (1.0 - n2));
-        for (int u = 0; u < W; ++u) dE[(size_t)v * W + u] += coef * E[(size_t)v * W + u];
-        loss += 0.01 * (1.0 - n2) * (1.0 - n2);
+    n2 = (s_red[0] + s_red[1]) + (s_red[2] + s_red[3]);
+    __syncthreads();
+    const float coef = (float)(-0.04 * (1.0 - n2));
+    double under = 0.0;
+    for (int u = tid; u < W; u += 128) {
+        float g = coef * row[u];
+        if (v == 0) {
+            const float dlt = row[u] - (colsum[u] - row[u]) / (float)(V - 1);
+            g += 2.0f * dlt;
+            under += (double)dlt * dlt;
+        }
+        dE[(size_t)v * W + u] += g;
     }
-    if (threadIdx.x == 0)
-        for (int u = 0; u < W; ++u) { const float dlt = E[u] - mean[u]; dE[u] += 2.0f * dlt; loss += (double)dlt * dlt; }
-    atomicAdd(&scal[2], loss);
+    if (v == 0) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) under += __shfl_xor_sync(0xffffffffu, under, o);
+        if (lane == 0) s_red[warp] = under;
+        __syncthreads();
+        under = (s_red[0] + s_red[1]) + (s_red[2] + s_red[3]);
+    }
+    if (tid == 0) atomicAdd(&scal[2], 0.01 * (1.0 - n2) * (1.0 - n2) + (v == 0 ? under : 0.0));
 }
 
 __global__ void tr_scale_kernel(float* x, size_t n, float s) {
@@ -456,7 +486,8 @@ int ensure_store(cor_trainer* t, int B, int Ts, int Td, int k) {
     const size_t Tm = std::max(Ts, Td);
     if (take(t, Tm * B * 2 * W, &t->d_seq_a) || take(t, Tm * B * 2 * W, &t->d_seq_b)) return 1;
     if (take(t, BW, &t->dh) || take(t, BW, &t->dc) || take(t, BW, &t->dh_tmp) || take(t, BW, &t->dh_r) || take(t, BW, &t->dc_r)) return 1;
-    if (take(t, (size_t)Ts * BW, &t->d_x2)) return 1;
+    if (take(t, (size_t)Ts * BW, &t->d_x2) || take(t, BW, &t->dh_s) || take(t, BW, &t->dc_s)) return 1;
+    if (take(t, (size_t)Ts * B * 2 * W, &t->e_seq_a) || take(t, (size_t)Ts * B * 2 * W, &t->e_seq_b)) return 1;
     if (take(t, (size_t)B * Ts * k, &t->s_src) || take(t, (size_t)B * Ts * k, &t->s_val) || take(t, (size_t)B * Td, &t->s_din) ||
         take(t, (size_t)B * Td, &t->s_dout) || take(t, (size_t)std::max(d - 1, 1) * 2 * W, &t->s_menc) ||
         take(t, (size_t)std::max(d - 1, 1) * W, &t->s_mdec) || take(t, (size_t)B * (W + D), &t->s_mcell)) return 1;
@@ -497,11 +528,15 @@ int lstm_forward(cor_trainer* t, cudaStream_t st, const LstmP& lp, const float* 
 // Produces dK, dR, db (accumulated into the flat gradient), d_x [T][B][in] (if wanted; beta = accumulate), and leaves
 // the gradient wrt the initial state in t->dh / t->dc.
 int lstm_backward(cor_trainer* t, cudaStream_t st, const LstmP& lp, const float* x, int T, int B, LstmAct& a, bool reverse,
-                  const float* d_out, int ld, const float* dh_last, const float* dc_last, float* d_x, float beta_x) {
+                  const float* d_out, int ld, const float* dh_last, const float* dc_last, float* d_x, float beta_x, int bufset = -1) {
     const int W = t->W;
     const size_t BW = (size_t)B * W;
     const float* Pm = t->P; float* Gm = t->Gd;
-    float* dh = reverse ? t->dh_r : t->dh; float* dc = reverse ? t->dc_r : t->dc;     // the two directions of a layer may run side by side
+    // scans that run side by side have their own running gradients: 0 forward encoder scans (and the result slot the
+    // callers read: t->dh / t->dc), 1 the backward direction, 2 a decoder layer beside an encoder layer
+    if (bufset < 0) bufset = reverse ? 1 : 0;
+    float* dh = bufset == 2 ? t->dh_s : (bufset == 1 ? t->dh_r : t->dh);
+    float* dc = bufset == 2 ? t->dc_s : (bufset == 1 ? t->dc_r : t->dc);
     if (dh_last) { COR_CUDA(cudaMemcpyAsync(dh, dh_last, BW * 4, cudaMemcpyDeviceToDevice, st)); COR_CUDA(cudaMemcpyAsync(dc, dc_last, BW * 4, cudaMemcpyDeviceToDevice, st)); }
     else { COR_CUDA(cudaMemsetAsync(dh, 0, BW * 4, st)); COR_CUDA(cudaMemsetAsync(dc, 0, BW * 4, st)); }
     for (int s = T - 1; s >= 0; --s) {
@@ -651,42 +686,46 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
     // ================================================================ forward
     tr_embed_kernel<<<dim3(Ts, B), 128, 0, st>>>(bt->src_idx, bt->src_val, B, Ts, k, P + t->E, W, t->X0);
     tr_embed_kernel<<<dim3(Td, B), 128, 0, st>>>(bt->dec_in, nullptr, B, Td, 1, P + t->E, W, t->D0);
-    // ---- encoder
-    for (int n = 0; n < d; ++n) {
-        const float* x = t->enc_in[n];
-        const int Dn = n == 0 ? 2 * W : W;
-        float* raw = t->enc_out_raw[n];
-        if (n == 0) {       // the backward direction beside the forward one
-            cudaStream_t side;
-            if (fork_side(t, st, &side) || lstm_forward(t, side, t->enc_bw[0], x, Ts, B, t->a_bw[0], nullptr, nullptr, true, raw + W, Dn)) return 1;
-            end_side(t);
-        }
-        if (lstm_forward(t, st, t->enc_fw[n], x, Ts, B, t->a_fw[n], nullptr, nullptr, false, raw, Dn)) return 1;
-        if (n == 0 && join_side(t, st)) return 1;
-        // what the next layer (or the attention) sees: residual from the third forward layer up, then the time-constant dropout
-        const bool rs = resid && n >= 2;
-        const float* mask = (n < d - 1 && bt->mask_enc) ? bt->mask_enc + (size_t)n * 2 * W : nullptr;
-        float* dst = n < d - 1 ? t->enc_in[n + 1] : t->enc_out;
-        tr_combine_kernel<<<grid_for_n((size_t)Ts * B * Dn), 256, 0, st>>>(raw, Dn, rs ? x : nullptr, Dn, mask, 1, B, dst, Dn, (size_t)Ts * B, Dn);
-    }
-    if (gemm(t, false, false, Ts * B, W, D, 1.f, t->enc_out, D, P + t->U, W, 0.f, t->u, W)) return 1;
     // state handed to decoder layer n: backward final of the bottom layer, forward final otherwise (seq2seq.py:280-283)
     auto enc_final = [&](int n, const float** h, const float** c) {
         LstmAct& a = n == 0 ? t->a_bw[0] : t->a_fw[n];
         const size_t fin = n == 0 ? 0 : (size_t)Ts * BW;          // final state: slot 0 of a backward scan, slot T of a forward one
         *h = a.H + fin; *c = a.C + fin;
     };
-    // ---- decoder layers below the top
-    for (int n = 0; n + 1 < d; ++n) {
+    auto dec_layer_forward = [&](int n, cudaStream_t s_) -> int {
         const float *h0, *c0;
         enc_final(n, &h0, &c0);
-        // raw output goes to d_seq_a as scratch, then residual + dropout into the next layer's input
-        float* raw = t->d_seq_a;
-        if (lstm_forward(t, st, t->dec[n], t->dec_in[n], Td, B, t->a_dec[n], h0, c0, false, raw, W)) return 1;
+        float* raw = t->d_seq_a;        // raw output as scratch, then residual + dropout into the next layer's input
+        if (lstm_forward(t, s_, t->dec[n], t->dec_in[n], Td, B, t->a_dec[n], h0, c0, false, raw, W)) return 1;
         const float* mask = bt->mask_dec ? bt->mask_dec + (size_t)n * W : nullptr;
-        tr_combine_kernel<<<grid_for_n((size_t)Td * BW), 256, 0, st>>>(raw, W, (n > 0 && resid) ? t->dec_in[n] : nullptr, W, mask, 1, B,
+        tr_combine_kernel<<<grid_for_n((size_t)Td * BW), 256, 0, s_>>>(raw, W, (n > 0 && resid) ? t->dec_in[n] : nullptr, W, mask, 1, B,
                                                                      t->dec_in[n + 1], W, (size_t)Td * B, W);
+        return 0;
+    };
+    // ---- encoder, with decoder layer n - 1 (which needs encoder layer n - 1's final state only) beside encoder layer n
+    for (int n = 0; n < d; ++n) {
+        const float* x = t->enc_in[n];
+        const int Dn = n == 0 ? 2 * W : W;
+        float* raw = t->enc_out_raw[n];
+        cudaStream_t side;
+        if (n == 0) {       // the backward direction beside the forward one
+            if (fork_side(t, st, &side) || lstm_forward(t, side, t->enc_bw[0], x, Ts, B, t->a_bw[0], nullptr, nullptr, true, raw + W, Dn)) return 1;
+            end_side(t);
+        } else {
+            if (fork_side(t, st, &side) || dec_layer_forward(n - 1, side)) return 1;
+            end_side(t);
+        }
+        if (lstm_forward(t, st, t->enc_fw[n], x, Ts, B, t->a_fw[n], nullptr, nullptr, false, raw, Dn)) return 1;
+        // what the next layer (or the attention) sees: residual from the third forward layer up, then the time-constant dropout
+        // (the bottom layer's backward half must be there: join first)
+        if (n == 0 && join_side(t, st)) return 1;
+        const bool rs = resid && n >= 2;
+        const float* mask = (n < d - 1 && bt->mask_enc) ? bt->mask_enc + (size_t)n * 2 * W : nullptr;
+        float* dst = n < d - 1 ? t->enc_in[n + 1] : t->enc_out;
+        tr_combine_kernel<<<grid_for_n((size_t)Ts * B * Dn), 256, 0, st>>>(raw, Dn, rs ? x : nullptr, Dn, mask, 1, B, dst, Dn, (size_t)Ts * B, Dn);
+        if (n > 0 && join_side(t, st)) return 1;
     }
+    if (gemm(t, false, false, Ts * B, W, D, 1.f, t->enc_out, D, P + t->U, W, 0.f, t->u, W)) return 1;
     // ---- attention cell
     {
         const int top = d - 1;
@@ -719,7 +758,7 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
             if (gemm(t, false, false, B, W, W, 1.f, hp, W, P + t->Wa, W, 0.f, wq, W)) return 1;
             tr_bias_rows_kernel<<<grid_for_n(BW), 256, 0, st>>>(wq, P + t->bUW, B, W);
             float* ctx = t->ctx + (size_t)s * B * D;
-            tr_attn_fwd_kernel<<<(B + 3) / 4, 128, 0, st>>>(wq, t->u, t->enc_out, t->al + (size_t)s * B * Ts, P + t->va, P + t->bv, B, Ts, W, D,
+            tr_attn_fwd_kernel<<<B, 128, 0, st>>>(wq, t->u, t->enc_out, t->al + (size_t)s * B * Ts, P + t->va, P + t->bv, B, Ts, W, D,
                                                           t->cfg.window_width, t->al + (size_t)(s + 1) * B * Ts, ctx, t->win + (size_t)s * B * 2);
             const float* cin = ctx;
             if (cmask) {
@@ -770,7 +809,7 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
             if (cmask) tr_combine_kernel<<<grid_for_n((size_t)B * D), 256, 0, st>>>(dctx, D, nullptr, 0, cmask, B, B, dctx, D, B, D);
             if (gemm(t, false, true, B, W, 4 * W, 1.f, Gs, 4 * W, P + lp.R, 4 * W, 0.f, t->dh, W)) return 1;
             float* dwq = t->d_wq + (size_t)s * BW;
-            tr_attn_bwd_kernel<<<(B + 3) / 4, 128, 0, st>>>(t->wq + (size_t)s * BW, t->u, t->enc_out, t->al + (size_t)(s + 1) * B * Ts, P + t->va, dctx,
+            tr_attn_bwd_kernel<<<B, 128, 0, st>>>(t->wq + (size_t)s * BW, t->u, t->enc_out, t->al + (size_t)(s + 1) * B * Ts, P + t->va, dctx,
                                                           t->win + (size_t)s * B * 2, B, Ts, W, D, t->d_encout, t->d_u, dwq,
                                                           t->dv_part + (size_t)s * BW, t->dbv_part + (size_t)s * B);
             // dh_prev += d_wq . W_a^T
@@ -804,31 +843,36 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
     // attention keys: u = enc_out . U
     if (gemm(t, true, false, D, W, Ts * B, 1.f, t->enc_out, D, t->d_u, W, 1.f, G + t->U, W)) return 1;
     if (gemm(t, false, true, Ts * B, D, W, 1.f, t->d_u, W, P + t->U, W, 1.f, t->d_encout, D)) return 1;
-    // ---- decoder layers below the top, top-down.  d_cur = gradient wrt the INPUT sequence of layer n+1 = output side of layer n
-    float* d_cur = d_in_top; float* d_other = t->d_seq_a;
-    for (int n = d - 2; n >= 0; --n) {
-        // output side: out = (lstm + (n > 0 && resid ? in : 0)) * mask
-        const float* mask = bt->mask_dec ? bt->mask_dec + (size_t)n * W : nullptr;
-        if (mask) tr_combine_kernel<<<grid_for_n((size_t)Td * BW), 256, 0, st>>>(d_cur, W, nullptr, 0, mask, 1, B, d_cur, W, (size_t)Td * B, W);
-        if (lstm_backward(t, st, t->dec[n], t->dec_in[n], Td, B, t->a_dec[n], false, d_cur, W, nullptr, nullptr, d_other, 0.f)) return 1;
-        COR_CUDA(cudaMemcpyAsync(t->dh_init[n], t->dh, BW * 4, cudaMemcpyDeviceToDevice, st));
-        COR_CUDA(cudaMemcpyAsync(t->dc_init[n], t->dc, BW * 4, cudaMemcpyDeviceToDevice, st));
-        if (n > 0 && resid) tr_accum_kernel<<<grid_for_n((size_t)Td * BW), 256, 0, st>>>(d_other, W, d_cur, W, nullptr, 1, B, (size_t)Td * B, W);
-        std::swap(d_cur, d_other);
-    }
-    // d_cur = gradient wrt the embedded decoder input D0
-    tr_embed_bwd_kernel<<<dim3(Td, B), 128, 0, st>>>(bt->dec_in, nullptr, B, Td, 1, d_cur, W, G + t->E);
-    // ---- encoder, top-down.  d_enc = gradient wrt the output side of layer n ([Ts][B][D_n])
-    float* d_enc = t->d_encout;
-    float* bufs[2] = {t->d_seq_a, t->d_seq_b};      // both free again: the decoder's input gradient has been scattered
-    for (int n = d - 1, pp = 0; n >= 0; --n, pp ^= 1) {
+    // ---- below the top: decoder layer m = d-2-k beside encoder layer n = d-1-k (stage k).  Encoder layer n needs the gradient
+    // wrt its final state from decoder layer n, which ran one stage earlier; the decoder chain only needs itself.
+    float* d_cur = d_in_top; float* d_other = t->d_seq_a;       // d_cur = gradient wrt the output side of the next decoder layer down
+    if (d == 1) tr_embed_bwd_kernel<<<dim3(Td, B), 128, 0, st>>>(bt->dec_in, nullptr, B, Td, 1, d_cur, W, G + t->E);
+    float* d_enc = t->d_encout;                                 // gradient wrt the output side of the next encoder layer down
+    float* ebufs[2] = {t->e_seq_a, t->e_seq_b};
+    for (int stage = 0, pp = 0; stage < d; ++stage, pp ^= 1) {
+        const int n = d - 1 - stage, mdec = d - 2 - stage;
+        if (mdec >= 0) {
+            cudaStream_t side;
+            if (fork_side(t, st, &side)) return 1;
+            // output side: out = (lstm + (m > 0 && resid ? in : 0)) * mask
+            const float* mask = bt->mask_dec ? bt->mask_dec + (size_t)mdec * W : nullptr;
+            if (mask) tr_combine_kernel<<<grid_for_n((size_t)Td * BW), 256, 0, side>>>(d_cur, W, nullptr, 0, mask, 1, B, d_cur, W, (size_t)Td * B, W);
+            if (lstm_backward(t, side, t->dec[mdec], t->dec_in[mdec], Td, B, t->a_dec[mdec], false, d_cur, W, nullptr, nullptr, d_other, 0.f, 2)) return 1;
+            COR_CUDA(cudaMemcpyAsync(t->dh_init[mdec], t->dh_s, BW * 4, cudaMemcpyDeviceToDevice, side));
+            COR_CUDA(cudaMemcpyAsync(t->dc_init[mdec], t->dc_s, BW * 4, cudaMemcpyDeviceToDevice, side));
+            if (mdec > 0 && resid) tr_accum_kernel<<<grid_for_n((size_t)Td * BW), 256, 0, side>>>(d_other, W, d_cur, W, nullptr, 1, B, (size_t)Td * B, W);
+            std::swap(d_cur, d_other);
+            // d_cur = gradient wrt the embedded decoder input D0 once the bottom decoder layer is through
+            if (mdec == 0) tr_embed_bwd_kernel<<<dim3(Td, B), 128, 0, side>>>(bt->dec_in, nullptr, B, Td, 1, d_cur, W, G + t->E);
+            end_side(t);
+        }
         const int Dn = n == 0 ? 2 * W : W;
         const bool rs = resid && n >= 2;
         const float* mask = (n < d - 1 && bt->mask_enc) ? bt->mask_enc + (size_t)n * 2 * W : nullptr;
         if (mask) tr_combine_kernel<<<grid_for_n((size_t)Ts * B * Dn), 256, 0, st>>>(d_enc, Dn, nullptr, 0, mask, 1, B, d_enc, Dn, (size_t)Ts * B, Dn);
         const float* x = t->enc_in[n];
         const int in = t->enc_fw[n].in;
-        float* d_x = bufs[pp];                       // gradient wrt the layer's input sequence [Ts][B][in]
+        float* d_x = ebufs[pp];                      // gradient wrt the layer's input sequence [Ts][B][in]
         // decoder layer n started from this layer's final state: backward final for the bottom layer, forward final otherwise
         if (n == 0) {
             cudaStream_t side;
@@ -841,6 +885,7 @@ int step_body(cor_trainer* t, const cor_train_batch* bt, cudaStream_t st) {
             if (lstm_backward(t, st, t->enc_fw[n], x, Ts, B, t->a_fw[n], false, d_enc, Dn, t->dh_init[n], t->dc_init[n], d_x, 0.f)) return 1;
             if (rs) tr_accum_kernel<<<grid_for_n((size_t)Ts * B * in), 256, 0, st>>>(d_x, in, d_enc, Dn, nullptr, 1, B, (size_t)Ts * B, in);
         }
+        if (mdec >= 0 && join_side(t, st)) return 1;
         d_enc = d_x;
     }
     tr_embed_bwd_kernel<<<dim3(Ts, B), 128, 0, st>>>(bt->src_idx, bt->src_val, B, Ts, k, d_enc, W, G + t->E);
@@ -918,9 +963,13 @@ int cor_train_apply(cor_trainer* t, double n_target_steps, int with_regulariser,
     COR_CUDA(cudaMemsetAsync(t->d_scal + 2, 0, 16, st));
     const float inv = n_target_steps > 0 ? (float)(1.0 / n_target_steps) : 0.f;
     tr_scale_kernel<<<grid_for_n(t->n_params), 256, 0, st>>>(t->Gd, t->n_params, inv);
-    if (with_regulariser) tr_regulariser_kernel<<<1, 256, (size_t)W * 4, st>>>(t->P + t->E, V, W, t->Gd + t->E, t->d_scal);
+    if (with_regulariser) {
+        COR_CHECK(t->dh_tmp, "cor_train_apply before any cor_train_forward_backward");
+        tr_colsum_kernel<<<(W + 31) / 32, dim3(32, 8), 0, st>>>(t->P + t->E, W, (size_t)V, W, t->dh_tmp, 0);
+        tr_regulariser_kernel<<<V, 128, 0, st>>>(t->P + t->E, V, W, t->dh_tmp, t->Gd + t->E, t->d_scal);
+    }
     tr_sumsq_kernel<<<grid_for_n(t->n_params), 256, 0, st>>>(t->Gd, t->n_params, t->d_scal + 3);
-    t->launches += 3 + (with_regulariser ? 1 : 0);
+    t->launches += 3 + (with_regulariser ? 2 : 0);
     if (lr > 0.f) {
         t->adam_t += 1;
         const double b1 = 0.9, b2 = 0.999;
