@@ -89,7 +89,12 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu):
-        self.rows, self.proc, self.gpu = [], None, gpu
+        self.rows, self.proc, self.gpu, self.first = [], None, gpu, 0
+
+    def mark(self):
+        """Samples from here on count (the process is started before the warm-up: nvidia-smi's own start-up -- NVML
+        initialisation takes the driver lock for a few hundred ms -- must not fall into the timed region)."""
+        self.first = len(self.rows)
 
     def start(self):
         try:
@@ -113,7 +118,7 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for r in self.rows[self.first:]:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except (ValueError, IndexError):
@@ -304,20 +309,24 @@ def measure(args, eng, workload, lines, rank, world, local, sample_clocks, roofl
             dist.barrier()
         torch.cuda.synchronize()
 
-    for s in range(args.warmup):
-        device_step(s)
-    barrier()
     sampler = ClockSampler(local)
     if sample_clocks:
         sampler.start()
+    for s in range(args.warmup):
+        device_step(s)
+    barrier()
+    sampler.mark()
     eng.launch_count(reset=True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ev0.record()
     for s in range(args.warmup, total_steps):
         out = device_step(s)
+        marks[s - args.warmup].record()         # an event record, no synchronisation: shows WHICH step an outlier sits in
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
+    ms_each = [round(a.elapsed_time(b), 2) for a, b in zip([ev0] + marks[:-1], marks)]
     launches, host_launches = eng.launch_count(), eng.host_launch_count()
     clocks = sampler.stop() if sample_clocks else None
     if bp is None:
@@ -394,7 +403,7 @@ def measure(args, eng, workload, lines, rank, world, local, sample_clocks, roofl
     torch.cuda.empty_cache()
     return {"L": L, "ms": ms, "value": chars / (ms * 1e-3), "e2e_value": chars / (e2e_ms * 1e-3), "e2e_ms": e2e_ms,
             "h2d": h2d, "d2h": d2h, "api": api, "launches": launches, "host_launches": host_launches, "k_ms": k_ms, "k_n": k_n, "k_flops": k_flops,
-            "prof_ms": prof_ms, "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra, "parity": parity}
+            "prof_ms": prof_ms, "clocks": clocks, "algo_flops_line": algo_flops_line, "extra": extra, "parity": parity, "ms_each": ms_each}
 
 
 def measured_traffic(workload, rows):
@@ -541,13 +550,14 @@ def measure_train(args, local, rank, world, lines_per_gpu=64):
         torch.cuda.synchronize()
 
     losses = []
-    for s in range(args.warmup):
-        tr.train_on_batch(dev[s][0], None, dev[s][1], dev[s][2], tr.dropout_masks(rng, 0.2, lines_per_gpu))
-    barrier()
-    tr.launch_count(reset=True)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for s in range(args.warmup):
+        tr.train_on_batch(dev[s][0], None, dev[s][1], dev[s][2], tr.dropout_masks(rng, 0.2, lines_per_gpu))
+    barrier()
+    sampler.mark()
+    tr.launch_count(reset=True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for s in range(args.warmup, total):
@@ -724,6 +734,7 @@ def bench_line(args, r, workload, world, peaks):
     line = {
         "metric": "corrected chars/sec (%s)" % workload, "value": r["value"], "unit": "chars/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps,
+        "ms_each_step": r["ms_each"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f16" if args.gemm_mode == 3 else "f32", "data": "synthetic", "config": workload_config(workload, r["L"]),
         "e2e": {"value": r["e2e_value"], "unit": "chars/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
@@ -869,7 +880,7 @@ def main():
         except OSError:
             pass
         line = bench_line(args, main_r, args.workload, world, peaks)
-        keys = ("metric", "value", "unit", "steps", "ms_per_step", "config", "e2e", "gpu_launches", "host_launch_calls", "clocks", "roofline",
+        keys = ("metric", "value", "unit", "steps", "ms_per_step", "ms_each_step", "config", "e2e", "gpu_launches", "host_launch_calls", "clocks", "roofline",
                 "algorithmic_gflop_per_line", "parity", "beam_iterations_per_line", "hypothesis_steps_per_line",
                 "hypotheses_per_line_and_iteration", "hypothesis_steps_per_s", "finals_per_line", "fringe_peak_mean", "fringe_peak_max",
                 "near_tie_decisions_per_line", "lines_without_final", "lines_equal_to_input", "near_tie_argmaxes_last_step")
