@@ -185,6 +185,7 @@ def parity_check(workload, idx_rows, got, n_check):
     t0 = time.perf_counter()
     same = ties = 0
     worst = 0.0
+    diffs = []
     if spec["beam"] is None:
         n_check = batch.shape[0]
         text, r_probs, _, _ = od.decode_batch_greedy(topo, w, mapping, x)
@@ -208,10 +209,15 @@ def parity_check(workload, idx_rows, got, n_check):
                 same += 1
                 if r is not None:
                     worst = max(worst, float(np.abs(probs[j, :lens[j]] - np.asarray(r[1], np.float32)).max()))
-            elif stats[j, 5] > 0 or want[5] > 0:
-                ties += 1
+            else:
+                if stats[j, 5] > 0 or want[5] > 0:
+                    ties += 1
+                got_s = ''.join(mapping[1][int(v)] for v in chars[j, :lens[j]]) if lens[j] > 0 else None
+                diffs.append({"line": j, "string_equal": (r is None and got_s is None) or (r is not None and got_s == r[0]),
+                              "gpu_stats[iterations,hyp_steps,finals,open_left,score_ties,near_ties]": [int(v) for v in stats[j, :6]],
+                              "oracle_stats": [int(v) for v in want[:6]], "checksum_equal": bool(stats[j, 6] == want[6])})
     return {"parity_rows_checked": n_check, "rows_identical": same, "rows_differing_at_logged_near_tie": ties,
-            "rows_differing_otherwise": n_check - same - ties, "max_abs_dp": worst,
+            "rows_differing_otherwise": n_check - same - ties, "max_abs_dp": worst, "differing_rows": diffs,
             "compared": "strings + per-character probabilities" + ("" if spec["beam"] is None else " + search statistics and expansion checksum"),
             "oracle_s": time.perf_counter() - t0}
 
@@ -707,7 +713,10 @@ def measure_strong(args, topo, w, mapping, local, rank, world):
         mine = indices_to_lines(make_indices(hi - lo, seed + 31 * rank), mapping[1]) if hi > lo else []
         job = shard.LocalPart(n_lines, lo, mine)
         runner = shard.engine_runner(s, fast=fast, greedy=fast)
-        shard.decode_job(runner, indices_to_lines(make_indices(2 * REF_BATCH, 9), mapping[1]), batch_size=REF_BATCH)    # warm-up
+        # warm-up on every rank THROUGH the collectives: NCCL sets up its point-to-point channels on first use (the gather),
+        # and the engine records its loop graph for the super-batch geometry
+        shard.decode_job(runner, indices_to_lines(make_indices(world * 64 * REF_BATCH, 9), mapping[1]), batch_size=REF_BATCH,
+                         superbatch=64, rank=rank, world_size=world)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
