@@ -53,7 +53,7 @@ def correct_lines_sharded(correct_batch, lines, conf=None, batch_size=256, rank=
 # ----------------------------------------------------------------------------- fixed jobs as arrays (strong scaling)
 
 class JobResult:
-    """Results of a whole job in input order, as arrays: chars int32 [n, S] (index 0 = nothing), lens int32 [n],
+    """Results of a whole job in input order, as arrays: chars int16 or int32 [n, S] (index 0 = nothing), lens int32 [n],
     scores float64 [n] and, for the beamed decoder, stats int64 [n, 8].  Strings are made on demand."""
 
     def __init__(self, chars, lens, scores, stats=None):
@@ -160,15 +160,35 @@ def decode_job(runner, lines, conf=None, batch_size=256, superbatch=64, rank=0, 
         off += b
     assert off == n_local
 
+    def to_host(t):
+        """device -> pinned host memory (a pageable .cpu() of the 1 M-line result runs at a fraction of the link rate)"""
+        if not t.is_cuda:
+            return t
+        host = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        host.copy_(t, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return host
+
     def to_root(t):
         if world_size == 1:
-            return t[:n_local].cpu()
+            return to_host(t[:n_local])
         import torch.distributed as dist
-        parts = [torch.empty_like(t) for _ in range(world_size)] if rank == 0 else None
-        dist.gather(t, parts, dst=0, group=group)
+        wire = t.view(torch.uint8) if t.dtype == torch.int16 else t       # NCCL has no 16-bit integer type: bytes on the wire
+        parts = [torch.empty_like(wire) for _ in range(world_size)] if rank == 0 else None
+        dist.gather(wire, parts, dst=0, group=group)
         if rank != 0:
             return None
-        return torch.cat([p[:n] for p, n in zip(parts, per_rank)]).cpu()
+        return to_host(torch.cat([p[:n] for p, n in zip(parts, per_rank)]).view(t.dtype))
+
+    # character indices travel as int16 when the alphabet allows (decided over all ranks: the gather needs one dtype):
+    # half the bytes through the gather and the D2H copy
+    if chars.is_cuda:
+        cmax = chars.max().reshape(1).to(torch.int64) if chars.numel() else torch.zeros(1, dtype=torch.int64, device=dev)
+        if world_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(cmax, op=dist.ReduceOp.MAX, group=group)
+        if int(cmax.item()) < 32768:
+            chars = chars.to(torch.int16)
 
     out = [to_root(t) for t in (chars, lens, scores)]
     st_out = to_root(stats) if stats is not None else None
