@@ -900,6 +900,14 @@ def main():
             also[wl] = {k: o[k] for k in keys if k in o}
         if also:
             line["also"] = also
+        if "beam_competitive" in also:
+            # the literal config is a one-hypothesis search with random weights (see the module docstring); the search
+            # under competition is measured beside it and is the number to read for "what does the beam search cost"
+            c = also["beam_competitive"]
+            line["co_primary"] = {"workload": "beam_competitive", "value": c["value"], "unit": "chars/s", "e2e": c["e2e"]["value"],
+                                  "hypothesis_steps_per_s": c.get("hypothesis_steps_per_s"),
+                                  "hypotheses_per_line_and_iteration": c.get("hypotheses_per_line_and_iteration"),
+                                  "fringe_peak_max": c.get("fringe_peak_max"), "parity": c.get("parity")}
         if c1_r is not None:
             line.setdefault("also", {})["c1"] = c1_r
         if early_r is not None:

@@ -25,7 +25,6 @@ namespace cor {
 
 namespace {
 
-constexpr int MAXWIN = 13;       // 2*window_width+1 with window_width <= 6
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
