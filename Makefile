@@ -2,7 +2,7 @@
 NVCC ?= nvcc
 ARCH := -gencode arch=compute_100a,code=sm_100a
 CSRC := cor_asv_ann_b200/csrc
-SRCS := $(CSRC)/api.cu $(CSRC)/kernels.cu $(CSRC)/attention.cu $(CSRC)/gemm_ffma.cu $(CSRC)/gemm_tc.cu $(CSRC)/beam.cu $(CSRC)/alignpath.cu $(CSRC)/recur.cu $(CSRC)/decpage.cu $(CSRC)/train.cu
+SRCS := $(CSRC)/api.cu $(CSRC)/kernels.cu $(CSRC)/attention.cu $(CSRC)/gemm_ffma.cu $(CSRC)/gemm_tc.cu $(CSRC)/beam.cu $(CSRC)/alignpath.cu $(CSRC)/recur.cu $(CSRC)/decpage.cu $(CSRC)/train.cu $(CSRC)/noalloc.cu
 OBJS := $(SRCS:.cu=.o)
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/cor_b200.h
 LIB  := cor_asv_ann_b200/libcor_b200.so

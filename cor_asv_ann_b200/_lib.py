@@ -64,6 +64,8 @@ PROTOTYPES = {
     "cor_host_launch_count": (C.c_int64, [C.c_void_p, C.c_int]),
     "cor_debug_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_int]),
     "cor_debug_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cor_gemm_noalloc": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cor_gemm_noalloc_max_bytes": (C.c_size_t, []),
     "cor_prof_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "cor_prof_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),
 }

@@ -235,6 +235,16 @@ int64_t cor_host_launch_count(cor_model* m, int reset);
 int cor_debug_counters(cor_model* m, int64_t* out, int reset);
 /* test hook: C[M,N] = A[M,K] . B[N,K]^T (device fp32) through one GEMM kernel: 1 = FFMA, 2 = tcgen05 3-pass fp16 hi/lo, 3 = the same with the page-sized 128x32 tiles forced */
 int cor_debug_gemm(int mode, int M, int N, int K, const float* A, const float* B, float* C, void* stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  C[M,N] = A[M,K] . B[N,K]^T (device
+ * fp32, K a multiple of 64) through the tcgen05 3-pass kernel like cor_debug_gemm(2, ...), but the fp16 (head, residual)
+ * copies of A and B go into a 16 MiB file-scope array in device memory (csrc/noalloc.cu) instead of cudaMalloc'ed
+ * buffers: no cudaMalloc / cudaFree / allocating library call.  4 * (M + N) * K bytes (each of the four parts rounded
+ * up to 256) must fit in cor_gemm_noalloc_max_bytes() = 16 MiB, else the call fails with an error and launches nothing.
+ * Stream-ordered, does not synchronise.  Every call on a device shares the one array: calls that overlap on the GPU
+ * (different streams without a dependency) race; calls on one stream are safe. */
+int cor_gemm_noalloc(int M, int N, int K, const float* A, const float* B, float* C, void* stream);
+size_t cor_gemm_noalloc_max_bytes(void);
 int cor_prof_enable(cor_model* m, int on);   /* on: reset and start bracketing every LSTM-GEMM launch with events */
 int cor_prof_read(cor_model* m, double* total_ms, int64_t* launches, double* flops);   /* synchronizes the device */
 
