@@ -59,6 +59,9 @@ struct BeamDev {
     // diagnostics per line (stats[4..7]): exact top-2 score ties, near-tie ordering decisions, order-sensitive checksum of
     // the popped hypotheses, peak fringe length
     long long *score_ties, *near_ties; unsigned long long* pop_sum; int32_t* fr_peak;
+    // Reach truncation (see reach_keep): the fringe in memory is a PREFIX of the reference's list; fr_gone = entries of that
+    // list beyond the prefix (dropped because no remaining iteration can pop them), fin_in = upper bound of the finals in the prefix
+    int32_t *fr_gone, *fin_in; int reach_trunc;
     // final hypotheses in pop order, the first FMAX of them (decode_sequence_beam yields every final, best first)
     uint32_t* fin_id; double* fin_key; int n_best;
     int32_t* r_chars; float* r_probs; double* r_score; int32_t* r_len;      // result staging [L][n_best][...]
@@ -113,6 +116,7 @@ __global__ void beam_init_kernel(BeamDev b) {
         b.finals_count[line] = 0; b.best_final[line] = -1; b.open_left[line] = 0;
         b.best_key[line] = INFINITY; b.hyp_steps[line] = 0;
         b.score_ties[line] = 0; b.near_ties[line] = 0; b.pop_sum[line] = 0ull; b.fr_peak[line] = 1;
+        b.fr_gone[line] = 0; b.fin_in[line] = 0;
         b.fr_key[(size_t)line * b.cap] = 3.0 * fabs(1.0 - (double)Tl);
         b.fr_id[(size_t)line * b.cap] = 0u;
     }
@@ -128,7 +132,7 @@ __device__ void pop_line(const BeamDev& b, int line, int lane, bool bump = false
     const int Tl = b.row_T[line];
     const int len = b.fr_len[line];
     if (b.iter[line] >= 2 * Tl) {                    // max_batches reached (:1397-1398)
-        if (lane == 0) { b.status[line] = ST_DONE; b.beam_count[line] = 0; b.open_left[line] = len; }
+        if (lane == 0) { b.status[line] = ST_DONE; b.beam_count[line] = 0; b.open_left[line] = len + b.fr_gone[line]; }
         return;
     }
     const int cur = b.fr_buf[line];
@@ -196,11 +200,13 @@ __device__ void pop_line(const BeamDev& b, int line, int lane, bool bump = false
     }
     b.finals_count[line] = fc;
     b.fr_off[line] = consumed;
+    b.fin_in[line] -= nfin;
+    const int gone = b.fr_gone[line];
     int out = count;
     if (count == 0) {
-        b.status[line] = ST_DONE; b.open_left[line] = len - consumed;
+        b.status[line] = ST_DONE; b.open_left[line] = len + gone - consumed;
     } else if (fc > b.width_out && bk < keys[first_open]) {       // :1418-1420
-        b.status[line] = ST_DONE; b.open_left[line] = len - consumed; out = 0;
+        b.status[line] = ST_DONE; b.open_left[line] = len + gone - consumed; out = 0;
     } else if (b.x_count[line] + count > b.quota_x) {
         b.status[line] = ST_OVERFLOW; out = 0;
     } else {
@@ -901,6 +907,29 @@ __global__ void __launch_bounds__(128) beam_expand_warp_kernel(BeamDev b, int sp
 }
 
 // ------------------------------------------------------------------ push: insort of the new children (:1515-1532)
+// Reach truncation.  The reference keeps the best max_batches * batch_size entries (:1531) -- "more than can ever be
+// processed within limits" at the START of a line.  Later the same argument cuts deeper: with R pop rounds still to come
+// (R = 2T - iterations done) a round consumes a prefix of the list holding at most batch_size open nodes (:1400-1415), and
+// insertions only push an entry further back, so an entry with at least R * batch_size open nodes ahead of it is never
+// popped.  Such entries need not be stored: the fringe in memory is a prefix of the reference's list, `fr_gone` counts the
+// rest (list length, `open nodes left` and the peak statistic stay the reference's).  How long the merged prefix may be:
+//   * `keep`, the reference's own truncation;
+//   * if entries have been dropped before: up to and including the last OLD entry -- new children behind it may belong
+//     behind dropped entries; they are unreachable too (every dropped entry had > R * batch_size open nodes ahead after
+//     this round's pop, all of them in the stored prefix, hence ahead of those children);
+//   * R * batch_size + (finals in the prefix, upper bound) + 1 entries hold R * batch_size + 1 open nodes: the +1 keeps
+//     the entry behind the last pop in memory (the near-tie statistic of pop_line looks at it).
+// Results, statistics and checksums are unchanged (tests/test_gpu_beam.py against the oracle's); what changes is the
+// length of the merge copy, which dominated the competitive / stress brackets (fringe at its cap of 2T * 256 entries).
+__device__ __forceinline__ int reach_keep(const BeamDev& b, int line, int Tl, int keep, int n_old, int n_new,
+                                          int new_before_last_old, int new_finals) {
+    int q = min(keep, n_old + n_new);
+    if (!b.reach_trunc) return q;
+    if (b.fr_gone[line] > 0) q = min(q, n_old > 0 ? n_old + new_before_last_old : 0);
+    const long long rounds = max(0, 2 * Tl - b.iter[line]);
+    const long long reach = rounds * b.batch + (long long)b.fin_in[line] + new_finals + 1;
+    return (int)min((long long)q, reach);
+}
 __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, NW = NT >> 5;
     const int c = b.beam_count[line];
@@ -956,8 +985,27 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
     double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     // truncation to the best max_batches * batch_size = 2T * batch_size of THIS line's reference batch (seq2seq.py:1397, 1531)
-    const int keep = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);
-    for (int i = tid; i < n_old; i += NT) {
+    const int keep_ref = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);
+    __shared__ int s_new_finals;
+    if (tid == 0) s_new_finals = 0;
+    __syncthreads();
+    {
+        int nf = 0;
+        for (int j = tid; j < n_new; j += NT) nf += (sid[j] & FINAL_BIT) ? 1 : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nf += __shfl_xor_sync(0xffffffffu, nf, o);
+        if (lane == 0 && nf) atomicAdd(&s_new_finals, nf);
+    }
+    __syncthreads();
+    const int new_finals = s_new_finals;
+    int lo_last = 0;                              // new entries that precede the LAST old entry (same search in every thread)
+    if (n_old > 0) {
+        const double k = okey[n_old - 1]; const uint32_t id = oid[n_old - 1];
+        int hi = n_new;
+        while (lo_last < hi) { const int mid = (lo_last + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo_last = mid + 1; else hi = mid; }
+    }
+    const int keep = reach_keep(b, line, Tl, keep_ref, n_old, n_new, lo_last, new_finals);
+    for (int i = tid; i < min(n_old, keep); i += NT) {       // (an old entry never moves forward: pos >= i)
         const double k = okey[i]; const uint32_t id = oid[i];
         int lo = 0, hi = n_new;                   // new entries that precede this old one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo = mid + 1; else hi = mid; }
@@ -973,11 +1021,13 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
     }
     __syncthreads();
     if (tid == 0) {
-        const int nl = min(n_old + n_new, keep);
-        b.fr_len[line] = nl;
+        const int listed = (int)min((long long)n_old + b.fr_gone[line] + n_new, (long long)keep_ref);    // the reference's list
+        b.fr_len[line] = keep;
+        b.fr_gone[line] = listed - keep;
+        b.fin_in[line] += new_finals;
         b.fr_off[line] = 0;
         b.fr_buf[line] = cur ^ 1;
-        if (nl > b.fr_peak[line]) b.fr_peak[line] = nl;
+        if (listed > b.fr_peak[line]) b.fr_peak[line] = listed;
     }
 }
 
@@ -1020,7 +1070,14 @@ __device__ bool push_small_line(const BeamDev& b, int line, int lane, double* s_
     const uint32_t* oid = b.fr_id + ((size_t)cur * b.L + line) * b.cap + o_off;
     double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
     uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
-    const int keep = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);     // see push_line
+    const int keep_ref = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);     // see push_line
+    const int new_finals = __popc(__ballot_sync(FULL, lane < n_new && (s_id_w[lane < n_new ? lane : 0] & FINAL_BIT)));
+    int lo_last = 0;
+    if (n_old > 0) {
+        const double kz = okey[n_old - 1]; const uint32_t iz = oid[n_old - 1];
+        lo_last = __popc(__ballot_sync(FULL, lane < n_new && key_less(s_key_w[lane < n_new ? lane : 0], s_id_w[lane < n_new ? lane : 0], kz, iz)));
+    }
+    const int keep = reach_keep(b, line, Tl, keep_ref, n_old, n_new, lo_last, new_finals);
     if (lane < n_new) {
         const double k = s_key_w[lane]; const uint32_t id = s_id_w[lane];
         int rank = 0;
@@ -1030,7 +1087,7 @@ __device__ bool push_small_line(const BeamDev& b, int line, int lane, double* s_
         const int pos = rank + lo;
         if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
-    for (int i = lane; i < n_old; i += 32) {
+    for (int i = lane; i < min(n_old, keep); i += 32) {
         const double k = okey[i]; const uint32_t id = oid[i];
         int before = 0;                           // new entries that precede this old one
         for (int t = 0; t < n_new; ++t) before += key_less(s_key_w[t], s_id_w[t], k, id);
@@ -1039,11 +1096,13 @@ __device__ bool push_small_line(const BeamDev& b, int line, int lane, double* s_
     }
     __syncwarp();
     if (lane == 0) {
-        const int nl = min(n_old + n_new, keep);
-        b.fr_len[line] = nl;
+        const int listed = (int)min((long long)n_old + b.fr_gone[line] + n_new, (long long)keep_ref);
+        b.fr_len[line] = keep;
+        b.fr_gone[line] = listed - keep;
+        b.fin_in[line] += new_finals;
         b.fr_off[line] = 0;
         b.fr_buf[line] = cur ^ 1;
-        if (nl > b.fr_peak[line]) b.fr_peak[line] = nl;
+        if (listed > b.fr_peak[line]) b.fr_peak[line] = listed;
     }
     return false;
 }
@@ -1165,7 +1224,7 @@ __global__ void __launch_bounds__(128) beam_finish_kernel(BeamDev b, int32_t* o_
         os[0] = st == ST_OVERFLOW ? -1 : (st == ST_EMPTY ? -2 : b.iter[line]);
         os[1] = b.hyp_steps[line];
         os[2] = b.finals_count[line];
-        os[3] = st == ST_ACTIVE ? b.fr_len[line] : b.open_left[line];
+        os[3] = st == ST_ACTIVE ? b.fr_len[line] + b.fr_gone[line] : b.open_left[line];
         os[4] = b.score_ties[line];
         os[5] = b.near_ties[line];
         os[6] = (long long)b.pop_sum[line];
@@ -1234,6 +1293,8 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     b->best_key = c.take<double>(L); b->hyp_steps = c.take<long long>(L);
     b->score_ties = c.take<long long>(L); b->near_ties = c.take<long long>(L); b->pop_sum = c.take<unsigned long long>(L);
     b->fr_peak = c.take<int32_t>(L);
+    b->fr_gone = c.take<int32_t>(L); b->fin_in = c.take<int32_t>(L);
+    b->reach_trunc = getenv("COR_NO_REACH_TRUNC") ? 0 : 1;
     b->fr_key = c.take<double>((size_t)2 * L * cap); b->fr_id = c.take<uint32_t>((size_t)2 * L * cap);
     b->beam_nodes = c.take<uint32_t>((size_t)L * bp->batch_size);
     b->rej_table = c.take<int32_t>((size_t)L * T);
