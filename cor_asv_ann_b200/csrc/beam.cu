@@ -62,6 +62,7 @@ struct BeamDev {
     // Reach truncation (see reach_keep): the fringe in memory is a PREFIX of the reference's list; fr_gone = entries of that
     // list beyond the prefix (dropped because no remaining iteration can pop them), fin_in = upper bound of the finals in the prefix
     int32_t *fr_gone, *fin_in; int reach_trunc;
+    int32_t* push_done;                    // parts of beam_push_kernel that have finished a line's merge
     // final hypotheses in pop order, the first FMAX of them (decode_sequence_beam yields every final, best first)
     uint32_t* fin_id; double* fin_key; int n_best;
     int32_t* r_chars; float* r_probs; double* r_score; int32_t* r_len;      // result staging [L][n_best][...]
@@ -116,7 +117,7 @@ __global__ void beam_init_kernel(BeamDev b) {
         b.finals_count[line] = 0; b.best_final[line] = -1; b.open_left[line] = 0;
         b.best_key[line] = INFINITY; b.hyp_steps[line] = 0;
         b.score_ties[line] = 0; b.near_ties[line] = 0; b.pop_sum[line] = 0ull; b.fr_peak[line] = 1;
-        b.fr_gone[line] = 0; b.fin_in[line] = 0;
+        b.fr_gone[line] = 0; b.fin_in[line] = 0; b.push_done[line] = 0;
         b.fr_key[(size_t)line * b.cap] = 3.0 * fabs(1.0 - (double)Tl);
         b.fr_id[(size_t)line * b.cap] = 0u;
     }
@@ -930,34 +931,47 @@ __device__ __forceinline__ int reach_keep(const BeamDev& b, int line, int Tl, in
     const long long reach = rounds * b.batch + (long long)b.fin_in[line] + new_finals + 1;
     return (int)min((long long)q, reach);
 }
-__device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum) {
+// Three steps, so that several blocks can share one line's merge (beam_push_kernel):
+//   push_sort    the line's new children, sorted by (key, id), in shared memory + what the merge has to know (PushDesc);
+//                reads the line's state, changes nothing
+//   push_merge   rank-merge of slice `part` of `parts` of the old fringe and of the new children into the other buffer
+//   push_commit  the line's new state (one thread, after every part has finished)
+struct PushDesc { int n_new, n_old, cur, o_off, keep, keep_ref, new_finals; };
+
+__device__ bool push_sort(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum, PushDesc& d) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, NW = NT >> 5;
+    __shared__ int s_off[257];                   // first child of row j in the unsorted list (batch_size <= 256 rows per line)
+    __shared__ int s_new_finals;
     const int c = b.beam_count[line];
-    if (c <= 0) return;
+    if (c <= 0) return false;
     const int Tl = b.row_T[line];
     const int xb = b.x_base[line];
-    // ---- collect: row j of this line holds record xb+j with rec_nacc children, in insertion order
+    // ---- collect: row j of this line holds record xb+j with rec_nacc children
     const int nj = tid < c ? b.rec_nacc[(size_t)line * b.quota_x + xb + tid] : 0;
     int incl = nj;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
     if (lane == 31) s_wsum[warp] = incl;
+    if (tid == 0) s_new_finals = 0;
     __syncthreads();
     int off = 0, n_new = 0;
     for (int w = 0; w < NW; ++w) { if (w < warp) off += s_wsum[w]; n_new += s_wsum[w]; }
     off += incl - nj;
-    if (tid < c) {
-        const size_t g = (size_t)line * b.quota_x + xb + tid;
+    if (tid < c) s_off[tid] = off;
+    __syncthreads();
+    // one child per thread and round (a thread per ROW walked its up to 16 children one memory round trip after the other)
+    for (int e = tid; e < n_new; e += NT) {
+        int lo = 0, hi = c;                       // the last row whose first child is <= e (rows without children share an offset)
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= e) lo = mid; else hi = mid; }
+        const int q = e - s_off[lo];
+        const size_t g = (size_t)line * b.quota_x + xb + lo;
         const int len_child = b.rec_len[g] + 1;
         const double pen = 3.0 * fabs((double)(len_child - Tl));      // cost0 * |length - length0| (:1588-1595)
-        for (int q = 0; q < nj; ++q) {
-            skey[off + q] = b.ch_cum[g * KMAX + q] + pen;
-            sid[off + q] = (1u + (uint32_t)(xb + tid) * KMAX + q) | (b.ch_v[g * KMAX + q] == b.eos ? FINAL_BIT : 0u);
-        }
+        skey[e] = b.ch_cum[g * KMAX + q] + pen;
+        sid[e] = (1u + (uint32_t)(xb + lo) * KMAX + q) | (b.ch_v[g * KMAX + q] == b.eos ? FINAL_BIT : 0u);
     }
     int npad = 1;
     while (npad < n_new) npad <<= 1;
-    __syncthreads();
     for (int i = n_new + tid; i < npad; i += NT) { skey[i] = INFINITY; sid[i] = 0x7fffffffu; }
     __syncthreads();
     // ---- bitonic sort ascending by (key, id)
@@ -976,19 +990,6 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
             __syncthreads();
         }
     }
-    // ---- rank-merge with what is left of the old fringe into the other buffer, best first, truncated
-    const int cur = b.fr_buf[line];
-    const int o_off = b.fr_off[line];
-    const int n_old = b.fr_len[line] - o_off;
-    const double* okey = b.fr_key + ((size_t)cur * b.L + line) * b.cap + o_off;
-    const uint32_t* oid = b.fr_id + ((size_t)cur * b.L + line) * b.cap + o_off;
-    double* nkey = b.fr_key + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
-    uint32_t* nid = b.fr_id + ((size_t)(cur ^ 1) * b.L + line) * b.cap;
-    // truncation to the best max_batches * batch_size = 2T * batch_size of THIS line's reference batch (seq2seq.py:1397, 1531)
-    const int keep_ref = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);
-    __shared__ int s_new_finals;
-    if (tid == 0) s_new_finals = 0;
-    __syncthreads();
     {
         int nf = 0;
         for (int j = tid; j < n_new; j += NT) nf += (sid[j] & FINAL_BIT) ? 1 : 0;
@@ -997,38 +998,67 @@ __device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* si
         if (lane == 0 && nf) atomicAdd(&s_new_finals, nf);
     }
     __syncthreads();
-    const int new_finals = s_new_finals;
+    d.n_new = n_new;
+    d.new_finals = s_new_finals;
+    d.cur = b.fr_buf[line];
+    d.o_off = b.fr_off[line];
+    d.n_old = b.fr_len[line] - d.o_off;
+    const double* okey = b.fr_key + ((size_t)d.cur * b.L + line) * b.cap + d.o_off;
+    const uint32_t* oid = b.fr_id + ((size_t)d.cur * b.L + line) * b.cap + d.o_off;
     int lo_last = 0;                              // new entries that precede the LAST old entry (same search in every thread)
-    if (n_old > 0) {
-        const double k = okey[n_old - 1]; const uint32_t id = oid[n_old - 1];
+    if (d.n_old > 0) {
+        const double k = okey[d.n_old - 1]; const uint32_t id = oid[d.n_old - 1];
         int hi = n_new;
         while (lo_last < hi) { const int mid = (lo_last + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo_last = mid + 1; else hi = mid; }
     }
-    const int keep = reach_keep(b, line, Tl, keep_ref, n_old, n_new, lo_last, new_finals);
-    for (int i = tid; i < min(n_old, keep); i += NT) {       // (an old entry never moves forward: pos >= i)
+    // truncation to the best max_batches * batch_size = 2T * batch_size of THIS line's reference batch (seq2seq.py:1397, 1531) ...
+    d.keep_ref = (int)min((long long)b.cap, (long long)2 * Tl * b.batch);
+    d.keep = reach_keep(b, line, Tl, d.keep_ref, d.n_old, n_new, lo_last, d.new_finals);      // ... and to what can still be popped
+    return true;
+}
+
+__device__ void push_merge(const BeamDev& b, int line, const PushDesc& d, const double* skey, const uint32_t* sid, int part, int parts) {
+    const int tid = threadIdx.x, NT = blockDim.x;
+    const double* okey = b.fr_key + ((size_t)d.cur * b.L + line) * b.cap + d.o_off;
+    const uint32_t* oid = b.fr_id + ((size_t)d.cur * b.L + line) * b.cap + d.o_off;
+    double* nkey = b.fr_key + ((size_t)(d.cur ^ 1) * b.L + line) * b.cap;
+    uint32_t* nid = b.fr_id + ((size_t)(d.cur ^ 1) * b.L + line) * b.cap;
+    const int keep = d.keep, n_new = d.n_new;
+    const int m_old = min(d.n_old, keep);        // an old entry never moves forward: pos >= i
+    const int per_o = (m_old + parts - 1) / parts, o1 = min(m_old, (part + 1) * per_o);
+    for (int i = part * per_o + tid; i < o1; i += NT) {
         const double k = okey[i]; const uint32_t id = oid[i];
         int lo = 0, hi = n_new;                   // new entries that precede this old one
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(skey[mid], sid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = i + lo;
         if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
-    for (int j = tid; j < n_new; j += NT) {
+    const int per_n = (n_new + parts - 1) / parts, n1 = min(n_new, (part + 1) * per_n);
+    for (int j = part * per_n + tid; j < n1; j += NT) {
         const double k = skey[j]; const uint32_t id = sid[j];
-        int lo = 0, hi = n_old;                   // old entries that precede this new one
+        int lo = 0, hi = m_old;                   // old entries that precede this new one (past m_old: pos >= keep anyway)
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (key_less(okey[mid], oid[mid], k, id)) lo = mid + 1; else hi = mid; }
         const int pos = j + lo;
         if (pos < keep) { nkey[pos] = k; nid[pos] = id; }
     }
+}
+
+__device__ void push_commit(const BeamDev& b, int line, const PushDesc& d) {
+    const int listed = (int)min((long long)d.n_old + b.fr_gone[line] + d.n_new, (long long)d.keep_ref);    // the reference's list
+    b.fr_len[line] = d.keep;
+    b.fr_gone[line] = listed - d.keep;
+    b.fin_in[line] += d.new_finals;
+    b.fr_off[line] = 0;
+    b.fr_buf[line] = d.cur ^ 1;
+    if (listed > b.fr_peak[line]) b.fr_peak[line] = listed;
+}
+
+__device__ void push_line(const BeamDev& b, int line, double* skey, uint32_t* sid, int* s_wsum) {
+    PushDesc d;
+    if (!push_sort(b, line, skey, sid, s_wsum, d)) return;
+    push_merge(b, line, d, skey, sid, 0, 1);
     __syncthreads();
-    if (tid == 0) {
-        const int listed = (int)min((long long)n_old + b.fr_gone[line] + n_new, (long long)keep_ref);    // the reference's list
-        b.fr_len[line] = keep;
-        b.fr_gone[line] = listed - keep;
-        b.fin_in[line] += new_finals;
-        b.fr_off[line] = 0;
-        b.fr_buf[line] = cur ^ 1;
-        if (listed > b.fr_peak[line]) b.fr_peak[line] = listed;
-    }
+    if (threadIdx.x == 0) push_commit(b, line, d);
 }
 
 // Small case, one warp per line: at most 32 new children (the common case once the rejection candidate
@@ -1119,14 +1149,28 @@ __global__ void __launch_bounds__(256) beam_push_small_kernel(BeamDev b) {
 // 1024 threads per line: the bitonic sort of up to 4096 children and the rank-merge with a fringe of up to 2T*256 entries are
 // per-line work that a wave of a few dozen lines cannot spread over more SMs, only over more threads of one.
 constexpr int PUSH_THREADS = 1024;
+// gridDim.x blocks share a line (a wave of a page's worth of lines leaves most SMs without one): each sorts the children
+// for itself -- cheap beside the merge -- and merges its slice; the block that finishes last writes the line's new state,
+// which no other block reads any more by then (push_done counts the finished parts; nobody waits for anybody).
 __global__ void __launch_bounds__(PUSH_THREADS) beam_push_kernel(BeamDev b) {
     extern __shared__ unsigned char smraw[];
     double* skey = reinterpret_cast<double*>(smraw);                 // [npad]
     uint32_t* sid = reinterpret_cast<uint32_t*>(skey + MAX_NEW);     // [npad]
     __shared__ int s_wsum[PUSH_THREADS / 32];
     const int n = b.counters[2];
-    for (int i = blockIdx.x; i < n; i += gridDim.x) {
-        push_line(b, b.heavy[i], skey, sid, s_wsum);
+    const int parts = gridDim.x;
+    for (int i = blockIdx.y; i < n; i += gridDim.y) {
+        const int line = b.heavy[i];
+        PushDesc d;
+        if (push_sort(b, line, skey, sid, s_wsum, d)) {
+            push_merge(b, line, d, skey, sid, blockIdx.x, parts);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                bool last = true;
+                if (parts > 1) { __threadfence(); last = atomicAdd(&b.push_done[line], 1) == parts - 1; }
+                if (last) { if (parts > 1) b.push_done[line] = 0; push_commit(b, line, d); }
+            }
+        }
         __syncthreads();
     }
 }
@@ -1293,7 +1337,7 @@ int layout(const cor_model* m, int L, int T, int k, const cor_beam_params* bp, i
     b->best_key = c.take<double>(L); b->hyp_steps = c.take<long long>(L);
     b->score_ties = c.take<long long>(L); b->near_ties = c.take<long long>(L); b->pop_sum = c.take<unsigned long long>(L);
     b->fr_peak = c.take<int32_t>(L);
-    b->fr_gone = c.take<int32_t>(L); b->fin_in = c.take<int32_t>(L);
+    b->fr_gone = c.take<int32_t>(L); b->fin_in = c.take<int32_t>(L); b->push_done = c.take<int32_t>(L);
     b->reach_trunc = getenv("COR_NO_REACH_TRUNC") ? 0 : 1;
     b->fr_key = c.take<double>((size_t)2 * L * cap); b->fr_id = c.take<uint32_t>((size_t)2 * L * cap);
     b->beam_nodes = c.take<uint32_t>((size_t)L * bp->batch_size);
@@ -1419,6 +1463,8 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
     const int row_grid = std::min(plan.Rcap, 148 * 8);
     const size_t expand_smem = (size_t)(m->cfg.lm_predict ? 2 : 1) * m->Vp * 4;
     const size_t push_smem = (size_t)MAX_NEW * 12;
+    // blocks per line of beam_push_kernel: as many as keep 2 x 148 blocks busy when every line is on the heavy list
+    const int push_parts = getenv("COR_PUSH_PARTS") ? std::max(1, std::min(16, atoi(getenv("COR_PUSH_PARTS")))) : std::max(1, std::min(8, 148 * 2 / L));
     const int t_hi = T;      // every row_T is <= t_max
     // pop + scan: which hypotheses of every line are expanded next, their rows, and whether anything is left to do
     const bool small_sel = L <= kSelectSmall && !getenv("COR_NO_SELECT_SMALL");
@@ -1479,7 +1525,7 @@ int run_wave(cor_model* m, int L, int T, int k, const int32_t* h_row_T, const in
             default:   beam_expand_kernel<<<row_grid, 128, expand_smem, s_>>>(b, split);
         }
         beam_push_small_kernel<<<(L + 7) / 8, 256, 0, s_>>>(b);
-        beam_push_kernel<<<std::min(L, 148 * 2), PUSH_THREADS, push_smem, s_>>>(b);
+        beam_push_kernel<<<dim3(push_parts, std::min(L, std::max(1, 148 * 2 / push_parts))), PUSH_THREADS, push_smem, s_>>>(b);
         ctx().launches += 3;
         COR_CUDA(cudaGetLastError());
         return 0;
