@@ -77,7 +77,7 @@ struct LoopGraphCache {
     cudaStream_t capture[2] = {nullptr, nullptr};
     uint64_t tick = 0;
 };
-constexpr size_t kGraphCacheSize = 8;
+constexpr size_t kGraphCacheSize = 16;
 static LoopGraphCache* graph_cache(cor_model* m) {
     if (!m->loop_graphs) m->loop_graphs = new LoopGraphCache();
     return static_cast<LoopGraphCache*>(m->loop_graphs);

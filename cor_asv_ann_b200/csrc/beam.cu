@@ -1268,7 +1268,8 @@ __global__ void __launch_bounds__(128) beam_finish_kernel(BeamDev b, int32_t* o_
         os[0] = st == ST_OVERFLOW ? -1 : (st == ST_EMPTY ? -2 : b.iter[line]);
         os[1] = b.hyp_steps[line];
         os[2] = b.finals_count[line];
-        os[3] = st == ST_ACTIVE ? b.fr_len[line] + b.fr_gone[line] : b.open_left[line];
+        // (a line that ran out of records is retried: its row tells the host how far it came, beam_correct sizes the retry from it)
+        os[3] = st == ST_ACTIVE ? b.fr_len[line] + b.fr_gone[line] : (st == ST_OVERFLOW ? b.iter[line] : b.open_left[line]);
         os[4] = b.score_ties[line];
         os[5] = b.near_ties[line];
         os[6] = (long long)b.pop_sum[line];
@@ -1703,13 +1704,34 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
     std::vector<int> pending(B);
     for (int j = 0; j < B; ++j) pending[j] = j;
     std::vector<int64_t> hstats;
-    int wave_cap = B;
+    // Lines that run out of expansion records are retried with a larger share of the workspace.  How large: a failed
+    // line reports the records it used and the iterations it came through (stats[1], stats[3]); 1.5 x that rate over all
+    // 2T iterations, at least twice what it had, at most the 2T * batch_size it can ever use.  The retry waves take the
+    // lines in the order of that need, each wave as many lines as its hardest line allows (a power of two, so that few
+    // distinct wave geometries -- loop graphs -- exist): easy lines share large waves, only the hard ones get small ones.
+    const long long q_full = (long long)2 * T * bp->batch_size;
+    std::vector<long long> need(B, 0);
+    const bool sized_retry = getenv("COR_NO_SIZED_RETRY") == nullptr;
     for (int level = 0; !pending.empty(); ++level) {
         COR_CHECK(level < 16, "beam search: retry depth exceeded");
         Plan plan;
-        if (make_plan(m, std::min<int>(wave_cap, (int)pending.size()), T, k, bp, out_align != nullptr, workspace_bytes, &plan)) return 1;
+        if (level > 0) std::stable_sort(pending.begin(), pending.end(), [&](int a, int b2) { return need[a] < need[b2]; });
         std::vector<int> failed;
         for (size_t p0 = 0; p0 < pending.size(); p0 += plan.L) {
+            const int rest = (int)(pending.size() - p0);
+            if (level == 0) {
+                if (p0 == 0 && make_plan(m, rest, T, k, bp, out_align != nullptr, workspace_bytes, &plan)) return 1;
+            } else {
+                // the largest wave (all the rest, or a power of two) whose plan gives its hardest line what it needs
+                int best = 0;
+                for (int cand = rest; cand >= 1; cand = cand == rest ? (1 << (31 - __builtin_clz((unsigned)std::max(1, rest - 1)))) : cand / 2) {
+                    Plan tmp;
+                    if (make_plan(m, cand, T, k, bp, out_align != nullptr, workspace_bytes, &tmp)) return 1;
+                    if (tmp.L == cand && tmp.quota_x >= need[pending[p0 + cand - 1]]) { best = cand; plan = tmp; break; }
+                    if (cand == 1) break;
+                }
+                if (!best && make_plan(m, 1, T, k, bp, out_align != nullptr, workspace_bytes, &plan)) return 1;     // all there is for one line
+            }
             const int L = (int)std::min<size_t>(plan.L, pending.size() - p0);
             const bool direct = level == 0 && L == B;        // first wave over everything: use the caller's buffers
             Stage stage(on_device);
@@ -1740,7 +1762,14 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                          on_device, hstats.data(), st)) return 1;
             for (int j = 0; j < L; ++j) {
                 const int dst = pending[p0 + j];
-                if (hstats[(size_t)j * kStats] == -1) { failed.push_back(dst); continue; }
+                if (hstats[(size_t)j * kStats] == -1) {
+                    COR_CHECK(wp.L > 1, "beam search: a single line overflows the whole workspace");
+                    const long long used = hstats[(size_t)j * kStats + 1], its = hstats[(size_t)j * kStats + 3];
+                    const long long est = (sized_retry && its > 0) ? (long long)(1.5 * (double)used / (double)its * 2.0 * T) + bp->batch_size : q_full;
+                    need[dst] = std::min(q_full, std::max(std::max<long long>(2 * wp.quota_x, 8), est));
+                    failed.push_back(dst);
+                    continue;
+                }
                 if (direct) continue;
                 if (xcopy(out_chars + (size_t)dst * S, w_chars + (size_t)j * S, S * 4) ||
                     xcopy(out_probs + (size_t)dst * S, w_probs + (size_t)j * S, S * 4) ||
@@ -1750,10 +1779,6 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                 if (out_align && xcopy(out_align + (size_t)dst * S * T, w_align + (size_t)j * S * T, S * T * 4)) return 1;
             }
             if (on_device) COR_CUDA(cudaStreamSynchronize(st));      // staging is freed at the end of this scope
-        }
-        if (!failed.empty()) {
-            COR_CHECK(plan.L > 1, "beam search: a single line overflows the whole workspace");
-            wave_cap = std::max(1, plan.L / 8);
         }
         pending.swap(failed);
     }
