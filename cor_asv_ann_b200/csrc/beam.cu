@@ -28,6 +28,7 @@
 #include <math.h>
 #include <float.h>
 #include <string.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <algorithm>
 #include <vector>
@@ -1710,7 +1711,8 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
     // lines in the order of that need, each wave as many lines as its hardest line allows (a power of two, so that few
     // distinct wave geometries -- loop graphs -- exist): easy lines share large waves, only the hard ones get small ones.
     const long long q_full = (long long)2 * T * bp->batch_size;
-    std::vector<long long> need(B, 0);
+    std::vector<long long> need(B, m->beam_full_hint ? q_full : 0);
+    int lines_done = 0, lines_heavy = 0;         // ... of which used more than half of the full quota
     const bool sized_retry = getenv("COR_NO_SIZED_RETRY") == nullptr;
     for (int level = 0; !pending.empty(); ++level) {
         COR_CHECK(level < 16, "beam search: retry depth exceeded");
@@ -1719,7 +1721,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
         std::vector<int> failed;
         for (size_t p0 = 0; p0 < pending.size(); p0 += plan.L) {
             const int rest = (int)(pending.size() - p0);
-            if (level == 0) {
+            if (level == 0 && !(sized_retry && m->beam_full_hint)) {
                 if (p0 == 0 && make_plan(m, rest, T, k, bp, out_align != nullptr, workspace_bytes, &plan)) return 1;
             } else {
                 // the largest wave (all the rest, or a power of two) whose plan gives its hardest line what it needs
@@ -1760,6 +1762,12 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
             hstats.assign((size_t)L * kStats, 0);
             if (run_wave(m, L, T, k, w_T, w_idx, w_val, bp, wp, workspace, w_chars, w_probs, w_scores, w_len, w_align, w_stats,
                          on_device, hstats.data(), st)) return 1;
+            if (getenv("COR_BEAM_TRACE")) {
+                int nfail = 0; long long used = 0, its = 0;
+                for (int j = 0; j < L; ++j) { nfail += hstats[(size_t)j * kStats] == -1; used += hstats[(size_t)j * kStats + 1]; its = std::max<long long>(its, hstats[(size_t)j * kStats] == -1 ? hstats[(size_t)j * kStats + 3] : hstats[(size_t)j * kStats]); }
+                fprintf(stderr, "[beam] level %d wave of %d lines, %d records per line, %d rows per iteration: %d lines out of records, %lld records used, longest line %lld iterations\n",
+                        level, L, wp.quota_x, wp.Rcap, nfail, used, its);
+            }
             for (int j = 0; j < L; ++j) {
                 const int dst = pending[p0 + j];
                 if (hstats[(size_t)j * kStats] == -1) {
@@ -1770,6 +1778,8 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                     failed.push_back(dst);
                     continue;
                 }
+                ++lines_done;
+                if (2 * hstats[(size_t)j * kStats + 1] > q_full) ++lines_heavy;
                 if (direct) continue;
                 if (xcopy(out_chars + (size_t)dst * S, w_chars + (size_t)j * S, S * 4) ||
                     xcopy(out_probs + (size_t)dst * S, w_probs + (size_t)j * S, S * 4) ||
@@ -1782,6 +1792,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
         }
         pending.swap(failed);
     }
+    m->beam_full_hint = lines_done >= 8 && 10 * lines_heavy >= 9 * lines_done;
     return 0;
 }
 

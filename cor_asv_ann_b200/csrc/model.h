@@ -67,6 +67,9 @@ struct cor_model {
     bool use_xtab = false;
     bool fuse_pe = false;     // PE exists (3*Vp <= 4*W: the fused product is the cheaper one)
     cudaStream_t side = nullptr;          // attention runs here, beside the lower-cell GEMMs
+    // beam_correct: the previous call's lines nearly all needed (more than half of) the full record quota -- the next call
+    // starts with full-quota waves instead of probing every line with a share of the workspace that is sure to run out
+    bool beam_full_hint = false;
     bool side_attention = false;          // ... as the register-only kernel that fits on an SM next to the GEMM's CTA
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cor::Mat LowCat, TopCat;  // page decoder (decpage.cu): [E.Kx | R] and [Kx | Kc | R] concatenated along K (depth 2 only)

@@ -21,11 +21,14 @@ out = None
 eng.launch_count(reset=True)
 torch.cuda.synchronize()
 t0 = time.perf_counter()
+each = []
 for s in range(reps):
+    t1 = time.perf_counter()
     out = eng.beam_device(idx, None, row_T, bp, budget_bytes=budget, out=out)
-torch.cuda.synchronize()
+    torch.cuda.synchronize()
+    each.append(round((time.perf_counter() - t1) * 1e3, 1))
 dt = (time.perf_counter() - t0) / reps
 st = out[5].cpu().numpy()
 print(json.dumps({"workload": workload, "lines": n_lines, "ms_per_call": dt * 1e3, "kernels_per_call": eng.launch_count() / reps,
                   "iterations_max": int(st[:, 0].max()), "hyp_steps": int(st[:, 1].sum()), "hyp_steps_per_s": float(st[:, 1].sum() / dt),
-                  "fringe_peak_max": int(st[:, 7].max())}))
+                  "fringe_peak_max": int(st[:, 7].max()), "ms_each_call": each}))
