@@ -1714,6 +1714,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
     std::vector<long long> need(B, m->beam_full_hint ? q_full : 0);
     int lines_done = 0, lines_heavy = 0;         // ... of which used more than half of the full quota
     const bool sized_retry = getenv("COR_NO_SIZED_RETRY") == nullptr;
+    const double retry_factor = getenv("COR_RETRY_FACTOR") ? atof(getenv("COR_RETRY_FACTOR")) : 1.5;
     for (int level = 0; !pending.empty(); ++level) {
         COR_CHECK(level < 16, "beam search: retry depth exceeded");
         Plan plan;
@@ -1773,7 +1774,7 @@ static int beam_correct(cor_model* m, const cor_lines* hl, bool on_device, const
                 if (hstats[(size_t)j * kStats] == -1) {
                     COR_CHECK(wp.L > 1, "beam search: a single line overflows the whole workspace");
                     const long long used = hstats[(size_t)j * kStats + 1], its = hstats[(size_t)j * kStats + 3];
-                    const long long est = (sized_retry && its > 0) ? (long long)(1.5 * (double)used / (double)its * 2.0 * T) + bp->batch_size : q_full;
+                    const long long est = (sized_retry && its > 0) ? (long long)(retry_factor * (double)used / (double)its * 2.0 * T) + bp->batch_size : q_full;
                     need[dst] = std::min(q_full, std::max(std::max<long long>(2 * wp.quota_x, 8), est));
                     failed.push_back(dst);
                     continue;
