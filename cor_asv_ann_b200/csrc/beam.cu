@@ -148,32 +148,51 @@ __device__ void pop_line(const BeamDev& b, int line, int lane, bool bump = false
     const unsigned long long it_odd = 2ull * (unsigned long long)b.iter[line] + 1ull;
     unsigned long long csum = 0ull;
     const int fc0 = b.finals_count[line];
-    for (int base = 0; base < len && open_total < b.batch; base += 32) {
-        const int i = base + lane;
-        const bool valid = i < len;
-        const uint32_t id = valid ? ids[i] : 0u;
-        const bool fin = valid && (id & FINAL_BIT);
-        const bool open = valid && !fin;
-        const unsigned bal = __ballot_sync(0xffffffffu, open);
-        const int excl = open_total + __popc(bal & ((1u << lane) - 1u));
-        // an entry is popped iff fewer than batch_size open nodes precede it (:1400-1415)
-        const bool take = valid && excl < b.batch;
-        if (take && open) {
-            b.beam_nodes[(size_t)line * b.batch + excl] = id;
-            unsigned long long x = (1ull << 16) + 1ull;            // root: length 1, no character
-            if (id != 0u) {
-                const size_t pg = (size_t)line * b.quota_x + (id - 1u) / KMAX;
-                x = ((unsigned long long)(b.rec_len[pg] + 1) << 16) + (unsigned long long)b.ch_v[pg * KMAX + (id - 1u) % KMAX] + 1ull;
+    // Rounds of PC chunks of 32 entries: the ids of a round are fetched together, and so are the record reads of the
+    // checksum (one chunk after the other made every chunk two dependent memory round trips: 8+ chunks per batch of 256).
+    constexpr int PC = 4;
+    for (int base = 0; base < len && open_total < b.batch; base += 32 * PC) {
+        uint32_t idv[PC];
+        int slot[PC];                                   // >= 0: a popped open node and its place in the batch
+#pragma unroll
+        for (int c = 0; c < PC; ++c) { const int i = base + 32 * c + lane; idv[c] = i < len ? ids[i] : 0u; }
+#pragma unroll
+        for (int c = 0; c < PC; ++c) {
+            slot[c] = -1;
+            const int cb = base + 32 * c;
+            if (cb < len && open_total < b.batch) {     // (the same for every lane)
+                const bool valid = cb + lane < len;
+                const bool fin = valid && (idv[c] & FINAL_BIT);
+                const bool open = valid && !fin;
+                const unsigned bal = __ballot_sync(0xffffffffu, open);
+                const int excl = open_total + __popc(bal & ((1u << lane) - 1u));
+                // an entry is popped iff fewer than batch_size open nodes precede it (:1400-1415)
+                const bool take = valid && excl < b.batch;
+                if (take && open) slot[c] = excl;
+                const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
+                const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);
+                if (t_open && first_open == 0x7fffffff) first_open = cb + __ffs(t_open) - 1;
+                if (t_fin && first_final == 0x7fffffff) first_final = cb + __ffs(t_fin) - 1;
+                consumed += __popc(t_open | t_fin);
+                nfin += __popc(t_fin);
+                open_total += __popc(bal);
             }
-            csum += x * it_odd * 0x9E3779B97F4A7C15ull;
         }
-        const unsigned t_open = __ballot_sync(0xffffffffu, take && open);
-        const unsigned t_fin = __ballot_sync(0xffffffffu, take && fin);
-        if (t_open && first_open == 0x7fffffff) first_open = base + __ffs(t_open) - 1;
-        if (t_fin && first_final == 0x7fffffff) first_final = base + __ffs(t_fin) - 1;
-        consumed += __popc(t_open | t_fin);
-        nfin += __popc(t_fin);
-        open_total += __popc(bal);
+#pragma unroll
+        for (int c = 0; c < PC; ++c) {
+            if (slot[c] >= 0) {
+                const uint32_t id = idv[c];
+                unsigned long long x = (1ull << 16) + 1ull;            // root: length 1, no character
+                if (id != 0u) {
+                    const size_t pg = (size_t)line * b.quota_x + (id - 1u) / KMAX;
+                    x = ((unsigned long long)(b.rec_len[pg] + 1) << 16) + (unsigned long long)b.ch_v[pg * KMAX + (id - 1u) % KMAX] + 1ull;
+                }
+                csum += x * it_odd * 0x9E3779B97F4A7C15ull;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < PC; ++c)
+            if (slot[c] >= 0) b.beam_nodes[(size_t)line * b.batch + slot[c]] = idv[c];
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, o);
@@ -563,7 +582,7 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
             if (r >= 0) rej = r;
         }
         bool near_pos = len_node > 1 && ((!onehot && fabs(fabs(cur - floor(cur)) - 0.5) <= 1e-5) || fabs(mis - 0.1) <= 1e-6);
-        if (rej >= 0 && fabs((double)sp[rej] - b.rej_thr) <= (double)kTieMargin * b.rej_thr) near_pos = true;
+        if (rej >= 0 && fabs((double)sp[rej] - b.rej_thr) <= (double)kTieMargin * b.rej_thr + (double)kTieAbs) near_pos = true;
         __syncthreads();
         if (rej >= 0 && tid == 0 && (double)sp[rej] < b.rej_thr) sp[rej] = (float)b.rej_thr;
         __syncthreads();
@@ -598,7 +617,7 @@ __global__ void __launch_bounds__(128) beam_expand_kernel(BeamDev b, int split) 
         // packed counters: [0,10) scores >= bound, [10,20) scores equal to the maximum, [20,30) scores within the tie margin of the bound
         for (int v = tid; v < b.V; v += 128) {
             const double x = (double)sp[v];
-            cnt += (x >= bound) + ((sp[v] == hi) << 10) + ((fabs(x - bound) <= (double)kTieMargin * bound) << 20);
+            cnt += (x >= bound) + ((sp[v] == hi) << 10) + ((fabs(x - bound) <= (double)kTieMargin * bound + (double)kTieAbs) << 20);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
@@ -749,7 +768,7 @@ __device__ __forceinline__ void expand_row(const BeamDev& b, int split, int row,
         float rej_p = 0.f;
         if (rej >= 0) {
             rej_p = fetch(p, rej);
-            if (fabs((double)rej_p - b.rej_thr) <= (double)kTieMargin * b.rej_thr) near_pos = true;
+            if (fabs((double)rej_p - b.rej_thr) <= (double)kTieMargin * b.rej_thr + (double)kTieAbs) near_pos = true;
             if ((double)rej_p < b.rej_thr) {
                 rej_p = (float)b.rej_thr;
 #pragma unroll
@@ -838,7 +857,7 @@ __device__ __forceinline__ void expand_row(const BeamDev& b, int split, int row,
         for (int k = 0; k < NVL; ++k)
             if (lane + 32 * k < b.V) {
                 const double x = (double)p[k];
-                cnt += (x >= bound) + ((p[k] == hi) << 10) + ((fabs(x - bound) <= (double)kTieMargin * bound) << 20);
+                cnt += (x >= bound) + ((p[k] == hi) << 10) + ((fabs(x - bound) <= (double)kTieMargin * bound + (double)kTieAbs) << 20);
             }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULL, cnt, o);
@@ -975,20 +994,72 @@ __device__ bool push_sort(const BeamDev& b, int line, double* skey, uint32_t* si
     while (npad < n_new) npad <<= 1;
     for (int i = n_new + tid; i < npad; i += NT) { skey[i] = INFINITY; sid[i] = 0x7fffffffu; }
     __syncthreads();
-    // ---- bitonic sort ascending by (key, id)
-    for (int k2 = 2; k2 <= npad; k2 <<= 1) {
-        for (int j = k2 >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < npad; i += NT) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    const bool up = (i & k2) == 0;
-                    const double ka = skey[i], kb = skey[ixj];
-                    const uint32_t ia = sid[i], ib = sid[ixj];
-                    const bool a_gt_b = key_less(kb, ib, ka, ia);
-                    if (a_gt_b == up) { skey[i] = kb; skey[ixj] = ka; sid[i] = ib; sid[ixj] = ia; }
+    // ---- bitonic sort ascending by (key, id).  Thread t owns elements t + m * NT; partners at distance j < 32 sit in the
+    // same warp, so those steps run on registers with shuffles (no shared-memory traffic, no block barrier): 21 barriers
+    // instead of 55 for 1 024 children.  More than 4 elements per thread (256-thread callers): all steps through shared memory.
+    const int M = (npad + NT - 1) / NT;
+    if (M <= 4) {
+        double kr[4]; uint32_t ir[4];
+        auto load = [&]() {
+#pragma unroll
+            for (int m = 0; m < 4; ++m) { const int i = tid + m * NT; const bool in = m < M && i < npad; kr[m] = in ? skey[i] : INFINITY; ir[m] = in ? sid[i] : 0x7fffffffu; }
+        };
+        auto store = [&]() {
+#pragma unroll
+            for (int m = 0; m < 4; ++m) { const int i = tid + m * NT; if (m < M && i < npad) { skey[i] = kr[m]; sid[i] = ir[m]; } }
+        };
+        auto in_warp = [&](int j, int k2) {
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                if (m < M) {                            // (the same for every thread)
+                    const int i = tid + m * NT;
+                    const double ko = __shfl_xor_sync(0xffffffffu, kr[m], j);
+                    const uint32_t io = __shfl_xor_sync(0xffffffffu, ir[m], j);
+                    const bool want_min = ((i & j) == 0) == ((i & k2) == 0);     // lower index of an ascending pair, or upper of a descending one
+                    const bool take = want_min ? key_less(ko, io, kr[m], ir[m]) : key_less(kr[m], ir[m], ko, io);
+                    if (take) { kr[m] = ko; ir[m] = io; }
                 }
             }
+        };
+        load();
+        for (int k2 = 2; k2 <= min(32, npad); k2 <<= 1)
+            for (int j = k2 >> 1; j > 0; j >>= 1) in_warp(j, k2);
+        store();
+        __syncthreads();
+        for (int k2 = 64; k2 <= npad; k2 <<= 1) {
+            for (int j = k2 >> 1; j >= 32; j >>= 1) {
+                for (int i = tid; i < npad; i += NT) {
+                    const int ixj = i ^ j;
+                    if (ixj > i) {
+                        const bool up = (i & k2) == 0;
+                        const double ka = skey[i], kb = skey[ixj];
+                        const uint32_t ia = sid[i], ib = sid[ixj];
+                        const bool a_gt_b = key_less(kb, ib, ka, ia);
+                        if (a_gt_b == up) { skey[i] = kb; skey[ixj] = ka; sid[i] = ib; sid[ixj] = ia; }
+                    }
+                }
+                __syncthreads();
+            }
+            load();
+            for (int j = 16; j > 0; j >>= 1) in_warp(j, k2);
+            store();
             __syncthreads();
+        }
+    } else {
+        for (int k2 = 2; k2 <= npad; k2 <<= 1) {
+            for (int j = k2 >> 1; j > 0; j >>= 1) {
+                for (int i = tid; i < npad; i += NT) {
+                    const int ixj = i ^ j;
+                    if (ixj > i) {
+                        const bool up = (i & k2) == 0;
+                        const double ka = skey[i], kb = skey[ixj];
+                        const uint32_t ia = sid[i], ib = sid[ixj];
+                        const bool a_gt_b = key_less(kb, ib, ka, ia);
+                        if (a_gt_b == up) { skey[i] = kb; skey[ixj] = ka; sid[i] = ib; sid[ixj] = ia; }
+                    }
+                }
+                __syncthreads();
+            }
         }
     }
     {

@@ -210,6 +210,9 @@ struct GreedyArgs {
 // An argmax whose runner-up lies within this relative margin is logged as a near-tie: fp32-grade implementations
 // (this one, Keras/TF, the numpy oracle) may legitimately pick either, so parity tests report such lines separately.
 constexpr float kTieMargin = 1e-6f;
+// the beam's threshold cuts (relative beam threshold, rejection threshold) compare probabilities that agree with the oracle's to ~1e-6 ABSOLUTE (small
+// probabilities: far more than 1e-6 relative), so its near-tie log adds an absolute term
+constexpr float kTieAbs = 2e-6f;
 int launch_softmax_greedy(cudaStream_t st, const GreedyArgs& a);
 int launch_softmax(cudaStream_t st, const float* logits, float* p, float* p_lo, int R, const int* r_dev, int V);
 int launch_split(cudaStream_t st, const float* x, float* hi, float* lo, size_t n);

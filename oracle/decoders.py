@@ -310,12 +310,12 @@ def decode_sequence_beam(topo, w, mapping, source_seq, enc_slices, *, batch_size
             if stats is not None and V > 1 and sc[order[-1]] == sc[order[-2]]:
                 n_score_ties += 1
             if stats is not None:
-                # near-tie ordering decisions of this expansion (same definition as csrc/beam.cu, margin 1e-6 relative):
+                # near-tie ordering decisions of this expansion (same definition as csrc/beam.cu, margin 1e-6 relative, + 2e-6 absolute at the threshold cut):
                 # two consecutive walked candidates, the last one taken against the first left out, the threshold cut
                 so = sc[order[::-1]].astype(np.float64)
                 bound = np.float64(so[0]) * beam_threshold_in
                 nw = min(beampos + 1, V)
-                tie = bool(np.any(np.abs(so - bound) <= 1e-6 * bound))
+                tie = bool(np.any(np.abs(so - bound) <= 1e-6 * bound + 2e-6))
                 tie = tie or bool(np.any(so[:nw - 1] - so[1:nw] <= 1e-6 * so[:nw - 1]))
                 if node.length > 1:      # position rounding, misalignment threshold
                     onehot = np.max(node.alignment) == 1.0
