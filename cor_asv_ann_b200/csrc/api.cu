@@ -769,7 +769,7 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
     // device (loop graph; `off` = position of the step inside the graph body)
     auto timestep = [&](cudaStream_t s_, int s, int off, int cur_) -> int {
         StepIO io{};
-        io.R = B; io.first = (s == 0);
+        io.R = B; io.first = false;           // step 0 multiplies a zero feedback row (below), like every other step multiplies its own
         io.p = ws.p; io.p_lo = ws.p_lo; io.x = ws.x; io.x_lo = ws.x_lo;
         for (int n = 0; n < d; ++n) {
             io.h_in[n] = ws.dh[cur_][n]; io.h_in_lo[n] = ws.dh_lo[cur_][n];
@@ -892,6 +892,10 @@ static int greedy_loop(cor_model* m, const Ws& ws, cudaStream_t st) {
         ctx().launches += 1; ctx().in_graph += 1; ctx().graph_launches += 1;     // the graph's first node
         return launch_finish_scores(st, ws.o_score, ws.o_len, B);
     }
+    // host-driven loop: the same K-segments in every step as in the graph (a GEMM whose k-blocks are shared out among several
+    // accumulators -- the 128x32-tile kernel -- rounds differently when a segment of zeros is left out)
+    COR_CUDA(cudaMemsetAsync(ws.p, 0, (size_t)B * m->Vp * 4, st));
+    if (ws.p_lo) COR_CUDA(cudaMemsetAsync(ws.p_lo, 0, (size_t)B * m->Vp * 4, st));
     for (int s = 0; s < S; ++s) {
         if (timestep(st, s, 0, cur)) return 1;
         cur ^= 1;

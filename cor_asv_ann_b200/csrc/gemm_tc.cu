@@ -32,6 +32,8 @@ constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int BN_WIDE = 256, BN_NARROW = 32;   // tile widths: full tiles / page-sized M (see pick_bn)
 constexpr int ELT = 2;                          // bytes per operand element (fp16)
 constexpr int A_TILE = BM * BK * ELT;          // 16 KB
+constexpr int NSUB_NARROW = 3;                // MMA issuer warps of the 128x32-tile kernel, each with its own accumulator
+constexpr int A_BOX_NARROW = 32;               // rows per TMA box of the A operand in the 128x32-tile kernel (a multiple of the 8-row swizzle atom)
 // LSTM epilogue staging (per epilogue warp): the results of a 32-row x 8-unit chunk -- c (fp32), h (hi, lo), sequence
 // output (hi, lo) -- are written to shared memory as [32][8] tiles and leave through TMA box stores.  The epilogue is
 // "one row per lane", so every direct global store of it touches 32 different lines (32 LSU wavefronts whatever its
@@ -457,7 +459,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), EPI_WARPS * NCTA); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), BN == BN_NARROW ? NSUB_NARROW : 1); mbar_init(tempty_bar(a), EPI_WARPS * NCTA); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -487,7 +489,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                         const uint32_t sa = smem_base + stage * STAGE_BYTES;
                         const bool lo = p.passes == 3;          // heads-only mode leaves the residual tiles out
                         const uint32_t bytes = lo ? STAGE_BYTES : A_TILE + B_TILE;
-                        if constexpr (NCTA == 1) {
+                        if constexpr (NCTA == 1 && BN == BN_NARROW) {
+                            // Page regime: a tile has a few dozen valid rows.  The A operand comes in boxes of A_BOX_NARROW
+                            // rows, only as many as hold valid rows (a 128-row box moves 16 KB per operand part and k-block
+                            // whatever M is -- zero fill included -- and the k-loop of this kernel runs at the speed one SM
+                            // takes its stage in: 40 KB per k-block became 16 KB for a 32-line page).  The other rows of the
+                            // tile keep whatever shared memory held: they feed accumulator rows >= M, which nothing reads.
+                            const int nbox = (min(BM, M - m0) + A_BOX_NARROW - 1) / A_BOX_NARROW;
+                            constexpr uint32_t BOX_BYTES = A_BOX_NARROW * BK * ELT;
+                            mbar_expect_tx(full_bar(stage), (lo ? 2u : 1u) * (nbox * BOX_BYTES + B_TILE));
+                            for (int r = 0; r < nbox; ++r) {
+                                tma_load_2d(sa + r * BOX_BYTES, &p.a_hi[s], kb * BK, m0 + r * A_BOX_NARROW, full_bar(stage));
+                                if (lo) tma_load_2d(sa + A_TILE + r * BOX_BYTES, &p.a_lo[s], kb * BK, m0 + r * A_BOX_NARROW, full_bar(stage));
+                            }
+                            tma_load_2d(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, full_bar(stage));
+                            if (lo) tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
+                        } else if constexpr (NCTA == 1) {
                             mbar_expect_tx(full_bar(stage), bytes);
                             tma_load_2d(sa, &p.a_hi[s], kb * BK, m0, full_bar(stage));
                             if (lo) tma_load_2d(sa + A_TILE, &p.a_lo[s], kb * BK, m0, full_bar(stage));
@@ -503,6 +520,58 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                         }
                         if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
+                }
+            }
+        }
+    } else if (BN == BN_NARROW && warp >= 1 && warp <= NSUB_NARROW) {
+        // ===== MMA issuers of the page regime (BN = 32) =====
+        // One thread gets a tcgen05.mma out every ~85 cycles whatever its shape: the 288 small MMAs of a tile at K = 1536
+        // were 13 of the kernel's 17 us.  Warps 1..3 therefore share the k-blocks round robin (k-block kb belongs to issuer
+        // kb % 3); MMAs of different threads are not ordered against each other, so each issuer owns an accumulator, and the
+        // epilogue adds the three up in a fixed order.  Another summation order than the wide tiles' (still fp32 sums of the
+        // same products): page-sized and batch-sized calls agree to rounding, not bit for bit.
+        if constexpr (BN == BN_NARROW) {
+            const int qi = warp - 1;
+            if (lane == 0) {
+                long long g0 = 0;                       // k-blocks of the tiles before this one (stage and phase follow from the count)
+                int acc = 0; uint32_t acc_phase = 0;
+                for (int tile = unit; tile < num_tiles; tile += n_units) {
+                    mbar_wait(tempty_bar(acc), acc_phase ^ 1);      // epilogue(s) have drained this accumulator
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + acc * (NSUB_NARROW * BN) + qi * BN;
+                    bool first = true;
+                    for (int kb = qi; kb < kb_total; kb += NSUB_NARROW) {
+                        const long long g = g0 + kb;
+                        const int stage = (int)(g % STAGES);
+                        mbar_wait(full_bar(stage), (uint32_t)((g / STAGES) & 1));
+                        tc_fence_after();
+                        const uint32_t sa = smem_base + stage * STAGE_BYTES;
+                        const uint64_t a_hi = make_smem_desc(sa), a_lo = make_smem_desc(sa + A_TILE);
+                        const uint64_t b_hi = make_smem_desc(sa + 2 * A_TILE), b_lo = make_smem_desc(sa + 2 * A_TILE + B_TILE);
+                        const bool lo = p.passes == 3;
+                        if (lo) {
+#pragma unroll
+                            for (int k = 0; k < BK / UMMA_K; ++k) {
+                                const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
+                                umma_f16(d_tmem, a_lo + adv, b_hi + adv, G::IDESC, !(first && k == 0));
+                            }
+#pragma unroll
+                            for (int k = 0; k < BK / UMMA_K; ++k) {
+                                const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
+                                umma_f16(d_tmem, a_hi + adv, b_lo + adv, G::IDESC, 1);
+                            }
+                        }
+#pragma unroll
+                        for (int k = 0; k < BK / UMMA_K; ++k) {
+                            const uint64_t adv = (uint64_t)((k * UMMA_K * ELT) >> 4);
+                            umma_f16(d_tmem, a_hi + adv, b_hi + adv, G::IDESC, lo || !(first && k == 0));
+                        }
+                        first = false;
+                        umma_commit(empty_bar(stage));      // frees the smem stage when this issuer's MMAs retire
+                    }
+                    g0 += kb_total;
+                    umma_commit(tfull_bar(acc));            // this issuer's part of the accumulator is complete (NSUB_NARROW arrivals)
+                    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
                 }
             }
         }
@@ -560,7 +629,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
         for (int tile = unit; tile < num_tiles; tile += n_units) {
             const int m0 = (tile / p.tiles_n) * (BM * NCTA) + (int)rank * BM, n0 = (tile % p.tiles_n) * BN;
             const int row = m0 + wq * 32 + lane;
-            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
+            constexpr int ACC_STRIDE = BN == BN_NARROW ? NSUB_NARROW * BN : BN;
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * ACC_STRIDE;
+            // accumulator chunk `ch` as 32 fp32 bit patterns; the 128x32-tile kernel adds up its issuers' accumulators in a fixed
+            // order (an issuer without a k-block -- fewer k-blocks than issuers -- has written nothing)
+            auto load_acc = [&](int ch, uint32_t (&z)[32]) {
+                tmem_ld32(taddr + ch * 32, z);
+                tmem_ld_wait();
+                if constexpr (BN == BN_NARROW) {
+                    const int nsub = min(NSUB_NARROW, kb_total);
+#pragma unroll 1
+                    for (int q = 1; q < nsub; ++q) {
+                        uint32_t y[32];
+                        tmem_ld32(taddr + q * BN + ch * 32, y);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int k = 0; k < 32; ++k) z[k] = __float_as_uint(__uint_as_float(z[k]) + __uint_as_float(y[k]));
+                    }
+                }
+            };
             if constexpr (EPI == 1) {
                 // everything that does not depend on the accumulator is fetched before waiting for it
                 const RowCtx rc = lstm_row_begin(epi, row, row < M);
@@ -580,8 +667,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                     if (live && rc.active) lstm_chunk_operands(epi, rc, row, col0 >> 2, b, c);
                     if (!waited) { mbar_wait(tfull_bar(acc), acc_phase); tc_fence_after(); waited = true; }
                     uint32_t z[32];
-                    tmem_ld32(taddr + ch * 32, z);
-                    tmem_ld_wait();
+                    load_acc(ch, z);
                     if (staged && col0 < p.N) {
                         const int unit0 = col0 >> 2;
                         if (lane == 0) bulk_wait_read();            // the previous chunk's tiles have been read out
@@ -612,8 +698,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
 #pragma unroll 1
                 for (int ch = half; ch < BN / 32; ch += EPI_WARPS / 4) {
                     uint32_t z[32];
-                    tmem_ld32(taddr + ch * 32, z);
-                    tmem_ld_wait();
+                    load_acc(ch, z);
                     const int col0 = n0 + ch * 32;
                     if (row < M && col0 < p.N) store_row32(epi, row, col0, p.N, z);
                 }
@@ -768,7 +853,8 @@ int fill_params(int ncta, int bn, int M, const int* m_dev, int N, const GemmSeg*
         COR_CHECK(g.A_lo && g.B_lo, "tcgen05 path needs split (hi, lo) operands");
         COR_CHECK(g.K > 0 && g.K % BK == 0, "K must be a positive multiple of 64");
         p->kblocks[s] = g.K / BK;
-        if (get_map(g.A, M, g.K, g.lda, BM, &p->a_hi[s]) || get_map(g.A_lo, M, g.K, g.lda, BM, &p->a_lo[s]) ||
+        const int a_box = (ncta == 1 && bn == BN_NARROW) ? A_BOX_NARROW : BM;
+        if (get_map(g.A, M, g.K, g.lda, a_box, &p->a_hi[s]) || get_map(g.A_lo, M, g.K, g.lda, a_box, &p->a_lo[s]) ||
             get_map(g.B, N, g.K, g.ldb, bn / ncta, &p->b_hi[s]) || get_map(g.B_lo, N, g.K, g.ldb, bn / ncta, &p->b_lo[s])) return 1;
     }
     return 0;

@@ -1,0 +1,12 @@
+# round 2, call 40: 128x32-tile GEMM with the A operand in 32-row boxes (only boxes that hold valid rows): GEMM tests,
+# the page-regime parity tests, warm kernel time (before: 8.7-9.0 us at K = 512, 17.5-17.8 us at K = 1536, 32 rows), page leg
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_core.py tests/test_gpu_loop_graph.py tests/test_gpu_beam.py tests/test_gpu_seq2seq.py tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -3
+for shape in "32 2048 512" "32 2048 1536" "64 2048 1536" "128 2048 1536" "256 2048 1536"; do
+  timeout 600 ncu --metrics gpu__time_duration.sum --cache-control none --clock-control none -k regex:gemm_tc_kernel --csv python scripts/gemm_probe.py 3 $shape 2>&1 | grep gemm_tc | awk -F'","' -v s="$shape" '{print s, $NF}' | tail -2
+done
+timeout 600 python bench.py --page-only 2>/dev/null | python -c "
+import sys, json
+d = json.loads(sys.stdin.read().strip().splitlines()[-1]); p = d.get('page', d); print('page greedy', p['ms_per_call'], 'beam', p['beam']['ms_per_call'])"
+timeout 300 python scripts/page_beam_probe.py 32 5 2>&1 | tail -1
+timeout 300 python scripts/page_beam_probe.py 64 5 2>&1 | tail -1
