@@ -61,6 +61,7 @@ template <int NCTA, int BN> struct Geo {
 };
 constexpr int EPI_WARPS = 8;                   // two per TMEM lane quarter: each takes half of the tile's columns
 constexpr int NTHREADS = 128 + 32 * EPI_WARPS;
+constexpr int NTHREADS_NARROW = NTHREADS + 32;  // the 128x32-tile kernel has a second TMA producer warp (warp 12)
 constexpr int TMEM_COLS = 512;
 
 struct TcParams {
@@ -424,7 +425,7 @@ __device__ __forceinline__ void store_row32(const StoreEpi& e, int row, int col0
 
 // ------------------------------------------------------------------ the kernel
 template <int EPI, int NCTA, int BN, typename Epi>
-__global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_constant__ TcParams p, const Epi epi) {
+__global__ void __launch_bounds__(NTHREADS_NARROW, 1) gemm_tc_kernel(const __grid_constant__ TcParams p, const Epi epi) {
     using G = Geo<NCTA, BN>;
     constexpr int STAGES = G::STAGES, STAGE_BYTES = G::STAGE_BYTES, B_TILE = G::B_TILE;
     extern __shared__ uint8_t smem_raw[];
@@ -458,7 +459,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
         }
     }
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), BN == BN_NARROW ? 2 : 1); mbar_init(empty_bar(s), 1); }   // 128x32 tiles: two producers
         for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), BN == BN_NARROW ? NSUB_NARROW : 1); mbar_init(tempty_bar(a), EPI_WARPS * NCTA); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -495,15 +496,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                             // whatever M is -- zero fill included -- and the k-loop of this kernel runs at the speed one SM
                             // takes its stage in: 40 KB per k-block became 16 KB for a 32-line page).  The other rows of the
                             // tile keep whatever shared memory held: they feed accumulator rows >= M, which nothing reads.
+                            // This thread loads A only: a TMA instruction costs its issuing thread ~85 cycles like an MMA does,
+                            // and with three MMA issuers the four loads of a k-block were the kernel's bound (366 ns per
+                            // k-block).  Warp 12 loads B (below); the full barrier counts both producers.
                             const int nbox = (min(BM, M - m0) + A_BOX_NARROW - 1) / A_BOX_NARROW;
                             constexpr uint32_t BOX_BYTES = A_BOX_NARROW * BK * ELT;
-                            mbar_expect_tx(full_bar(stage), (lo ? 2u : 1u) * (nbox * BOX_BYTES + B_TILE));
+                            mbar_expect_tx(full_bar(stage), (lo ? 2u : 1u) * (nbox * BOX_BYTES));
                             for (int r = 0; r < nbox; ++r) {
                                 tma_load_2d(sa + r * BOX_BYTES, &p.a_hi[s], kb * BK, m0 + r * A_BOX_NARROW, full_bar(stage));
                                 if (lo) tma_load_2d(sa + A_TILE + r * BOX_BYTES, &p.a_lo[s], kb * BK, m0 + r * A_BOX_NARROW, full_bar(stage));
                             }
-                            tma_load_2d(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, full_bar(stage));
-                            if (lo) tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
                         } else if constexpr (NCTA == 1) {
                             mbar_expect_tx(full_bar(stage), bytes);
                             tma_load_2d(sa, &p.a_hi[s], kb * BK, m0, full_bar(stage));
@@ -621,7 +623,28 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tc_kernel(const __grid_const
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
-    } else if (warp >= 4) {
+    } else if (BN == BN_NARROW && warp == 12) {
+        // ===== second TMA producer of the page regime: the B (weight) tiles =====
+        if constexpr (BN == BN_NARROW) {
+            if (lane == 0) {
+                int stage = 0; uint32_t phase = 0;
+                for (int tile = unit; tile < num_tiles; tile += n_units) {
+                    const int n0 = (tile % p.tiles_n) * BN;
+                    for (int s = 0; s < p.nseg; ++s) {
+                        for (int kb = 0; kb < p.kblocks[s]; ++kb) {
+                            mbar_wait(empty_bar(stage), phase ^ 1);
+                            const uint32_t sa = smem_base + stage * STAGE_BYTES;
+                            const bool lo = p.passes == 3;
+                            mbar_expect_tx(full_bar(stage), (lo ? 2u : 1u) * B_TILE);
+                            tma_load_2d(sa + 2 * A_TILE, &p.b_hi[s], kb * BK, n0, full_bar(stage));
+                            if (lo) tma_load_2d(sa + 2 * A_TILE + B_TILE, &p.b_lo[s], kb * BK, n0, full_bar(stage));
+                            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp >= 4 && warp < 4 + EPI_WARPS) {
         // ===== epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31 of its own CTA =====
         // the LSTM epilogue is a chain of MUFU and load latencies per row: two warps per scheduler hide them
         const int wq = (warp - 4) & 3, half = (warp - 4) >> 2;
@@ -886,7 +909,7 @@ int grid_for(int ncta, int bn, int M, int N) {
 template <int EPI, int NCTA, int BN, typename Epi>
 int launch_tc(cudaStream_t st, int M, int N, const TcParams& p, const Epi& epi) {
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid_for(NCTA, BN, M, N)); cfg.blockDim = dim3(NTHREADS);
+    cfg.gridDim = dim3(grid_for(NCTA, BN, M, N)); cfg.blockDim = dim3(BN == BN_NARROW ? NTHREADS_NARROW : NTHREADS);
     cfg.dynamicSmemBytes = Geo<NCTA, BN>::SMEM_BYTES; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = NCTA; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
